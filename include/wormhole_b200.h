@@ -1,0 +1,194 @@
+/*
+ * wormhole_b200.h -- C ABI of libwormhole_b200.so
+ *
+ * The sparse minibatch training hot path of dmlc wormhole (learn/linear async SGD /
+ * AdaGrad / FTRL, shared by learn/difacto) as hand-written sm_100a CUDA kernels.
+ * The reference has no FFI for this path: its seams are C++ header interfaces
+ * compiled into each app.  Every entry point below names the reference interface
+ * it stands in for (paths relative to the reference tree).  The header-only C++
+ * facade in wormhole_b200/host/ gives them back the reference's class names and
+ * signatures; INTEGRATION.md shows the binding a maintainer would add.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; no CUDA or torch types in signatures
+ *     (a CUDA stream crosses as void*).
+ *   - `mem` says where EVERY array argument of that call lives: WH_HOST (pageable
+ *     or pinned host memory; the call copies in, computes on the GPU, copies out,
+ *     and is synchronous) or WH_DEVICE (device pointers on the context's device;
+ *     the call only enqueues work on the context's stream -- wh_sync() to wait).
+ *   - every function returns WH_OK (0) or an error code; wh_last_error() gives the
+ *     message of the calling thread's last failure.  There is no CPU fallback: a
+ *     call that cannot run on the GPU fails.
+ *   - one whContext per GPU; calls on one context must be serialised by the caller.
+ */
+#ifndef WORMHOLE_B200_H_
+#define WORMHOLE_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define WH_API __attribute__((visibility("default")))
+
+enum { WH_OK = 0, WH_ERR_INVALID = 1, WH_ERR_CUDA = 2, WH_ERR_NOMEM = 3, WH_ERR_UNSUPPORTED = 4 };
+enum { WH_HOST = 0, WH_DEVICE = 1 };
+/* learn/linear/config.proto:30-38 (Config::Loss) */
+enum { WH_LOSS_SQUARE = 1, WH_LOSS_LOGIT = 2, WH_LOSS_SQUARE_HINGE = 4 };
+/* learn/linear/config.proto:45-52 (Config::Algo) */
+enum { WH_ALGO_SGD = 1, WH_ALGO_ADAGRAD = 2, WH_ALGO_FTRL = 3 };
+/* localizer strategy */
+enum { WH_LOC_AUTO = 0, WH_LOC_DIRECT = 1, WH_LOC_SORT = 2,
+       WH_LOC_WITH_COUNTS = 16 /* OR into method: also produce the per-key counts (idx_frq) */ };
+/* ps::FLAGS_max_key default: no hashing, keys are nibble-reversed ids (learn/base/localizer.h:10,108-121) */
+#define WH_NO_MAX_KEY UINT64_MAX
+
+typedef struct whContext whContext; /* one GPU: device, stream, scratch */
+typedef struct whBatch whBatch;     /* a localized minibatch, device resident */
+typedef struct whServer whServer;   /* one key range of the model, HBM resident */
+typedef struct whWorker whWorker;   /* the per-minibatch pipeline of one worker stream */
+
+/* dmlc::RowBlock<uint64_t> by value: what MinibatchIter hands to ProcessMinibatch
+ * (learn/solver/minibatch_solver.h:211, learn/base/minibatch_iter.h:123-125).
+ * offset[0] must be 0 (learn/base/localizer.h:102); value may be NULL (all ones). */
+typedef struct {
+  size_t size;           /* rows */
+  const size_t* offset;  /* size+1 */
+  const float* label;    /* size, may be NULL */
+  const float* weight;   /* unused by this path */
+  const uint64_t* index; /* offset[size] feature ids */
+  const float* value;    /* offset[size] or NULL */
+} whRowBlock;
+
+/* dmlc::RowBlock<unsigned>: a localized block (learn/base/spmv.h:48, SpMV::SpMat). */
+typedef struct {
+  size_t size;
+  const size_t* offset;
+  const float* label;
+  const uint32_t* index;
+  const float* value;
+} whLocalBlock;
+
+/* ---- context -------------------------------------------------------------------------- */
+WH_API const char* wh_last_error(void);
+WH_API const char* wh_version(void);
+/* Number of kernels this library has launched from the calling process (all contexts). */
+WH_API uint64_t wh_kernel_launches(void);
+WH_API int wh_create(int device, whContext** out);
+WH_API int wh_destroy(whContext* ctx);
+/* Use an existing CUDA stream (cudaStream_t as void*) instead of the context's own. */
+WH_API int wh_set_stream(whContext* ctx, void* cuda_stream);
+WH_API int wh_sync(whContext* ctx);
+
+/* ---- (1) localizer ---------------------------------------------------------------------- */
+/* dmlc::ReverseBytes, learn/base/localizer.h:16-26 (a nibble reversal). Host-side scalar helper
+ * for callers that need to name a key (model files, key ranges); the kernels apply it on device. */
+WH_API uint64_t wh_reverse_bytes(uint64_t x);
+
+/* Localizer<uint64_t>::Localize, learn/base/localizer.h:42-51 (= CountUniqIndex :96-167 then
+ * RemapIndex :169-221 against the block's own unique list). max_key is ps::FLAGS_max_key.
+ * method: WH_LOC_AUTO picks direct addressing for hashed key spaces and the radix sort otherwise.
+ * The result stays on the device; read it with wh_batch_*. */
+WH_API int wh_localize(whContext* ctx, const whRowBlock* blk, int mem, uint64_t max_key, int method,
+                       whBatch** out);
+/* CountUniqIndex(blk) then RemapIndex(blk, dict): entries whose transformed key is not in the
+ * ascending dictionary are dropped and the CSR is compacted (learn/base/localizer.h:179-213).
+ * wh_batch uniq/cnt then describe blk itself, index/offset/value the remapped block. */
+WH_API int wh_localize_with_dict(whContext* ctx, const whRowBlock* blk, int mem, uint64_t max_key,
+                                 const uint64_t* dict, size_t ndict, whBatch** out);
+WH_API size_t wh_batch_rows(const whBatch* b);
+WH_API size_t wh_batch_nnz(const whBatch* b);
+WH_API size_t wh_batch_num_uniq(const whBatch* b);
+WH_API int wh_batch_has_value(const whBatch* b);
+WH_API int wh_batch_has_label(const whBatch* b);
+/* Copies the parts asked for (NULL = skip) to host arrays sized by the getters above:
+ * uniq[U] ascending transformed keys, cnt_u32[U] multiplicities (C = unsigned), cnt_f32[U] the
+ * same cast to float (C = float, learn/difacto/async_sgd.h:366), offset[rows+1], index[nnz],
+ * value[nnz], label[rows]. */
+WH_API int wh_batch_copy(whContext* ctx, const whBatch* b, uint64_t* uniq, uint32_t* cnt_u32,
+                         float* cnt_f32, size_t* offset, uint32_t* index, float* value, float* label);
+/* Device views of the same arrays (valid until wh_batch_destroy). */
+WH_API int wh_batch_device_view(const whBatch* b, const uint64_t** uniq, const uint32_t** cnt,
+                                whLocalBlock* local);
+WH_API int wh_batch_destroy(whBatch* b);
+
+/* ---- (2) SpMV, (5) SpMM ----------------------------------------------------------------- */
+/* SpMV::Times, learn/base/spmv.h:72-91: y[i] = sum_j x[index[j]] * value[j] in CSR order
+ * (sequential fp32, bit-exact with the reference); rows without entries leave y[i] untouched. */
+WH_API int wh_spmv_times(whContext* ctx, const whLocalBlock* D, int mem, const float* x, size_t xsize,
+                         float* y);
+/* SpMV::TransTimes, learn/base/spmv.h:95-119: y[0..ysize) = D^T x. */
+WH_API int wh_spmv_trans_times(whContext* ctx, const whLocalBlock* D, int mem, const float* x,
+                               float* y, size_t ysize);
+/* SpMM::Times, learn/base/spmm.h:23-29,56-81: Y[rows x dim] = D X[xrows x dim], row major. */
+WH_API int wh_spmm_times(whContext* ctx, const whLocalBlock* D, int mem, const float* x, size_t xsize,
+                         float* y, int dim);
+/* SpMM::TransTimes, learn/base/spmm.h:34-52,85-123: Y[ysize] = p*Z + D^T X (z may be NULL). */
+WH_API int wh_spmm_trans_times(whContext* ctx, const whLocalBlock* D, int mem, const float* x, float p,
+                               const float* z, float* y, size_t ysize, int dim);
+
+/* ---- (3) loss --------------------------------------------------------------------------- */
+/* BinClassEval<float>, learn/base/binary_class_evaluation.h:17-74.
+ * out = {AUC, Accuracy(0), LogLoss, LogitObjv, AUC_lo, AUC_hi}. Examples with equal scores are
+ * left in unspecified order by the reference's std::sort (:25-26); AUC counts a tied
+ * (positive, negative) pair as 1/2 and AUC_lo / AUC_hi bound every possible tie order. */
+WH_API int wh_bin_eval(whContext* ctx, const float* label, const float* predict, size_t n, int mem,
+                       float* out6);
+/* CreateLoss(loss)->Init(D, w, nt); Evaluate(&prog); CalcGrad(&grad)
+ * (learn/linear/loss.h:32-49,81-115,128-156,172-182).
+ * prog[6] = {objv, acc, auc, count, new_ex, new_w} (learn/linear/progress.h:28-34), host memory.
+ * grad[U] (NULL: skip CalcGrad), xw[rows] and dual[rows] (NULL: not returned) follow `mem`.
+ * WH_LOSS_SQUARE is unimplemented in the reference (loss.h:163-166,178-180) and fails here too. */
+WH_API int wh_linear_loss(whContext* ctx, int loss, const whLocalBlock* D, int mem, const float* w,
+                          size_t U, double* prog, float* grad, float* xw, float* dual);
+
+/* ---- (4) server side: the model shard and its update handles ---------------------------- */
+typedef struct {
+  int algo;                /* WH_ALGO_* : SGDHandle / AdaGradHandle / FTRLHandle */
+  float lambda_l1;         /* conf.lambda_l1(), learn/linear/async_sgd.h:203 */
+  float lambda_l2;         /* conf.lambda_l2(), :204 */
+  int has_lr_eta;          /* handle alpha stays 0.1 unless the key is present (:49,205) */
+  float lr_eta;
+  int has_lr_beta;         /* handle beta stays 1 unless the key is present (:49,206) */
+  float lr_beta;
+  uint64_t key_begin;      /* this shard owns transformed keys in [key_begin, key_end) */
+  uint64_t key_end;        /* dense direct-addressed table: key_end - key_begin entries */
+} whServerConfig;
+
+/* AsgdServer::CreateServer<Entry,Handle>, learn/linear/async_sgd.h:200-213. */
+WH_API int wh_server_create(whContext* ctx, const whServerConfig* conf, whServer** out);
+WH_API int wh_server_destroy(whServer* s);
+/* One pull message: Handle::Pull per key (learn/linear/async_sgd.h:97-99,137-139,177-179). */
+WH_API int wh_server_pull(whServer* s, const uint64_t* keys, size_t n, int mem, float* vals);
+/* One push message: Handle::Start(push) (SGD: eta from t, t += 1, :85-90), Handle::Push per key
+ * in message order (:91-95,123-135,160-175), Handle::Finish. Keys must be distinct (they are the
+ * unique list of one minibatch). */
+WH_API int wh_server_push(whServer* s, const uint64_t* keys, size_t n, int mem, const float* grads);
+/* ISGDHandle::new_w accumulated so far: the number of non-zero weights (:35-41). Synchronises. */
+WH_API int wh_server_nnz_w(whServer* s, int64_t* out);
+/* Entry fields for the given keys: w, z (FTRL), sq_cum_grad (AdaGrad/FTRL); NULL = skip. */
+WH_API int wh_server_get_state(whServer* s, const uint64_t* keys, size_t n, int mem, float* w, float* z,
+                               float* sq_cum_grad);
+WH_API int wh_server_set_state(whServer* s, const uint64_t* keys, size_t n, int mem, const float* w,
+                               const float* z, const float* sq_cum_grad);
+/* SGDHandle::t (learn/linear/async_sgd.h:100). */
+WH_API int wh_server_sgd_t(const whServer* s);
+
+/* ---- the per-minibatch pipeline --------------------------------------------------------- */
+/* AsgdWorker, learn/linear/async_sgd.h:229-305, bound to one server shard that owns every key
+ * (1 worker, 1 server). max_key is ps::FLAGS_max_key. */
+WH_API int wh_worker_create(whContext* ctx, whServer* server, int loss, uint64_t max_key,
+                            whWorker** out);
+WH_API int wh_worker_destroy(whWorker* w);
+/* AsgdWorker::ProcessMinibatch, learn/linear/async_sgd.h:240-288: Localize -> ZPull ->
+ * Init/Evaluate -> (train) CalcGrad -> ZPush. prog[6] as in wh_linear_loss, with new_w the
+ * server's change of |w|_0 for this minibatch. Synchronous. */
+WH_API int wh_worker_process_minibatch(whWorker* w, const whRowBlock* blk, int mem, int train,
+                                       double* prog);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* WORMHOLE_B200_H_ */

@@ -1,0 +1,330 @@
+"""Parity of the CUDA path (through the C-ABI, host-pointer convention) against the CPU checker:
+oracle/_ref (the reference's own headers) when it travelled with the snapshot, else the C port.
+
+Bars (BASELINE.json north_star): localized keys / index remaps / counts bit-exact; forward
+products bit-exact; gradients and weights within 1e-5 relative in fp32, where "relative" for a
+sum of signed terms means relative to the sum of |terms| (the reference's own fp32 accumulation
+error is of that order and depends on its summation order); AUC within 1e-4."""
+import numpy as np
+import pytest
+
+from tests.util import random_block, wide_ids
+from wormhole_b200 import capi
+from wormhole_b200.rowblock import RowBlock
+
+pytestmark = pytest.mark.gpu
+
+RTOL = 1e-5   # north_star: "within 1e-5 relative in fp32"
+NO = capi.NO_MAX_KEY
+
+
+@pytest.fixture(scope="module")
+def gpu():
+    c = capi.Context(0)
+    yield c
+    c.close()
+
+
+def same_loc(a, b, counts=True):
+    assert np.array_equal(a.uniq, b.uniq)
+    if counts:
+        assert np.array_equal(a.cnt, b.cnt)
+    assert np.array_equal(a.offset, b.offset)
+    assert np.array_equal(a.index, b.index)
+    assert (a.value is None) == (b.value is None)
+    if a.value is not None:
+        assert np.array_equal(a.value, b.value)
+    assert np.array_equal(a.label, b.label)
+
+
+def abs_terms(D, x, U):
+    """sum_j |x_i * val_ij| per output column: the scale of a transposed product's rounding."""
+    rows = np.repeat(np.arange(D.rows), np.diff(D.offset.astype(np.int64)))
+    t = np.abs(x[rows].astype(np.float64) * (1.0 if D.value is None else D.value.astype(np.float64)))
+    out = np.zeros(U)
+    np.add.at(out, D.index, t)
+    return out
+
+
+def close_sum(got, want, scale, rtol=RTOL):
+    err = np.abs(got.astype(np.float64) - want.astype(np.float64))
+    bound = rtol * scale + 1e-30
+    bad = err > bound
+    assert not bad.any(), "max err/bound = %g at %d" % ((err / bound).max(), int(np.argmax(err / bound)))
+
+
+# ---------------------------------------------------------------- (1) localizer ------------
+
+def test_known_answers(gpu):
+    assert capi.reverse_bytes(5) == 0x5000000000000000
+    blk = RowBlock([0, 4, 6], [5, 1000000007, 5, 42, 42, 7], None, [1, 0])
+    r = gpu.localize(blk)
+    assert [hex(int(x)) for x in r.uniq] == ["0x5000000000000000", "0x7000000000000000",
+                                             "0x70aca9b300000000", "0xa200000000000000"]
+    assert r.index.tolist() == [0, 2, 0, 3, 3, 1]
+    assert r.cnt.tolist() == [2, 1, 1, 2]
+
+
+@pytest.mark.parametrize("max_key", [NO, 2 ** 24, 1000003, 7, 2 ** 28])
+@pytest.mark.parametrize("with_value", [False, True])
+def test_localize_bit_exact(gpu, checker, max_key, with_value):
+    rng = np.random.default_rng(11)
+    methods = [capi.LOC_SORT] + ([capi.LOC_DIRECT] if max_key <= 2 ** 28 else [])
+    for rows, mx, space in [(1, 3, 10), (50, 8, 100), (3000, 40, 2 ** 40), (20000, 39, 2 ** 62)]:
+        blk = random_block(rng, rows, mx, space, with_value, empty_rows=(rows > 1))
+        if blk.nnz == 0:
+            continue
+        want = checker.localize(blk, max_key)
+        for m in methods:
+            same_loc(gpu.localize(blk, max_key, method=m), want)
+        same_loc(gpu.localize(blk, max_key, float_cnt=True), checker.localize(blk, max_key, float_cnt=True))
+        same_loc(gpu.localize(blk, max_key, counts=False), want, counts=False)
+
+
+def test_localize_wide_keys_all_digits(gpu, checker):
+    rng = np.random.default_rng(12)
+    n = 100000
+    blk = RowBlock(np.arange(0, n + 1, 4), wide_ids(rng, n), None, np.zeros(n // 4))
+    same_loc(gpu.localize(blk, NO), checker.localize(blk, NO))
+    same_loc(gpu.localize(blk, 2 ** 24, method=capi.LOC_SORT), checker.localize(blk, 2 ** 24))
+
+
+def test_localize_criteo_shape(gpu, checker):
+    from wormhole_b200 import synth
+    blk = synth.criteo_minibatch(3, rows=100000)
+    want = checker.localize(blk, 2 ** 24)
+    same_loc(gpu.localize(blk, 2 ** 24, method=capi.LOC_DIRECT), want)
+    same_loc(gpu.localize(blk, 2 ** 24, method=capi.LOC_SORT), want)
+    # properties that hold at any size: ascending unique keys, ranks consistent, counts sum to nnz
+    got = gpu.localize(blk, 2 ** 24)
+    assert np.all(np.diff(got.uniq.astype(np.int64)) > 0)
+    assert np.array_equal(got.uniq[got.index], blk.index % np.uint64(2 ** 24))
+    assert int(got.cnt.sum()) == blk.nnz
+
+
+def test_localize_device_input(gpu, checker):
+    import torch
+    rng = np.random.default_rng(13)
+    blk = random_block(rng, 5000, 30, 2 ** 30, True, empty_rows=True)
+    dev = RowBlock.__new__(RowBlock)
+    dev.offset = torch.from_numpy(blk.offset.astype(np.int64)).cuda()
+    dev.index = torch.from_numpy(blk.index.astype(np.int64)).cuda()
+    dev.value = torch.from_numpy(blk.value).cuda()
+    dev.label = torch.from_numpy(blk.label).cuda()
+    torch.cuda.synchronize()
+    same_loc(gpu.localize(dev, 2 ** 24, mem=capi.WH_DEVICE), checker.localize(blk, 2 ** 24))
+
+
+def test_remap_with_foreign_dict(gpu, checker):
+    rng = np.random.default_rng(14)
+    blk = random_block(rng, 2000, 10, 300, True)
+    full = checker.localize(blk, 2 ** 24).uniq
+    for keep in (full[::2], full[:1], full[-3:], np.array([2 ** 30], np.uint64), full):
+        a, b = gpu.remap(blk, keep, 2 ** 24), checker.remap(blk, keep, 2 ** 24)
+        assert np.array_equal(a.offset, b.offset) and np.array_equal(a.index, b.index)
+        if b.value is not None:
+            assert np.array_equal(a.value, b.value)
+        assert np.array_equal(a.label, b.label)
+
+
+def test_empty_block(gpu):
+    blk = RowBlock([0], np.zeros(0, np.uint64), None, np.zeros(0, np.float32))
+    r = gpu.localize(blk, 2 ** 24)
+    assert len(r.uniq) == 0 and len(r.index) == 0
+
+
+def test_errors_are_reported(gpu):
+    blk = RowBlock([0, 1], [3], None, [1])
+    with pytest.raises(capi.WormholeError):
+        gpu.localize(blk, 2 ** 40, method=capi.LOC_DIRECT)   # direct addressing needs a hashed space
+    with pytest.raises(capi.WormholeError):
+        gpu.linear_loss(capi.LOSS_SQUARE, gpu.localize(blk), np.zeros(1, np.float32))  # loss.h:178-180
+
+
+# ---------------------------------------------------------------- (2)/(5) SpMV, SpMM -------
+
+@pytest.mark.parametrize("with_value", [False, True])
+def test_spmv(gpu, checker, with_value):
+    rng = np.random.default_rng(21)
+    for rows, mx, space in [(1, 5, 10), (800, 30, 5000), (30000, 39, 2 ** 30), (300, 300, 100)]:
+        blk = random_block(rng, rows, mx, space, with_value)
+        if blk.nnz == 0:
+            continue
+        D = checker.localize(blk, 2 ** 24)
+        U = len(D.uniq)
+        x = rng.standard_normal(U).astype(np.float32)
+        d = rng.standard_normal(D.rows).astype(np.float32)
+        y0 = rng.standard_normal(D.rows).astype(np.float32)   # rows without entries keep y (spmv.h:79)
+        assert np.array_equal(gpu.spmv_times(D, x, y0.copy()), checker.spmv_times(D, x, y0.copy()))
+        close_sum(gpu.spmv_trans_times(D, d, U), checker.spmv_trans_times(D, d, U), abs_terms(D, d, U))
+
+
+def test_spmv_trans_is_order_independent(gpu, checker):
+    """Fixed-point accumulation: bit-identical run to run, and closer to the fp64 truth than 1e-5."""
+    rng = np.random.default_rng(22)
+    blk = random_block(rng, 50000, 39, 2000, False)      # hot columns: ~1000 entries per key
+    D = checker.localize(blk, 2 ** 24)
+    U = len(D.uniq)
+    d = rng.standard_normal(D.rows).astype(np.float32)
+    a, b = gpu.spmv_trans_times(D, d, U), gpu.spmv_trans_times(D, d, U)
+    assert np.array_equal(a, b)
+    rows = np.repeat(np.arange(D.rows), np.diff(D.offset.astype(np.int64)))
+    truth = np.zeros(U)
+    np.add.at(truth, D.index, d[rows].astype(np.float64))
+    close_sum(a, truth.astype(np.float32), abs_terms(D, d, U), rtol=1e-6)
+    close_sum(checker.spmv_trans_times(D, d, U), truth.astype(np.float32), abs_terms(D, d, U))
+
+
+@pytest.mark.parametrize("dim", [1, 5, 16])
+@pytest.mark.parametrize("with_value", [False, True])
+def test_spmm(gpu, checker, dim, with_value):
+    rng = np.random.default_rng(23)
+    blk = random_block(rng, 2000, 30, 5000, with_value)
+    D = checker.localize(blk, 2 ** 24)
+    U = len(D.uniq)
+    X = rng.standard_normal(U * dim).astype(np.float32)
+    Y = rng.standard_normal(D.rows * dim).astype(np.float32)
+    Z = rng.standard_normal(U * dim).astype(np.float32)
+    assert np.array_equal(gpu.spmm_times(D, X, dim), checker.spmm_times(D, X, dim))
+    scale = np.stack([abs_terms(D, np.ascontiguousarray(Y.reshape(-1, dim)[:, k]), U) for k in range(dim)], 1).reshape(-1)
+    close_sum(gpu.spmm_trans_times(D, Y, U * dim, dim), checker.spmm_trans_times(D, Y, U * dim, dim), scale)
+    close_sum(gpu.spmm_trans_times(D, Y, U * dim, dim, 0.5, Z),
+              checker.spmm_trans_times(D, Y, U * dim, dim, 0.5, Z), scale + np.abs(Z) * 0.5)
+
+
+# ---------------------------------------------------------------- (3) loss ------------------
+
+def test_bin_eval(gpu, checker):
+    rng = np.random.default_rng(31)
+    for n in (1, 2, 777, 20000, 300000):
+        label = (rng.random(n) < 0.3).astype(np.float32)
+        pred = (rng.standard_normal(n) * 3).astype(np.float32)
+        a, b = gpu.bin_eval(label, pred), checker.bin_eval(label, pred, 2)
+        assert a["acc"] == b["acc"]
+        assert abs(a["logit_objv"] - b["logit_objv"]) <= 2e-6 * abs(b["logit_objv"]) + 1e-6
+        assert abs(a["logloss"] - b["logloss"]) <= 2e-6 * abs(b["logloss"]) + 1e-6
+        assert abs(a["auc"] - b["auc"]) <= 1e-4       # reference accumulates the area in fp32
+        assert a["auc_lo"] - 1e-4 <= b["auc"] <= a["auc_hi"] + 1e-4
+    # equal scores: any tie order of the reference's unstable sort lies inside [auc_lo, auc_hi]
+    label = (rng.random(5000) < 0.5).astype(np.float32)
+    pred = rng.integers(0, 7, 5000).astype(np.float32)
+    a, b = gpu.bin_eval(label, pred), checker.bin_eval(label, pred, 2)
+    assert a["auc_lo"] - 1e-5 <= b["auc"] <= a["auc_hi"] + 1e-5
+    assert a["auc_lo"] <= a["auc"] <= a["auc_hi"]
+    one = np.ones(10, np.float32)
+    assert gpu.bin_eval(one, one)["auc"] == 1.0      # single class (binary_class_evaluation.h:36)
+
+
+@pytest.mark.parametrize("loss", [capi.LOSS_LOGIT, capi.LOSS_SQUARE_HINGE])
+@pytest.mark.parametrize("with_value", [False, True])
+def test_linear_loss(gpu, checker, loss, with_value):
+    rng = np.random.default_rng(32)
+    blk = random_block(rng, 20000, 25, 30000, with_value)
+    D = checker.localize(blk, 2 ** 24)
+    U = len(D.uniq)
+    w = (rng.standard_normal(U) * 0.3).astype(np.float32)
+    pg, gg, xw, dual = gpu.linear_loss(loss, D, w, want_xw=True)
+    pc, gc = checker.linear_loss(loss, D, w, 2)
+    assert np.array_equal(xw, checker.spmv_times(D, w))                      # Xw bit-exact
+    assert pg[1] == pc[1] and pg[3] == pc[3] and pg[4] == pc[4]             # acc, count, new_ex
+    assert abs(pg[0] - pc[0]) <= 2e-6 * abs(pc[0])                           # objv
+    assert abs(pg[2] - pc[2]) <= 1e-4                                        # auc
+    mul = 2.0 if loss == capi.LOSS_SQUARE_HINGE else 1.0
+    close_sum(gg, gc, mul * abs_terms(D, dual, U))
+    # normwise: ||g_gpu - g_ref|| <= 1e-5 ||g_ref||
+    assert np.linalg.norm(gg.astype(np.float64) - gc) <= RTOL * np.linalg.norm(gc.astype(np.float64))
+
+
+# ---------------------------------------------------------------- (4) server handles -------
+
+@pytest.mark.parametrize("algo", [capi.ALGO_SGD, capi.ALGO_ADAGRAD, capi.ALGO_FTRL])
+def test_handle_push_bit_exact(gpu, checker, algo):
+    """Same gradients in -> bit-identical {w, z, sq_cum_grad}, |w|_0 and SGD t out."""
+    rng = np.random.default_rng(41)
+    n = 20000
+    for eta, beta, l1, l2 in [(None, None, 1.0, 0.0), (0.1, 1.0, 1.0, 0.1), (0.05, 2.0, 0.0, 0.0)]:
+        srv = capi.Server(gpu, algo, l1, l2, eta, beta, 1000, 1000 + 4 * n)
+        keys = (1000 + np.sort(rng.choice(4 * n, n, replace=False))).astype(np.uint64)
+        w = (rng.standard_normal(n) * (rng.random(n) < 0.7)).astype(np.float32)
+        z = (rng.standard_normal(n)).astype(np.float32)
+        cg = np.abs(rng.standard_normal(n)).astype(np.float32)
+        srv.set_state(keys, w, z, cg)
+        nnz0 = srv.nnz_w()
+        assert nnz0 == int((w != 0).sum())
+        t = 1
+        for step in range(3):
+            g = (rng.standard_normal(n) * 2).astype(np.float32)
+            srv.push(keys, g)
+            dn, t = checker.handle_push(algo, l1, l2, eta, beta, g, w, z, cg, t)
+            nnz0 += dn
+            gw, gz, gc = srv.get_state(keys)
+            assert np.array_equal(gw, w)
+            if algo == capi.ALGO_FTRL:
+                assert np.array_equal(gz, z)
+            if algo != capi.ALGO_SGD:
+                assert np.array_equal(gc, cg)
+            assert srv.nnz_w() == nnz0
+            assert np.array_equal(srv.pull(keys), w)
+        if algo == capi.ALGO_SGD:
+            assert srv.sgd_t() == t
+        srv.close()
+
+
+def test_server_rejects_foreign_keys(gpu):
+    srv = capi.Server(gpu, capi.ALGO_FTRL, key_begin=100, key_end=200)
+    with pytest.raises(capi.WormholeError):
+        srv.pull(np.array([5], np.uint64))
+    with pytest.raises(capi.WormholeError):
+        srv.push(np.array([200], np.uint64), np.ones(1, np.float32))
+    srv.close()
+
+
+# ---------------------------------------------------------------- the whole path ------------
+
+def weights_close(gpu_state, ref_state, rtol=1e-5):
+    """Per-entry fields within rtol of the field's magnitude scale; reports the worst offender."""
+    for name, a, b in zip(("w", "z", "cg"), gpu_state, ref_state):
+        err = np.abs(a.astype(np.float64) - b)
+        tol = rtol * np.maximum(np.abs(b), 1.0)
+        assert (err <= tol).all(), "%s: worst %g at %d" % (name, (err / tol).max(), int(np.argmax(err / tol)))
+
+
+@pytest.mark.parametrize("algo", [capi.ALGO_SGD, capi.ALGO_ADAGRAD, capi.ALGO_FTRL])
+@pytest.mark.parametrize("loss", [capi.LOSS_LOGIT, capi.LOSS_SQUARE_HINGE])
+@pytest.mark.parametrize("max_key", [2 ** 20, 1000003])
+def test_process_minibatch_vs_reference(gpu, checker, algo, loss, max_key):
+    """AsgdWorker::ProcessMinibatch, 1 worker + 1 server, max_concurrency = 1."""
+    rng = np.random.default_rng(51)
+    l1, l2, eta, beta = 0.5, 0.1, 0.1, 1.0
+    job = checker.linear_create(algo, loss, l1, l2, eta, beta, max_key)
+    srv = capi.Server(gpu, algo, l1, l2, eta, beta, 0, max_key)
+    wk = capi.Worker(gpu, srv, loss, max_key)
+    nnz_w = 0
+    for m in range(8):
+        blk = random_block(rng, 3000, 12, 20000, with_value=(m % 2 == 1), empty_rows=False)
+        pg = wk.process_minibatch(blk)
+        pc = checker.linear_minibatch(job, blk)
+        assert pg[4] == pc[4] and pg[3] == pc[3]
+        assert abs(pg[0] - pc[0]) <= 1e-5 * abs(pc[0]) + 1e-6, (m, pg, pc)
+        assert abs(pg[1] - pc[1]) <= 1e-3
+        nnz_w += pg[5]
+        keys, w, z, cg = checker.linear_model(job)
+        weights_close(srv.get_state(keys), (w, z, cg))
+    assert abs(nnz_w - srv.nnz_w()) == 0
+    keys, w, z, cg = checker.linear_model(job)
+    assert abs(srv.nnz_w() - int((w != 0).sum())) <= max(2, 1e-3 * len(w))
+    wk.close(); srv.close(); checker.linear_destroy(job)
+
+
+def test_default_key_mode_uses_sort_path(gpu, checker):
+    """ps::FLAGS_max_key at its default: nibble-reversed 64-bit keys (learn/base/localizer.h:116-121).
+    The dense shard cannot hold them; the localizer + loss still must agree."""
+    rng = np.random.default_rng(52)
+    blk = random_block(rng, 4000, 22, 127, False, empty_rows=False)   # agaricus-like ids
+    D = gpu.localize(blk)
+    same_loc(D, checker.localize(blk))
+    w = (rng.standard_normal(len(D.uniq)) * 0.2).astype(np.float32)
+    pg, gg = gpu.linear_loss(capi.LOSS_LOGIT, D, w)
+    pc, gc = checker.linear_loss(capi.LOSS_LOGIT, D, w, 2)
+    assert abs(pg[0] - pc[0]) <= 2e-6 * abs(pc[0])
+    assert np.linalg.norm(gg.astype(np.float64) - gc) <= RTOL * np.linalg.norm(gc.astype(np.float64))

@@ -1,0 +1,289 @@
+"""ctypes binding of include/wormhole_b200.h plus a thin Python mirror of the reference's
+operator interface for this path (same names and argument meaning as the C++ headers under
+learn/base and learn/linear), so parity tests read like the reference's call sites.
+
+There is no CPU fallback: loading fails loudly when libwormhole_b200.so is missing, and every
+compute call needs a CUDA device (wh_create fails otherwise).
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+from .rowblock import LocalBlock, RowBlock
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libwormhole_b200.so")
+
+WH_HOST, WH_DEVICE = 0, 1
+LOSS_SQUARE, LOSS_LOGIT, LOSS_SQUARE_HINGE = 1, 2, 4
+ALGO_SGD, ALGO_ADAGRAD, ALGO_FTRL = 1, 2, 3
+LOC_AUTO, LOC_DIRECT, LOC_SORT, LOC_WITH_COUNTS = 0, 1, 2, 16
+NO_MAX_KEY = 2 ** 64 - 1
+
+
+class WormholeError(RuntimeError):
+    pass
+
+
+class _RowBlock(C.Structure):
+    _fields_ = [("size", C.c_size_t), ("offset", C.c_void_p), ("label", C.c_void_p),
+                ("weight", C.c_void_p), ("index", C.c_void_p), ("value", C.c_void_p)]
+
+
+class _LocalBlock(C.Structure):
+    _fields_ = [("size", C.c_size_t), ("offset", C.c_void_p), ("label", C.c_void_p),
+                ("index", C.c_void_p), ("value", C.c_void_p)]
+
+
+class _ServerConfig(C.Structure):
+    _fields_ = [("algo", C.c_int), ("lambda_l1", C.c_float), ("lambda_l2", C.c_float),
+                ("has_lr_eta", C.c_int), ("lr_eta", C.c_float), ("has_lr_beta", C.c_int),
+                ("lr_beta", C.c_float), ("key_begin", C.c_uint64), ("key_end", C.c_uint64)]
+
+
+_lib = None
+
+
+def lib():
+    """The loaded extension. Raises if it was not built: the product has no other path."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise WormholeError(
+                "wormhole_b200: %s is missing. Build it with `python -m wormhole_b200.build` "
+                "(or __graft_entry__.build()); there is no CPU fallback." % LIB_PATH)
+        L = C.CDLL(LIB_PATH)
+        L.wh_last_error.restype = C.c_char_p
+        L.wh_version.restype = C.c_char_p
+        L.wh_kernel_launches.restype = C.c_uint64
+        L.wh_reverse_bytes.restype = C.c_uint64
+        L.wh_reverse_bytes.argtypes = [C.c_uint64]
+        for n in ("wh_batch_rows", "wh_batch_nnz", "wh_batch_num_uniq"):
+            getattr(L, n).restype = C.c_size_t
+            getattr(L, n).argtypes = [C.c_void_p]
+        for n in ("wh_batch_has_value", "wh_batch_has_label", "wh_batch_destroy", "wh_destroy",
+                  "wh_sync", "wh_server_destroy", "wh_worker_destroy", "wh_server_sgd_t"):
+            getattr(L, n).argtypes = [C.c_void_p]
+        _lib = L
+    return _lib
+
+
+def _check(rc):
+    if rc != 0:
+        raise WormholeError("wormhole_b200 error %d: %s" % (rc, lib().wh_last_error().decode()))
+
+
+def _ptr(a):
+    """Pointer of a numpy array, a torch tensor (host or device) or None."""
+    if a is None:
+        return None
+    if isinstance(a, np.ndarray):
+        return C.c_void_p(a.ctypes.data)
+    return C.c_void_p(a.data_ptr())  # torch.Tensor
+
+
+def _rowblock(blk):
+    r = _RowBlock()
+    r.size = blk.rows
+    r.offset, r.label, r.weight = _ptr(blk.offset), _ptr(blk.label), None
+    r.index, r.value = _ptr(blk.index), _ptr(blk.value)
+    return r
+
+
+def _localblock(D):
+    r = _LocalBlock()
+    r.size = D.rows
+    r.offset, r.label, r.index, r.value = _ptr(D.offset), _ptr(D.label), _ptr(D.index), _ptr(D.value)
+    return r
+
+
+def _f32(a):
+    return None if a is None else np.ascontiguousarray(a, dtype=np.float32)
+
+
+def reverse_bytes(x):
+    """dmlc::ReverseBytes (learn/base/localizer.h:16-26)."""
+    return int(lib().wh_reverse_bytes(C.c_uint64(int(x))))
+
+
+def kernel_launches():
+    return int(lib().wh_kernel_launches())
+
+
+class Context:
+    """One GPU (whContext)."""
+
+    def __init__(self, device=0):
+        self.h = C.c_void_p()
+        _check(lib().wh_create(C.c_int(device), C.byref(self.h)))
+        self.device = device
+
+    def set_stream(self, cuda_stream):
+        _check(lib().wh_set_stream(self.h, C.c_void_p(cuda_stream)))
+
+    def sync(self):
+        _check(lib().wh_sync(self.h))
+
+    def close(self):
+        if self.h:
+            lib().wh_destroy(self.h)
+            self.h = None
+
+    # ---- Localizer<uint64_t> (learn/base/localizer.h) --------------------------------------
+    def localize(self, blk, max_key=NO_MAX_KEY, method=LOC_AUTO, counts=True, float_cnt=False,
+                 mem=WH_HOST):
+        """Localizer::Localize(blk, &localized, &uniq_idx, &idx_frq) -> LocalBlock (host arrays)."""
+        b = C.c_void_p()
+        rb = _rowblock(blk)
+        m = method | (LOC_WITH_COUNTS if counts else 0)
+        _check(lib().wh_localize(self.h, C.byref(rb), C.c_int(mem), C.c_uint64(max_key), C.c_int(m),
+                                 C.byref(b)))
+        return self._collect(b, counts, float_cnt)
+
+    def remap(self, blk, dict_keys, max_key=NO_MAX_KEY):
+        """CountUniqIndex(blk) then RemapIndex(blk, dict_keys, &localized)."""
+        d = np.ascontiguousarray(dict_keys, np.uint64)
+        b = C.c_void_p()
+        rb = _rowblock(blk)
+        _check(lib().wh_localize_with_dict(self.h, C.byref(rb), C.c_int(WH_HOST), C.c_uint64(max_key),
+                                           _ptr(d), C.c_size_t(len(d)), C.byref(b)))
+        return self._collect(b, True, False)
+
+    def _collect(self, b, counts, float_cnt):
+        L = lib()
+        try:
+            U, n, rows = L.wh_batch_num_uniq(b), L.wh_batch_nnz(b), L.wh_batch_rows(b)
+            out = LocalBlock()
+            out.uniq = np.zeros(U, np.uint64)
+            out.cnt = np.zeros(U, np.float32 if float_cnt else np.uint32) if counts else None
+            out.offset = np.zeros(rows + 1, np.uint64)
+            out.index = np.zeros(n, np.uint32)
+            out.value = np.zeros(n, np.float32) if L.wh_batch_has_value(b) else None
+            out.label = np.zeros(rows, np.float32) if L.wh_batch_has_label(b) else None
+            _check(L.wh_batch_copy(self.h, b, _ptr(out.uniq),
+                                   _ptr(out.cnt) if counts and not float_cnt else None,
+                                   _ptr(out.cnt) if counts and float_cnt else None,
+                                   _ptr(out.offset), _ptr(out.index), _ptr(out.value), _ptr(out.label)))
+            return out
+        finally:
+            L.wh_batch_destroy(b)
+
+    # ---- SpMV / SpMM (learn/base/spmv.h, spmm.h) ---------------------------------------------
+    def spmv_times(self, D, x, y=None):
+        x = _f32(x)
+        y = np.zeros(D.rows, np.float32) if y is None else y
+        lb = _localblock(D)
+        _check(lib().wh_spmv_times(self.h, C.byref(lb), C.c_int(WH_HOST), _ptr(x), C.c_size_t(len(x)), _ptr(y)))
+        return y
+
+    def spmv_trans_times(self, D, x, ysize):
+        x = _f32(x)
+        y = np.empty(ysize, np.float32)
+        lb = _localblock(D)
+        _check(lib().wh_spmv_trans_times(self.h, C.byref(lb), C.c_int(WH_HOST), _ptr(x), _ptr(y), C.c_size_t(ysize)))
+        return y
+
+    def spmm_times(self, D, x, dim):
+        x = _f32(x)
+        y = np.zeros(D.rows * dim, np.float32)
+        lb = _localblock(D)
+        _check(lib().wh_spmm_times(self.h, C.byref(lb), C.c_int(WH_HOST), _ptr(x), C.c_size_t(len(x)), _ptr(y), C.c_int(dim)))
+        return y
+
+    def spmm_trans_times(self, D, x, ysize, dim, p=0.0, z=None):
+        x, z = _f32(x), _f32(z)
+        y = np.zeros(ysize, np.float32)
+        lb = _localblock(D)
+        _check(lib().wh_spmm_trans_times(self.h, C.byref(lb), C.c_int(WH_HOST), _ptr(x), C.c_float(p), _ptr(z),
+                                         _ptr(y), C.c_size_t(ysize), C.c_int(dim)))
+        return y
+
+    # ---- BinClassEval / ScalarLoss (learn/base/binary_class_evaluation.h, learn/linear/loss.h) --
+    def bin_eval(self, label, predict):
+        label, predict = _f32(label), _f32(predict)
+        out = np.zeros(6, np.float32)
+        _check(lib().wh_bin_eval(self.h, _ptr(label), _ptr(predict), C.c_size_t(len(label)), C.c_int(WH_HOST), _ptr(out)))
+        return dict(auc=out[0], acc=out[1], logloss=out[2], logit_objv=out[3], auc_lo=out[4], auc_hi=out[5])
+
+    def linear_loss(self, loss, D, w, want_grad=True, want_xw=False):
+        """CreateLoss(loss)->Init(D, w); Evaluate(&prog); CalcGrad(&grad)."""
+        w = _f32(w)
+        prog = np.zeros(6, np.float64)
+        grad = np.empty(len(w), np.float32) if want_grad else None
+        xw = np.empty(D.rows, np.float32) if want_xw else None
+        dual = np.empty(D.rows, np.float32) if want_xw else None
+        lb = _localblock(D)
+        _check(lib().wh_linear_loss(self.h, C.c_int(loss), C.byref(lb), C.c_int(WH_HOST), _ptr(w),
+                                    C.c_size_t(len(w)), _ptr(prog), _ptr(grad), _ptr(xw), _ptr(dual)))
+        return (prog, grad, xw, dual) if want_xw else (prog, grad)
+
+
+class Server:
+    """One model shard with its update handle (AsgdServer::CreateServer + SGD/AdaGrad/FTRL handle,
+    learn/linear/async_sgd.h:83-213). eta / beta None = key absent from the conf."""
+
+    def __init__(self, ctx, algo=ALGO_FTRL, l1=1.0, l2=0.0, eta=None, beta=None, key_begin=0,
+                 key_end=2 ** 24):
+        self.ctx = ctx
+        cfg = _ServerConfig(algo, l1, l2, int(eta is not None), eta or 0.0, int(beta is not None),
+                            beta or 0.0, key_begin, key_end)
+        self.h = C.c_void_p()
+        _check(lib().wh_server_create(ctx.h, C.byref(cfg), C.byref(self.h)))
+        self.algo = algo
+
+    def pull(self, keys):
+        keys = np.ascontiguousarray(keys, np.uint64)
+        vals = np.empty(len(keys), np.float32)
+        _check(lib().wh_server_pull(self.h, _ptr(keys), C.c_size_t(len(keys)), C.c_int(WH_HOST), _ptr(vals)))
+        return vals
+
+    def push(self, keys, grads):
+        keys, grads = np.ascontiguousarray(keys, np.uint64), _f32(grads)
+        _check(lib().wh_server_push(self.h, _ptr(keys), C.c_size_t(len(keys)), C.c_int(WH_HOST), _ptr(grads)))
+
+    def nnz_w(self):
+        out = C.c_int64()
+        _check(lib().wh_server_nnz_w(self.h, C.byref(out)))
+        return out.value
+
+    def sgd_t(self):
+        return lib().wh_server_sgd_t(self.h)
+
+    def get_state(self, keys):
+        keys = np.ascontiguousarray(keys, np.uint64)
+        w, z, cg = (np.zeros(len(keys), np.float32) for _ in range(3))
+        _check(lib().wh_server_get_state(self.h, _ptr(keys), C.c_size_t(len(keys)), C.c_int(WH_HOST),
+                                         _ptr(w), _ptr(z), _ptr(cg)))
+        return w, z, cg
+
+    def set_state(self, keys, w=None, z=None, cg=None):
+        keys = np.ascontiguousarray(keys, np.uint64)
+        _check(lib().wh_server_set_state(self.h, _ptr(keys), C.c_size_t(len(keys)), C.c_int(WH_HOST),
+                                         _ptr(_f32(w)), _ptr(_f32(z)), _ptr(_f32(cg))))
+
+    def close(self):
+        if self.h:
+            lib().wh_server_destroy(self.h)
+            self.h = None
+
+
+class Worker:
+    """AsgdWorker (learn/linear/async_sgd.h:229-305) bound to one server on the same GPU."""
+
+    def __init__(self, ctx, server, loss=LOSS_LOGIT, max_key=NO_MAX_KEY):
+        self.ctx, self.server = ctx, server
+        self.h = C.c_void_p()
+        _check(lib().wh_worker_create(ctx.h, server.h, C.c_int(loss), C.c_uint64(max_key), C.byref(self.h)))
+
+    def process_minibatch(self, blk, train=True, mem=WH_HOST):
+        """ProcessMinibatch(mb, wl): -> progress {objv, acc, auc, count, new_ex, new_w}."""
+        prog = np.zeros(6, np.float64)
+        rb = _rowblock(blk)
+        _check(lib().wh_worker_process_minibatch(self.h, C.byref(rb), C.c_int(mem), C.c_int(train), _ptr(prog)))
+        return prog
+
+    def close(self):
+        if self.h:
+            lib().wh_worker_destroy(self.h)
+            self.h = None

@@ -1,0 +1,39 @@
+// whBatch: a localized minibatch living in HBM.
+#pragma once
+#include "common.cuh"
+#include "radix_sort.cuh"
+
+struct whBatch {
+  whContext* ctx = nullptr;
+  size_t rows = 0;
+  size_t nnz = 0;        // entries of the localized block (after any dictionary drop)
+  size_t nuniq = 0;      // unique transformed keys of the input block
+  bool has_value = false, has_label = false, has_cnt = false;
+  wh::DevBuf uniq;       // uint64[nuniq]
+  wh::DevBuf cnt;        // uint32[nuniq]
+  wh::DevBuf offset;     // size_t[rows+1]
+  wh::DevBuf index;      // uint32[nnz]
+  wh::DevBuf value;      // float[nnz]
+  wh::DevBuf label;      // float[rows]
+  ~whBatch() { uniq.release(); cnt.release(); offset.release(); index.release(); value.release(); label.release(); }
+};
+
+namespace wh {
+
+// Device-side inputs of one localize call.
+struct LocInput {
+  const uint64_t* index;   // nnz raw ids
+  size_t nnz;
+  KeyXform xf;
+};
+
+// Direct-addressed localizer (hashed key spaces): outputs uniq (ascending), local ids, optional
+// counts; *d_nuniq receives U. All stream-ordered, no host sync.
+int localize_direct(whContext* ctx, const LocInput& in, uint64_t* d_uniq, uint32_t* d_cnt,
+                    uint32_t* d_index, unsigned* d_nuniq);
+// Radix-sort localizer (any 64-bit keys).
+int localize_sort(whContext* ctx, const LocInput& in, uint64_t* d_uniq, uint32_t* d_cnt,
+                  uint32_t* d_index, unsigned* d_nuniq);
+bool direct_supported(uint64_t max_key);
+
+}  // namespace wh

@@ -1,0 +1,180 @@
+// Shared internals of libwormhole_b200.so: error plumbing, the per-GPU context with its
+// scratch arena, and small device helpers. Not part of the public ABI.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <atomic>
+#include <string>
+#include <vector>
+
+#include "../../include/wormhole_b200.h"
+
+namespace wh {
+
+void set_error(const char* fmt, ...);
+extern std::atomic<uint64_t> g_launches;
+
+#define WH_CUDA(expr)                                                                      \
+  do {                                                                                     \
+    cudaError_t e__ = (expr);                                                              \
+    if (e__ != cudaSuccess) {                                                              \
+      wh::set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #expr, cudaGetErrorString(e__)); \
+      return WH_ERR_CUDA;                                                                  \
+    }                                                                                      \
+  } while (0)
+
+#define WH_TRY(expr)               \
+  do {                             \
+    int r__ = (expr);              \
+    if (r__ != WH_OK) return r__;  \
+  } while (0)
+
+#define WH_REQUIRE(cond, ...)        \
+  do {                               \
+    if (!(cond)) {                   \
+      wh::set_error(__VA_ARGS__);    \
+      return WH_ERR_INVALID;         \
+    }                                \
+  } while (0)
+
+// Launch + count + check. Grid sizes of zero are skipped (empty inputs).
+#define WH_LAUNCH(kernel, grid, block, smem, stream, ...)                      \
+  do {                                                                         \
+    if ((grid) > 0) {                                                          \
+      kernel<<<(grid), (block), (smem), (stream)>>>(__VA_ARGS__);              \
+      wh::g_launches.fetch_add(1, std::memory_order_relaxed);                  \
+      WH_CUDA(cudaGetLastError());                                             \
+    }                                                                          \
+  } while (0)
+
+static inline size_t div_up(size_t a, size_t b) { return (a + b - 1) / b; }
+static inline size_t align_up(size_t a, size_t b) { return div_up(a, b) * b; }
+
+// A grow-only device buffer: reused across calls, reallocated only when too small.
+struct DevBuf {
+  void* p = nullptr;
+  size_t cap = 0;
+  int reserve(size_t bytes);
+  void release();
+  template <typename T> T* as() const { return reinterpret_cast<T*>(p); }
+};
+
+struct PinnedBuf {
+  void* p = nullptr;
+  size_t cap = 0;
+  int reserve(size_t bytes);
+  void release();
+  template <typename T> T* as() const { return reinterpret_cast<T*>(p); }
+};
+
+}  // namespace wh
+
+struct whContext {
+  int device = 0;
+  int num_sms = 148;
+  size_t l2_bytes = 0;
+  cudaStream_t stream = nullptr;
+  bool own_stream = true;
+  // scratch shared by the stateless entry points (grow-only)
+  wh::DevBuf directory;      // direct-address localizer: {bits, prefix} per 32 keys
+  size_t directory_words = 0;  // words currently known to be all-zero
+  wh::DevBuf scan_tmp;       // block sums of the directory scan
+  wh::DevBuf sort_tmp[6];    // radix sort ping-pong + histograms
+  wh::DevBuf acc;            // int64 fixed-point accumulators of the transposed products
+  wh::DevBuf small;          // device scalars (counts, plans, metric partials)
+  wh::DevBuf stage[8];       // staging of host arguments
+  wh::PinnedBuf pinned;      // host landing zone for small read-backs
+};
+
+namespace wh {
+
+struct DeviceGuard {
+  int prev = -1;
+  explicit DeviceGuard(int dev) { cudaGetDevice(&prev); if (prev != dev) cudaSetDevice(dev); else prev = -1; }
+  ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
+// Brings a host array to the device (stage buffer) or passes a device pointer through.
+template <typename T>
+int to_device(whContext* ctx, DevBuf& buf, const T* src, size_t n, int mem, const T** out) {
+  if (mem == WH_DEVICE || src == nullptr) { *out = src; return WH_OK; }
+  WH_TRY(buf.reserve((n ? n : 1) * sizeof(T)));
+  if (n) WH_CUDA(cudaMemcpyAsync(buf.p, src, n * sizeof(T), cudaMemcpyHostToDevice, ctx->stream));
+  *out = buf.as<T>();
+  return WH_OK;
+}
+
+// Output side of the same convention: compute into a stage buffer for host callers, copy back.
+template <typename T>
+int out_buffer(whContext* ctx, DevBuf& buf, T* user, size_t n, int mem, T** dev) {
+  if (mem == WH_DEVICE) { *dev = user; return WH_OK; }
+  WH_TRY(buf.reserve((n ? n : 1) * sizeof(T)));
+  *dev = buf.as<T>();
+  return WH_OK;
+}
+template <typename T>
+int out_commit(whContext* ctx, T* user, const T* dev, size_t n, int mem) {
+  if (mem == WH_HOST && n && user) WH_CUDA(cudaMemcpyAsync(user, dev, n * sizeof(T), cudaMemcpyDeviceToHost, ctx->stream));
+  return WH_OK;
+}
+
+// ---- device helpers ---------------------------------------------------------------------
+#ifdef __CUDACC__
+
+// learn/base/localizer.h:16-26 ReverseBytes (nibble reversal)
+__host__ __device__ __forceinline__ uint64_t reverse_nibbles(uint64_t x) {
+  x = x << 32 | x >> 32;
+  x = (x & 0x0000FFFF0000FFFFULL) << 16 | (x & 0xFFFF0000FFFF0000ULL) >> 16;
+  x = (x & 0x00FF00FF00FF00FFULL) << 8 | (x & 0xFF00FF00FF00FF00ULL) >> 8;
+  x = (x & 0x0F0F0F0F0F0F0F0FULL) << 4 | (x & 0xF0F0F0F0F0F0F0F0ULL) >> 4;
+  return x;
+}
+
+// learn/base/localizer.h:106-128: the key transform for I = uint64.
+// mode 0: id % max_key (general), 1: id & (max_key-1) (power of two), 2: nibble reversal.
+struct KeyXform {
+  uint64_t max_key;
+  int mode;
+  __host__ __device__ __forceinline__ uint64_t operator()(uint64_t id) const {
+    if (mode == 1) return id & (max_key - 1);
+    if (mode == 0) return id % max_key;
+    return reverse_nibbles(id);
+  }
+};
+static inline KeyXform make_xform(uint64_t max_key) {
+  KeyXform x;
+  x.max_key = max_key;
+  if (max_key == UINT64_MAX) x.mode = 2;
+  else x.mode = ((max_key & (max_key - 1)) == 0 && max_key != 0) ? 1 : 0;
+  return x;
+}
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ unsigned lane_id() { return threadIdx.x & 31; }
+__device__ __forceinline__ unsigned lanemask_lt() {
+  unsigned m;
+  asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m));
+  return m;
+}
+
+// Streaming loads that do not pollute L1 (inputs read once).
+__device__ __forceinline__ uint64_t ld_stream_u64(const uint64_t* p) {
+  uint64_t v;
+  asm volatile("ld.global.nc.L1::no_allocate.u64 %0, [%1];" : "=l"(v) : "l"(p));
+  return v;
+}
+__device__ __forceinline__ uint32_t ld_stream_u32(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.global.nc.L1::no_allocate.u32 %0, [%1];" : "=r"(v) : "l"(p));
+  return v;
+}
+
+#endif  // __CUDACC__
+}  // namespace wh

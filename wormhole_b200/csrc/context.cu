@@ -1,0 +1,119 @@
+// Context life cycle, error strings, scratch buffers.
+#include <stdarg.h>
+
+#include "common.cuh"
+
+namespace wh {
+
+static thread_local char g_err[1024] = "";
+std::atomic<uint64_t> g_launches{0};
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+int DevBuf::reserve(size_t bytes) {
+  if (bytes <= cap) return WH_OK;
+  if (p) { WH_CUDA(cudaFree(p)); p = nullptr; cap = 0; }
+  size_t want = align_up(bytes + bytes / 8, 256);
+  cudaError_t e = cudaMalloc(&p, want);
+  if (e != cudaSuccess) {
+    p = nullptr;
+    set_error("cudaMalloc(%zu bytes) failed: %s", want, cudaGetErrorString(e));
+    return WH_ERR_NOMEM;
+  }
+  cap = want;
+  return WH_OK;
+}
+void DevBuf::release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+
+int PinnedBuf::reserve(size_t bytes) {
+  if (bytes <= cap) return WH_OK;
+  if (p) { WH_CUDA(cudaFreeHost(p)); p = nullptr; cap = 0; }
+  size_t want = align_up(bytes, 4096);
+  cudaError_t e = cudaMallocHost(&p, want);
+  if (e != cudaSuccess) {
+    p = nullptr;
+    set_error("cudaMallocHost(%zu bytes) failed: %s", want, cudaGetErrorString(e));
+    return WH_ERR_NOMEM;
+  }
+  cap = want;
+  return WH_OK;
+}
+void PinnedBuf::release() { if (p) cudaFreeHost(p); p = nullptr; cap = 0; }
+
+}  // namespace wh
+
+extern "C" {
+
+const char* wh_last_error(void) { return wh::g_err; }
+const char* wh_version(void) { return "wormhole_b200 0.1 (sm_100a)"; }
+uint64_t wh_kernel_launches(void) { return wh::g_launches.load(); }
+
+int wh_create(int device, whContext** out) {
+  WH_REQUIRE(out != nullptr, "wh_create: out is NULL");
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess || n == 0) {
+    wh::set_error("wh_create: no CUDA device (%s); this library has no CPU path",
+                  e == cudaSuccess ? "count is 0" : cudaGetErrorString(e));
+    return WH_ERR_CUDA;
+  }
+  WH_REQUIRE(device >= 0 && device < n, "wh_create: device %d out of range [0,%d)", device, n);
+  WH_CUDA(cudaSetDevice(device));
+  cudaDeviceProp prop;
+  WH_CUDA(cudaGetDeviceProperties(&prop, device));
+  if (prop.major < 10) {
+    wh::set_error("wh_create: device %d is sm_%d%d; the kernels are built for sm_100a only", device,
+                  prop.major, prop.minor);
+    return WH_ERR_UNSUPPORTED;
+  }
+  whContext* c = new whContext();
+  c->device = device;
+  c->num_sms = prop.multiProcessorCount;
+  c->l2_bytes = (size_t)prop.l2CacheSize;
+  WH_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+  c->own_stream = true;
+  int r = c->pinned.reserve(1 << 16);
+  if (r == WH_OK) r = c->small.reserve(1 << 16);
+  if (r != WH_OK) { delete c; return r; }
+  *out = c;
+  return WH_OK;
+}
+
+int wh_destroy(whContext* c) {
+  if (!c) return WH_OK;
+  wh::DeviceGuard g(c->device);
+  cudaStreamSynchronize(c->stream);
+  c->directory.release(); c->scan_tmp.release(); c->acc.release(); c->small.release();
+  for (auto& b : c->sort_tmp) b.release();
+  for (auto& b : c->stage) b.release();
+  c->pinned.release();
+  if (c->own_stream) cudaStreamDestroy(c->stream);
+  delete c;
+  return WH_OK;
+}
+
+int wh_set_stream(whContext* c, void* s) {
+  WH_REQUIRE(c != nullptr, "wh_set_stream: ctx is NULL");
+  wh::DeviceGuard g(c->device);
+  WH_CUDA(cudaStreamSynchronize(c->stream));
+  if (c->own_stream) cudaStreamDestroy(c->stream);
+  c->stream = (cudaStream_t)s;
+  c->own_stream = false;
+  return WH_OK;
+}
+
+int wh_sync(whContext* c) {
+  WH_REQUIRE(c != nullptr, "wh_sync: ctx is NULL");
+  wh::DeviceGuard g(c->device);
+  WH_CUDA(cudaStreamSynchronize(c->stream));
+  return WH_OK;
+}
+
+uint64_t wh_reverse_bytes(uint64_t x) { return wh::reverse_nibbles(x); }
+
+}  // extern "C"

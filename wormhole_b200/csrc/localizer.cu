@@ -1,0 +1,385 @@
+// Piece (1): the feature-id localizer.
+//
+// Replaces Localizer<uint64_t>::{CountUniqIndex, RemapIndex, Localize}
+// (learn/base/localizer.h:42-51,96-221) and the ParallelSort under it
+// (learn/base/parallel_sort.h:15-41). Two device strategies, bit-identical outputs:
+//
+//  direct  For hashed key spaces (ps::FLAGS_max_key <= 2^28). The transformed key indexes a
+//          directory of {presence bits, rank prefix} per 32 keys. One pass marks presence, a
+//          scan over the directory ranks the words and emits the ascending unique list, one
+//          more pass turns every id into its rank. No sort: per minibatch the ids are read
+//          twice and the directory (max_key/4 bytes, L2 resident for 2^24) is touched at random.
+//  sort    For arbitrary 64-bit keys (the reference's default: nibble-reversed ids). Stable LSD
+//          radix sort of (key, position), run-length heads -> ranks, scatter by position.
+#include "batch.cuh"
+#include "scan.cuh"
+
+namespace wh {
+
+constexpr uint64_t kDirectMaxKey = 1ull << 28;
+bool direct_supported(uint64_t max_key) { return max_key != 0 && max_key <= kDirectMaxKey; }
+
+// ------------------------------------------------------------------------------- direct --
+
+// learn/base/localizer.h:107-115 (key transform) fused with "is this key present".
+__global__ void __launch_bounds__(256) loc_mark_kernel(const uint64_t* __restrict__ index, size_t n,
+                                                       KeyXform xf, uint2* dir) {
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    uint64_t k = xf(ld_stream_u64(index + i));
+    unsigned* w = &dir[k >> 5].x;
+    unsigned bit = 1u << (k & 31);
+    // most ids repeat (power-law features): test first, only new keys pay for an atomic
+    if (!(*(volatile unsigned*)w & bit)) atomicOr(w, bit);
+  }
+}
+
+struct DirPopc {
+  const uint2* dir;
+  __device__ unsigned operator()(size_t i) const { return __popc(dir[i].x); }
+};
+// learn/base/localizer.h:139-166: the ascending unique list, here read off the directory.
+struct DirEmit {
+  uint2* dir;
+  uint64_t* uniq;
+  __device__ void operator()(size_t i, unsigned v, unsigned prefix) const {
+    dir[i].y = prefix;
+    if (v) {
+      unsigned bits = dir[i].x;
+      uint64_t base = (uint64_t)i << 5;
+      while (bits) {
+        int b = __ffs(bits) - 1;
+        uniq[prefix++] = base + b;
+        bits &= bits - 1;
+      }
+    }
+  }
+};
+
+// learn/base/localizer.h:179-194,210: local id = rank of the transformed key.
+__global__ void __launch_bounds__(256) loc_rank_kernel(const uint64_t* __restrict__ index, size_t n,
+                                                       KeyXform xf, const uint2* __restrict__ dir,
+                                                       uint32_t* __restrict__ out, uint32_t* cnt) {
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    uint64_t k = xf(ld_stream_u64(index + i));
+    uint2 e = __ldg(dir + (k >> 5));
+    unsigned r = e.y + __popc(e.x & ((1u << (k & 31)) - 1u));
+    out[i] = r;
+    if (cnt) atomicAdd(cnt + r, 1u);
+  }
+}
+
+int localize_direct(whContext* ctx, const LocInput& in, uint64_t* d_uniq, uint32_t* d_cnt,
+                    uint32_t* d_index, unsigned* d_nuniq) {
+  const size_t words = div_up(in.xf.max_key, 32);
+  // the directory is kept all-zero between calls; (re)allocation zeroes it once
+  if (ctx->directory.cap < words * sizeof(uint2) || ctx->directory_words < words) {
+    WH_TRY(ctx->directory.reserve(words * sizeof(uint2)));
+    WH_CUDA(cudaMemsetAsync(ctx->directory.p, 0, ctx->directory.cap, ctx->stream));
+    ctx->directory_words = ctx->directory.cap / sizeof(uint2);
+  }
+  uint2* dir = ctx->directory.as<uint2>();
+  WH_TRY(ctx->scan_tmp.reserve(div_up(words, kScanTile) * sizeof(unsigned) + 256));
+  const size_t n = in.nnz;
+  const unsigned grid = (unsigned)std::min<size_t>(div_up(n ? n : 1, 256), (size_t)ctx->num_sms * 16);
+  if (n) WH_LAUNCH(loc_mark_kernel, grid, 256, 0, ctx->stream, in.index, n, in.xf, dir);
+  WH_TRY(scan_and_apply<unsigned>(ctx, DirPopc{dir}, DirEmit{dir, d_uniq}, words, ctx->scan_tmp.as<unsigned>(),
+                        d_nuniq));
+  if (d_cnt && n) WH_CUDA(cudaMemsetAsync(d_cnt, 0, std::min<uint64_t>(n, in.xf.max_key) * 4, ctx->stream));
+  if (n) WH_LAUNCH(loc_rank_kernel, grid, 256, 0, ctx->stream, in.index, n, in.xf, dir, d_index, d_cnt);
+  WH_CUDA(cudaMemsetAsync(dir, 0, words * sizeof(uint2), ctx->stream));
+  return WH_OK;
+}
+
+// --------------------------------------------------------------------------------- sort --
+
+// learn/base/localizer.h:107-128: pair[i] = {T(index[i]), i}; also folds the OR / AND of all
+// keys so that the sort can skip constant digits.
+__global__ void __launch_bounds__(256) loc_xform_kernel(const uint64_t* __restrict__ index, size_t n,
+                                                        KeyXform xf, uint64_t* keys, uint32_t* vals,
+                                                        SortPlan* plan) {
+  unsigned long long o = 0ull, a = ~0ull;
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    uint64_t k = xf(ld_stream_u64(index + i));
+    keys[i] = k;
+    vals[i] = (uint32_t)i;
+    o |= k;
+    a &= k;
+  }
+#pragma unroll
+  for (int s = 16; s > 0; s >>= 1) {
+    o |= __shfl_xor_sync(0xffffffffu, o, s);
+    a &= __shfl_xor_sync(0xffffffffu, a, s);
+  }
+  if ((threadIdx.x & 31) == 0) {
+    atomicOr(&plan->bits_or, o);
+    atomicAnd(&plan->bits_and, a);
+  }
+}
+
+// learn/base/localizer.h:139-166 (run-length encode the sorted pairs) and :179-194 (rank -> position)
+struct HeadFlag {
+  SortBufs b;
+  __device__ unsigned operator()(size_t i) const {
+    const uint64_t* k = sorted_keys(b);
+    return (i == 0 || k[i] != k[i - 1]) ? 1u : 0u;
+  }
+};
+struct HeadApply {
+  SortBufs b;
+  uint64_t* uniq;
+  uint32_t* headpos;
+  uint32_t* index;
+  __device__ void operator()(size_t i, unsigned v, unsigned prefix) const {
+    unsigned rank = prefix + v - 1;
+    index[sorted_vals(b)[i]] = rank;
+    if (v) { uniq[rank] = sorted_keys(b)[i]; headpos[rank] = (uint32_t)i; }
+  }
+};
+__global__ void loc_count_kernel(const uint32_t* __restrict__ headpos, const unsigned* nuniq, size_t n,
+                                 uint32_t* cnt) {
+  const unsigned U = *nuniq;
+  for (size_t r = (size_t)blockIdx.x * blockDim.x + threadIdx.x; r < U; r += (size_t)gridDim.x * blockDim.x)
+    cnt[r] = (r + 1 < U ? headpos[r + 1] : (uint32_t)n) - headpos[r];
+}
+
+int localize_sort(whContext* ctx, const LocInput& in, uint64_t* d_uniq, uint32_t* d_cnt,
+                  uint32_t* d_index, unsigned* d_nuniq) {
+  const size_t n = in.nnz;
+  if (n == 0) { WH_CUDA(cudaMemsetAsync(d_nuniq, 0, sizeof(unsigned), ctx->stream)); return WH_OK; }
+  SortBufs b;
+  WH_TRY(ctx->sort_tmp[0].reserve(n * 8)); WH_TRY(ctx->sort_tmp[1].reserve(n * 8));
+  WH_TRY(ctx->sort_tmp[2].reserve(n * 4)); WH_TRY(ctx->sort_tmp[3].reserve(n * 4));
+  WH_TRY(ctx->sort_tmp[4].reserve(sort_counts_bytes(n) + sizeof(SortPlan) + 256));
+  WH_TRY(ctx->sort_tmp[5].reserve(n * 4));
+  WH_TRY(ctx->scan_tmp.reserve(div_up(n, kScanTile) * sizeof(unsigned) + 256));
+  b.keys[0] = ctx->sort_tmp[0].as<uint64_t>(); b.keys[1] = ctx->sort_tmp[1].as<uint64_t>();
+  b.vals[0] = ctx->sort_tmp[2].as<uint32_t>(); b.vals[1] = ctx->sort_tmp[3].as<uint32_t>();
+  b.plan = ctx->sort_tmp[4].as<SortPlan>();
+  b.counts = reinterpret_cast<uint32_t*>(ctx->sort_tmp[4].as<char>() + 256);
+  uint32_t* headpos = ctx->sort_tmp[5].as<uint32_t>();
+  WH_TRY(sort_plan_reset(ctx, b.plan));
+  const unsigned grid = (unsigned)std::min<size_t>(div_up(n, 256), (size_t)ctx->num_sms * 16);
+  WH_LAUNCH(loc_xform_kernel, grid, 256, 0, ctx->stream, in.index, n, in.xf, b.keys[0], b.vals[0], b.plan);
+  WH_TRY(radix_sort_pairs(ctx, b, n));
+  WH_TRY(scan_and_apply<unsigned>(ctx, HeadFlag{b}, HeadApply{b, d_uniq, headpos, d_index}, n,
+                        ctx->scan_tmp.as<unsigned>(), d_nuniq));
+  if (d_cnt) WH_LAUNCH(loc_count_kernel, grid, 256, 0, ctx->stream, headpos, d_nuniq, n, d_cnt);
+  return WH_OK;
+}
+
+// --------------------------------------------------------- RemapIndex with a foreign dict --
+
+// dictpos[u] = 1 + position of uniq[u] in the ascending dictionary, 0 if absent
+// (the two-pointer merge of learn/base/localizer.h:179-194, as a search per unique key).
+__global__ void loc_dictpos_kernel(const uint64_t* __restrict__ uniq, const unsigned* nuniq,
+                                   const uint64_t* __restrict__ dict, size_t ndict, uint32_t* dictpos) {
+  const unsigned U = *nuniq;
+  for (size_t u = (size_t)blockIdx.x * blockDim.x + threadIdx.x; u < U; u += (size_t)gridDim.x * blockDim.x) {
+    uint64_t k = uniq[u];
+    size_t lo = 0, hi = ndict;
+    while (lo < hi) { size_t mid = (lo + hi) >> 1; if (dict[mid] < k) lo = mid + 1; else hi = mid; }
+    dictpos[u] = (lo < ndict && dict[lo] == k) ? (uint32_t)(lo + 1) : 0u;
+  }
+}
+struct KeepFlag {
+  const uint32_t* index; const uint32_t* dictpos;
+  __device__ unsigned operator()(size_t i) const { return dictpos[index[i]] != 0 ? 1u : 0u; }
+};
+// learn/base/localizer.h:203-213: drop unmatched entries, keep order.
+struct KeepApply {
+  const uint32_t* index; const uint32_t* dictpos; const float* value;
+  uint32_t* scanpos; uint32_t* out_index; float* out_value;
+  __device__ void operator()(size_t i, unsigned v, unsigned prefix) const {
+    scanpos[i] = prefix;
+    if (v) { out_index[prefix] = dictpos[index[i]] - 1; if (value) out_value[prefix] = value[i]; }
+  }
+};
+__global__ void loc_reoffset_kernel(const size_t* __restrict__ offset, size_t rows, size_t n,
+                                    const uint32_t* __restrict__ scanpos, const unsigned* total,
+                                    size_t* out) {
+  for (size_t r = (size_t)blockIdx.x * blockDim.x + threadIdx.x; r <= rows; r += (size_t)gridDim.x * blockDim.x) {
+    size_t o = offset[r];
+    out[r] = o < n ? scanpos[o] : *total;
+  }
+}
+
+}  // namespace wh
+
+using namespace wh;
+
+static int localize_common(whContext* ctx, const whRowBlock* blk, int mem, uint64_t max_key, int method,
+                           const uint64_t* dict, size_t ndict, bool with_dict, whBatch** out) {
+  WH_REQUIRE(ctx && blk && out, "wh_localize: NULL argument");
+  WH_REQUIRE(mem == WH_HOST || mem == WH_DEVICE, "wh_localize: bad mem %d", mem);
+  WH_REQUIRE(max_key != 0, "wh_localize: max_key must be positive");
+  DeviceGuard g(ctx->device);
+  const bool want_cnt = (method & 16) != 0;
+  method &= 15;
+  whBatch* b = new whBatch();
+  b->ctx = ctx;
+  *out = b;
+  if (blk->size == 0) return WH_OK;  // learn/base/localizer.h:101,173: nothing is written
+  WH_REQUIRE(blk->offset != nullptr && (blk->index != nullptr), "wh_localize: offset/index is NULL");
+  const size_t rows = blk->size;
+  // the entry count lives in offset[rows]
+  size_t n = 0, first = 0;
+  if (mem == WH_HOST) { n = blk->offset[rows]; first = blk->offset[0]; }
+  else {
+    WH_CUDA(cudaMemcpyAsync(ctx->pinned.p, blk->offset + rows, sizeof(size_t), cudaMemcpyDeviceToHost, ctx->stream));
+    WH_CUDA(cudaMemcpyAsync(ctx->pinned.as<size_t>() + 1, blk->offset, sizeof(size_t), cudaMemcpyDeviceToHost, ctx->stream));
+    WH_CUDA(cudaStreamSynchronize(ctx->stream));
+    n = ctx->pinned.as<size_t>()[0]; first = ctx->pinned.as<size_t>()[1];
+  }
+  WH_REQUIRE(first == 0, "wh_localize: offset[0] must be 0 (learn/base/localizer.h:102)");
+  WH_REQUIRE(n < (size_t)UINT32_MAX, "wh_localize: %zu entries; positions are 32-bit (learn/base/localizer.h:103)", n);
+  if (method == WH_LOC_AUTO) method = direct_supported(max_key) ? WH_LOC_DIRECT : WH_LOC_SORT;
+  WH_REQUIRE(method == WH_LOC_SORT || direct_supported(max_key),
+             "wh_localize: direct addressing needs max_key <= 2^28");
+
+  const uint64_t* d_index; const size_t* d_offset; const float* d_value; const float* d_label;
+  WH_TRY(to_device(ctx, ctx->stage[0], blk->index, n, mem, &d_index));
+  // offset / value / label are copied into the batch (Localize hands back its own container)
+  b->rows = rows;
+  WH_TRY(b->offset.reserve((rows + 1) * sizeof(size_t)));
+  cudaMemcpyKind kind = mem == WH_HOST ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToDevice;
+  WH_CUDA(cudaMemcpyAsync(b->offset.p, blk->offset, (rows + 1) * sizeof(size_t), kind, ctx->stream));
+  d_offset = b->offset.as<size_t>();
+  if (blk->label) {
+    WH_TRY(b->label.reserve(rows * 4));
+    WH_CUDA(cudaMemcpyAsync(b->label.p, blk->label, rows * 4, kind, ctx->stream));
+    b->has_label = true;
+  }
+  d_label = b->label.as<float>(); (void)d_label;
+  d_value = nullptr;
+  if (blk->value && n) {
+    WH_TRY(b->value.reserve(n * 4));
+    WH_CUDA(cudaMemcpyAsync(b->value.p, blk->value, n * 4, kind, ctx->stream));
+    b->has_value = true;
+    d_value = b->value.as<float>();
+  }
+  const size_t ucap = (size_t)std::min<uint64_t>(n ? n : 1, max_key);
+  WH_TRY(b->uniq.reserve(ucap * 8));
+  WH_TRY(b->index.reserve((n ? n : 1) * 4));
+  if (want_cnt) { WH_TRY(b->cnt.reserve(ucap * 4)); b->has_cnt = true; }
+  unsigned* d_nuniq = ctx->small.as<unsigned>();
+  LocInput in{d_index, n, make_xform(max_key)};
+  if (method == WH_LOC_DIRECT)
+    WH_TRY(localize_direct(ctx, in, b->uniq.as<uint64_t>(), want_cnt ? b->cnt.as<uint32_t>() : nullptr,
+                           b->index.as<uint32_t>(), d_nuniq));
+  else
+    WH_TRY(localize_sort(ctx, in, b->uniq.as<uint64_t>(), want_cnt ? b->cnt.as<uint32_t>() : nullptr,
+                         b->index.as<uint32_t>(), d_nuniq));
+  b->nnz = n;
+
+  unsigned* d_total = d_nuniq + 1;
+  if (with_dict) {
+    if (ndict == 0 || n == 0) {
+      // RemapIndex returns before touching `localized` (learn/base/localizer.h:173)
+      b->rows = 0; b->nnz = 0; b->has_value = b->has_label = false;
+    } else {
+      const uint64_t* d_dict;
+      WH_TRY(to_device(ctx, ctx->stage[1], dict, ndict, mem, &d_dict));
+      WH_TRY(ctx->stage[2].reserve(ucap * 4));           // dictpos
+      WH_TRY(ctx->stage[3].reserve(n * 4));              // scanpos
+      WH_TRY(ctx->stage[4].reserve(n * 4));              // compacted index
+      WH_TRY(ctx->stage[5].reserve(n * 4));              // compacted value
+      WH_TRY(ctx->stage[6].reserve((rows + 1) * sizeof(size_t)));
+      WH_TRY(ctx->scan_tmp.reserve(div_up(n, kScanTile) * sizeof(unsigned) + 256));
+      uint32_t* dictpos = ctx->stage[2].as<uint32_t>();
+      const unsigned grid = (unsigned)std::min<size_t>(div_up(ucap, 256), (size_t)ctx->num_sms * 8);
+      WH_LAUNCH(loc_dictpos_kernel, grid, 256, 0, ctx->stream, b->uniq.as<uint64_t>(), d_nuniq, d_dict, ndict, dictpos);
+      KeepFlag kf{b->index.as<uint32_t>(), dictpos};
+      KeepApply ka{b->index.as<uint32_t>(), dictpos, d_value, ctx->stage[3].as<uint32_t>(),
+                   ctx->stage[4].as<uint32_t>(), ctx->stage[5].as<float>()};
+      WH_TRY(scan_and_apply<unsigned>(ctx, kf, ka, n, ctx->scan_tmp.as<unsigned>(), d_total));
+      const unsigned g2 = (unsigned)std::min<size_t>(div_up(rows + 1, 256), (size_t)ctx->num_sms * 8);
+      WH_LAUNCH(loc_reoffset_kernel, g2, 256, 0, ctx->stream, d_offset, rows, n, ctx->stage[3].as<uint32_t>(),
+                d_total, ctx->stage[6].as<size_t>());
+      WH_CUDA(cudaMemcpyAsync(b->offset.p, ctx->stage[6].p, (rows + 1) * sizeof(size_t), cudaMemcpyDeviceToDevice, ctx->stream));
+      WH_CUDA(cudaMemcpyAsync(b->index.p, ctx->stage[4].p, n * 4, cudaMemcpyDeviceToDevice, ctx->stream));
+      if (d_value) WH_CUDA(cudaMemcpyAsync(b->value.p, ctx->stage[5].p, n * 4, cudaMemcpyDeviceToDevice, ctx->stream));
+    }
+  }
+  WH_CUDA(cudaMemcpyAsync(ctx->pinned.p, d_nuniq, 2 * sizeof(unsigned), cudaMemcpyDeviceToHost, ctx->stream));
+  WH_CUDA(cudaStreamSynchronize(ctx->stream));
+  b->nuniq = ctx->pinned.as<unsigned>()[0];
+  if (with_dict && b->rows) {
+    b->nnz = ctx->pinned.as<unsigned>()[1];
+    if (b->nnz == 0) b->has_value = false;
+  }
+  return WH_OK;
+}
+
+extern "C" {
+
+int wh_localize(whContext* ctx, const whRowBlock* blk, int mem, uint64_t max_key, int method, whBatch** out) {
+  int r = localize_common(ctx, blk, mem, max_key, method, nullptr, 0, false, out);
+  if (r != WH_OK && out && *out) { delete *out; *out = nullptr; }
+  return r;
+}
+int wh_localize_with_dict(whContext* ctx, const whRowBlock* blk, int mem, uint64_t max_key,
+                          const uint64_t* dict, size_t ndict, whBatch** out) {
+  int r = localize_common(ctx, blk, mem, max_key, WH_LOC_AUTO | 16, dict, ndict, true, out);
+  if (r != WH_OK && out && *out) { delete *out; *out = nullptr; }
+  return r;
+}
+size_t wh_batch_rows(const whBatch* b) { return b ? b->rows : 0; }
+size_t wh_batch_nnz(const whBatch* b) { return b ? b->nnz : 0; }
+size_t wh_batch_num_uniq(const whBatch* b) { return b ? b->nuniq : 0; }
+int wh_batch_has_value(const whBatch* b) { return b && b->has_value; }
+int wh_batch_has_label(const whBatch* b) { return b && b->has_label; }
+
+__global__ void cnt_to_float_kernel(const uint32_t* c, size_t n, float* out) {
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = (float)c[i];  // learn/base/localizer.h:151,163: static_cast<C>(cnt), C = float
+}
+
+int wh_batch_copy(whContext* ctx, const whBatch* b, uint64_t* uniq, uint32_t* cnt_u32, float* cnt_f32,
+                  size_t* offset, uint32_t* index, float* value, float* label) {
+  WH_REQUIRE(ctx && b, "wh_batch_copy: NULL argument");
+  DeviceGuard g(ctx->device);
+  cudaStream_t s = ctx->stream;
+  if (uniq && b->nuniq) WH_CUDA(cudaMemcpyAsync(uniq, b->uniq.p, b->nuniq * 8, cudaMemcpyDeviceToHost, s));
+  if ((cnt_u32 || cnt_f32) && b->nuniq) {
+    WH_REQUIRE(b->has_cnt, "wh_batch_copy: counts were not requested (method | 16)");
+    if (cnt_u32) WH_CUDA(cudaMemcpyAsync(cnt_u32, b->cnt.p, b->nuniq * 4, cudaMemcpyDeviceToHost, s));
+    if (cnt_f32) {
+      WH_TRY(ctx->stage[7].reserve(b->nuniq * 4));
+      WH_LAUNCH(cnt_to_float_kernel, (unsigned)div_up(b->nuniq, 256), 256, 0, s, b->cnt.as<uint32_t>(), b->nuniq, ctx->stage[7].as<float>());
+      WH_CUDA(cudaMemcpyAsync(cnt_f32, ctx->stage[7].p, b->nuniq * 4, cudaMemcpyDeviceToHost, s));
+    }
+  }
+  if (offset && b->rows) WH_CUDA(cudaMemcpyAsync(offset, b->offset.p, (b->rows + 1) * sizeof(size_t), cudaMemcpyDeviceToHost, s));
+  if (index && b->nnz) WH_CUDA(cudaMemcpyAsync(index, b->index.p, b->nnz * 4, cudaMemcpyDeviceToHost, s));
+  if (value && b->nnz && b->has_value) WH_CUDA(cudaMemcpyAsync(value, b->value.p, b->nnz * 4, cudaMemcpyDeviceToHost, s));
+  if (label && b->rows && b->has_label) WH_CUDA(cudaMemcpyAsync(label, b->label.p, b->rows * 4, cudaMemcpyDeviceToHost, s));
+  WH_CUDA(cudaStreamSynchronize(s));
+  return WH_OK;
+}
+
+int wh_batch_device_view(const whBatch* b, const uint64_t** uniq, const uint32_t** cnt, whLocalBlock* local) {
+  WH_REQUIRE(b, "wh_batch_device_view: NULL batch");
+  if (uniq) *uniq = b->uniq.as<uint64_t>();
+  if (cnt) *cnt = b->has_cnt ? b->cnt.as<uint32_t>() : nullptr;
+  if (local) {
+    local->size = b->rows;
+    local->offset = b->offset.as<size_t>();
+    local->label = b->has_label ? b->label.as<float>() : nullptr;
+    local->index = b->index.as<uint32_t>();
+    local->value = b->has_value ? b->value.as<float>() : nullptr;
+  }
+  return WH_OK;
+}
+
+int wh_batch_destroy(whBatch* b) {
+  if (!b) return WH_OK;
+  DeviceGuard g(b->ctx ? b->ctx->device : 0);
+  if (b->ctx) cudaStreamSynchronize(b->ctx->stream);
+  delete b;
+  return WH_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,278 @@
+// Piece (3): ScalarLoss / LogitLoss / SquareHingeLoss (learn/linear/loss.h) and BinClassEval
+// (learn/base/binary_class_evaluation.h) on the device.
+//
+// Arithmetic notes (fp32 parity with the reference's glibc build):
+//  * exp/log are evaluated in fp64 and rounded to fp32: that is the correctly rounded fp32
+//    result in all but ~1e-9 of cases, which is also what glibc's expf/logf deliver; every other
+//    step (the +1, the division, the products) is a single IEEE fp32 operation, compiled with
+//    -fmad=false so that nothing is contracted.
+//  * sums over examples (objective) are taken in fp64 in a fixed order; the reference sums in
+//    fp32 under an OpenMP reduction whose order depends on the thread count.
+//  * AUC is exact integer pair counting. Equal scores: the reference's std::sort leaves their
+//    order unspecified (binary_class_evaluation.h:25-26); here tied (pos,neg) pairs count 1/2,
+//    and the two extremes are reported as auc_lo / auc_hi.
+#include "loss.cuh"
+#include "scan.cuh"
+#include "spmv.cuh"
+
+namespace wh {
+
+__device__ __forceinline__ float exp_rn(float a) { return (float)exp((double)a); }
+__device__ __forceinline__ float log_rn(float a) { return (float)log((double)a); }
+
+__global__ void eval_reset_kernel(EvalOut* out) {
+  out->objv = 0; out->logloss = 0; out->correct = 0; out->npos = 0; out->ngroups = 0;
+  out->area_lo = 0; out->ties = 0;
+}
+
+// learn/linear/loss.h:109-113 (logit dual), :145-149 (squared hinge dual), :131-138 and
+// binary_class_evaluation.h:66-74 (objectives), :40-51 (accuracy), :53-64 (logloss).
+__global__ void __launch_bounds__(256)
+loss_forward_kernel(int loss, size_t rows, const float* __restrict__ label, const float* __restrict__ xw,
+                    float* __restrict__ dual, double* part_objv, double* part_ll, unsigned* part_correct,
+                    int want_logloss) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  double objv = 0, ll = 0;
+  unsigned correct = 0;
+  if (i < rows) {
+    const float lab = label[i], p = xw[i];
+    const float y = lab > 0 ? 1.f : -1.f;
+    if (loss == WH_LOSS_LOGIT) {
+      if (dual) dual[i] = -y / (1.f + exp_rn(y * p));
+      objv = (double)log_rn(1.f + exp_rn(-y * p));
+    } else {  // WH_LOSS_SQUARE_HINGE, as written in the reference (active when the margin is > 1)
+      if (dual) dual[i] = y * ((y * p > 1.0f) ? 1.f : 0.f);
+      float t = fmaxf(1.f - y * p, 0.f);
+      objv = (double)(t * t);
+    }
+    correct = ((lab > 0 && p > 0.f) || (lab <= 0 && p <= 0.f)) ? 1u : 0u;
+    if (want_logloss) {
+      float yy = lab > 0 ? 1.f : 0.f;
+      float q = 1.f / (1.f + exp_rn(-p));
+      q = q < 1e-10f ? 1e-10f : q;
+      ll = (double)(yy * log_rn(q) + (1.f - yy) * log_rn(1.f - q));
+    }
+  }
+  // fixed-order block reduction
+  __shared__ double s_o[8], s_l[8];
+  __shared__ unsigned s_c[8];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    objv += __shfl_down_sync(0xffffffffu, objv, o);
+    ll += __shfl_down_sync(0xffffffffu, ll, o);
+    correct += __shfl_down_sync(0xffffffffu, correct, o);
+  }
+  const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (lane == 0) { s_o[warp] = objv; s_l[warp] = ll; s_c[warp] = correct; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double o = 0, l = 0; unsigned c = 0;
+    for (int w = 0; w < 8; ++w) { o += s_o[w]; l += s_l[w]; c += s_c[w]; }
+    part_objv[blockIdx.x] = o; part_ll[blockIdx.x] = l; part_correct[blockIdx.x] = c;
+  }
+}
+
+__global__ void __launch_bounds__(256)
+loss_reduce_kernel(unsigned nparts, const double* part_objv, const double* part_ll,
+                   const unsigned* part_correct, EvalOut* out) {
+  __shared__ double s_o[256], s_l[256];
+  __shared__ unsigned long long s_c[256];
+  double o = 0, l = 0; unsigned long long c = 0;
+  for (unsigned i = threadIdx.x; i < nparts; i += 256) { o += part_objv[i]; l += part_ll[i]; c += part_correct[i]; }
+  s_o[threadIdx.x] = o; s_l[threadIdx.x] = l; s_c[threadIdx.x] = c;
+  __syncthreads();
+  for (int s = 128; s > 0; s >>= 1) {
+    if (threadIdx.x < s) { s_o[threadIdx.x] += s_o[threadIdx.x + s]; s_l[threadIdx.x] += s_l[threadIdx.x + s]; s_c[threadIdx.x] += s_c[threadIdx.x + s]; }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) { out->objv = s_o[0]; out->logloss = s_l[0]; out->correct = s_c[0]; }
+}
+
+int loss_forward_launch(whContext* ctx, int loss, size_t rows, const float* label, const float* xw,
+                        float* dual, EvalOut* out, int want_logloss) {
+  WH_LAUNCH(eval_reset_kernel, 1, 1, 0, ctx->stream, out);
+  if (rows == 0) return WH_OK;
+  const unsigned nb = (unsigned)div_up(rows, 256);
+  WH_TRY(ctx->stage[7].reserve((size_t)nb * 24 + 64));
+  double* po = ctx->stage[7].as<double>();
+  double* pl = po + nb;
+  unsigned* pc = reinterpret_cast<unsigned*>(pl + nb);
+  WH_LAUNCH(loss_forward_kernel, nb, 256, 0, ctx->stream, loss, rows, label, xw, dual, po, pl, pc, want_logloss);
+  WH_LAUNCH(loss_reduce_kernel, 1, 256, 0, ctx->stream, nb, po, pl, pc, out);
+  return WH_OK;
+}
+
+// ---------------------------------------------------------------------------------- AUC --
+
+// Order-preserving map float -> uint32 (-0 and +0 compare equal, as in the reference's "<").
+__device__ __forceinline__ unsigned ordered_bits(float f) {
+  if (f == 0.f) f = 0.f;
+  unsigned b = __float_as_uint(f);
+  return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+
+// key = ordered(score) << 1 | (label > 0): ascending by score, negatives first among equals.
+__global__ void __launch_bounds__(256)
+auc_keys_kernel(size_t n, const float* __restrict__ label, const float* __restrict__ xw, uint64_t* keys,
+                uint32_t* vals, SortPlan* plan) {
+  unsigned long long o = 0ull, a = ~0ull;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    uint64_t k = ((uint64_t)ordered_bits(xw[i]) << 1) | (label[i] > 0 ? 1u : 0u);
+    keys[i] = k; vals[i] = 0;
+    o |= k; a &= k;
+  }
+#pragma unroll
+  for (int s = 16; s > 0; s >>= 1) { o |= __shfl_xor_sync(0xffffffffu, o, s); a &= __shfl_xor_sync(0xffffffffu, a, s); }
+  if ((threadIdx.x & 31) == 0) { atomicOr(&plan->bits_or, o); atomicAnd(&plan->bits_and, a); }
+}
+
+// scanned value: (is positive) << 32 | (starts a new score group)
+struct AucFlag {
+  SortBufs b;
+  __device__ unsigned long long operator()(size_t i) const {
+    const uint64_t* k = sorted_keys(b);
+    unsigned long long head = (i == 0 || (k[i] >> 1) != (k[i - 1] >> 1)) ? 1ull : 0ull;
+    return ((k[i] & 1ull) << 32) | head;
+  }
+};
+// at each group start remember how many positives / negatives precede it
+struct AucApply {
+  uint32_t* gpos; uint32_t* gneg;
+  __device__ void operator()(size_t i, unsigned long long v, unsigned long long prefix) const {
+    if (v & 1ull) {
+      unsigned g = (unsigned)(prefix & 0xffffffffull);
+      unsigned pos_before = (unsigned)(prefix >> 32);
+      gpos[g] = pos_before;
+      gneg[g] = (unsigned)i - pos_before;
+    }
+  }
+};
+// per score group g: negatives in g each see gpos[g] positives strictly below; ties = P_g * N_g
+__global__ void __launch_bounds__(256)
+auc_groups_kernel(size_t n, const uint32_t* __restrict__ gpos, const uint32_t* __restrict__ gneg,
+                  const unsigned long long* total, EvalOut* out) {
+  const unsigned long long tot = *total;
+  const unsigned ngroups = (unsigned)(tot & 0xffffffffull), P = (unsigned)(tot >> 32);
+  const unsigned N = (unsigned)n - P;
+  unsigned long long area = 0, ties = 0;
+  for (size_t g = (size_t)blockIdx.x * blockDim.x + threadIdx.x; g < ngroups; g += (size_t)gridDim.x * blockDim.x) {
+    unsigned p0 = gpos[g], n0 = gneg[g];
+    unsigned p1 = (g + 1 < ngroups) ? gpos[g + 1] : P, n1 = (g + 1 < ngroups) ? gneg[g + 1] : N;
+    area += (unsigned long long)(n1 - n0) * p0;
+    ties += (unsigned long long)(n1 - n0) * (p1 - p0);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) { area += __shfl_xor_sync(0xffffffffu, area, o); ties += __shfl_xor_sync(0xffffffffu, ties, o); }
+  if ((threadIdx.x & 31) == 0) { atomicAdd(&out->area_lo, area); atomicAdd(&out->ties, ties); }
+  if (blockIdx.x == 0 && threadIdx.x == 0) { out->npos = P; out->ngroups = ngroups; }
+}
+
+int auc_launch(whContext* ctx, size_t n, const float* label, const float* xw, EvalOut* out) {
+  if (n == 0) return WH_OK;
+  WH_REQUIRE(n < (size_t)INT32_MAX, "AUC: %zu examples exceed 32-bit counters", n);
+  SortBufs b;
+  WH_TRY(ctx->sort_tmp[0].reserve(n * 8)); WH_TRY(ctx->sort_tmp[1].reserve(n * 8));
+  WH_TRY(ctx->sort_tmp[2].reserve(n * 4)); WH_TRY(ctx->sort_tmp[3].reserve(n * 4));
+  WH_TRY(ctx->sort_tmp[4].reserve(sort_counts_bytes(n) + sizeof(SortPlan) + 256));
+  WH_TRY(ctx->sort_tmp[5].reserve((n + 1) * 8));
+  WH_TRY(ctx->scan_tmp.reserve(div_up(n, kScanTile) * sizeof(unsigned long long) + 256));
+  b.keys[0] = ctx->sort_tmp[0].as<uint64_t>(); b.keys[1] = ctx->sort_tmp[1].as<uint64_t>();
+  b.vals[0] = ctx->sort_tmp[2].as<uint32_t>(); b.vals[1] = ctx->sort_tmp[3].as<uint32_t>();
+  b.plan = ctx->sort_tmp[4].as<SortPlan>();
+  b.counts = reinterpret_cast<uint32_t*>(ctx->sort_tmp[4].as<char>() + 256);
+  uint32_t* gpos = ctx->sort_tmp[5].as<uint32_t>();
+  uint32_t* gneg = gpos + n + 1;
+  unsigned long long* sums = ctx->scan_tmp.as<unsigned long long>();
+  unsigned long long* total = reinterpret_cast<unsigned long long*>(ctx->small.as<char>() + 2048);
+  WH_TRY(sort_plan_reset(ctx, b.plan));
+  const unsigned grid = (unsigned)std::min<size_t>(div_up(n, 256), (size_t)ctx->num_sms * 8);
+  WH_LAUNCH(auc_keys_kernel, grid, 256, 0, ctx->stream, n, label, xw, b.keys[0], b.vals[0], b.plan);
+  WH_TRY(radix_sort_pairs(ctx, b, n));
+  WH_TRY(scan_and_apply<unsigned long long>(ctx, AucFlag{b}, AucApply{gpos, gneg}, n, sums, total));
+  WH_LAUNCH(auc_groups_kernel, grid, 256, 0, ctx->stream, n, gpos, gneg, total, out);
+  return WH_OK;
+}
+
+EvalHost eval_finish(const EvalOut& e, size_t rows) {
+  EvalHost h;
+  h.objv = e.objv;
+  h.logloss = -e.logloss;
+  // binary_class_evaluation.h:49-50
+  float acc = rows ? (float)e.correct / (float)rows : 0.f;
+  h.acc = acc > 0.5f ? acc : 1.f - acc;
+  // binary_class_evaluation.h:36-38
+  const double P = (double)e.npos, N = (double)rows - P;
+  if (e.npos == 0 || e.npos == rows) { h.auc = h.auc_lo = h.auc_hi = 1.0; return h; }
+  const double lo = (double)e.area_lo / (P * N), hi = (double)(e.area_lo + e.ties) / (P * N);
+  auto fold = [](double a) { return a < 0.5 ? 1.0 - a : a; };
+  h.auc = fold(0.5 * (lo + hi));
+  const double flo = fold(lo), fhi = fold(hi);
+  h.auc_hi = flo > fhi ? flo : fhi;
+  h.auc_lo = (lo <= 0.5 && hi >= 0.5) ? 0.5 : (flo < fhi ? flo : fhi);
+  return h;
+}
+
+}  // namespace wh
+
+using namespace wh;
+
+extern "C" {
+
+int wh_bin_eval(whContext* ctx, const float* label, const float* predict, size_t n, int mem, float* out6) {
+  WH_REQUIRE(ctx && out6 && (n == 0 || (label && predict)), "wh_bin_eval: NULL argument");
+  DeviceGuard g(ctx->device);
+  const float *dl, *dp;
+  WH_TRY(to_device(ctx, ctx->stage[0], label, n, mem, &dl));
+  WH_TRY(to_device(ctx, ctx->stage[1], predict, n, mem, &dp));
+  EvalOut* dev = reinterpret_cast<EvalOut*>(ctx->small.as<char>() + 4096);
+  WH_TRY(loss_forward_launch(ctx, WH_LOSS_LOGIT, n, dl, dp, nullptr, dev, 1));
+  WH_TRY(auc_launch(ctx, n, dl, dp, dev));
+  WH_CUDA(cudaMemcpyAsync(ctx->pinned.p, dev, sizeof(EvalOut), cudaMemcpyDeviceToHost, ctx->stream));
+  WH_CUDA(cudaStreamSynchronize(ctx->stream));
+  EvalHost h = eval_finish(*ctx->pinned.as<EvalOut>(), n);
+  out6[0] = (float)h.auc; out6[1] = (float)h.acc; out6[2] = (float)h.logloss; out6[3] = (float)h.objv;
+  out6[4] = (float)h.auc_lo; out6[5] = (float)h.auc_hi;
+  return WH_OK;
+}
+
+int wh_linear_loss(whContext* ctx, int loss, const whLocalBlock* D, int mem, const float* w, size_t U,
+                   double* prog, float* grad, float* xw, float* dual) {
+  WH_REQUIRE(ctx && D && prog, "wh_linear_loss: NULL argument");
+  WH_REQUIRE(loss == WH_LOSS_LOGIT || loss == WH_LOSS_SQUARE_HINGE,
+             "wh_linear_loss: unknown loss type %d (SQUARE is unimplemented in the reference, learn/linear/loss.h:163-180)", loss);
+  DeviceGuard g(ctx->device);
+  DevLocal d;
+  WH_TRY(stage_local(ctx, D, mem, &d));
+  WH_REQUIRE(d.rows == 0 || d.label != nullptr, "wh_linear_loss: label is NULL");
+  const float* dw; float *dxw, *ddual, *dgrad = nullptr;
+  WH_TRY(to_device(ctx, ctx->stage[4], w, U, mem, &dw));
+  // Init: Xw = X w (loss.h:32-39); Xw_ starts zeroed (vector::resize), rows without entries stay 0
+  WH_TRY(out_buffer(ctx, ctx->stage[5], xw, d.rows, xw ? mem : WH_HOST, &dxw));
+  WH_TRY(out_buffer(ctx, ctx->stage[6], dual, d.rows, dual ? mem : WH_HOST, &ddual));
+  if (d.rows) WH_CUDA(cudaMemsetAsync(dxw, 0, d.rows * 4, ctx->stream));
+  WH_TRY(spmv_times_launch(ctx, d.rows, d.offset, d.index, d.value, dw, dxw));
+  EvalOut* dev = reinterpret_cast<EvalOut*>(ctx->small.as<char>() + 4096);
+  WH_TRY(loss_forward_launch(ctx, loss, d.rows, d.label, dxw, ddual, dev, 0));
+  WH_TRY(auc_launch(ctx, d.rows, d.label, dxw, dev));
+  if (grad) {  // CalcGrad: grad = X^T dual (loss.h:114), squared hinge then scales by -2 (:152-155)
+    long long* acc;
+    WH_TRY(ensure_acc(ctx, U, &acc));
+    FixedScale* fs = reinterpret_cast<FixedScale*>(ctx->small.as<char>() + 1024);
+    // the staged w is dead after Init: reuse its slot for the gradient of host callers
+    WH_TRY(out_buffer(ctx, ctx->stage[4], grad, U, mem, &dgrad));
+    if (d.rows == 0) { if (U) WH_CUDA(cudaMemsetAsync(dgrad, 0, U * 4, ctx->stream)); }
+    else WH_TRY(spmv_trans_times_launch(ctx, d.rows, d.nnz, d.offset, d.index, d.value, ddual, dgrad, U, acc, fs,
+                                        loss == WH_LOSS_SQUARE_HINGE ? -2.f : 1.f));
+    WH_TRY(out_commit(ctx, grad, dgrad, U, mem));
+  }
+  if (xw) WH_TRY(out_commit(ctx, xw, dxw, d.rows, mem));
+  if (dual) WH_TRY(out_commit(ctx, dual, ddual, d.rows, mem));
+  WH_CUDA(cudaMemcpyAsync(ctx->pinned.p, dev, sizeof(EvalOut), cudaMemcpyDeviceToHost, ctx->stream));
+  WH_CUDA(cudaStreamSynchronize(ctx->stream));
+  EvalHost h = eval_finish(*ctx->pinned.as<EvalOut>(), d.rows);
+  // learn/linear/progress.h:28-34
+  prog[0] = h.objv; prog[1] = h.acc; prog[2] = h.auc; prog[3] = 1; prog[4] = (double)d.rows; prog[5] = 0;
+  return WH_OK;
+}
+
+}  // extern "C"

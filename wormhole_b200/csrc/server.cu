@@ -1,0 +1,291 @@
+// Piece (4): server-side sparse updates, applied in place to a dense direct-addressed table.
+//
+// Replaces the ps-lite server loop plus the three handles of learn/linear/async_sgd.h:
+//   SGDHandle :83-102, AdaGradHandle :122-140, FTRLHandle :158-180, ISGDHandle::Update :35-41,
+// with L1L2::Solve from learn/linear/penalty.h:36-41. One thread per key; entries are padded to
+// 16 B (FTRL) / 8 B (AdaGrad) / 4 B (SGD) so that a key costs one vector load and one store.
+// All fp32 steps are single IEEE operations (-fmad=false; sqrtf and '/' are correctly rounded),
+// so given the same gradient the new state is bit-identical to the reference's.
+#include "server.cuh"
+
+namespace wh {
+
+// learn/linear/penalty.h:36-41
+__device__ __forceinline__ float l1l2_solve(float z, float eta, float l1, float l2) {
+  if (z <= l1 && z >= -l1) return 0.f;
+  return (z > 0.f ? z - l1 : z + l1) / (eta + l2);
+}
+
+struct HandleParams {
+  int algo;
+  float l1, l2, alpha, beta;
+  float eta_sgd;            // SGDHandle::eta for this push message
+  uint64_t key_begin, key_end;
+};
+
+// One key of one push message. Returns the change of |w|_0 (learn/linear/async_sgd.h:35-41).
+__device__ __forceinline__ int handle_push(const HandleParams& h, void* table, uint64_t slot, float g) {
+  float old_w, new_w;
+  if (h.algo == WH_ALGO_FTRL) {        // async_sgd.h:160-175
+    float4* e = reinterpret_cast<float4*>(table) + slot;
+    float4 v = *e;
+    old_w = v.x;
+    float sqrt_n = v.z;
+    float n2 = sqrtf(sqrt_n * sqrt_n + g * g);
+    float sigma = (n2 - sqrt_n) / h.alpha;
+    float z = v.y + (g - sigma * old_w);
+    new_w = l1l2_solve(-z, (h.beta + n2) / h.alpha, h.l1, h.l2);
+    *e = make_float4(new_w, z, n2, 0.f);
+  } else if (h.algo == WH_ALGO_ADAGRAD) {  // async_sgd.h:123-135
+    float2* e = reinterpret_cast<float2*>(table) + slot;
+    float2 v = *e;
+    old_w = v.x;
+    float n2 = sqrtf(v.y * v.y + g * g);
+    float eta = (n2 + h.beta) / h.alpha;
+    new_w = l1l2_solve(eta * old_w - g, eta, h.l1, h.l2);
+    *e = make_float2(new_w, n2);
+  } else {                              // async_sgd.h:91-95
+    float* e = reinterpret_cast<float*>(table) + slot;
+    old_w = *e;
+    new_w = l1l2_solve(h.eta_sgd * old_w - g, h.eta_sgd, h.l1, h.l2);
+    *e = new_w;
+  }
+  return (old_w == 0.f && new_w != 0.f) ? 1 : ((old_w != 0.f && new_w == 0.f) ? -1 : 0);
+}
+
+__device__ __forceinline__ void commit_counters(long long* counters, int delta, int bad) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    delta += __shfl_xor_sync(0xffffffffu, delta, o);
+    bad += __shfl_xor_sync(0xffffffffu, bad, o);
+  }
+  if ((threadIdx.x & 31) == 0) {
+    if (delta) atomicAdd(reinterpret_cast<unsigned long long*>(counters), (unsigned long long)(long long)delta);
+    if (bad) atomicAdd(reinterpret_cast<unsigned long long*>(counters + 1), (unsigned long long)bad);
+  }
+}
+
+template <bool FROM_ACC>
+__global__ void __launch_bounds__(256)
+server_push_kernel(HandleParams h, void* table, const uint64_t* __restrict__ keys, size_t n,
+                   const unsigned* d_n, const float* __restrict__ grads, long long* acc,
+                   const FixedScale* fs, float mul, long long* counters) {
+  if (d_n) n = *d_n;
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int delta = 0, bad = 0;
+  if (i < n) {
+    float g;
+    if (FROM_ACC) {
+      long long a = acc[i];
+      acc[i] = 0;
+      g = (float)((double)a * fs->inv) * mul;
+    } else {
+      g = grads[i];
+    }
+    uint64_t k = keys[i];
+    if (k >= h.key_begin && k < h.key_end) delta = handle_push(h, table, k - h.key_begin, g);
+    else bad = 1;
+  }
+  commit_counters(counters, delta, bad);
+}
+
+// learn/linear/async_sgd.h:97-99,137-139,177-179: send[0] = w
+__global__ void __launch_bounds__(256)
+server_pull_kernel(int algo, const void* table, uint64_t key_begin, uint64_t key_end,
+                   const uint64_t* __restrict__ keys, size_t n, const unsigned* d_n,
+                   float* __restrict__ vals, long long* counters) {
+  if (d_n) n = *d_n;
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int bad = 0;
+  if (i < n) {
+    uint64_t k = keys[i];
+    if (k >= key_begin && k < key_end) {
+      const uint64_t s = k - key_begin;
+      float w;
+      if (algo == WH_ALGO_FTRL) w = __ldg(reinterpret_cast<const float*>(reinterpret_cast<const float4*>(table) + s));
+      else if (algo == WH_ALGO_ADAGRAD) w = __ldg(reinterpret_cast<const float*>(reinterpret_cast<const float2*>(table) + s));
+      else w = __ldg(reinterpret_cast<const float*>(table) + s);
+      vals[i] = w;
+    } else { vals[i] = 0.f; bad = 1; }
+  }
+  commit_counters(counters, 0, bad);
+}
+
+__global__ void server_state_kernel(int algo, void* table, uint64_t key_begin, uint64_t key_end,
+                                    const uint64_t* __restrict__ keys, size_t n, float* w, float* z,
+                                    float* cg, const float* sw, const float* sz, const float* scg,
+                                    int set, long long* counters) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  uint64_t k = keys[i];
+  if (k < key_begin || k >= key_end) { atomicAdd(reinterpret_cast<unsigned long long*>(counters + 1), 1ull); return; }
+  const uint64_t s = k - key_begin;
+  float vw, vz = 0.f, vc = 0.f;
+  if (algo == WH_ALGO_FTRL) { float4 v = reinterpret_cast<float4*>(table)[s]; vw = v.x; vz = v.y; vc = v.z; }
+  else if (algo == WH_ALGO_ADAGRAD) { float2 v = reinterpret_cast<float2*>(table)[s]; vw = v.x; vc = v.y; }
+  else vw = reinterpret_cast<float*>(table)[s];
+  if (!set) { if (w) w[i] = vw; if (z) z[i] = vz; if (cg) cg[i] = vc; return; }
+  float nw = sw ? sw[i] : vw, nz = sz ? sz[i] : vz, nc = scg ? scg[i] : vc;
+  if (algo == WH_ALGO_FTRL) reinterpret_cast<float4*>(table)[s] = make_float4(nw, nz, nc, 0.f);
+  else if (algo == WH_ALGO_ADAGRAD) reinterpret_cast<float2*>(table)[s] = make_float2(nw, nc);
+  else reinterpret_cast<float*>(table)[s] = nw;
+  int delta = (vw == 0.f && nw != 0.f) ? 1 : ((vw != 0.f && nw == 0.f) ? -1 : 0);  // TLoad: Update(w, 0), :59-62
+  if (delta) atomicAdd(reinterpret_cast<unsigned long long*>(counters), (unsigned long long)(long long)delta);
+}
+
+static HandleParams make_params(whServer* s, bool start_push) {
+  HandleParams h;
+  h.algo = s->algo; h.l1 = s->l1; h.l2 = s->l2; h.alpha = s->alpha; h.beta = s->beta;
+  h.key_begin = s->key_begin; h.key_end = s->key_end;
+  h.eta_sgd = 0.f;
+  if (start_push && s->algo == WH_ALGO_SGD) {  // SGDHandle::Start, async_sgd.h:85-90
+    h.eta_sgd = (s->beta + sqrtf((float)s->t)) / s->alpha;
+    s->t += 1;
+  }
+  return h;
+}
+
+int server_pull_launch(whServer* s, const uint64_t* keys, size_t n, const unsigned* d_n, float* vals) {
+  if (n == 0) return WH_OK;
+  WH_LAUNCH(server_pull_kernel, (unsigned)div_up(n, 256), 256, 0, s->ctx->stream, s->algo, s->table.p,
+            s->key_begin, s->key_end, keys, n, d_n, vals, s->counters.as<long long>());
+  return WH_OK;
+}
+int server_push_launch(whServer* s, const uint64_t* keys, size_t n, const unsigned* d_n, const float* grads) {
+  HandleParams h = make_params(s, true);  // Start() runs even for an empty message
+  if (n == 0) return WH_OK;
+  WH_LAUNCH(server_push_kernel<false>, (unsigned)div_up(n, 256), 256, 0, s->ctx->stream, h, s->table.p, keys, n,
+            d_n, grads, (long long*)nullptr, (const FixedScale*)nullptr, 1.f, s->counters.as<long long>());
+  return WH_OK;
+}
+int server_push_acc_launch(whServer* s, const uint64_t* keys, size_t n, const unsigned* d_n, long long* acc,
+                           const FixedScale* fs, float mul) {
+  HandleParams h = make_params(s, true);
+  if (n == 0) return WH_OK;
+  WH_LAUNCH(server_push_kernel<true>, (unsigned)div_up(n, 256), 256, 0, s->ctx->stream, h, s->table.p, keys, n,
+            d_n, (const float*)nullptr, acc, fs, mul, s->counters.as<long long>());
+  return WH_OK;
+}
+
+}  // namespace wh
+
+using namespace wh;
+
+static int check_bad_keys(whServer* s, const char* what) {
+  whContext* ctx = s->ctx;
+  WH_CUDA(cudaMemcpyAsync(ctx->pinned.p, s->counters.p, 16, cudaMemcpyDeviceToHost, ctx->stream));
+  WH_CUDA(cudaStreamSynchronize(ctx->stream));
+  long long bad = ctx->pinned.as<long long>()[1];
+  if (bad) {
+    WH_CUDA(cudaMemsetAsync(s->counters.as<long long>() + 1, 0, 8, ctx->stream));
+    set_error("%s: %lld keys outside this shard's range [%llu, %llu)", what, bad,
+              (unsigned long long)s->key_begin, (unsigned long long)s->key_end);
+    return WH_ERR_INVALID;
+  }
+  return WH_OK;
+}
+
+extern "C" {
+
+int wh_server_create(whContext* ctx, const whServerConfig* c, whServer** out) {
+  WH_REQUIRE(ctx && c && out, "wh_server_create: NULL argument");
+  WH_REQUIRE(c->algo == WH_ALGO_SGD || c->algo == WH_ALGO_ADAGRAD || c->algo == WH_ALGO_FTRL,
+             "wh_server_create: unknown algo: %d", c->algo);
+  WH_REQUIRE(c->lambda_l1 >= 0 && c->lambda_l2 >= 0, "wh_server_create: lambda must be >= 0 (learn/linear/penalty.h:15,19)");
+  WH_REQUIRE(c->key_end > c->key_begin, "wh_server_create: empty key range");
+  WH_REQUIRE(c->key_end - c->key_begin <= (1ull << 32), "wh_server_create: dense shard of %llu keys is too large",
+             (unsigned long long)(c->key_end - c->key_begin));
+  DeviceGuard g(ctx->device);
+  whServer* s = new whServer();
+  s->ctx = ctx; s->algo = c->algo; s->l1 = c->lambda_l1; s->l2 = c->lambda_l2;
+  if (c->has_lr_eta) s->alpha = c->lr_eta;
+  if (c->has_lr_beta) s->beta = c->lr_beta;
+  s->key_begin = c->key_begin; s->key_end = c->key_end;
+  const size_t esz = c->algo == WH_ALGO_FTRL ? 16 : (c->algo == WH_ALGO_ADAGRAD ? 8 : 4);
+  int r = s->table.reserve(s->entries() * esz);
+  if (r == WH_OK) r = s->counters.reserve(64);
+  if (r != WH_OK) { delete s; return r; }
+  WH_CUDA(cudaMemsetAsync(s->table.p, 0, s->table.cap, ctx->stream));  // entries default to 0 (:72,108-109,146-148)
+  WH_CUDA(cudaMemsetAsync(s->counters.p, 0, 64, ctx->stream));
+  *out = s;
+  return WH_OK;
+}
+
+int wh_server_destroy(whServer* s) {
+  if (!s) return WH_OK;
+  DeviceGuard g(s->ctx->device);
+  cudaStreamSynchronize(s->ctx->stream);
+  s->table.release(); s->counters.release();
+  delete s;
+  return WH_OK;
+}
+
+int wh_server_pull(whServer* s, const uint64_t* keys, size_t n, int mem, float* vals) {
+  WH_REQUIRE(s && (n == 0 || (keys && vals)), "wh_server_pull: NULL argument");
+  whContext* ctx = s->ctx;
+  DeviceGuard g(ctx->device);
+  const uint64_t* dk; float* dv;
+  WH_TRY(to_device(ctx, ctx->stage[0], keys, n, mem, &dk));
+  WH_TRY(out_buffer(ctx, ctx->stage[1], vals, n, mem, &dv));
+  WH_TRY(server_pull_launch(s, dk, n, nullptr, dv));
+  WH_TRY(out_commit(ctx, vals, dv, n, mem));
+  if (mem == WH_HOST) return check_bad_keys(s, "wh_server_pull");
+  return WH_OK;
+}
+
+int wh_server_push(whServer* s, const uint64_t* keys, size_t n, int mem, const float* grads) {
+  WH_REQUIRE(s && (n == 0 || (keys && grads)), "wh_server_push: NULL argument");
+  whContext* ctx = s->ctx;
+  DeviceGuard g(ctx->device);
+  const uint64_t* dk; const float* dg;
+  WH_TRY(to_device(ctx, ctx->stage[0], keys, n, mem, &dk));
+  WH_TRY(to_device(ctx, ctx->stage[1], grads, n, mem, &dg));
+  WH_TRY(server_push_launch(s, dk, n, nullptr, dg));
+  if (mem == WH_HOST) return check_bad_keys(s, "wh_server_push");
+  return WH_OK;
+}
+
+int wh_server_nnz_w(whServer* s, int64_t* out) {
+  WH_REQUIRE(s && out, "wh_server_nnz_w: NULL argument");
+  whContext* ctx = s->ctx;
+  DeviceGuard g(ctx->device);
+  WH_CUDA(cudaMemcpyAsync(ctx->pinned.p, s->counters.p, 8, cudaMemcpyDeviceToHost, ctx->stream));
+  WH_CUDA(cudaStreamSynchronize(ctx->stream));
+  *out = ctx->pinned.as<long long>()[0];
+  return WH_OK;
+}
+
+static int state_io(whServer* s, const uint64_t* keys, size_t n, int mem, float* w, float* z, float* cg,
+                    const float* sw, const float* sz, const float* scg, int set) {
+  whContext* ctx = s->ctx;
+  DeviceGuard g(ctx->device);
+  if (n == 0) return WH_OK;
+  const uint64_t* dk; float *dw = nullptr, *dz = nullptr, *dc = nullptr; const float *dsw, *dsz, *dsc;
+  WH_TRY(to_device(ctx, ctx->stage[0], keys, n, mem, &dk));
+  if (w) WH_TRY(out_buffer(ctx, ctx->stage[1], w, n, mem, &dw));
+  if (z) WH_TRY(out_buffer(ctx, ctx->stage[2], z, n, mem, &dz));
+  if (cg) WH_TRY(out_buffer(ctx, ctx->stage[3], cg, n, mem, &dc));
+  WH_TRY(to_device(ctx, ctx->stage[4], sw, n, mem, &dsw));
+  WH_TRY(to_device(ctx, ctx->stage[5], sz, n, mem, &dsz));
+  WH_TRY(to_device(ctx, ctx->stage[6], scg, n, mem, &dsc));
+  WH_LAUNCH(server_state_kernel, (unsigned)div_up(n, 256), 256, 0, ctx->stream, s->algo, s->table.p, s->key_begin,
+            s->key_end, dk, n, dw, dz, dc, dsw, dsz, dsc, set, s->counters.as<long long>());
+  WH_TRY(out_commit(ctx, w, dw, n, mem));
+  WH_TRY(out_commit(ctx, z, dz, n, mem));
+  WH_TRY(out_commit(ctx, cg, dc, n, mem));
+  if (mem == WH_HOST) return check_bad_keys(s, set ? "wh_server_set_state" : "wh_server_get_state");
+  return WH_OK;
+}
+
+int wh_server_get_state(whServer* s, const uint64_t* keys, size_t n, int mem, float* w, float* z, float* cg) {
+  WH_REQUIRE(s && (n == 0 || keys), "wh_server_get_state: NULL argument");
+  return state_io(s, keys, n, mem, w, z, cg, nullptr, nullptr, nullptr, 0);
+}
+int wh_server_set_state(whServer* s, const uint64_t* keys, size_t n, int mem, const float* w, const float* z,
+                        const float* cg) {
+  WH_REQUIRE(s && (n == 0 || keys), "wh_server_set_state: NULL argument");
+  return state_io(s, keys, n, mem, nullptr, nullptr, nullptr, w, z, cg, 1);
+}
+int wh_server_sgd_t(const whServer* s) { return s ? s->t : 0; }
+
+}  // extern "C"

@@ -1,0 +1,348 @@
+// Pieces (2) and (5): SpMV::Times / TransTimes and SpMM::Times / TransTimes. See spmv.cuh.
+#include "spmv.cuh"
+
+namespace wh {
+
+constexpr int kRowsPerBlock = 128;   // one thread per row
+constexpr int kTileCap = 6144;       // staged entries per block (Criteo shape: 128 x 39 = 4992)
+
+// Loads the offsets of this block's rows and, if the rows' entries fit, their index (and value)
+// run into shared memory with coalesced loads. Returns whether the run was staged.
+template <bool HAS_VAL>
+__device__ __forceinline__ bool stage_rows(size_t rows, const size_t* __restrict__ offset,
+                                           const uint32_t* __restrict__ index,
+                                           const float* __restrict__ value, size_t* s_off,
+                                           uint32_t* s_idx, float* s_val) {
+  const size_t r0 = (size_t)blockIdx.x * kRowsPerBlock;
+  for (int t = threadIdx.x; t <= kRowsPerBlock; t += blockDim.x) s_off[t] = offset[min(r0 + t, rows)];
+  __syncthreads();
+  const size_t begin = s_off[0];
+  const size_t cnt = s_off[kRowsPerBlock] - begin;
+  const bool staged = cnt <= (size_t)kTileCap;
+  if (staged) {
+    for (unsigned i = threadIdx.x; i < (unsigned)cnt; i += blockDim.x) {
+      s_idx[i] = ld_stream_u32(index + begin + i);
+      if (HAS_VAL) s_val[i] = __ldg(value + begin + i);
+    }
+  }
+  __syncthreads();
+  return staged;
+}
+
+// learn/base/spmv.h:72-91. y[i] = sum over the row, sequential fp32 in CSR order.
+template <bool HAS_VAL>
+__global__ void __launch_bounds__(kRowsPerBlock)
+spmv_times_kernel(size_t rows, const size_t* __restrict__ offset, const uint32_t* __restrict__ index,
+                  const float* __restrict__ value, const float* __restrict__ x, float* __restrict__ y) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  __shared__ size_t s_off[kRowsPerBlock + 1];
+  uint32_t* s_idx = reinterpret_cast<uint32_t*>(smem);
+  float* s_val = reinterpret_cast<float*>(smem + sizeof(uint32_t) * kTileCap);
+  const bool staged = stage_rows<HAS_VAL>(rows, offset, index, value, s_off, s_idx, s_val);
+  const size_t r = (size_t)blockIdx.x * kRowsPerBlock + threadIdx.x;
+  if (r >= rows) return;
+  const size_t b = s_off[threadIdx.x], e = s_off[threadIdx.x + 1];
+  if (b == e) return;  // spmv.h:79: rows without entries leave y untouched
+  float acc = 0.f;
+  if (staged) {
+    const unsigned lb = (unsigned)(b - s_off[0]), le = (unsigned)(e - s_off[0]);
+    unsigned j = lb;
+    for (; j + 4 <= le; j += 4) {  // 4 gathers in flight, adds stay in order
+      float g0 = __ldg(x + s_idx[j]), g1 = __ldg(x + s_idx[j + 1]);
+      float g2 = __ldg(x + s_idx[j + 2]), g3 = __ldg(x + s_idx[j + 3]);
+      if (HAS_VAL) { g0 *= s_val[j]; g1 *= s_val[j + 1]; g2 *= s_val[j + 2]; g3 *= s_val[j + 3]; }
+      acc += g0; acc += g1; acc += g2; acc += g3;
+    }
+    for (; j < le; ++j) { float g = __ldg(x + s_idx[j]); if (HAS_VAL) g *= s_val[j]; acc += g; }
+  } else {
+    for (size_t j = b; j < e; ++j) { float g = __ldg(x + index[j]); if (HAS_VAL) g *= value[j]; acc += g; }
+  }
+  y[r] = acc;
+}
+
+int spmv_times_launch(whContext* ctx, size_t rows, const size_t* offset, const uint32_t* index,
+                      const float* value, const float* x, float* y) {
+  if (rows == 0) return WH_OK;
+  const unsigned grid = (unsigned)div_up(rows, kRowsPerBlock);
+  if (value) {
+    const size_t smem = kTileCap * 8;
+    static bool attr = false;
+    if (!attr) { WH_CUDA(cudaFuncSetAttribute(spmv_times_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); attr = true; }
+    WH_LAUNCH(spmv_times_kernel<true>, grid, kRowsPerBlock, smem, ctx->stream, rows, offset, index, value, x, y);
+  } else {
+    WH_LAUNCH(spmv_times_kernel<false>, grid, kRowsPerBlock, kTileCap * 4, ctx->stream, rows, offset, index, value, x, y);
+  }
+  return WH_OK;
+}
+
+// ---------------------------------------------------------------------- transposed SpMV --
+
+__global__ void fixed_reset_kernel(FixedScale* fs) { fs->maxx_bits = 0; fs->maxv_bits = 0; }
+
+__global__ void absmax_kernel(const float* __restrict__ v, size_t n, unsigned* target) {
+  float m = 0.f;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+    m = fmaxf(m, fabsf(v[i]));
+  absmax_commit(target, m);
+}
+
+// Picks e with  nnz * max|x| * max|val| * 2^e < 2^62  (no overflow however the terms fall).
+__global__ void fixed_scale_kernel(FixedScale* fs, size_t nnz, int has_val) {
+  float mx = __uint_as_float(fs->maxx_bits);
+  float mv = has_val ? __uint_as_float(fs->maxv_bits) : 1.f;
+  double m = (double)mx * (double)mv;
+  int e = 0;
+  if (m > 0.0 && isfinite(m)) {
+    int em; frexp(m, &em);                    // m < 2^em
+    int en = 64 - __clzll((unsigned long long)(nnz | 1));  // nnz < 2^en
+    e = 61 - em - en;
+  }
+  e = max(-120, min(120, e));
+  fs->scale = ldexpf(1.f, e);
+  fs->inv = ldexp(1.0, -e);
+}
+
+// learn/base/spmv.h:95-119: y[index[j]] += x[i] * value[j] for every entry of row i.
+template <bool HAS_VAL>
+__global__ void __launch_bounds__(kRowsPerBlock)
+spmv_trans_kernel(size_t rows, const size_t* __restrict__ offset, const uint32_t* __restrict__ index,
+                  const float* __restrict__ value, const float* __restrict__ x, long long* acc,
+                  const FixedScale* __restrict__ fs) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  __shared__ size_t s_off[kRowsPerBlock + 1];
+  uint32_t* s_idx = reinterpret_cast<uint32_t*>(smem);
+  float* s_val = reinterpret_cast<float*>(smem + sizeof(uint32_t) * kTileCap);
+  const bool staged = stage_rows<HAS_VAL>(rows, offset, index, value, s_off, s_idx, s_val);
+  const size_t r = (size_t)blockIdx.x * kRowsPerBlock + threadIdx.x;
+  if (r >= rows) return;
+  const size_t b = s_off[threadIdx.x], e = s_off[threadIdx.x + 1];
+  if (b == e) return;
+  const float xi = x[r];
+  const float scale = fs->scale;
+  if (staged) {
+    const unsigned lb = (unsigned)(b - s_off[0]), le = (unsigned)(e - s_off[0]);
+    for (unsigned j = lb; j < le; ++j) fixed_add(acc + s_idx[j], HAS_VAL ? xi * s_val[j] : xi, scale);
+  } else {
+    for (size_t j = b; j < e; ++j) fixed_add(acc + index[j], HAS_VAL ? xi * value[j] : xi, scale);
+  }
+}
+
+// y = fixed-point sum back to fp32 (+ p*z for SpMM); clears the accumulator for the next call.
+__global__ void fixed_finish_kernel(long long* acc, size_t n, const FixedScale* __restrict__ fs,
+                                    float p, const float* __restrict__ z, float* __restrict__ y,
+                                    float mul) {
+  const double inv = fs->inv;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    long long a = acc[i];
+    acc[i] = 0;
+    float s = (float)((double)a * inv) * mul;
+    y[i] = z ? z[i] * p + s : s;
+  }
+}
+
+int ensure_acc(whContext* ctx, size_t n, long long** out) {
+  if (ctx->acc.cap < n * sizeof(long long)) {
+    WH_TRY(ctx->acc.reserve(n * sizeof(long long)));
+    WH_CUDA(cudaMemsetAsync(ctx->acc.p, 0, ctx->acc.cap, ctx->stream));
+  }
+  *out = ctx->acc.as<long long>();
+  return WH_OK;
+}
+
+static int fixed_prepare(whContext* ctx, FixedScale* fs, const float* x, size_t nx, const float* value,
+                         size_t nnz) {
+  const unsigned cap = (unsigned)ctx->num_sms * 8;
+  WH_LAUNCH(fixed_reset_kernel, 1, 1, 0, ctx->stream, fs);
+  WH_LAUNCH(absmax_kernel, (unsigned)std::min<size_t>(div_up(nx ? nx : 1, 256), cap), 256, 0, ctx->stream, x, nx, &fs->maxx_bits);
+  if (value) WH_LAUNCH(absmax_kernel, (unsigned)std::min<size_t>(div_up(nnz ? nnz : 1, 256), cap), 256, 0, ctx->stream, value, nnz, &fs->maxv_bits);
+  WH_LAUNCH(fixed_scale_kernel, 1, 1, 0, ctx->stream, fs, nnz, value ? 1 : 0);
+  return WH_OK;
+}
+
+// Scale selection + accumulation only; the caller converts (fixed_finish or the fused push).
+int spmv_trans_accumulate_launch(whContext* ctx, size_t rows, size_t nnz, const size_t* offset,
+                                 const uint32_t* index, const float* value, const float* x,
+                                 long long* acc, FixedScale* fs) {
+  WH_TRY(fixed_prepare(ctx, fs, x, rows, value, nnz));
+  const unsigned grid = (unsigned)div_up(rows, kRowsPerBlock);
+  if (value) {
+    const size_t smem = kTileCap * 8;
+    static bool attr = false;
+    if (!attr) { WH_CUDA(cudaFuncSetAttribute(spmv_trans_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); attr = true; }
+    WH_LAUNCH(spmv_trans_kernel<true>, grid, kRowsPerBlock, smem, ctx->stream, rows, offset, index, value, x, acc, fs);
+  } else {
+    WH_LAUNCH(spmv_trans_kernel<false>, grid, kRowsPerBlock, kTileCap * 4, ctx->stream, rows, offset, index, value, x, acc, fs);
+  }
+  return WH_OK;
+}
+
+int spmv_trans_times_launch(whContext* ctx, size_t rows, size_t nnz, const size_t* offset,
+                            const uint32_t* index, const float* value, const float* x, float* y,
+                            size_t ysize, long long* acc, FixedScale* fs, float mul) {
+  if (ysize == 0) return WH_OK;
+  WH_TRY(spmv_trans_accumulate_launch(ctx, rows, nnz, offset, index, value, x, acc, fs));
+  const unsigned g2 = (unsigned)std::min<size_t>(div_up(ysize, 256), (size_t)ctx->num_sms * 8);
+  WH_LAUNCH(fixed_finish_kernel, g2, 256, 0, ctx->stream, acc, ysize, fs, 0.f, (const float*)nullptr, y, mul);
+  return WH_OK;
+}
+
+// --------------------------------------------------------------------------------- SpMM --
+
+// learn/base/spmm.h:56-81. One thread per (row, column): entries of the row in CSR order,
+// column k of X[index[j], :] gathered as a contiguous dim-wide run.
+__global__ void __launch_bounds__(256)
+spmm_times_kernel(size_t rows, const size_t* __restrict__ offset, const uint32_t* __restrict__ index,
+                  const float* __restrict__ value, const float* __restrict__ x, float* __restrict__ y,
+                  int dim) {
+  const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const size_t r = t / dim;
+  const int k = (int)(t % dim);
+  if (r >= rows) return;
+  float acc = 0.f;
+  const size_t b = offset[r], e = offset[r + 1];
+  for (size_t j = b; j < e; ++j) {
+    float g = __ldg(x + (size_t)index[j] * dim + k);
+    if (value) g *= value[j];
+    acc += g;
+  }
+  y[r * dim + k] = acc;  // spmm.h:58 zeroes Y first, so empty rows read 0
+}
+
+int spmm_times_launch(whContext* ctx, size_t rows, const size_t* offset, const uint32_t* index,
+                      const float* value, const float* x, float* y, int dim) {
+  if (rows == 0 || dim <= 0) return WH_OK;
+  WH_LAUNCH(spmm_times_kernel, (unsigned)div_up(rows * dim, 256), 256, 0, ctx->stream, rows, offset, index, value, x, y, dim);
+  return WH_OK;
+}
+
+// learn/base/spmm.h:85-123: Y[index[j], :] += X[i, :] * value[j].
+__global__ void __launch_bounds__(256)
+spmm_trans_kernel(size_t rows, const size_t* __restrict__ offset, const uint32_t* __restrict__ index,
+                  const float* __restrict__ value, const float* __restrict__ x, int dim, long long* acc,
+                  const FixedScale* __restrict__ fs) {
+  const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const size_t r = t / dim;
+  const int k = (int)(t % dim);
+  if (r >= rows) return;
+  const float xi = x[r * dim + k];
+  const float scale = fs->scale;
+  const size_t b = offset[r], e = offset[r + 1];
+  for (size_t j = b; j < e; ++j)
+    fixed_add(acc + (size_t)index[j] * dim + k, value ? xi * value[j] : xi, scale);
+}
+
+int spmm_trans_times_launch(whContext* ctx, size_t rows, size_t nnz, const size_t* offset,
+                            const uint32_t* index, const float* value, const float* x, float p,
+                            const float* z, float* y, size_t ysize, int dim, long long* acc,
+                            FixedScale* fs) {
+  if (ysize == 0 || dim <= 0) return WH_OK;
+  WH_TRY(fixed_prepare(ctx, fs, x, rows * dim, value, nnz));
+  if (rows) WH_LAUNCH(spmm_trans_kernel, (unsigned)div_up(rows * dim, 256), 256, 0, ctx->stream, rows, offset, index, value, x, dim, acc, fs);
+  const unsigned g2 = (unsigned)std::min<size_t>(div_up(ysize, 256), (size_t)ctx->num_sms * 8);
+  WH_LAUNCH(fixed_finish_kernel, g2, 256, 0, ctx->stream, acc, ysize, fs, p, (z && p != 0.f) ? z : (const float*)nullptr, y, 1.f);
+  return WH_OK;
+}
+
+}  // namespace wh
+
+// ------------------------------------------------------------------------------ C ABI --
+using namespace wh;
+
+namespace wh {
+// Brings a whLocalBlock to the device (stage slots 0..3) and learns its entry count.
+int stage_local(whContext* ctx, const whLocalBlock* D, int mem, DevLocal* out) {
+  WH_REQUIRE(ctx && D, "NULL argument");
+  WH_REQUIRE(mem == WH_HOST || mem == WH_DEVICE, "bad mem %d", mem);
+  out->rows = D->size;
+  if (D->size == 0) return WH_OK;
+  WH_REQUIRE(D->offset != nullptr, "offset is NULL");
+  size_t n;
+  if (mem == WH_HOST) n = D->offset[D->size];
+  else {
+    WH_CUDA(cudaMemcpyAsync(ctx->pinned.p, D->offset + D->size, sizeof(size_t), cudaMemcpyDeviceToHost, ctx->stream));
+    WH_CUDA(cudaStreamSynchronize(ctx->stream));
+    n = ctx->pinned.as<size_t>()[0];
+  }
+  out->nnz = n;
+  WH_TRY(to_device(ctx, ctx->stage[0], D->offset, D->size + 1, mem, &out->offset));
+  WH_TRY(to_device(ctx, ctx->stage[1], D->index, n, mem, &out->index));
+  WH_TRY(to_device(ctx, ctx->stage[2], D->value, n, mem, &out->value));
+  WH_TRY(to_device(ctx, ctx->stage[3], D->label, D->size, mem, &out->label));
+  return WH_OK;
+}
+}  // namespace wh
+
+extern "C" {
+
+int wh_spmv_times(whContext* ctx, const whLocalBlock* D, int mem, const float* x, size_t xsize, float* y) {
+  DevLocal d;
+  WH_REQUIRE(ctx && D && y, "wh_spmv_times: NULL argument");
+  DeviceGuard g(ctx->device);
+  WH_TRY(stage_local(ctx, D, mem, &d));
+  if (d.rows == 0) return WH_OK;
+  const float* dx; float* dy;
+  WH_TRY(to_device(ctx, ctx->stage[4], x, xsize, mem, &dx));
+  WH_TRY(out_buffer(ctx, ctx->stage[5], y, d.rows, mem, &dy));
+  // rows without entries keep the caller's y (spmv.h:79): bring the old contents along
+  if (mem == WH_HOST) WH_CUDA(cudaMemcpyAsync(dy, y, d.rows * 4, cudaMemcpyHostToDevice, ctx->stream));
+  WH_TRY(spmv_times_launch(ctx, d.rows, d.offset, d.index, d.value, dx, dy));
+  WH_TRY(out_commit(ctx, y, dy, d.rows, mem));
+  if (mem == WH_HOST) WH_CUDA(cudaStreamSynchronize(ctx->stream));
+  return WH_OK;
+}
+
+int wh_spmv_trans_times(whContext* ctx, const whLocalBlock* D, int mem, const float* x, float* y, size_t ysize) {
+  DevLocal d;
+  WH_REQUIRE(ctx && D && y, "wh_spmv_trans_times: NULL argument");
+  DeviceGuard g(ctx->device);
+  WH_TRY(stage_local(ctx, D, mem, &d));
+  const float* dx; float* dy; long long* acc;
+  WH_TRY(to_device(ctx, ctx->stage[4], x, d.rows, mem, &dx));
+  WH_TRY(out_buffer(ctx, ctx->stage[5], y, ysize, mem, &dy));
+  WH_TRY(ensure_acc(ctx, ysize, &acc));
+  FixedScale* fs = reinterpret_cast<FixedScale*>(ctx->small.as<char>() + 1024);
+  if (d.rows == 0) { if (ysize) WH_CUDA(cudaMemsetAsync(dy, 0, ysize * 4, ctx->stream)); }
+  else WH_TRY(spmv_trans_times_launch(ctx, d.rows, d.nnz, d.offset, d.index, d.value, dx, dy, ysize, acc, fs, 1.f));
+  WH_TRY(out_commit(ctx, y, dy, ysize, mem));
+  if (mem == WH_HOST) WH_CUDA(cudaStreamSynchronize(ctx->stream));
+  return WH_OK;
+}
+
+int wh_spmm_times(whContext* ctx, const whLocalBlock* D, int mem, const float* x, size_t xsize, float* y, int dim) {
+  DevLocal d;
+  WH_REQUIRE(ctx && D && y, "wh_spmm_times: NULL argument");
+  WH_REQUIRE(dim > 0, "wh_spmm_times: dim must be positive");
+  DeviceGuard g(ctx->device);
+  if (xsize == 0) return WH_OK;  // spmm.h:26: if (x.empty()) return
+  WH_TRY(stage_local(ctx, D, mem, &d));
+  if (d.rows == 0) return WH_OK;
+  const float* dx; float* dy;
+  WH_TRY(to_device(ctx, ctx->stage[4], x, xsize, mem, &dx));
+  WH_TRY(out_buffer(ctx, ctx->stage[5], y, d.rows * dim, mem, &dy));
+  WH_TRY(spmm_times_launch(ctx, d.rows, d.offset, d.index, d.value, dx, dy, dim));
+  WH_TRY(out_commit(ctx, y, dy, d.rows * dim, mem));
+  if (mem == WH_HOST) WH_CUDA(cudaStreamSynchronize(ctx->stream));
+  return WH_OK;
+}
+
+int wh_spmm_trans_times(whContext* ctx, const whLocalBlock* D, int mem, const float* x, float p,
+                        const float* z, float* y, size_t ysize, int dim) {
+  DevLocal d;
+  WH_REQUIRE(ctx && D && y, "wh_spmm_trans_times: NULL argument");
+  WH_REQUIRE(dim > 0, "wh_spmm_trans_times: dim must be positive");
+  DeviceGuard g(ctx->device);
+  WH_TRY(stage_local(ctx, D, mem, &d));
+  if (d.rows == 0) return WH_OK;  // spmm.h:46: if (x.empty()) return
+  const float* dx; const float* dz; float* dy; long long* acc;
+  WH_TRY(to_device(ctx, ctx->stage[4], x, d.rows * dim, mem, &dx));
+  WH_TRY(to_device(ctx, ctx->stage[6], z, ysize, mem, &dz));
+  WH_TRY(out_buffer(ctx, ctx->stage[5], y, ysize, mem, &dy));
+  WH_TRY(ensure_acc(ctx, ysize, &acc));
+  FixedScale* fs = reinterpret_cast<FixedScale*>(ctx->small.as<char>() + 1024);
+  WH_TRY(spmm_trans_times_launch(ctx, d.rows, d.nnz, d.offset, d.index, d.value, dx, p, dz, dy, ysize, dim, acc, fs));
+  WH_TRY(out_commit(ctx, y, dy, ysize, mem));
+  if (mem == WH_HOST) WH_CUDA(cudaStreamSynchronize(ctx->stream));
+  return WH_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,64 @@
+// Pieces (2) and (5): CSR products on a localized block. Internal launch API (device pointers).
+//
+// Forward products (Times) walk each row sequentially in CSR order with one thread per row (or
+// one thread per row and column for SpMM), which reproduces the reference's fp32 summation
+// order exactly (learn/base/spmv.h:72-91, learn/base/spmm.h:56-81). The block first stages its
+// rows' index/value run in shared memory with coalesced loads, so global traffic is one
+// streaming pass over the CSR plus the gathers.
+//
+// Transposed products (TransTimes) cannot keep the reference's order (ascending rows per output,
+// learn/base/spmv.h:103-117) without serialising hot features, so they accumulate in 64-bit
+// FIXED POINT: every term x_i*val_ij is computed in fp32 exactly as the reference does, scaled
+// by a power of two chosen from max|x|, max|val| and the entry count, and added with integer
+// atomics. Integer addition is associative, so the result is independent of thread order
+// (bit-reproducible run to run) and differs from the reference only by the reference's own
+// fp32 accumulation rounding (tests bound it by 1e-5 of the sum of |terms|).
+#pragma once
+#include "common.cuh"
+
+namespace wh {
+
+struct FixedScale {
+  float scale;     // 2^e
+  double inv;      // 2^-e
+  unsigned maxx_bits, maxv_bits;  // float bit patterns of max|x|, max|val| (atomicMax targets)
+};
+
+int spmv_times_launch(whContext* ctx, size_t rows, const size_t* offset, const uint32_t* index,
+                      const float* value, const float* x, float* y);
+// acc: int64[ysize], all zero on entry and left all zero on exit. fs: device scratch.
+// mul: exact post-scale of the result (the -2 of the squared hinge, learn/linear/loss.h:152-155).
+int spmv_trans_times_launch(whContext* ctx, size_t rows, size_t nnz, const size_t* offset,
+                            const uint32_t* index, const float* value, const float* x, float* y,
+                            size_t ysize, long long* acc, FixedScale* fs, float mul);
+int spmm_times_launch(whContext* ctx, size_t rows, const size_t* offset, const uint32_t* index,
+                      const float* value, const float* x, float* y, int dim);
+int spmm_trans_times_launch(whContext* ctx, size_t rows, size_t nnz, const size_t* offset,
+                            const uint32_t* index, const float* value, const float* x, float p,
+                            const float* z, float* y, size_t ysize, int dim, long long* acc,
+                            FixedScale* fs);
+// A whLocalBlock resolved to device pointers.
+struct DevLocal {
+  size_t rows = 0, nnz = 0;
+  const size_t* offset = nullptr; const uint32_t* index = nullptr; const float* value = nullptr;
+  const float* label = nullptr;
+};
+int stage_local(whContext* ctx, const whLocalBlock* D, int mem, DevLocal* out);
+// zero-on-growth accumulator of the context
+int ensure_acc(whContext* ctx, size_t n, long long** out);
+
+#ifdef __CUDACC__
+__device__ __forceinline__ void fixed_add(long long* acc, float term, float scale) {
+  long long q = __float2ll_rn(term * scale);
+  atomicAdd(reinterpret_cast<unsigned long long*>(acc), static_cast<unsigned long long>(q));
+}
+// max|v| over an array as an atomicMax on the bit pattern (non-negative floats order like uints)
+__device__ __forceinline__ void absmax_commit(unsigned* target, float m) {
+  m = fabsf(m);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+  if ((threadIdx.x & 31) == 0 && m > 0.f) atomicMax(target, __float_as_uint(m));
+}
+#endif
+
+}  // namespace wh
