@@ -81,6 +81,13 @@ WH_API int wh_destroy(whContext* ctx);
 /* Use an existing CUDA stream (cudaStream_t as void*) instead of the context's own. */
 WH_API int wh_set_stream(whContext* ctx, void* cuda_stream);
 WH_API int wh_sync(whContext* ctx);
+/* Opt-in timing of the library's own kernels with CUDA events on the context's stream (what
+ * bench.py's roofline figures are measured with). Enabling clears the accumulated numbers.
+ * Segment i: name, summed milliseconds, number of times it ran. No counterpart in the reference
+ * beyond its wall-clock workload_time_ (learn/linear/async_sgd.h:245-248,258,285). */
+WH_API int wh_profile_enable(whContext* ctx, int on);
+WH_API int wh_profile_count(whContext* ctx);
+WH_API int wh_profile_get(whContext* ctx, int i, const char** name, double* total_ms, uint64_t* count);
 
 /* ---- (1) localizer ---------------------------------------------------------------------- */
 /* dmlc::ReverseBytes, learn/base/localizer.h:16-26 (a nibble reversal). Host-side scalar helper

@@ -201,8 +201,15 @@ def test_bin_eval(gpu, checker):
         pred = (rng.standard_normal(n) * 3).astype(np.float32)
         a, b = gpu.bin_eval(label, pred), checker.bin_eval(label, pred, 2)
         assert a["acc"] == b["acc"]
-        assert abs(a["logit_objv"] - b["logit_objv"]) <= 2e-6 * abs(b["logit_objv"]) + 1e-6
-        assert abs(a["logloss"] - b["logloss"]) <= 2e-6 * abs(b["logloss"]) + 1e-6
+        # the objective is a sum over examples: the device sums the fp32 terms in fp64, the
+        # reference in fp32 (binary_class_evaluation.h:66-74), whose rounding grows with n.
+        y = np.where(label > 0, 1, -1).astype(np.float32)
+        terms = np.log((1 + np.exp(-y * pred, dtype=np.float32)).astype(np.float32), dtype=np.float32)
+        exact = float(terms.astype(np.float64).sum())
+        assert abs(a["logit_objv"] - exact) <= 2e-6 * exact + 1e-6
+        ref_tol = (2e-6 + 2e-10 * n) * exact + 1e-6
+        assert abs(a["logit_objv"] - b["logit_objv"]) <= ref_tol
+        assert abs(a["logloss"] - b["logloss"]) <= ref_tol
         assert abs(a["auc"] - b["auc"]) <= 1e-4       # reference accumulates the area in fp32
         assert a["auc_lo"] - 1e-4 <= b["auc"] <= a["auc_hi"] + 1e-4
     # equal scores: any tie order of the reference's unstable sort lies inside [auc_lo, auc_hi]
@@ -227,7 +234,9 @@ def test_linear_loss(gpu, checker, loss, with_value):
     pc, gc = checker.linear_loss(loss, D, w, 2)
     assert np.array_equal(xw, checker.spmv_times(D, w))                      # Xw bit-exact
     assert pg[1] == pc[1] and pg[3] == pc[3] and pg[4] == pc[4]             # acc, count, new_ex
-    assert abs(pg[0] - pc[0]) <= 2e-6 * abs(pc[0])                           # objv
+    # objv: the reference adds the per-example terms in fp32 (rounding grows with the row count,
+    # ~2e-5 relative at a few thousand rows); the device adds the same fp32 terms in fp64.
+    assert abs(pg[0] - pc[0]) <= 1e-4 * abs(pc[0])                           # objv (north_star: logloss 1e-4)
     assert abs(pg[2] - pc[2]) <= 1e-4                                        # auc
     mul = 2.0 if loss == capi.LOSS_SQUARE_HINGE else 1.0
     close_sum(gg, gc, mul * abs_terms(D, dual, U))
@@ -305,7 +314,7 @@ def test_process_minibatch_vs_reference(gpu, checker, algo, loss, max_key):
         pg = wk.process_minibatch(blk)
         pc = checker.linear_minibatch(job, blk)
         assert pg[4] == pc[4] and pg[3] == pc[3]
-        assert abs(pg[0] - pc[0]) <= 1e-5 * abs(pc[0]) + 1e-6, (m, pg, pc)
+        assert abs(pg[0] - pc[0]) <= 1e-4 * abs(pc[0]) + 1e-6, (m, pg, pc)   # fp32 vs fp64 accumulation
         assert abs(pg[1] - pc[1]) <= 1e-3
         nnz_w += pg[5]
         keys, w, z, cg = checker.linear_model(job)
@@ -326,5 +335,5 @@ def test_default_key_mode_uses_sort_path(gpu, checker):
     w = (rng.standard_normal(len(D.uniq)) * 0.2).astype(np.float32)
     pg, gg = gpu.linear_loss(capi.LOSS_LOGIT, D, w)
     pc, gc = checker.linear_loss(capi.LOSS_LOGIT, D, w, 2)
-    assert abs(pg[0] - pc[0]) <= 2e-6 * abs(pc[0])
+    assert abs(pg[0] - pc[0]) <= 1e-4 * abs(pc[0])
     assert np.linalg.norm(gg.astype(np.float64) - gc) <= RTOL * np.linalg.norm(gc.astype(np.float64))

@@ -72,8 +72,21 @@ struct PinnedBuf {
 
 }  // namespace wh
 
+namespace wh {
+// Opt-in per-kernel timing with CUDA events on the launching stream (bench.py's roofline leg).
+struct Profiler {
+  bool on = false;
+  std::vector<cudaEvent_t> ev;        // ev[i] recorded right after segment i-1's kernels
+  std::vector<const char*> name;      // name[i]: what ran between ev[i] and ev[i+1]
+  size_t used = 0;
+  struct Acc { std::string name; double ms = 0; unsigned long long count = 0; };
+  std::vector<Acc> acc;
+};
+}  // namespace wh
+
 struct whContext {
   int device = 0;
+  wh::Profiler prof;
   int num_sms = 148;
   size_t l2_bytes = 0;
   cudaStream_t stream = nullptr;
@@ -96,6 +109,12 @@ struct DeviceGuard {
   explicit DeviceGuard(int dev) { cudaGetDevice(&prev); if (prev != dev) cudaSetDevice(dev); else prev = -1; }
   ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
 };
+
+// Marks the end of a named segment of device work (no-op unless profiling is enabled).
+int prof_begin(whContext* ctx);
+int prof_mark(whContext* ctx, const char* name);
+int prof_collect(whContext* ctx);  // after a stream sync: folds event pairs into the accumulators
+#define WH_PROF(ctx, name) do { if ((ctx)->prof.on) WH_TRY(wh::prof_mark((ctx), (name))); } while (0)
 
 // Brings a host array to the device (stage buffer) or passes a device pointer through.
 template <typename T>

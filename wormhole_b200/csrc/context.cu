@@ -45,9 +45,58 @@ int PinnedBuf::reserve(size_t bytes) {
 }
 void PinnedBuf::release() { if (p) cudaFreeHost(p); p = nullptr; cap = 0; }
 
+int prof_begin(whContext* ctx) {
+  if (!ctx->prof.on) return WH_OK;
+  return prof_mark(ctx, nullptr);
+}
+int prof_mark(whContext* ctx, const char* name) {
+  Profiler& p = ctx->prof;
+  if (p.used == p.ev.size()) {
+    cudaEvent_t e;
+    WH_CUDA(cudaEventCreate(&e));
+    p.ev.push_back(e);
+    p.name.push_back(nullptr);
+  }
+  WH_CUDA(cudaEventRecord(p.ev[p.used], ctx->stream));
+  p.name[p.used] = name;  // name of the segment that ENDS at this event (NULL = start marker)
+  p.used++;
+  return WH_OK;
+}
+int prof_collect(whContext* ctx) {
+  Profiler& p = ctx->prof;
+  for (size_t i = 1; i < p.used; ++i) {
+    if (!p.name[i]) continue;
+    float ms = 0;
+    WH_CUDA(cudaEventElapsedTime(&ms, p.ev[i - 1], p.ev[i]));
+    Profiler::Acc* a = nullptr;
+    for (auto& x : p.acc) if (x.name == p.name[i]) { a = &x; break; }
+    if (!a) { p.acc.push_back(Profiler::Acc()); a = &p.acc.back(); a->name = p.name[i]; }
+    a->ms += ms; a->count++;
+  }
+  p.used = 0;
+  return WH_OK;
+}
+
 }  // namespace wh
 
 extern "C" {
+
+int wh_profile_enable(whContext* c, int on) {
+  WH_REQUIRE(c != nullptr, "wh_profile_enable: ctx is NULL");
+  wh::DeviceGuard g(c->device);
+  WH_CUDA(cudaStreamSynchronize(c->stream));
+  c->prof.on = on != 0; c->prof.used = 0;
+  if (on) c->prof.acc.clear();
+  return WH_OK;
+}
+int wh_profile_count(whContext* c) { return c ? (int)c->prof.acc.size() : 0; }
+int wh_profile_get(whContext* c, int i, const char** name, double* total_ms, uint64_t* count) {
+  WH_REQUIRE(c && i >= 0 && i < (int)c->prof.acc.size(), "wh_profile_get: bad index");
+  if (name) *name = c->prof.acc[i].name.c_str();
+  if (total_ms) *total_ms = c->prof.acc[i].ms;
+  if (count) *count = c->prof.acc[i].count;
+  return WH_OK;
+}
 
 const char* wh_last_error(void) { return wh::g_err; }
 const char* wh_version(void) { return "wormhole_b200 0.1 (sm_100a)"; }
@@ -92,6 +141,7 @@ int wh_destroy(whContext* c) {
   for (auto& b : c->sort_tmp) b.release();
   for (auto& b : c->stage) b.release();
   c->pinned.release();
+  for (auto e : c->prof.ev) cudaEventDestroy(e);
   if (c->own_stream) cudaStreamDestroy(c->stream);
   delete c;
   return WH_OK;

@@ -84,11 +84,15 @@ int localize_direct(whContext* ctx, const LocInput& in, uint64_t* d_uniq, uint32
   const size_t n = in.nnz;
   const unsigned grid = (unsigned)std::min<size_t>(div_up(n ? n : 1, 256), (size_t)ctx->num_sms * 16);
   if (n) WH_LAUNCH(loc_mark_kernel, grid, 256, 0, ctx->stream, in.index, n, in.xf, dir);
+  WH_PROF(ctx, "loc_mark");
   WH_TRY(scan_and_apply<unsigned>(ctx, DirPopc{dir}, DirEmit{dir, d_uniq}, words, ctx->scan_tmp.as<unsigned>(),
                         d_nuniq));
+  WH_PROF(ctx, "loc_dir_scan");
   if (d_cnt && n) WH_CUDA(cudaMemsetAsync(d_cnt, 0, std::min<uint64_t>(n, in.xf.max_key) * 4, ctx->stream));
   if (n) WH_LAUNCH(loc_rank_kernel, grid, 256, 0, ctx->stream, in.index, n, in.xf, dir, d_index, d_cnt);
+  WH_PROF(ctx, "loc_rank");
   WH_CUDA(cudaMemsetAsync(dir, 0, words * sizeof(uint2), ctx->stream));
+  WH_PROF(ctx, "loc_dir_clear");
   return WH_OK;
 }
 
@@ -163,10 +167,13 @@ int localize_sort(whContext* ctx, const LocInput& in, uint64_t* d_uniq, uint32_t
   WH_TRY(sort_plan_reset(ctx, b.plan));
   const unsigned grid = (unsigned)std::min<size_t>(div_up(n, 256), (size_t)ctx->num_sms * 16);
   WH_LAUNCH(loc_xform_kernel, grid, 256, 0, ctx->stream, in.index, n, in.xf, b.keys[0], b.vals[0], b.plan);
+  WH_PROF(ctx, "loc_xform");
   WH_TRY(radix_sort_pairs(ctx, b, n));
+  WH_PROF(ctx, "loc_radix_sort");
   WH_TRY(scan_and_apply<unsigned>(ctx, HeadFlag{b}, HeadApply{b, d_uniq, headpos, d_index}, n,
                         ctx->scan_tmp.as<unsigned>(), d_nuniq));
   if (d_cnt) WH_LAUNCH(loc_count_kernel, grid, 256, 0, ctx->stream, headpos, d_nuniq, n, d_cnt);
+  WH_PROF(ctx, "loc_heads_rank");
   return WH_OK;
 }
 

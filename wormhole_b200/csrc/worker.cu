@@ -91,30 +91,38 @@ int wh_worker_process_minibatch(whWorker* w, const whRowBlock* blk, int mem, int
   FixedScale* fs = reinterpret_cast<FixedScale*>(w->scal.as<char>() + 256);
   EvalOut* d_eval = reinterpret_cast<EvalOut*>(w->scal.as<char>() + 512);
 
+  WH_TRY(prof_begin(ctx));
   // Localize
   LocInput in{d_index, n, make_xform(w->max_key)};
   if (direct) WH_TRY(localize_direct(ctx, in, w->uniq.as<uint64_t>(), nullptr, w->index.as<uint32_t>(), d_nuniq));
   else WH_TRY(localize_sort(ctx, in, w->uniq.as<uint64_t>(), nullptr, w->index.as<uint32_t>(), d_nuniq));
   // ZPull: one Handle::Pull per unique key
   WH_TRY(server_pull_launch(s, w->uniq.as<uint64_t>(), ucap, d_nuniq, w->w.as<float>()));
+  WH_PROF(ctx, "pull");
   // Init: Xw
   WH_CUDA(cudaMemsetAsync(w->xw.p, 0, rows * 4, ctx->stream));
   WH_TRY(spmv_times_launch(ctx, rows, d_offset, w->index.as<uint32_t>(), d_value, w->w.as<float>(), w->xw.as<float>()));
+  WH_PROF(ctx, "spmv_times");
   // Evaluate (+ the dual of CalcGrad, which falls out of the same pass)
   WH_TRY(loss_forward_launch(ctx, w->loss, rows, d_label, w->xw.as<float>(), train ? w->dual.as<float>() : nullptr, d_eval, 0));
+  WH_PROF(ctx, "loss_forward");
   WH_TRY(auc_launch(ctx, rows, d_label, w->xw.as<float>(), d_eval));
+  WH_PROF(ctx, "auc");
   if (train) {
     // CalcGrad: X^T dual into the fixed-point accumulator; ZPush: convert + update in one pass
     long long* acc;
     WH_TRY(ensure_acc(ctx, ucap, &acc));
     WH_TRY(spmv_trans_accumulate_launch(ctx, rows, n, d_offset, w->index.as<uint32_t>(), d_value, w->dual.as<float>(), acc, fs));
+    WH_PROF(ctx, "spmv_trans");
     WH_TRY(server_push_acc_launch(s, w->uniq.as<uint64_t>(), ucap, d_nuniq, acc, fs, w->loss == WH_LOSS_SQUARE_HINGE ? -2.f : 1.f));
   }
+  if (train) WH_PROF(ctx, "push");
   // progress read-back (the one synchronisation of the step)
   char* pin = ctx->pinned.as<char>();
   WH_CUDA(cudaMemcpyAsync(pin, d_eval, sizeof(EvalOut), cudaMemcpyDeviceToHost, ctx->stream));
   WH_CUDA(cudaMemcpyAsync(pin + 256, s->counters.p, 16, cudaMemcpyDeviceToHost, ctx->stream));
   WH_CUDA(cudaStreamSynchronize(ctx->stream));
+  if (ctx->prof.on) WH_TRY(prof_collect(ctx));
   const long long* cnt = reinterpret_cast<const long long*>(pin + 256);
   if (cnt[1]) {
     WH_CUDA(cudaMemsetAsync(s->counters.as<long long>() + 1, 0, 8, ctx->stream));
