@@ -129,6 +129,24 @@ WH_API int wh_spmv_times(whContext* ctx, const whLocalBlock* D, int mem, const f
 /* SpMV::TransTimes, learn/base/spmv.h:95-119: y[0..ysize) = D^T x. */
 WH_API int wh_spmv_trans_times(whContext* ctx, const whLocalBlock* D, int mem, const float* x,
                                float* y, size_t ysize);
+/* Allocation-free variant of wh_spmv_trans_times. It has no counterpart in the reference.
+ * For callers that must not allocate device memory: a worker whose GPU also runs other minibatch
+ * streams (cudaMalloc / cudaFree stall the whole device) or a process whose device memory is
+ * already fully owned by someone else (cudaMalloc fails). Needs no whContext and calls no
+ * cudaMalloc, cudaFree or any allocating routine: its scratch (the fixed-point accumulators) is a
+ * static 2 MiB array inside the library, held by every GPU that loads it until the process exits.
+ *   - all arrays are DEVICE pointers on the current device; work is enqueued on `cuda_stream`
+ *     (cudaStream_t as void*, NULL = default stream); nnz = offset[D->size], passed by the caller
+ *     because reading it back would need a synchronising copy.
+ *   - ysize must not exceed WH_STATIC_SCRATCH_MAX_OUTPUTS; larger requests fail with
+ *     WH_ERR_INVALID and a message naming the limit.
+ *   - the first call on each device looks up the array's device address; make that first call
+ *     before any stream capture begins.
+ *   - the array is shared by every call on that GPU and keeps the last call's contents (each call
+ *     clears the part it uses first). Calls that overlap on the same GPU race: serialise them. */
+#define WH_STATIC_SCRATCH_MAX_OUTPUTS 262144
+WH_API int wh_spmv_trans_times_static(void* cuda_stream, const whLocalBlock* D, size_t nnz, const float* x,
+                                      float* y, size_t ysize);
 /* SpMM::Times, learn/base/spmm.h:23-29,56-81: Y[rows x dim] = D X[xrows x dim], row major. */
 WH_API int wh_spmm_times(whContext* ctx, const whLocalBlock* D, int mem, const float* x, size_t xsize,
                          float* y, int dim);

@@ -346,3 +346,88 @@ int wh_spmm_trans_times(whContext* ctx, const whLocalBlock* D, int mem, const fl
 }
 
 }  // extern "C"
+
+// ------------------------------------------------------------ allocation-free variant --
+//
+// wh_spmv_trans_times_static: the transposed product for callers that must not allocate.
+//
+// Who that is: a worker that shares its GPU with minibatch streams it must not stall
+// (cudaMalloc/cudaFree synchronise the whole device, so an allocation in one stream's path
+// freezes every other stream until it returns), and a process whose device memory has already
+// been handed out in full to some other owner (a framework's caching pool, a co-located
+// server's model shard), where a fresh cudaMalloc simply fails. The other entry points grow
+// their scratch with cudaMalloc on first use or when a larger minibatch arrives; this one
+// never does. Its scratch -- the int64 fixed-point accumulators and the scale record -- lives
+// in a fixed array inside the library image, so every GPU that loads the library holds those
+// 2 MiB until the process exits, and the number of outputs is capped at
+// WH_STATIC_SCRATCH_MAX_OUTPUTS.
+//
+// The array is one per device and shared by every call: two calls that overlap on the same
+// GPU (different streams, or different threads) race on it. Serialise them.
+#include <mutex>
+
+namespace {
+
+struct StaticScratch {
+  long long acc[WH_STATIC_SCRATCH_MAX_OUTPUTS];
+  wh::FixedScale fs;
+};
+// File-scope device array. In host code this name is only a handle for the runtime: the device
+// address has to be asked for with cudaGetSymbolAddress (below), never passed to a kernel as is.
+static __device__ __align__(256) unsigned char g_static_scratch[sizeof(StaticScratch)];
+
+constexpr int kStaticMaxDevices = 64;
+std::mutex g_static_mu;
+StaticScratch* g_static_ptr[kStaticMaxDevices] = {};  // device address of the array, per device
+int g_static_sms[kStaticMaxDevices] = {};
+
+// Once per device, with that device current: resolve the array's device address.
+int static_scratch_setup(int dev, StaticScratch** out, int* sms) {
+  std::lock_guard<std::mutex> lk(g_static_mu);
+  if (g_static_ptr[dev] == nullptr) {
+    void* p = nullptr;
+    WH_CUDA(cudaGetSymbolAddress(&p, g_static_scratch));
+    int n = 0;
+    WH_CUDA(cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev));
+    g_static_sms[dev] = n;
+    g_static_ptr[dev] = static_cast<StaticScratch*>(p);
+  }
+  *out = g_static_ptr[dev];
+  *sms = g_static_sms[dev];
+  return WH_OK;
+}
+
+}  // namespace
+
+extern "C" int wh_spmv_trans_times_static(void* cuda_stream, const whLocalBlock* D, size_t nnz,
+                                          const float* x, float* y, size_t ysize) {
+  WH_REQUIRE(D && y, "wh_spmv_trans_times_static: NULL argument");
+  WH_REQUIRE(ysize <= (size_t)WH_STATIC_SCRATCH_MAX_OUTPUTS,
+             "wh_spmv_trans_times_static: %zu outputs exceed the static scratch limit of %d; "
+             "use wh_spmv_trans_times, which allocates its scratch",
+             ysize, WH_STATIC_SCRATCH_MAX_OUTPUTS);
+  WH_REQUIRE(D->size == 0 || (D->offset && D->index && x), "wh_spmv_trans_times_static: NULL array");
+  WH_REQUIRE(nnz < (size_t)UINT32_MAX, "wh_spmv_trans_times_static: %zu entries", nnz);
+  if (ysize == 0) return WH_OK;
+  int dev = 0;
+  WH_CUDA(cudaGetDevice(&dev));
+  WH_REQUIRE(dev >= 0 && dev < kStaticMaxDevices, "wh_spmv_trans_times_static: device %d not supported", dev);
+  StaticScratch* sc = nullptr;
+  int sms = 0;
+  WH_TRY(static_scratch_setup(dev, &sc, &sms));  // first call on this device resolves the address
+  cudaStream_t stream = static_cast<cudaStream_t>(cuda_stream);
+  // a launch context on the stack: no buffers, no events, just the stream and the SM count
+  whContext lc;
+  lc.device = dev;
+  lc.num_sms = sms;
+  lc.stream = stream;
+  lc.own_stream = false;
+  // The array still holds whatever the previous call left: the accumulators must start at zero.
+  WH_CUDA(cudaMemsetAsync(sc->acc, 0, ysize * sizeof(long long), stream));
+  if (D->size == 0) {
+    WH_CUDA(cudaMemsetAsync(y, 0, ysize * sizeof(float), stream));
+    return WH_OK;
+  }
+  return wh::spmv_trans_times_launch(&lc, D->size, nnz, D->offset, D->index, D->value, x, y, ysize,
+                                     sc->acc, &sc->fs, 1.f);
+}
