@@ -186,8 +186,12 @@ def test_gpu_agaricus_epoch_matches_golden(gpu):
         progs = np.array([wk.process_minibatch(ag.slice(b, min(ag.rows, b + 1000))) for b in range(0, ag.rows, 1000)])
         want = g[name + "_prog"]
         # epoch aggregates exactly as the scheduler prints them (learn/linear/progress.h:21-23)
-        logloss = progs[:, 0].sum() / progs[:, 4].sum()
-        assert abs(logloss - want[:, 0].sum() / want[:, 4].sum()) <= 1e-4
+        # (with the guide's learning rate some margins overflow expf: the reference's objective is
+        # +inf on those minibatches, and so must ours be)
+        assert np.array_equal(np.isinf(progs[:, 0]), np.isinf(want[:, 0])), name
+        fin = np.isfinite(want[:, 0])
+        logloss = progs[fin, 0].sum() / progs[fin, 4].sum()
+        assert abs(logloss - want[fin, 0].sum() / want[fin, 4].sum()) <= 1e-4
         assert np.array_equal(progs[:, 1], want[:, 1])                 # accuracy per minibatch
         assert progs[:, 5].sum() == want[:, 5].sum()                   # |w|_0
         # AUC: minibatch 0 starts from w = 0 (all scores equal: any value is a valid tie order);
