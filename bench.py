@@ -175,7 +175,7 @@ def run_ours(args):
     stream = torch.cuda.current_stream()
     ctx.set_stream(stream.cuda_stream)
     srv = capi.Server(ctx, capi.ALGO_FTRL, FTRL["l1"], FTRL["l2"], FTRL["eta"], FTRL["beta"], 0, MAX_KEY)
-    wk = capi.Worker(ctx, srv, capi.LOSS_LOGIT, MAX_KEY)
+    wk = capi.Worker(ctx, srv, capi.LOSS_LOGIT, MAX_KEY, depth=args.depth)
 
     # the minibatch pool: distinct minibatches, resident in HBM (device leg) and in pinned host
     # memory (e2e leg). pool_n x ~32 MB exceeds the 126 MB L2, so every step streams from HBM.
@@ -202,16 +202,26 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
+    def run(blocks, mem, first, count):
+        # up to `depth` minibatches in flight (conf max_concurrency); every one is waited for,
+        # so its progress numbers have reached the host before the clock stops
+        pending = []
+        for i in range(count):
+            if len(pending) == args.depth:
+                wk.wait(pending.pop(0))
+            b = blocks[(first + i) % pool_n]
+            pending.append(wk.submit(b, True, mem, N))
+        for t in pending:
+            wk.wait(t)
+
     def timed(blocks, mem, steps, warmup):
-        for i in range(warmup):
-            wk.process_minibatch(blocks[i % pool_n], True, mem)
+        run(blocks, mem, 0, warmup)
         barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         l0 = capi.kernel_launches()
         t0 = time.perf_counter()
         e0.record(stream)
-        for i in range(steps):
-            wk.process_minibatch(blocks[(warmup + i) % pool_n], True, mem)
+        run(blocks, mem, warmup, steps)
         e1.record(stream)
         torch.cuda.synchronize()
         wall = time.perf_counter() - t0
@@ -261,7 +271,8 @@ def run_ours(args):
             "config": {"workload": WORKLOAD, "rows_per_minibatch": rows, "nnz_per_minibatch": N,
                        "max_key": MAX_KEY, "unique_keys_per_row_r": round(r, 4), "pool_minibatches": pool_n,
                        "l2_policy": "inputs larger than L2 (pool of %d distinct minibatches, %.0f MB)" % (pool_n, pool_n * N * 8 / 1e6),
-                       "parallelism": "key-range shards x%d" % world, "updater": FTRL},
+                       "parallelism": "key-range shards x%d" % world, "updater": FTRL,
+                       "minibatches_in_flight": args.depth},
             "e2e": {"value": e2e, "unit": "examples/s", "h2d_bytes_per_step": N * 8 + (rows + 1) * 8 + rows * 4,
                     "d2h_bytes_per_step": 72 + 16},
             "gpu_launches": int(launches),
@@ -300,6 +311,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--rows", type=int, default=ROWS)
     ap.add_argument("--pool", type=int, default=8, help="distinct minibatches kept resident")
+    ap.add_argument("--depth", type=int, default=3, help="minibatches in flight (conf max_concurrency)")
     ap.add_argument("--cpu-procs", type=int, default=0, help="reference arm: worker+server pairs (0 = cores/2)")
     args = ap.parse_args()
     if args.impl == "reference":

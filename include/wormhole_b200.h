@@ -206,7 +206,22 @@ WH_API int wh_server_sgd_t(const whServer* s);
  * (1 worker, 1 server). max_key is ps::FLAGS_max_key. */
 WH_API int wh_worker_create(whContext* ctx, whServer* server, int loss, uint64_t max_key,
                             whWorker** out);
+/* Same, with `depth` minibatches allowed in flight (conf max_concurrency,
+ * learn/solver/minibatch_solver.h:289-290,307-322); depth in [1, 8]. */
+WH_API int wh_worker_create_ex(whContext* ctx, whServer* server, int loss, uint64_t max_key, int depth,
+                               whWorker** out);
 WH_API int wh_worker_destroy(whWorker* w);
+/* The two halves of ProcessMinibatch for callers that keep several minibatches in flight
+ * (MinibatchWorker::Process / WaitMinibatch / FinishMinibatch, learn/solver/minibatch_solver.h:
+ * 261-276,307-322). submit enqueues the whole minibatch and returns at once; nnz = offset[size]
+ * (only read for WH_DEVICE blocks; 0 = unknown, costs a synchronising read); the arrays of blk must
+ * stay valid and unchanged until the matching wait. wait blocks until that minibatch is done and
+ * fills prog[6]. Tickets are collected in submission order. Every pull sees all earlier pushes, so
+ * the numbers equal strictly sequential processing; staging, localize and AUC of neighbouring
+ * minibatches overlap. */
+WH_API int wh_worker_submit(whWorker* w, const whRowBlock* blk, int mem, size_t nnz, int train,
+                            uint64_t* ticket);
+WH_API int wh_worker_wait(whWorker* w, uint64_t ticket, double* prog);
 /* AsgdWorker::ProcessMinibatch, learn/linear/async_sgd.h:240-288: Localize -> ZPull ->
  * Init/Evaluate -> (train) CalcGrad -> ZPush. prog[6] as in wh_linear_loss, with new_w the
  * server's change of |w|_0 for this minibatch. Synchronous. */

@@ -196,7 +196,7 @@ def test_spmm(gpu, checker, dim, with_value):
 
 def test_bin_eval(gpu, checker):
     rng = np.random.default_rng(31)
-    for n in (1, 2, 777, 20000, 300000):
+    for n in (1, 2, 31, 33, 777, 20000, 300000, 1200000):   # > 2^20 takes the multi-launch sort
         label = (rng.random(n) < 0.3).astype(np.float32)
         pred = (rng.standard_normal(n) * 3).astype(np.float32)
         a, b = gpu.bin_eval(label, pred), checker.bin_eval(label, pred, 2)
@@ -207,7 +207,7 @@ def test_bin_eval(gpu, checker):
         terms = np.log((1 + np.exp(-y * pred, dtype=np.float32)).astype(np.float32), dtype=np.float32)
         exact = float(terms.astype(np.float64).sum())
         assert abs(a["logit_objv"] - exact) <= 2e-6 * exact + 1e-6
-        ref_tol = (2e-6 + 2e-10 * n) * exact + 1e-6
+        ref_tol = (2e-6 + 4e-10 * n) * exact + 1e-6
         assert abs(a["logit_objv"] - b["logit_objv"]) <= ref_tol
         assert abs(a["logloss"] - b["logloss"]) <= ref_tol
         assert abs(a["auc"] - b["auc"]) <= 1e-4       # reference accumulates the area in fp32
@@ -337,3 +337,28 @@ def test_default_key_mode_uses_sort_path(gpu, checker):
     pc, gc = checker.linear_loss(capi.LOSS_LOGIT, D, w, 2)
     assert abs(pg[0] - pc[0]) <= 1e-4 * abs(pc[0])
     assert np.linalg.norm(gg.astype(np.float64) - gc) <= RTOL * np.linalg.norm(gc.astype(np.float64))
+
+
+def test_minibatches_in_flight_equal_sequential(gpu):
+    """submit/wait with 3 minibatches in flight gives the very numbers of one-at-a-time processing:
+    every pull is ordered after all earlier pushes (max_concurrency changes overlap, not results)."""
+    rng = np.random.default_rng(53)
+    blks = [random_block(rng, 4000, 20, 30000, with_value=(m % 3 == 0), empty_rows=False) for m in range(7)]
+    states, progs = [], []
+    for depth in (1, 3):
+        srv = capi.Server(gpu, capi.ALGO_FTRL, 0.5, 0.1, 0.1, 1.0, 0, 2 ** 20)
+        wk = capi.Worker(gpu, srv, capi.LOSS_LOGIT, 2 ** 20, depth=depth)
+        out, pending = [], []
+        for b in blks:
+            if len(pending) == depth:
+                out.append(wk.wait(pending.pop(0)))
+            pending.append(wk.submit(b))
+        out += [wk.wait(t) for t in pending]
+        keys = np.unique(np.concatenate([b.index % np.uint64(2 ** 20) for b in blks]))
+        states.append(srv.get_state(keys)); progs.append(np.array(out))
+        with pytest.raises(capi.WormholeError):
+            wk.wait(12345)                      # not in flight
+        wk.close(); srv.close()
+    assert np.array_equal(progs[0], progs[1])
+    for a, b in zip(states[0], states[1]):
+        assert np.array_equal(a, b)

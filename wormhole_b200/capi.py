@@ -271,10 +271,26 @@ class Server:
 class Worker:
     """AsgdWorker (learn/linear/async_sgd.h:229-305) bound to one server on the same GPU."""
 
-    def __init__(self, ctx, server, loss=LOSS_LOGIT, max_key=NO_MAX_KEY):
-        self.ctx, self.server = ctx, server
+    def __init__(self, ctx, server, loss=LOSS_LOGIT, max_key=NO_MAX_KEY, depth=1):
+        self.ctx, self.server, self.depth = ctx, server, depth
         self.h = C.c_void_p()
-        _check(lib().wh_worker_create(ctx.h, server.h, C.c_int(loss), C.c_uint64(max_key), C.byref(self.h)))
+        _check(lib().wh_worker_create_ex(ctx.h, server.h, C.c_int(loss), C.c_uint64(max_key), C.c_int(depth),
+                                         C.byref(self.h)))
+        self._keep = {}
+
+    def submit(self, blk, train=True, mem=WH_HOST, nnz=0):
+        """Enqueue one minibatch (up to `depth` in flight); returns a ticket for wait()."""
+        t = C.c_uint64()
+        rb = _rowblock(blk)
+        _check(lib().wh_worker_submit(self.h, C.byref(rb), C.c_int(mem), C.c_size_t(nnz), C.c_int(train), C.byref(t)))
+        self._keep[t.value] = blk   # the arrays must outlive the call
+        return t.value
+
+    def wait(self, ticket):
+        prog = np.zeros(6, np.float64)
+        _check(lib().wh_worker_wait(self.h, C.c_uint64(ticket), _ptr(prog)))
+        self._keep.pop(ticket, None)
+        return prog
 
     def process_minibatch(self, blk, train=True, mem=WH_HOST):
         """ProcessMinibatch(mb, wl): -> progress {objv, acc, auc, count, new_ex, new_w}."""

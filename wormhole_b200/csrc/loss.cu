@@ -11,6 +11,8 @@
 //  * AUC is exact integer pair counting. Equal scores: the reference's std::sort leaves their
 //    order unspecified (binary_class_evaluation.h:25-26); here tied (pos,neg) pairs count 1/2,
 //    and the two extremes are reported as auc_lo / auc_hi.
+#include <cooperative_groups.h>
+
 #include "loss.cuh"
 #include "scan.cuh"
 #include "spmv.cuh"
@@ -167,7 +169,7 @@ auc_groups_kernel(size_t n, const uint32_t* __restrict__ gpos, const uint32_t* _
   if (blockIdx.x == 0 && threadIdx.x == 0) { out->npos = P; out->ngroups = ngroups; }
 }
 
-int auc_launch(whContext* ctx, size_t n, const float* label, const float* xw, EvalOut* out) {
+int auc_launch_multiblock(whContext* ctx, size_t n, const float* label, const float* xw, EvalOut* out) {
   if (n == 0) return WH_OK;
   WH_REQUIRE(n < (size_t)INT32_MAX, "AUC: %zu examples exceed 32-bit counters", n);
   SortBufs b;
@@ -191,6 +193,407 @@ int auc_launch(whContext* ctx, size_t n, const float* label, const float* xw, Ev
   WH_TRY(scan_and_apply<unsigned long long>(ctx, AucFlag{b}, AucApply{gpos, gneg}, n, sums, total));
   WH_LAUNCH(auc_groups_kernel, grid, 256, 0, ctx->stream, n, gpos, gneg, total, out);
   return WH_OK;
+}
+
+
+// ---- AUC in ONE launch: a thread-block cluster sorts and counts -------------------------------
+// 8 CTAs x 1024 threads (one cluster: hardware barrier + distributed shared memory) run the
+// whole AUC: build the keys, LSD radix sort them (8-bit digits, constant digits skipped), then
+// count pairs. Per pass each warp owns a contiguous run, so "rank among equal digits" is
+// (earlier CTAs) + (earlier warps) + (earlier rounds) + (lower lanes); CTA totals are exchanged
+// through DSMEM between two cluster barriers. The sort of 100k 33-bit keys costs ~10 cluster
+// barriers instead of ~30 kernel launches.
+namespace cg = cooperative_groups;
+constexpr int kAucCtas = 8, kAucThreads = 1024, kAucWarps = kAucThreads / 32;
+constexpr size_t kAucClusterMax = 1u << 20;
+
+__device__ __forceinline__ uint64_t auc_key(const float* __restrict__ label, const float* __restrict__ xw, size_t i) {
+  return ((uint64_t)ordered_bits(xw[i]) << 1) | (label[i] > 0 ? 1u : 0u);
+}
+
+__global__ void __cluster_dims__(kAucCtas, 1, 1) __launch_bounds__(kAucThreads)
+auc_cluster_kernel(size_t n, const float* __restrict__ label, const float* __restrict__ xw,
+                   uint64_t* bufA, uint64_t* bufB, uint32_t* gpos, uint32_t* gneg, EvalOut* out) {
+  cg::cluster_group cluster = cg::this_cluster();
+  const unsigned cta = cluster.block_rank();
+  const unsigned warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const unsigned lt = lanemask_lt();
+  __shared__ unsigned cnt[kAucWarps][256];
+  __shared__ unsigned tot[256];
+  __shared__ unsigned scan_tmp[8];
+  __shared__ unsigned long long s_bits[2];          // OR / AND of this CTA's keys
+  __shared__ unsigned w_pos[kAucWarps], w_head[kAucWarps];
+  __shared__ unsigned c_pos, c_head;                // this CTA's totals
+  __shared__ unsigned long long s_red[2][kAucWarps];
+
+  // each of the 256 warps of the cluster owns a contiguous, 32-aligned run of the array
+  const size_t chunk = ((n + kAucCtas * kAucWarps - 1) / (kAucCtas * kAucWarps) + 31) / 32 * 32;
+  const size_t gw = (size_t)cta * kAucWarps + warp;
+  const size_t lo = min(n, gw * chunk), hi = min(n, lo + chunk);
+
+  // ---- keys + which bytes vary
+  if (threadIdx.x == 0) { s_bits[0] = 0ull; s_bits[1] = ~0ull; }
+  __syncthreads();
+  {
+    unsigned long long o = 0ull, a = ~0ull;
+    for (size_t i = lo + lane; i < hi; i += 32) {
+      uint64_t k = auc_key(label, xw, i);
+      bufA[i] = k; o |= k; a &= k;
+    }
+#pragma unroll
+    for (int s = 16; s > 0; s >>= 1) { o |= __shfl_xor_sync(0xffffffffu, o, s); a &= __shfl_xor_sync(0xffffffffu, a, s); }
+    if (lane == 0) { atomicOr(&s_bits[0], o); atomicAnd(&s_bits[1], a); }
+  }
+  __threadfence();
+  cluster.sync();
+  unsigned long long diff;
+  {
+    unsigned long long o = 0ull, a = ~0ull;
+    for (int r = 0; r < kAucCtas; ++r) {
+      const unsigned long long* rb = cluster.map_shared_rank(s_bits, r);
+      o |= rb[0]; a &= rb[1];
+    }
+    diff = o ^ a;
+  }
+
+  // ---- LSD passes over the bytes that vary (33-bit keys: bytes 0..4)
+  uint64_t* src = bufA;
+  uint64_t* dst = bufB;
+  for (int byte = 0; byte < 5; ++byte) {
+    if (((diff >> (8 * byte)) & 0xffull) == 0) continue;   // same decision in every CTA
+    const int shift = 8 * byte;
+    for (int w = 0; w < kAucWarps; ++w) if (threadIdx.x < 256) cnt[w][threadIdx.x] = 0;
+    __syncthreads();
+    for (size_t i = lo + lane; i < hi + ((32 - ((hi - lo) & 31)) & 31); i += 32) {   // full rounds
+      const bool valid = i < hi;
+      unsigned d = valid ? (unsigned)((src[i] >> shift) & 0xff) : 0u;
+      unsigned peers = match_any_bits<8>(d, valid);
+      if (valid && (__ffs(peers) - 1) == (int)lane) cnt[warp][d] += __popc(peers);
+      __syncwarp();
+    }
+    __syncthreads();
+    if (threadIdx.x < 256) {
+      unsigned run = 0;
+      for (int w = 0; w < kAucWarps; ++w) { unsigned c = cnt[w][threadIdx.x]; cnt[w][threadIdx.x] = run; run += c; }
+      tot[threadIdx.x] = run;
+    }
+    cluster.sync();
+    {
+      unsigned before = 0, total = 0;
+      if (threadIdx.x < 256) {
+        for (int r = 0; r < kAucCtas; ++r) {
+          unsigned v = cluster.map_shared_rank(tot, r)[threadIdx.x];
+          if (r < (int)cta) before += v;
+          total += v;
+        }
+      }
+      // exclusive scan of `total` over the 256 digits (warps 0..7)
+      unsigned incl = total;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) { unsigned t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
+      if (warp < 8 && lane == 31) scan_tmp[warp] = incl;
+      __syncthreads();
+      if (threadIdx.x < 256) {
+        unsigned wbase = 0;
+        for (int w = 0; w < (int)warp; ++w) wbase += scan_tmp[w];
+        unsigned base = wbase + incl - total + before;
+        for (int w = 0; w < kAucWarps; ++w) cnt[w][threadIdx.x] += base;
+      }
+    }
+    __syncthreads();
+    for (size_t i = lo + lane; i < hi + ((32 - ((hi - lo) & 31)) & 31); i += 32) {
+      const bool valid = i < hi;
+      uint64_t k = valid ? src[i] : 0;
+      unsigned d = valid ? (unsigned)((k >> shift) & 0xff) : 0u;
+      unsigned peers = match_any_bits<8>(d, valid);
+      unsigned old = valid ? cnt[warp][d] : 0;
+      __syncwarp();
+      if (valid && (__ffs(peers) - 1) == (int)lane) cnt[warp][d] = old + __popc(peers);
+      __syncwarp();
+      if (valid) dst[old + __popc(peers & lt)] = k;
+    }
+    __threadfence();
+    cluster.sync();   // dst complete and visible; `tot` free for reuse
+    uint64_t* t = src; src = dst; dst = t;
+  }
+  const uint64_t* sorted = src;
+
+  // ---- pair counting. Sorted ascending by score, negatives first among equal scores.
+  // sweep 1: per-warp number of positives and of score-group heads
+  unsigned npos = 0, nhead = 0;
+  for (size_t i = lo + lane; i < hi + ((32 - ((hi - lo) & 31)) & 31); i += 32) {
+    const bool valid = i < hi;
+    uint64_t k = valid ? sorted[i] : 0;
+    uint64_t prev = (valid && i > 0) ? sorted[i - 1] : ~0ull;
+    bool head = valid && (i == 0 || (k >> 1) != (prev >> 1));
+    npos += __popc(__ballot_sync(0xffffffffu, valid && (k & 1)));
+    nhead += __popc(__ballot_sync(0xffffffffu, head));
+  }
+  if (lane == 0) { w_pos[warp] = npos; w_head[warp] = nhead; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    unsigned p = 0, h = 0;
+    for (int w = 0; w < kAucWarps; ++w) { unsigned a = w_pos[w], b = w_head[w]; w_pos[w] = p; w_head[w] = h; p += a; h += b; }
+    c_pos = p; c_head = h;
+  }
+  cluster.sync();
+  unsigned pos_before = w_pos[warp], head_before = w_head[warp], P = 0, G = 0;
+  for (int r = 0; r < kAucCtas; ++r) {
+    unsigned p = *cluster.map_shared_rank(&c_pos, r), h = *cluster.map_shared_rank(&c_head, r);
+    if (r < (int)cta) { pos_before += p; head_before += h; }
+    P += p; G += h;
+  }
+  // sweep 2: at every group head remember how many positives / negatives precede it
+  for (size_t i = lo + lane; i < hi + ((32 - ((hi - lo) & 31)) & 31); i += 32) {
+    const bool valid = i < hi;
+    uint64_t k = valid ? sorted[i] : 0;
+    uint64_t prev = (valid && i > 0) ? sorted[i - 1] : ~0ull;
+    bool head = valid && (i == 0 || (k >> 1) != (prev >> 1));
+    unsigned pb = __ballot_sync(0xffffffffu, valid && (k & 1)), hb = __ballot_sync(0xffffffffu, head);
+    if (head) {
+      unsigned g = head_before + __popc(hb & lt), pbefore = pos_before + __popc(pb & lt);
+      gpos[g] = pbefore;
+      gneg[g] = (unsigned)i - pbefore;
+    }
+    pos_before += __popc(pb); head_before += __popc(hb);
+  }
+  __threadfence();
+  cluster.sync();
+  // per group g: its negatives each see gpos[g] positives strictly below; ties = P_g * N_g
+  const unsigned N = (unsigned)n - P;
+  unsigned long long area = 0, ties = 0;
+  for (size_t g = (size_t)cta * kAucThreads + threadIdx.x; g < G; g += (size_t)kAucCtas * kAucThreads) {
+    unsigned p0 = gpos[g], n0 = gneg[g];
+    unsigned p1 = (g + 1 < G) ? gpos[g + 1] : P, n1 = (g + 1 < G) ? gneg[g + 1] : N;
+    area += (unsigned long long)(n1 - n0) * p0;
+    ties += (unsigned long long)(n1 - n0) * (p1 - p0);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) { area += __shfl_xor_sync(0xffffffffu, area, o); ties += __shfl_xor_sync(0xffffffffu, ties, o); }
+  if (lane == 0) { s_red[0][warp] = area; s_red[1][warp] = ties; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    unsigned long long a = 0, t = 0;
+    for (int w = 0; w < kAucWarps; ++w) { a += s_red[0][w]; t += s_red[1][w]; }
+    if (a) atomicAdd(&out->area_lo, a);
+    if (t) atomicAdd(&out->ties, t);
+    if (cta == 0) { out->npos = P; out->ngroups = G; }
+  }
+  cluster.sync();   // no CTA may exit while a peer can still read its shared memory
+}
+
+
+// Register-resident variant for the usual minibatch sizes (n <= 128 warps x 32 x R): every warp
+// keeps its run of keys in registers, so a pass costs one L2 round trip for the loads, one for
+// the scatter, and three cluster barriers.
+constexpr int kAucRegThreads = 512, kAucRegWarps = kAucRegThreads / 32;
+
+template <int R>
+__global__ void __cluster_dims__(kAucCtas, 1, 1) __launch_bounds__(kAucRegThreads)
+auc_cluster_reg_kernel(size_t n, const float* __restrict__ label, const float* __restrict__ xw,
+                       uint64_t* bufA, uint64_t* bufB, uint32_t* gpos, uint32_t* gneg, EvalOut* out) {
+  cg::cluster_group cluster = cg::this_cluster();
+  const unsigned cta = cluster.block_rank();
+  const unsigned warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const unsigned lt = lanemask_lt();
+  __shared__ unsigned cnt[kAucRegWarps][256];
+  __shared__ unsigned tot[256];
+  __shared__ unsigned scan_tmp[8];
+  __shared__ unsigned long long s_bits[2];
+  __shared__ unsigned w_pos[kAucRegWarps], w_head[kAucRegWarps];
+  __shared__ unsigned c_pos, c_head;
+  __shared__ unsigned long long s_red[2][kAucRegWarps];
+
+  const size_t chunk = 32 * R;
+  const size_t gw = (size_t)cta * kAucRegWarps + warp;
+  const size_t lo = min(n, gw * chunk), hi = min(n, lo + chunk);
+
+  uint64_t k[R];
+  if (threadIdx.x == 0) { s_bits[0] = 0ull; s_bits[1] = ~0ull; }
+  __syncthreads();
+  {
+    unsigned long long o = 0ull, a = ~0ull;
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const size_t i = lo + r * 32 + lane;
+      k[r] = 0;
+      if (i < hi) { k[r] = auc_key(label, xw, i); o |= k[r]; a &= k[r]; }
+    }
+#pragma unroll
+    for (int s = 16; s > 0; s >>= 1) { o |= __shfl_xor_sync(0xffffffffu, o, s); a &= __shfl_xor_sync(0xffffffffu, a, s); }
+    if (lane == 0) { atomicOr(&s_bits[0], o); atomicAnd(&s_bits[1], a); }
+  }
+  cluster.sync();
+  unsigned long long diff;
+  {
+    unsigned long long o = 0ull, a = ~0ull;
+    for (int r = 0; r < kAucCtas; ++r) {
+      const unsigned long long* rb = cluster.map_shared_rank(s_bits, r);
+      o |= rb[0]; a &= rb[1];
+    }
+    diff = o ^ a;
+  }
+
+  uint64_t* dst = bufA;
+  uint64_t* other = bufB;
+  bool in_regs = true;   // before the first active pass the keys exist only in registers
+  for (int byte = 0; byte < 5; ++byte) {
+    if (((diff >> (8 * byte)) & 0xffull) == 0) continue;
+    const int shift = 8 * byte;
+    if (!in_regs) {
+#pragma unroll
+      for (int r = 0; r < R; ++r) { const size_t i = lo + r * 32 + lane; k[r] = (i < hi) ? other[i] : 0; }
+    }
+    for (int w = 0; w < kAucRegWarps; ++w) if (threadIdx.x < 256) cnt[w][threadIdx.x] = 0;
+    __syncthreads();
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const bool valid = lo + r * 32 + lane < hi;
+      unsigned d = valid ? (unsigned)((k[r] >> shift) & 0xff) : 0u;
+      unsigned peers = match_any_bits<8>(d, valid);
+      if (valid && (__ffs(peers) - 1) == (int)lane) cnt[warp][d] += __popc(peers);
+      __syncwarp();
+    }
+    __syncthreads();
+    if (threadIdx.x < 256) {
+      unsigned run = 0;
+#pragma unroll
+      for (int w = 0; w < kAucRegWarps; ++w) { unsigned c = cnt[w][threadIdx.x]; cnt[w][threadIdx.x] = run; run += c; }
+      tot[threadIdx.x] = run;
+    }
+    cluster.sync();
+    {
+      unsigned before = 0, total = 0;
+      if (threadIdx.x < 256) {
+#pragma unroll
+        for (int r = 0; r < kAucCtas; ++r) {
+          unsigned v = cluster.map_shared_rank(tot, r)[threadIdx.x];
+          if (r < (int)cta) before += v;
+          total += v;
+        }
+      }
+      unsigned incl = total;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) { unsigned t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
+      if (warp < 8 && lane == 31) scan_tmp[warp] = incl;
+      __syncthreads();
+      if (threadIdx.x < 256) {
+        unsigned wbase = 0;
+        for (int w = 0; w < (int)warp; ++w) wbase += scan_tmp[w];
+        unsigned base = wbase + incl - total + before;
+#pragma unroll
+        for (int w = 0; w < kAucRegWarps; ++w) cnt[w][threadIdx.x] += base;
+      }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const bool valid = lo + r * 32 + lane < hi;
+      unsigned d = valid ? (unsigned)((k[r] >> shift) & 0xff) : 0u;
+      unsigned peers = match_any_bits<8>(d, valid);
+      unsigned old = valid ? cnt[warp][d] : 0;
+      __syncwarp();
+      if (valid && (__ffs(peers) - 1) == (int)lane) cnt[warp][d] = old + __popc(peers);
+      __syncwarp();
+      if (valid) dst[old + __popc(peers & lt)] = k[r];
+    }
+    __threadfence();
+    cluster.sync();
+    uint64_t* t = dst; dst = other; other = t;   // `other` now holds the pass's output
+    in_regs = false;
+  }
+  if (!in_regs) {
+#pragma unroll
+    for (int r = 0; r < R; ++r) { const size_t i = lo + r * 32 + lane; k[r] = (i < hi) ? other[i] : 0; }
+  }
+  // the key just before this warp's run (all keys equal if no pass ran: then nothing is a head but i == 0)
+  uint64_t before_run = (lo > 0 && lo < n) ? (in_regs ? k[0] : other[lo - 1]) : ~0ull;
+  if (in_regs && lo > 0) before_run = __shfl_sync(0xffffffffu, k[0], 0);
+
+  unsigned npos = 0, nhead = 0;
+  unsigned posb[R], headb[R];
+  uint64_t carry = before_run;
+#pragma unroll
+  for (int r = 0; r < R; ++r) {
+    const size_t i = lo + r * 32 + lane;
+    const bool valid = i < hi;
+    uint64_t prev = __shfl_up_sync(0xffffffffu, k[r], 1);
+    if (lane == 0) prev = carry;
+    carry = __shfl_sync(0xffffffffu, k[r], 31);
+    bool head = valid && (i == 0 || (k[r] >> 1) != (prev >> 1));
+    posb[r] = __ballot_sync(0xffffffffu, valid && (k[r] & 1));
+    headb[r] = __ballot_sync(0xffffffffu, head);
+    npos += __popc(posb[r]); nhead += __popc(headb[r]);
+  }
+  if (lane == 0) { w_pos[warp] = npos; w_head[warp] = nhead; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    unsigned p = 0, h = 0;
+    for (int w = 0; w < kAucRegWarps; ++w) { unsigned a = w_pos[w], b = w_head[w]; w_pos[w] = p; w_head[w] = h; p += a; h += b; }
+    c_pos = p; c_head = h;
+  }
+  cluster.sync();
+  unsigned pos_before = w_pos[warp], head_before = w_head[warp], P = 0, G = 0;
+  for (int r = 0; r < kAucCtas; ++r) {
+    unsigned p = *cluster.map_shared_rank(&c_pos, r), h = *cluster.map_shared_rank(&c_head, r);
+    if (r < (int)cta) { pos_before += p; head_before += h; }
+    P += p; G += h;
+  }
+#pragma unroll
+  for (int r = 0; r < R; ++r) {
+    const size_t i = lo + r * 32 + lane;
+    if ((headb[r] >> lane) & 1u) {
+      unsigned g = head_before + __popc(headb[r] & lt), pbefore = pos_before + __popc(posb[r] & lt);
+      gpos[g] = pbefore;
+      gneg[g] = (unsigned)i - pbefore;
+    }
+    pos_before += __popc(posb[r]); head_before += __popc(headb[r]);
+  }
+  __threadfence();
+  cluster.sync();
+  const unsigned N = (unsigned)n - P;
+  unsigned long long area = 0, ties = 0;
+  for (size_t g = (size_t)cta * kAucRegThreads + threadIdx.x; g < G; g += (size_t)kAucCtas * kAucRegThreads) {
+    unsigned p0 = gpos[g], n0 = gneg[g];
+    unsigned p1 = (g + 1 < G) ? gpos[g + 1] : P, n1 = (g + 1 < G) ? gneg[g + 1] : N;
+    area += (unsigned long long)(n1 - n0) * p0;
+    ties += (unsigned long long)(n1 - n0) * (p1 - p0);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) { area += __shfl_xor_sync(0xffffffffu, area, o); ties += __shfl_xor_sync(0xffffffffu, ties, o); }
+  if (lane == 0) { s_red[0][warp] = area; s_red[1][warp] = ties; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    unsigned long long a = 0, t = 0;
+    for (int w = 0; w < kAucRegWarps; ++w) { a += s_red[0][w]; t += s_red[1][w]; }
+    if (a) atomicAdd(&out->area_lo, a);
+    if (t) atomicAdd(&out->ties, t);
+    if (cta == 0) { out->npos = P; out->ngroups = G; }
+  }
+  cluster.sync();
+}
+
+int auc_launch(whContext* ctx, size_t n, const float* label, const float* xw, EvalOut* out) {
+  if (n == 0) return WH_OK;
+  WH_REQUIRE(n < (size_t)INT32_MAX, "AUC: %zu examples exceed 32-bit counters", n);
+  if (n <= kAucClusterMax) {
+    WH_TRY(ctx->sort_tmp[0].reserve(n * 8)); WH_TRY(ctx->sort_tmp[1].reserve(n * 8));
+    WH_TRY(ctx->sort_tmp[5].reserve((n + 1) * 8));
+    uint32_t* gpos = ctx->sort_tmp[5].as<uint32_t>();
+    const size_t warps = (size_t)kAucCtas * kAucRegWarps;
+#define WH_AUC_REG(R)                                                                                     \
+    if (n <= warps * 32 * (R)) {                                                                           \
+      WH_LAUNCH(auc_cluster_reg_kernel<R>, kAucCtas, kAucRegThreads, 0, ctx->stream, n, label, xw,         \
+                ctx->sort_tmp[0].as<uint64_t>(), ctx->sort_tmp[1].as<uint64_t>(), gpos, gpos + n + 1, out); \
+      return WH_OK;                                                                                        \
+    }
+    WH_AUC_REG(4) WH_AUC_REG(8) WH_AUC_REG(16) WH_AUC_REG(32)
+#undef WH_AUC_REG
+    WH_LAUNCH(auc_cluster_kernel, kAucCtas, kAucThreads, 0, ctx->stream, n, label, xw, ctx->sort_tmp[0].as<uint64_t>(),
+              ctx->sort_tmp[1].as<uint64_t>(), gpos, gpos + n + 1, out);
+    return WH_OK;
+  }
+  return auc_launch_multiblock(ctx, n, label, xw, out);
 }
 
 EvalHost eval_finish(const EvalOut& e, size_t rows) {
@@ -262,7 +665,7 @@ int wh_linear_loss(whContext* ctx, int loss, const whLocalBlock* D, int mem, con
     WH_TRY(out_buffer(ctx, ctx->stage[4], grad, U, mem, &dgrad));
     if (d.rows == 0) { if (U) WH_CUDA(cudaMemsetAsync(dgrad, 0, U * 4, ctx->stream)); }
     else WH_TRY(spmv_trans_times_launch(ctx, d.rows, d.nnz, d.offset, d.index, d.value, ddual, dgrad, U, acc, fs,
-                                        loss == WH_LOSS_SQUARE_HINGE ? -2.f : 1.f));
+                                        loss == WH_LOSS_SQUARE_HINGE ? -2.f : 1.f, acc_copies()));
     WH_TRY(out_commit(ctx, grad, dgrad, U, mem));
   }
   if (xw) WH_TRY(out_commit(ctx, xw, dxw, d.rows, mem));

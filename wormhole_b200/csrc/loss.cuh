@@ -21,6 +21,8 @@ struct EvalOut {
 int loss_forward_launch(whContext* ctx, int loss, size_t rows, const float* label, const float* xw,
                         float* dual, EvalOut* out, int want_logloss);
 int auc_launch(whContext* ctx, size_t rows, const float* label, const float* xw, EvalOut* out);
+// the multi-launch radix-sort variant (any size); auc_launch uses it beyond 2^20 examples
+int auc_launch_multiblock(whContext* ctx, size_t rows, const float* label, const float* xw, EvalOut* out);
 
 // Host-side closing arithmetic of binary_class_evaluation.h:36-38 and :49-50.
 struct EvalHost { double auc, auc_lo, auc_hi, acc, objv, logloss; };

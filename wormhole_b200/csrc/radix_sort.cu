@@ -35,8 +35,8 @@ sort_count_kernel(SortBufs b, int p, size_t n, unsigned nblocks) {
   for (int r = 0; r < kSortItems; ++r) {
     size_t idx = base + (size_t)warp * (kSortItems * 32) + r * 32 + lane;
     bool valid = idx < n;
-    unsigned d = valid ? (unsigned)((keys[idx] >> shift) & 0xff) : (256u + lane);
-    unsigned peers = __match_any_sync(0xffffffffu, d);
+    unsigned d = valid ? (unsigned)((keys[idx] >> shift) & 0xff) : 0u;
+    unsigned peers = match_any_bits<8>(d, valid);
     if (valid && (__ffs(peers) - 1) == (int)lane) atomicAdd(&hist[d], __popc(peers));
   }
   __syncthreads();
@@ -106,8 +106,8 @@ sort_scatter_kernel(SortBufs b, int p, size_t n, unsigned nblocks) {
 #pragma unroll
   for (int r = 0; r < kSortItems; ++r) {
     bool valid = (base + r * 32) < n;
-    unsigned d = valid ? (unsigned)((key[r] >> shift) & 0xff) : (256u + lane);
-    unsigned peers = __match_any_sync(0xffffffffu, d);
+    unsigned d = valid ? (unsigned)((key[r] >> shift) & 0xff) : 0u;
+    unsigned peers = match_any_bits<8>(d, valid);
     unsigned old = valid ? cnt[warp][d] : 0;
     __syncwarp();
     if (valid && (__ffs(peers) - 1) == (int)lane) cnt[warp][d] = old + __popc(peers);

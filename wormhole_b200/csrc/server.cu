@@ -69,15 +69,15 @@ template <bool FROM_ACC>
 __global__ void __launch_bounds__(256)
 server_push_kernel(HandleParams h, void* table, const uint64_t* __restrict__ keys, size_t n,
                    const unsigned* d_n, const float* __restrict__ grads, long long* acc,
-                   const FixedScale* fs, float mul, long long* counters) {
+                   const FixedScale* fs, float mul, long long* counters, unsigned copies, size_t stride) {
   if (d_n) n = *d_n;
   const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   int delta = 0, bad = 0;
   if (i < n) {
     float g;
     if (FROM_ACC) {
-      long long a = acc[i];
-      acc[i] = 0;
+      long long a = 0;
+      for (unsigned c = 0; c < copies; ++c) { a += acc[c * stride + i]; acc[c * stride + i] = 0; }
       g = (float)((double)a * fs->inv) * mul;
     } else {
       g = grads[i];
@@ -145,25 +145,25 @@ static HandleParams make_params(whServer* s, bool start_push) {
   return h;
 }
 
-int server_pull_launch(whServer* s, const uint64_t* keys, size_t n, const unsigned* d_n, float* vals) {
+int server_pull_launch(whServer* s, cudaStream_t stream, const uint64_t* keys, size_t n, const unsigned* d_n, float* vals) {
   if (n == 0) return WH_OK;
-  WH_LAUNCH(server_pull_kernel, (unsigned)div_up(n, 256), 256, 0, s->ctx->stream, s->algo, s->table.p,
+  WH_LAUNCH(server_pull_kernel, (unsigned)div_up(n, 256), 256, 0, stream, s->algo, s->table.p,
             s->key_begin, s->key_end, keys, n, d_n, vals, s->counters.as<long long>());
   return WH_OK;
 }
-int server_push_launch(whServer* s, const uint64_t* keys, size_t n, const unsigned* d_n, const float* grads) {
+int server_push_launch(whServer* s, cudaStream_t stream, const uint64_t* keys, size_t n, const unsigned* d_n, const float* grads) {
   HandleParams h = make_params(s, true);  // Start() runs even for an empty message
   if (n == 0) return WH_OK;
-  WH_LAUNCH(server_push_kernel<false>, (unsigned)div_up(n, 256), 256, 0, s->ctx->stream, h, s->table.p, keys, n,
-            d_n, grads, (long long*)nullptr, (const FixedScale*)nullptr, 1.f, s->counters.as<long long>());
+  WH_LAUNCH(server_push_kernel<false>, (unsigned)div_up(n, 256), 256, 0, stream, h, s->table.p, keys, n,
+            d_n, grads, (long long*)nullptr, (const FixedScale*)nullptr, 1.f, s->counters.as<long long>(), 1u, (size_t)0);
   return WH_OK;
 }
-int server_push_acc_launch(whServer* s, const uint64_t* keys, size_t n, const unsigned* d_n, long long* acc,
-                           const FixedScale* fs, float mul) {
+int server_push_acc_launch(whServer* s, cudaStream_t stream, const uint64_t* keys, size_t n, const unsigned* d_n, long long* acc,
+                           const FixedScale* fs, float mul, unsigned copies, size_t stride) {
   HandleParams h = make_params(s, true);
   if (n == 0) return WH_OK;
-  WH_LAUNCH(server_push_kernel<true>, (unsigned)div_up(n, 256), 256, 0, s->ctx->stream, h, s->table.p, keys, n,
-            d_n, (const float*)nullptr, acc, fs, mul, s->counters.as<long long>());
+  WH_LAUNCH(server_push_kernel<true>, (unsigned)div_up(n, 256), 256, 0, stream, h, s->table.p, keys, n,
+            d_n, (const float*)nullptr, acc, fs, mul, s->counters.as<long long>(), copies, stride);
   return WH_OK;
 }
 
@@ -227,7 +227,7 @@ int wh_server_pull(whServer* s, const uint64_t* keys, size_t n, int mem, float* 
   const uint64_t* dk; float* dv;
   WH_TRY(to_device(ctx, ctx->stage[0], keys, n, mem, &dk));
   WH_TRY(out_buffer(ctx, ctx->stage[1], vals, n, mem, &dv));
-  WH_TRY(server_pull_launch(s, dk, n, nullptr, dv));
+  WH_TRY(server_pull_launch(s, ctx->stream, dk, n, nullptr, dv));
   WH_TRY(out_commit(ctx, vals, dv, n, mem));
   if (mem == WH_HOST) return check_bad_keys(s, "wh_server_pull");
   return WH_OK;
@@ -240,7 +240,7 @@ int wh_server_push(whServer* s, const uint64_t* keys, size_t n, int mem, const f
   const uint64_t* dk; const float* dg;
   WH_TRY(to_device(ctx, ctx->stage[0], keys, n, mem, &dk));
   WH_TRY(to_device(ctx, ctx->stage[1], grads, n, mem, &dg));
-  WH_TRY(server_push_launch(s, dk, n, nullptr, dg));
+  WH_TRY(server_push_launch(s, ctx->stream, dk, n, nullptr, dg));
   if (mem == WH_HOST) return check_bad_keys(s, "wh_server_push");
   return WH_OK;
 }

@@ -17,10 +17,10 @@ struct whServer {
 
 namespace wh {
 // All take device pointers; d_n (may be NULL) overrides n with a count held on the device.
-int server_pull_launch(whServer* s, const uint64_t* keys, size_t n, const unsigned* d_n, float* vals);
-int server_push_launch(whServer* s, const uint64_t* keys, size_t n, const unsigned* d_n, const float* grads);
+int server_pull_launch(whServer* s, cudaStream_t stream, const uint64_t* keys, size_t n, const unsigned* d_n, float* vals);
+int server_push_launch(whServer* s, cudaStream_t stream, const uint64_t* keys, size_t n, const unsigned* d_n, const float* grads);
 // Gradients still in the fixed-point accumulator of the transposed product: converts, clears the
 // accumulator and applies the update in one pass (no fp32 gradient array in between).
-int server_push_acc_launch(whServer* s, const uint64_t* keys, size_t n, const unsigned* d_n, long long* acc,
-                           const FixedScale* fs, float mul);
+int server_push_acc_launch(whServer* s, cudaStream_t stream, const uint64_t* keys, size_t n, const unsigned* d_n, long long* acc,
+                           const FixedScale* fs, float mul, unsigned copies, size_t stride);
 }  // namespace wh

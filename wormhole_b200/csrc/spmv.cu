@@ -1,4 +1,6 @@
 // Pieces (2) and (5): SpMV::Times / TransTimes and SpMM::Times / TransTimes. See spmv.cuh.
+#include <stdlib.h>
+
 #include "spmv.cuh"
 
 namespace wh {
@@ -107,7 +109,7 @@ template <bool HAS_VAL>
 __global__ void __launch_bounds__(kRowsPerBlock)
 spmv_trans_kernel(size_t rows, const size_t* __restrict__ offset, const uint32_t* __restrict__ index,
                   const float* __restrict__ value, const float* __restrict__ x, long long* acc,
-                  const FixedScale* __restrict__ fs) {
+                  const FixedScale* __restrict__ fs, unsigned copies, size_t stride) {
   extern __shared__ __align__(16) unsigned char smem[];
   __shared__ size_t s_off[kRowsPerBlock + 1];
   uint32_t* s_idx = reinterpret_cast<uint32_t*>(smem);
@@ -117,6 +119,9 @@ spmv_trans_kernel(size_t rows, const size_t* __restrict__ offset, const uint32_t
   if (r >= rows) return;
   const size_t b = s_off[threadIdx.x], e = s_off[threadIdx.x + 1];
   if (b == e) return;
+  // One feature can sit in most rows of a minibatch; atomics on one address serialise in L2
+  // (~1.3 ns each, measured), so blocks spread over `copies` replicas of the accumulator array.
+  acc += (size_t)(blockIdx.x & (copies - 1)) * stride;
   const float xi = x[r];
   const float scale = fs->scale;
   if (staged) {
@@ -127,20 +132,69 @@ spmv_trans_kernel(size_t rows, const size_t* __restrict__ offset, const uint32_t
   }
 }
 
+
+// Same product, but lanes of a warp that hit the same output merge their terms first. With one
+// thread per row, step j of the loop has every lane on its row's j-th entry -- for field-aligned
+// data (one id per field per row) the same field, whose popular values then repeat across the
+// lanes: one atomic per distinct output per warp step instead of one per lane. Integer sums are
+// associative, so the result is bit-identical to the plain kernel's.
+template <bool HAS_VAL>
+__global__ void __launch_bounds__(kRowsPerBlock)
+spmv_trans_agg_kernel(size_t rows, const size_t* __restrict__ offset, const uint32_t* __restrict__ index,
+                      const float* __restrict__ value, const float* __restrict__ x, long long* acc,
+                      const FixedScale* __restrict__ fs, unsigned copies, size_t stride) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  __shared__ size_t s_off[kRowsPerBlock + 1];
+  uint32_t* s_idx = reinterpret_cast<uint32_t*>(smem);
+  float* s_val = reinterpret_cast<float*>(smem + sizeof(uint32_t) * kTileCap);
+  const bool staged = stage_rows<HAS_VAL>(rows, offset, index, value, s_off, s_idx, s_val);
+  const size_t r = (size_t)blockIdx.x * kRowsPerBlock + threadIdx.x;
+  const bool live = r < rows;
+  const size_t b = s_off[threadIdx.x], e = live ? s_off[threadIdx.x + 1] : b;
+  acc += (size_t)(blockIdx.x & (copies - 1)) * stride;
+  const float xi = live ? x[r] : 0.f;
+  const float scale = fs->scale;
+  const unsigned len = (unsigned)(e - b);
+  const unsigned maxlen = __reduce_max_sync(0xffffffffu, len);
+  const unsigned lb = (unsigned)(b - s_off[0]);
+  const unsigned lane = threadIdx.x & 31;
+  for (unsigned j = 0; j < maxlen; ++j) {
+    const bool valid = j < len;
+    unsigned c = 0;
+    float t = 0.f;
+    if (valid) {
+      c = staged ? s_idx[lb + j] : index[b + j];
+      t = HAS_VAL ? xi * (staged ? s_val[lb + j] : value[b + j]) : xi;
+    }
+    long long q = __float2ll_rn(t * scale);
+    const unsigned g = group_equal_keys(c, valid);
+    if (g != (1u << lane)) q = group_sum_i64(g, q);
+    if (valid && (__ffs(g) - 1) == (int)lane)
+      atomicAdd(reinterpret_cast<unsigned long long*>(acc + c), (unsigned long long)q);
+  }
+}
+
 // y = fixed-point sum back to fp32 (+ p*z for SpMM); clears the accumulator for the next call.
 __global__ void fixed_finish_kernel(long long* acc, size_t n, const FixedScale* __restrict__ fs,
                                     float p, const float* __restrict__ z, float* __restrict__ y,
-                                    float mul) {
+                                    float mul, unsigned copies, size_t stride) {
   const double inv = fs->inv;
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
-    long long a = acc[i];
-    acc[i] = 0;
+    long long a = 0;
+    for (unsigned c = 0; c < copies; ++c) { a += acc[c * stride + i]; acc[c * stride + i] = 0; }
     float s = (float)((double)a * inv) * mul;
     y[i] = z ? z[i] * p + s : s;
   }
 }
 
+unsigned acc_copies() {
+  static int c = -1;
+  if (c < 0) { const char* e = getenv("WH_ACC_COPIES"); c = e ? atoi(e) : 1; if (c < 1 || c > (int)kAccCopies || (c & (c - 1))) c = 1; }
+  return (unsigned)c;
+}
+
 int ensure_acc(whContext* ctx, size_t n, long long** out) {
+  n *= kAccCopies;
   if (ctx->acc.cap < n * sizeof(long long)) {
     WH_TRY(ctx->acc.reserve(n * sizeof(long long)));
     WH_CUDA(cudaMemsetAsync(ctx->acc.p, 0, ctx->acc.cap, ctx->stream));
@@ -162,27 +216,35 @@ static int fixed_prepare(whContext* ctx, FixedScale* fs, const float* x, size_t 
 // Scale selection + accumulation only; the caller converts (fixed_finish or the fused push).
 int spmv_trans_accumulate_launch(whContext* ctx, size_t rows, size_t nnz, const size_t* offset,
                                  const uint32_t* index, const float* value, const float* x,
-                                 long long* acc, FixedScale* fs) {
+                                 long long* acc, FixedScale* fs, unsigned copies, size_t stride) {
   WH_TRY(fixed_prepare(ctx, fs, x, rows, value, nnz));
   const unsigned grid = (unsigned)div_up(rows, kRowsPerBlock);
+  static int mode = -1;   // WH_TRANS_MODE=0: one atomic per entry; 1 (default): merged within the warp
+  if (mode < 0) { const char* e = getenv("WH_TRANS_MODE"); mode = e ? atoi(e) : 1; }
   if (value) {
     const size_t smem = kTileCap * 8;
     static bool attr = false;
-    if (!attr) { WH_CUDA(cudaFuncSetAttribute(spmv_trans_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); attr = true; }
-    WH_LAUNCH(spmv_trans_kernel<true>, grid, kRowsPerBlock, smem, ctx->stream, rows, offset, index, value, x, acc, fs);
+    if (!attr) {
+      WH_CUDA(cudaFuncSetAttribute(spmv_trans_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      WH_CUDA(cudaFuncSetAttribute(spmv_trans_agg_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      attr = true;
+    }
+    if (mode == 0) WH_LAUNCH(spmv_trans_kernel<true>, grid, kRowsPerBlock, smem, ctx->stream, rows, offset, index, value, x, acc, fs, copies, stride);
+    else WH_LAUNCH(spmv_trans_agg_kernel<true>, grid, kRowsPerBlock, smem, ctx->stream, rows, offset, index, value, x, acc, fs, copies, stride);
   } else {
-    WH_LAUNCH(spmv_trans_kernel<false>, grid, kRowsPerBlock, kTileCap * 4, ctx->stream, rows, offset, index, value, x, acc, fs);
+    if (mode == 0) WH_LAUNCH(spmv_trans_kernel<false>, grid, kRowsPerBlock, kTileCap * 4, ctx->stream, rows, offset, index, value, x, acc, fs, copies, stride);
+    else WH_LAUNCH(spmv_trans_agg_kernel<false>, grid, kRowsPerBlock, kTileCap * 4, ctx->stream, rows, offset, index, value, x, acc, fs, copies, stride);
   }
   return WH_OK;
 }
 
 int spmv_trans_times_launch(whContext* ctx, size_t rows, size_t nnz, const size_t* offset,
                             const uint32_t* index, const float* value, const float* x, float* y,
-                            size_t ysize, long long* acc, FixedScale* fs, float mul) {
+                            size_t ysize, long long* acc, FixedScale* fs, float mul, unsigned copies) {
   if (ysize == 0) return WH_OK;
-  WH_TRY(spmv_trans_accumulate_launch(ctx, rows, nnz, offset, index, value, x, acc, fs));
+  WH_TRY(spmv_trans_accumulate_launch(ctx, rows, nnz, offset, index, value, x, acc, fs, copies, ysize));
   const unsigned g2 = (unsigned)std::min<size_t>(div_up(ysize, 256), (size_t)ctx->num_sms * 8);
-  WH_LAUNCH(fixed_finish_kernel, g2, 256, 0, ctx->stream, acc, ysize, fs, 0.f, (const float*)nullptr, y, mul);
+  WH_LAUNCH(fixed_finish_kernel, g2, 256, 0, ctx->stream, acc, ysize, fs, 0.f, (const float*)nullptr, y, mul, copies, ysize);
   return WH_OK;
 }
 
@@ -239,7 +301,7 @@ int spmm_trans_times_launch(whContext* ctx, size_t rows, size_t nnz, const size_
   WH_TRY(fixed_prepare(ctx, fs, x, rows * dim, value, nnz));
   if (rows) WH_LAUNCH(spmm_trans_kernel, (unsigned)div_up(rows * dim, 256), 256, 0, ctx->stream, rows, offset, index, value, x, dim, acc, fs);
   const unsigned g2 = (unsigned)std::min<size_t>(div_up(ysize, 256), (size_t)ctx->num_sms * 8);
-  WH_LAUNCH(fixed_finish_kernel, g2, 256, 0, ctx->stream, acc, ysize, fs, p, (z && p != 0.f) ? z : (const float*)nullptr, y, 1.f);
+  WH_LAUNCH(fixed_finish_kernel, g2, 256, 0, ctx->stream, acc, ysize, fs, p, (z && p != 0.f) ? z : (const float*)nullptr, y, 1.f, 1u, ysize);
   return WH_OK;
 }
 
@@ -302,7 +364,7 @@ int wh_spmv_trans_times(whContext* ctx, const whLocalBlock* D, int mem, const fl
   WH_TRY(ensure_acc(ctx, ysize, &acc));
   FixedScale* fs = reinterpret_cast<FixedScale*>(ctx->small.as<char>() + 1024);
   if (d.rows == 0) { if (ysize) WH_CUDA(cudaMemsetAsync(dy, 0, ysize * 4, ctx->stream)); }
-  else WH_TRY(spmv_trans_times_launch(ctx, d.rows, d.nnz, d.offset, d.index, d.value, dx, dy, ysize, acc, fs, 1.f));
+  else WH_TRY(spmv_trans_times_launch(ctx, d.rows, d.nnz, d.offset, d.index, d.value, dx, dy, ysize, acc, fs, 1.f, acc_copies()));
   WH_TRY(out_commit(ctx, y, dy, ysize, mem));
   if (mem == WH_HOST) WH_CUDA(cudaStreamSynchronize(ctx->stream));
   return WH_OK;
@@ -429,5 +491,5 @@ extern "C" int wh_spmv_trans_times_static(void* cuda_stream, const whLocalBlock*
     return WH_OK;
   }
   return wh::spmv_trans_times_launch(&lc, D->size, nnz, D->offset, D->index, D->value, x, y, ysize,
-                                     sc->acc, &sc->fs, 1.f);
+                                     sc->acc, &sc->fs, 1.f, 1u);
 }

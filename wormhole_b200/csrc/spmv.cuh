@@ -18,6 +18,10 @@
 
 namespace wh {
 
+// replicas of the accumulator array that blocks spread their atomics over (power of two)
+constexpr unsigned kAccCopies = 8;   // upper bound; acc_copies() picks the count in use
+unsigned acc_copies();
+
 struct FixedScale {
   float scale;     // 2^e
   double inv;      // 2^-e
@@ -26,11 +30,11 @@ struct FixedScale {
 
 int spmv_times_launch(whContext* ctx, size_t rows, const size_t* offset, const uint32_t* index,
                       const float* value, const float* x, float* y);
-// acc: int64[ysize], all zero on entry and left all zero on exit. fs: device scratch.
+// acc: int64[copies * ysize], all zero on entry and left all zero on exit. fs: device scratch.
 // mul: exact post-scale of the result (the -2 of the squared hinge, learn/linear/loss.h:152-155).
 int spmv_trans_times_launch(whContext* ctx, size_t rows, size_t nnz, const size_t* offset,
                             const uint32_t* index, const float* value, const float* x, float* y,
-                            size_t ysize, long long* acc, FixedScale* fs, float mul);
+                            size_t ysize, long long* acc, FixedScale* fs, float mul, unsigned copies);
 int spmm_times_launch(whContext* ctx, size_t rows, const size_t* offset, const uint32_t* index,
                       const float* value, const float* x, float* y, int dim);
 int spmm_trans_times_launch(whContext* ctx, size_t rows, size_t nnz, const size_t* offset,
@@ -44,7 +48,7 @@ struct DevLocal {
   const float* label = nullptr;
 };
 int stage_local(whContext* ctx, const whLocalBlock* D, int mem, DevLocal* out);
-// zero-on-growth accumulator of the context
+// zero-on-growth accumulator of the context: kAccCopies * n entries
 int ensure_acc(whContext* ctx, size_t n, long long** out);
 
 #ifdef __CUDACC__

@@ -1,140 +1,264 @@
-// The per-minibatch pipeline of one worker stream: AsgdWorker::ProcessMinibatch
+// The per-minibatch pipeline of one worker: AsgdWorker::ProcessMinibatch
 // (learn/linear/async_sgd.h:240-288) with the server on the same GPU.
 //
 //   Localize (:246-247) -> ZPull (:287) -> Init = X w (:260) -> Evaluate (:261) ->
 //   CalcGrad = X^T dual (:269) -> ZPush (:277-278)
 //
-// Everything is enqueued on the context's stream without host round trips: the number of unique
-// keys U stays on the device (kernels read it there), and the only synchronisation is the final
-// read-back of the progress numbers.
+// Minibatches in flight. The reference keeps up to max_concurrency minibatches in flight per
+// worker (learn/solver/minibatch_solver.h:289-290,307-322). Here a worker owns `depth` lanes,
+// each with its own CUDA stream and scratch; wh_worker_submit() enqueues a whole minibatch on
+// the next lane without any host round trip (the number of unique keys stays on the device) and
+// wh_worker_wait() collects its progress numbers. Lanes overlap freely except where the model
+// is touched: the pull of minibatch t+1 waits (CUDA event) for the push of minibatch t, so
+// every pull sees all earlier pushes -- the same numbers as strictly sequential processing
+// (max_concurrency = 1, the configuration parity is judged in), while staging, localize and AUC
+// of neighbouring minibatches run side by side. AUC, which nothing downstream depends on, runs on
+// a side stream of the lane.
 #include "batch.cuh"
 #include "loss.cuh"
 #include "server.cuh"
 #include "spmv.cuh"
+
+namespace wh {
+int spmv_trans_accumulate_launch(whContext* ctx, size_t rows, size_t nnz, const size_t* offset,
+                                 const uint32_t* index, const float* value, const float* x,
+                                 long long* acc, FixedScale* fs, unsigned copies, size_t stride);
+constexpr int kMaxDepth = 8;
+
+struct Lane {
+  whContext cx;              // main chain: own stream + directory / scan / accumulator scratch
+  whContext ax;              // AUC side stream + its sort scratch
+  cudaEvent_t ev_fork = nullptr, ev_auc = nullptr, ev_done = nullptr;
+  DevBuf in_index, in_offset, in_value, in_label;   // staged host input
+  DevBuf uniq, index, w, xw, dual, scal;
+  char* pinned = nullptr;    // 512 B of the worker's pinned block
+  bool busy = false, train = false;
+  size_t rows = 0;
+  unsigned long long ticket = 0;
+};
+}  // namespace wh
 
 struct whWorker {
   whContext* ctx = nullptr;
   whServer* server = nullptr;
   int loss = WH_LOSS_LOGIT;
   uint64_t max_key = WH_NO_MAX_KEY;
+  int depth = 1;
+  wh::Lane lane[wh::kMaxDepth];
+  wh::PinnedBuf pinned;
+  cudaEvent_t ev_pushed = nullptr;   // completion of the most recent push (or evaluation pull)
+  bool have_pushed = false;
+  unsigned long long next_ticket = 1, next_wait = 1;
   long long seen_new_w = 0;
-  wh::DevBuf in_index, in_offset, in_value, in_label;   // staged host input
-  wh::DevBuf uniq, index, w, xw, dual, scal;
 };
-
-namespace wh {
-int spmv_trans_accumulate_launch(whContext* ctx, size_t rows, size_t nnz, const size_t* offset,
-                                 const uint32_t* index, const float* value, const float* x,
-                                 long long* acc, FixedScale* fs);
-}
 
 using namespace wh;
 
+static void lane_release(Lane& l) {
+  for (DevBuf* b : {&l.in_index, &l.in_offset, &l.in_value, &l.in_label, &l.uniq, &l.index, &l.w, &l.xw, &l.dual,
+                    &l.scal, &l.cx.directory, &l.cx.scan_tmp, &l.cx.acc, &l.cx.small, &l.ax.scan_tmp, &l.ax.small})
+    b->release();
+  for (auto& b : l.cx.sort_tmp) b.release();
+  for (auto& b : l.ax.sort_tmp) b.release();
+  for (auto& b : l.cx.stage) b.release();
+  for (auto& b : l.ax.stage) b.release();
+  for (auto e : l.cx.prof.ev) cudaEventDestroy(e);
+  if (l.ev_fork) cudaEventDestroy(l.ev_fork);
+  if (l.ev_auc) cudaEventDestroy(l.ev_auc);
+  if (l.ev_done) cudaEventDestroy(l.ev_done);
+  if (l.cx.stream && l.cx.own_stream) cudaStreamDestroy(l.cx.stream);
+  if (l.ax.stream) cudaStreamDestroy(l.ax.stream);
+}
+
+static int lane_init(whWorker* w, int i) {
+  Lane& l = w->lane[i];
+  whContext* ctx = w->ctx;
+  l.cx.device = l.ax.device = ctx->device;
+  l.cx.num_sms = l.ax.num_sms = ctx->num_sms;
+  l.cx.l2_bytes = l.ax.l2_bytes = ctx->l2_bytes;
+  if (i == 0) { l.cx.stream = ctx->stream; l.cx.own_stream = false; }   // lane 0 rides the context's stream
+  else { WH_CUDA(cudaStreamCreateWithFlags(&l.cx.stream, cudaStreamNonBlocking)); l.cx.own_stream = true; }
+  WH_CUDA(cudaStreamCreateWithFlags(&l.ax.stream, cudaStreamNonBlocking));
+  l.ax.own_stream = true;
+  WH_CUDA(cudaEventCreateWithFlags(&l.ev_fork, cudaEventDisableTiming));
+  WH_CUDA(cudaEventCreateWithFlags(&l.ev_auc, cudaEventDisableTiming));
+  WH_CUDA(cudaEventCreateWithFlags(&l.ev_done, cudaEventDisableTiming));
+  WH_TRY(l.scal.reserve(4096));
+  WH_TRY(l.cx.small.reserve(1 << 14));
+  WH_TRY(l.ax.small.reserve(1 << 14));
+  l.pinned = w->pinned.as<char>() + 512 * i;
+  return WH_OK;
+}
+
 extern "C" {
 
-int wh_worker_create(whContext* ctx, whServer* server, int loss, uint64_t max_key, whWorker** out) {
+int wh_worker_create_ex(whContext* ctx, whServer* server, int loss, uint64_t max_key, int depth, whWorker** out) {
   WH_REQUIRE(ctx && server && out, "wh_worker_create: NULL argument");
   WH_REQUIRE(server->ctx == ctx, "wh_worker_create: server lives on another context");
   WH_REQUIRE(loss == WH_LOSS_LOGIT || loss == WH_LOSS_SQUARE_HINGE,
              "wh_worker_create: unknown loss type %d (SQUARE is unimplemented in the reference, learn/linear/loss.h:163-180)", loss);
   WH_REQUIRE(max_key != 0, "wh_worker_create: max_key must be positive");
-  whWorker* w = new whWorker();
-  w->ctx = ctx; w->server = server; w->loss = loss; w->max_key = max_key;
+  WH_REQUIRE(depth >= 1 && depth <= kMaxDepth, "wh_worker_create: depth %d outside [1, %d]", depth, kMaxDepth);
   DeviceGuard g(ctx->device);
-  int r = w->scal.reserve(4096);
-  if (r != WH_OK) { delete w; return r; }
+  whWorker* w = new whWorker();
+  w->ctx = ctx; w->server = server; w->loss = loss; w->max_key = max_key; w->depth = depth;
+  int r = w->pinned.reserve(512 * kMaxDepth);
+  for (int i = 0; r == WH_OK && i < depth; ++i) r = lane_init(w, i);
+  if (r == WH_OK && cudaEventCreateWithFlags(&w->ev_pushed, cudaEventDisableTiming) != cudaSuccess) r = WH_ERR_CUDA;
+  if (r != WH_OK) { for (int i = 0; i < depth; ++i) lane_release(w->lane[i]); w->pinned.release(); delete w; return r; }
   *out = w;
   return WH_OK;
+}
+
+int wh_worker_create(whContext* ctx, whServer* server, int loss, uint64_t max_key, whWorker** out) {
+  return wh_worker_create_ex(ctx, server, loss, max_key, 1, out);
 }
 
 int wh_worker_destroy(whWorker* w) {
   if (!w) return WH_OK;
   DeviceGuard g(w->ctx->device);
-  cudaStreamSynchronize(w->ctx->stream);
-  for (wh::DevBuf* b : {&w->in_index, &w->in_offset, &w->in_value, &w->in_label, &w->uniq, &w->index, &w->w,
-                        &w->xw, &w->dual, &w->scal}) b->release();
+  for (int i = 0; i < w->depth; ++i) {
+    cudaStreamSynchronize(w->lane[i].cx.stream);
+    cudaStreamSynchronize(w->lane[i].ax.stream);
+  }
+  for (int i = 0; i < w->depth; ++i) lane_release(w->lane[i]);
+  if (w->ev_pushed) cudaEventDestroy(w->ev_pushed);
+  w->pinned.release();
   delete w;
+  return WH_OK;
+}
+
+int wh_worker_wait(whWorker* w, uint64_t ticket, double* prog);
+
+int wh_worker_submit(whWorker* w, const whRowBlock* blk, int mem, size_t nnz, int train, uint64_t* ticket) {
+  WH_REQUIRE(w && blk && ticket, "wh_worker_submit: NULL argument");
+  WH_REQUIRE(mem == WH_HOST || mem == WH_DEVICE, "wh_worker_submit: bad mem %d", mem);
+  whContext* ctx = w->ctx;
+  whServer* s = w->server;
+  DeviceGuard g(ctx->device);
+  const size_t rows = blk->size;
+  WH_REQUIRE(rows > 0, "wh_worker_submit: empty minibatch");
+  WH_REQUIRE(blk->offset && blk->index && blk->label, "wh_worker_submit: offset/index/label is NULL");
+  Lane& l = w->lane[w->next_ticket % w->depth];
+  if (l.busy) {  // the lane's previous minibatch has not been collected: results would be lost
+    set_error("wh_worker_submit: %d minibatches already in flight; wh_worker_wait the oldest first", w->depth);
+    return WH_ERR_INVALID;
+  }
+  whContext* cx = &l.cx;
+  cx->prof.on = ctx->prof.on;
+  size_t n = nnz;
+  if (mem == WH_HOST) n = blk->offset[rows];
+  else if (n == 0) {
+    WH_CUDA(cudaMemcpyAsync(l.pinned + 384, blk->offset + rows, sizeof(size_t), cudaMemcpyDeviceToHost, cx->stream));
+    WH_CUDA(cudaStreamSynchronize(cx->stream));
+    n = *reinterpret_cast<size_t*>(l.pinned + 384);
+  }
+  WH_REQUIRE(n > 0 && n < (size_t)UINT32_MAX, "wh_worker_submit: %zu entries", n);
+  const bool direct = direct_supported(w->max_key);
+
+  // stage the minibatch
+  const uint64_t* d_index; const size_t* d_offset; const float* d_value; const float* d_label;
+  WH_TRY(to_device(cx, l.in_index, blk->index, n, mem, &d_index));
+  WH_TRY(to_device(cx, l.in_offset, blk->offset, rows + 1, mem, &d_offset));
+  WH_TRY(to_device(cx, l.in_value, blk->value, n, mem, &d_value));
+  WH_TRY(to_device(cx, l.in_label, blk->label, rows, mem, &d_label));
+
+  const size_t ucap = (size_t)std::min<uint64_t>(n, w->max_key);
+  WH_TRY(l.uniq.reserve(ucap * 8)); WH_TRY(l.index.reserve(n * 4)); WH_TRY(l.w.reserve(ucap * 4));
+  WH_TRY(l.xw.reserve(rows * 4)); WH_TRY(l.dual.reserve(rows * 4));
+  unsigned* d_nuniq = l.scal.as<unsigned>();
+  FixedScale* fs = reinterpret_cast<FixedScale*>(l.scal.as<char>() + 256);
+  EvalOut* d_eval = reinterpret_cast<EvalOut*>(l.scal.as<char>() + 512);
+  long long* acc = nullptr;
+  if (train) WH_TRY(ensure_acc(cx, ucap, &acc));
+
+  WH_TRY(prof_begin(cx));
+  // Localize
+  LocInput in{d_index, n, make_xform(w->max_key)};
+  if (direct) WH_TRY(localize_direct(cx, in, l.uniq.as<uint64_t>(), nullptr, l.index.as<uint32_t>(), d_nuniq));
+  else WH_TRY(localize_sort(cx, in, l.uniq.as<uint64_t>(), nullptr, l.index.as<uint32_t>(), d_nuniq));
+  // ZPull: one Handle::Pull per unique key, after every earlier push
+  if (w->have_pushed) WH_CUDA(cudaStreamWaitEvent(cx->stream, w->ev_pushed, 0));
+  WH_TRY(server_pull_launch(s, cx->stream, l.uniq.as<uint64_t>(), ucap, d_nuniq, l.w.as<float>()));
+  WH_PROF(cx, "pull");
+  // Init: Xw
+  WH_CUDA(cudaMemsetAsync(l.xw.p, 0, rows * 4, cx->stream));
+  WH_TRY(spmv_times_launch(cx, rows, d_offset, l.index.as<uint32_t>(), d_value, l.w.as<float>(), l.xw.as<float>()));
+  WH_PROF(cx, "spmv_times");
+  // Evaluate (+ the dual of CalcGrad, which falls out of the same pass)
+  WH_TRY(loss_forward_launch(cx, w->loss, rows, d_label, l.xw.as<float>(), train ? l.dual.as<float>() : nullptr, d_eval, 0));
+  WH_PROF(cx, "loss_forward");
+  // AUC on the side stream (nothing downstream of it but the progress numbers)
+  WH_CUDA(cudaEventRecord(l.ev_fork, cx->stream));
+  WH_CUDA(cudaStreamWaitEvent(l.ax.stream, l.ev_fork, 0));
+  WH_TRY(auc_launch(&l.ax, rows, d_label, l.xw.as<float>(), d_eval));
+  WH_CUDA(cudaEventRecord(l.ev_auc, l.ax.stream));
+  if (train) {
+    // CalcGrad: X^T dual into the fixed-point accumulator; ZPush: convert + update in one pass
+    WH_TRY(spmv_trans_accumulate_launch(cx, rows, n, d_offset, l.index.as<uint32_t>(), d_value, l.dual.as<float>(), acc, fs, acc_copies(), ucap));
+    WH_PROF(cx, "spmv_trans");
+    WH_TRY(server_push_acc_launch(s, cx->stream, l.uniq.as<uint64_t>(), ucap, d_nuniq, acc, fs,
+                                  w->loss == WH_LOSS_SQUARE_HINGE ? -2.f : 1.f, acc_copies(), ucap));
+    WH_PROF(cx, "push");
+  }
+  WH_CUDA(cudaMemcpyAsync(l.pinned + 256, s->counters.p, 16, cudaMemcpyDeviceToHost, cx->stream));
+  WH_CUDA(cudaEventRecord(w->ev_pushed, cx->stream));
+  w->have_pushed = true;
+  // join the AUC branch, then the progress read-back
+  WH_CUDA(cudaStreamWaitEvent(cx->stream, l.ev_auc, 0));
+  if (cx->prof.on) WH_TRY(prof_mark(cx, "auc_tail"));
+  WH_CUDA(cudaMemcpyAsync(l.pinned, d_eval, sizeof(EvalOut), cudaMemcpyDeviceToHost, cx->stream));
+  WH_CUDA(cudaEventRecord(l.ev_done, cx->stream));
+  l.busy = true; l.train = train != 0; l.rows = rows;
+  l.ticket = w->next_ticket++;
+  *ticket = l.ticket;
+  return WH_OK;
+}
+
+int wh_worker_wait(whWorker* w, uint64_t ticket, double* prog) {
+  WH_REQUIRE(w && prog, "wh_worker_wait: NULL argument");
+  WH_REQUIRE(ticket == w->next_wait, "wh_worker_wait: tickets are collected in submission order (expected %llu, got %llu)",
+             (unsigned long long)w->next_wait, (unsigned long long)ticket);
+  whContext* ctx = w->ctx;
+  whServer* s = w->server;
+  DeviceGuard g(ctx->device);
+  Lane& l = w->lane[ticket % w->depth];
+  WH_REQUIRE(l.busy && l.ticket == ticket, "wh_worker_wait: ticket %llu is not in flight", (unsigned long long)ticket);
+  WH_CUDA(cudaEventSynchronize(l.ev_done));
+  l.busy = false;
+  w->next_wait++;
+  if (l.cx.prof.on) {
+    WH_TRY(prof_collect(&l.cx));
+    for (auto& a : l.cx.prof.acc) {   // fold the lane's numbers into the context's
+      Profiler::Acc* t = nullptr;
+      for (auto& x : ctx->prof.acc) if (x.name == a.name) { t = &x; break; }
+      if (!t) { ctx->prof.acc.push_back(Profiler::Acc()); t = &ctx->prof.acc.back(); t->name = a.name; }
+      t->ms += a.ms; t->count += a.count;
+    }
+    l.cx.prof.acc.clear();
+  }
+  const long long* cnt = reinterpret_cast<const long long*>(l.pinned + 256);
+  if (cnt[1]) {
+    WH_CUDA(cudaMemsetAsync(s->counters.as<long long>() + 1, 0, 8, l.cx.stream));
+    set_error("wh_worker: %lld keys fall outside the server's range [%llu, %llu)", cnt[1],
+              (unsigned long long)s->key_begin, (unsigned long long)s->key_end);
+    return WH_ERR_INVALID;
+  }
+  EvalHost h = eval_finish(*reinterpret_cast<const EvalOut*>(l.pinned), l.rows);
+  prog[0] = h.objv; prog[1] = h.acc; prog[2] = h.auc; prog[3] = 1; prog[4] = (double)l.rows;
+  prog[5] = (double)(cnt[0] - w->seen_new_w);
+  w->seen_new_w = cnt[0];
   return WH_OK;
 }
 
 int wh_worker_process_minibatch(whWorker* w, const whRowBlock* blk, int mem, int train, double* prog) {
   WH_REQUIRE(w && blk && prog, "wh_worker_process_minibatch: NULL argument");
-  WH_REQUIRE(mem == WH_HOST || mem == WH_DEVICE, "wh_worker_process_minibatch: bad mem %d", mem);
-  whContext* ctx = w->ctx;
-  whServer* s = w->server;
-  DeviceGuard g(ctx->device);
   for (int i = 0; i < 6; ++i) prog[i] = 0;
-  const size_t rows = blk->size;
-  if (rows == 0) return WH_OK;
-  WH_REQUIRE(blk->offset && blk->index && blk->label, "wh_worker_process_minibatch: offset/index/label is NULL");
-  size_t n;
-  if (mem == WH_HOST) n = blk->offset[rows];
-  else {
-    WH_CUDA(cudaMemcpyAsync(ctx->pinned.p, blk->offset + rows, sizeof(size_t), cudaMemcpyDeviceToHost, ctx->stream));
-    WH_CUDA(cudaStreamSynchronize(ctx->stream));
-    n = ctx->pinned.as<size_t>()[0];
-  }
-  WH_REQUIRE(n > 0 && n < (size_t)UINT32_MAX, "wh_worker_process_minibatch: %zu entries", n);
-  const bool direct = direct_supported(w->max_key);
-
-  // stage the minibatch
-  const uint64_t* d_index; const size_t* d_offset; const float* d_value; const float* d_label;
-  WH_TRY(to_device(ctx, w->in_index, blk->index, n, mem, &d_index));
-  WH_TRY(to_device(ctx, w->in_offset, blk->offset, rows + 1, mem, &d_offset));
-  WH_TRY(to_device(ctx, w->in_value, blk->value, n, mem, &d_value));
-  WH_TRY(to_device(ctx, w->in_label, blk->label, rows, mem, &d_label));
-
-  const size_t ucap = (size_t)std::min<uint64_t>(n, w->max_key);
-  WH_TRY(w->uniq.reserve(ucap * 8)); WH_TRY(w->index.reserve(n * 4)); WH_TRY(w->w.reserve(ucap * 4));
-  WH_TRY(w->xw.reserve(rows * 4)); WH_TRY(w->dual.reserve(rows * 4));
-  unsigned* d_nuniq = w->scal.as<unsigned>();
-  FixedScale* fs = reinterpret_cast<FixedScale*>(w->scal.as<char>() + 256);
-  EvalOut* d_eval = reinterpret_cast<EvalOut*>(w->scal.as<char>() + 512);
-
-  WH_TRY(prof_begin(ctx));
-  // Localize
-  LocInput in{d_index, n, make_xform(w->max_key)};
-  if (direct) WH_TRY(localize_direct(ctx, in, w->uniq.as<uint64_t>(), nullptr, w->index.as<uint32_t>(), d_nuniq));
-  else WH_TRY(localize_sort(ctx, in, w->uniq.as<uint64_t>(), nullptr, w->index.as<uint32_t>(), d_nuniq));
-  // ZPull: one Handle::Pull per unique key
-  WH_TRY(server_pull_launch(s, w->uniq.as<uint64_t>(), ucap, d_nuniq, w->w.as<float>()));
-  WH_PROF(ctx, "pull");
-  // Init: Xw
-  WH_CUDA(cudaMemsetAsync(w->xw.p, 0, rows * 4, ctx->stream));
-  WH_TRY(spmv_times_launch(ctx, rows, d_offset, w->index.as<uint32_t>(), d_value, w->w.as<float>(), w->xw.as<float>()));
-  WH_PROF(ctx, "spmv_times");
-  // Evaluate (+ the dual of CalcGrad, which falls out of the same pass)
-  WH_TRY(loss_forward_launch(ctx, w->loss, rows, d_label, w->xw.as<float>(), train ? w->dual.as<float>() : nullptr, d_eval, 0));
-  WH_PROF(ctx, "loss_forward");
-  WH_TRY(auc_launch(ctx, rows, d_label, w->xw.as<float>(), d_eval));
-  WH_PROF(ctx, "auc");
-  if (train) {
-    // CalcGrad: X^T dual into the fixed-point accumulator; ZPush: convert + update in one pass
-    long long* acc;
-    WH_TRY(ensure_acc(ctx, ucap, &acc));
-    WH_TRY(spmv_trans_accumulate_launch(ctx, rows, n, d_offset, w->index.as<uint32_t>(), d_value, w->dual.as<float>(), acc, fs));
-    WH_PROF(ctx, "spmv_trans");
-    WH_TRY(server_push_acc_launch(s, w->uniq.as<uint64_t>(), ucap, d_nuniq, acc, fs, w->loss == WH_LOSS_SQUARE_HINGE ? -2.f : 1.f));
-  }
-  if (train) WH_PROF(ctx, "push");
-  // progress read-back (the one synchronisation of the step)
-  char* pin = ctx->pinned.as<char>();
-  WH_CUDA(cudaMemcpyAsync(pin, d_eval, sizeof(EvalOut), cudaMemcpyDeviceToHost, ctx->stream));
-  WH_CUDA(cudaMemcpyAsync(pin + 256, s->counters.p, 16, cudaMemcpyDeviceToHost, ctx->stream));
-  WH_CUDA(cudaStreamSynchronize(ctx->stream));
-  if (ctx->prof.on) WH_TRY(prof_collect(ctx));
-  const long long* cnt = reinterpret_cast<const long long*>(pin + 256);
-  if (cnt[1]) {
-    WH_CUDA(cudaMemsetAsync(s->counters.as<long long>() + 1, 0, 8, ctx->stream));
-    set_error("wh_worker_process_minibatch: %lld keys fall outside the server's range [%llu, %llu)", cnt[1],
-              (unsigned long long)s->key_begin, (unsigned long long)s->key_end);
-    return WH_ERR_INVALID;
-  }
-  EvalHost h = eval_finish(*reinterpret_cast<const EvalOut*>(pin), rows);
-  prog[0] = h.objv; prog[1] = h.acc; prog[2] = h.auc; prog[3] = 1; prog[4] = (double)rows;
-  prog[5] = (double)(cnt[0] - w->seen_new_w);
-  w->seen_new_w = cnt[0];
-  return WH_OK;
+  if (blk->size == 0) return WH_OK;
+  WH_REQUIRE(w->next_wait == w->next_ticket, "wh_worker_process_minibatch: minibatches submitted earlier are still in flight");
+  uint64_t t = 0;
+  WH_TRY(wh_worker_submit(w, blk, mem, 0, train, &t));
+  return wh_worker_wait(w, t, prog);
 }
 
 }  // extern "C"
