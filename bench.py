@@ -107,34 +107,46 @@ def run_reference(args):
 
 # ------------------------------------------------------------------ our arm -------------------
 
-class ClockSampler(threading.Thread):
+class ClockSampler:
+    """One `nvidia-smi -lms` process streaming clocks and throttle reasons while the timed region runs."""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index):
-        super().__init__(daemon=True)
-        self.index, self.rows, self.stop_flag = index, [], False
+        self.proc, self.rows = None, []
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "20"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except Exception:
+            pass
 
-    def run(self):
-        while not self.stop_flag:
-            try:
-                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                                      "--format=csv,noheader,nounits"], capture_output=True, text=True,
-                                     timeout=5).stdout.strip()
-                if out:
-                    self.rows.append([x.strip() for x in out.split(",")])
-            except Exception:
-                pass
-            time.sleep(0.05)
+    def stop(self):
+        if self.proc is None:
+            return
+        self.proc.terminate()
+        try:
+            out, _ = self.proc.communicate(timeout=5)
+        except Exception:
+            self.proc.kill()
+            out = ""
+        self.rows = [[x.strip() for x in l.split(",")] for l in out.splitlines() if l.count(",") >= 6]
 
     def summary(self):
         sm = [float(r[0]) for r in self.rows if r[0].replace(".", "").isdigit()]
         mx = [float(r[1]) for r in self.rows if r[1].replace(".", "").isdigit()]
+        pw = [float(r[2]) for r in self.rows if r[2].replace(".", "").isdigit()]
+        # "under load": the samples whose power draw is in the upper half of what was seen
+        if pw and len(pw) == len(sm):
+            cut = (min(pw) + max(pw)) / 2
+            load = [c for c, p in zip(sm, pw) if p >= cut] or sm
+        else:
+            load = sm
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         reasons = sorted({n for r in self.rows for n, v in zip(names, r[3:7]) if v.lower().startswith("active")})
-        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": reasons, "samples": len(self.rows)}
+        return {"sm_mhz": float(np.median(load)) if load else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(self.rows), "power_w_max": max(pw) if pw else None}
 
 
 def segment_bytes(name, N, B, U, words):
@@ -234,18 +246,16 @@ def run_ours(args):
         return ms, wall, capi.kernel_launches() - l0
 
     sampler = ClockSampler(local)
-    sampler.start()
     ms_dev, _, launches = timed(dev, capi.WH_DEVICE, args.steps, args.warmup)
-    sampler.stop_flag = True
     ms_e2e, wall_e2e, _ = timed(host, capi.WH_HOST, args.steps, max(3, args.warmup // 2))
     ms_e2e = max(ms_e2e, 1e3 * wall_e2e)  # host-side staging is part of the end-to-end time
-    sampler.join(timeout=2)
+    sampler.stop()
 
     # per-kernel timing (CUDA events on the launching stream), separate pass
     lib = capi.lib()
     import ctypes as C
     lib.wh_profile_enable(ctx.h, 1)
-    for i in range(args.steps):
+    for i in range(min(args.steps, 50)):
         wk.process_minibatch(dev[i % pool_n], True, capi.WH_DEVICE)
     segs = []
     for i in range(lib.wh_profile_count(ctx.h)):
@@ -258,7 +268,10 @@ def run_ours(args):
         pk, pk_kind = peaks()
         words = MAX_KEY // 32
         total_seg = sum(ms for _, ms in segs) or 1.0
-        top = max(segs, key=lambda s: s[1]) if segs else ("none", 0.0)
+        # the dominant kernel of the minibatch's dependent chain; "auc_tail" is the join on the AUC side
+        # stream (idle time in this one-at-a-time pass, hidden behind the next minibatch otherwise)
+        chain = [x for x in segs if x[0] != "auc_tail"]
+        top = max(chain, key=lambda s: s[1]) if chain else ("none", 0.0)
         top_bytes = segment_bytes(top[0], N, rows, uniq_per_mb, words)
         achieved = top_bytes / (top[1] * 1e-3) / 1e9 if top[1] > 0 else 0.0
         bytes_per_ex = NNZ_PER_ROW * 8 + 12 + r * (8 + 2 * 12)
@@ -306,8 +319,8 @@ def run_ours(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=40)
-    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=400)
+    ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--rows", type=int, default=ROWS)
     ap.add_argument("--pool", type=int, default=8, help="distinct minibatches kept resident")

@@ -11,6 +11,8 @@
 //          twice and the directory (max_key/4 bytes, L2 resident for 2^24) is touched at random.
 //  sort    For arbitrary 64-bit keys (the reference's default: nibble-reversed ids). Stable LSD
 //          radix sort of (key, position), run-length heads -> ranks, scatter by position.
+#include <stdlib.h>
+
 #include "batch.cuh"
 #include "scan.cuh"
 
@@ -22,17 +24,45 @@ bool direct_supported(uint64_t max_key) { return max_key != 0 && max_key <= kDir
 // ------------------------------------------------------------------------------- direct --
 
 // learn/base/localizer.h:107-115 (key transform) fused with "is this key present".
+// Feature ids follow a power law: a few thousand keys make up most of the entries. Each block keeps
+// a direct-mapped cache of keys it has already marked in shared memory (exact: the full key is
+// compared), so repeats cost one shared-memory probe instead of an L2 load of the same hot word
+// from every SM. Misses test the directory word first; only new keys pay for an atomic.
+constexpr int kMarkCache = 8192;
+constexpr int kLocIlp = 4;   // entries per thread per trip: the loads of a trip are issued together
 __global__ void __launch_bounds__(256) loc_mark_kernel(const uint64_t* __restrict__ index, size_t n,
                                                        KeyXform xf, uint2* dir) {
+  __shared__ unsigned cache[kMarkCache];
+  for (int i = threadIdx.x; i < kMarkCache; i += blockDim.x) cache[i] = 0xffffffffu;
+  __syncthreads();
   const size_t stride = (size_t)gridDim.x * blockDim.x;
-  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-    uint64_t k = xf(ld_stream_u64(index + i));
-    unsigned* w = &dir[k >> 5].x;
-    unsigned bit = 1u << (k & 31);
-    // most ids repeat (power-law features): test first, only new keys pay for an atomic
-    // (an L2 load: a stale answer only costs a redundant atomic; a volatile load here compiles
-    // to LDG.STRONG.SYS and was 75 % of this kernel's stall samples)
-    if (!(__ldcg(w) & bit)) atomicOr(w, bit);
+  for (size_t i0 = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i0 < n; i0 += stride * kLocIlp) {
+    uint64_t k[kLocIlp];
+    unsigned word[kLocIlp];
+    bool probe[kLocIlp];
+#pragma unroll
+    for (int u = 0; u < kLocIlp; ++u) {
+      const size_t i = i0 + u * stride;
+      probe[u] = i < n;
+      k[u] = probe[u] ? ld_stream_u64(index + i) : 0;
+    }
+#pragma unroll
+    for (int u = 0; u < kLocIlp; ++u) {
+      k[u] = xf(k[u]);
+      const unsigned k32 = (unsigned)k[u];            // direct addressing: keys < 2^28
+      const unsigned slot = (k32 * 0x9E3779B1u) >> (32 - 13);
+      if (probe[u]) {
+        if (cache[slot] == k32) probe[u] = false;     // this block already marked it
+        else cache[slot] = k32;                       // racy by design: a lost update only costs a re-probe
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < kLocIlp; ++u) word[u] = probe[u] ? __ldcg(&dir[k[u] >> 5].x) : 0xffffffffu;
+#pragma unroll
+    for (int u = 0; u < kLocIlp; ++u) {
+      const unsigned bit = 1u << (k[u] & 31);
+      if (probe[u] && !(word[u] & bit)) atomicOr(&dir[k[u] >> 5].x, bit);
+    }
   }
 }
 
@@ -63,13 +93,128 @@ __global__ void __launch_bounds__(256) loc_rank_kernel(const uint64_t* __restric
                                                        KeyXform xf, const uint2* __restrict__ dir,
                                                        uint32_t* __restrict__ out, uint32_t* cnt) {
   const size_t stride = (size_t)gridDim.x * blockDim.x;
-  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-    uint64_t k = xf(ld_stream_u64(index + i));
-    uint2 e = __ldg(dir + (k >> 5));
-    unsigned r = e.y + __popc(e.x & ((1u << (k & 31)) - 1u));
-    out[i] = r;
-    if (cnt) atomicAdd(cnt + r, 1u);
+  for (size_t i0 = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i0 < n; i0 += stride * kLocIlp) {
+    uint64_t k[kLocIlp];
+    uint2 e[kLocIlp];
+#pragma unroll
+    for (int u = 0; u < kLocIlp; ++u) { const size_t i = i0 + u * stride; k[u] = i < n ? ld_stream_u64(index + i) : 0; }
+#pragma unroll
+    for (int u = 0; u < kLocIlp; ++u) { k[u] = xf(k[u]); e[u] = __ldg(dir + (k[u] >> 5)); }
+#pragma unroll
+    for (int u = 0; u < kLocIlp; ++u) {
+      const size_t i = i0 + u * stride;
+      if (i < n) {
+        const unsigned r = e[u].y + __popc(e[u].x & ((1u << (k[u] & 31)) - 1u));
+        out[i] = r;
+        if (cnt) atomicAdd(cnt + r, 1u);
+      }
+    }
   }
+}
+
+
+// ---- the same two kernels, fed by TMA ------------------------------------------------------------
+// Tiles of 2048 ids (16 KB) stream into a 4-deep ring of shared-memory stages by cp.async.bulk; the
+// block's threads take 8 ids each from the stage that has landed. Requires a 16-byte aligned id
+// array (the plain kernels above remain for the unaligned case).
+constexpr int kTileIds = 2048, kTmaStages = 4, kTmaThreads = 256, kPerThread = kTileIds / kTmaThreads;
+
+struct IdRing {
+  uint64_t* stage;   // kTmaStages * kTileIds ids
+  uint64_t* bar;     // kTmaStages mbarriers
+  const uint64_t* index;
+  size_t n, ntiles;
+  __device__ unsigned tile_ids(size_t t) const { return (unsigned)min((size_t)kTileIds, n - t * kTileIds); }
+  __device__ void issue(size_t t, int s) const {   // one thread
+    const unsigned bytes = (tile_ids(t) * 8u + 15u) & ~15u;   // the array is padded to 16 B by the caller's contract
+    fence_proxy_async();
+    mbar_expect_tx(bar + s, bytes);
+    bulk_g2s(stage + (size_t)s * kTileIds, index + t * kTileIds, bytes, bar + s);
+  }
+};
+
+template <typename F>
+__device__ __forceinline__ void id_ring_run(const uint64_t* index, size_t n, uint64_t* stage, uint64_t* bar, F body) {
+  IdRing r{stage, bar, index, n, (n + kTileIds - 1) / kTileIds};
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < kTmaStages; ++s) mbar_init(bar + s, 1);
+    mbar_init_fence();
+  }
+  __syncthreads();
+  if (threadIdx.x == 0)
+    for (int s = 0; s < kTmaStages; ++s) {
+      const size_t t = blockIdx.x + (size_t)s * gridDim.x;
+      if (t < r.ntiles) r.issue(t, s);
+    }
+  size_t k = 0;
+  for (size_t t = blockIdx.x; t < r.ntiles; t += gridDim.x, ++k) {
+    const int s = (int)(k % kTmaStages);
+    mbar_wait(bar + s, (unsigned)((k / kTmaStages) & 1));
+    body(stage + (size_t)s * kTileIds, t * kTileIds, r.tile_ids(t));
+    __syncthreads();   // every thread is done with stage s
+    const size_t nt = t + (size_t)kTmaStages * gridDim.x;
+    if (threadIdx.x == 0 && nt < r.ntiles) r.issue(nt, s);
+  }
+}
+
+__global__ void __launch_bounds__(kTmaThreads) loc_mark_tma_kernel(const uint64_t* __restrict__ index, size_t n,
+                                                                   KeyXform xf, uint2* dir) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  uint64_t* stage = reinterpret_cast<uint64_t*>(smem);
+  uint64_t* bar = stage + (size_t)kTmaStages * kTileIds;
+  unsigned* cache = reinterpret_cast<unsigned*>(bar + kTmaStages);
+  for (int i = threadIdx.x; i < kMarkCache; i += blockDim.x) cache[i] = 0xffffffffu;
+  id_ring_run(index, n, stage, bar, [&](const uint64_t* ids, size_t, unsigned cnt) {
+    uint64_t k[kPerThread];
+    unsigned word[kPerThread];
+    bool probe[kPerThread];
+#pragma unroll
+    for (int u = 0; u < kPerThread; ++u) {
+      const unsigned j = u * kTmaThreads + threadIdx.x;
+      probe[u] = j < cnt;
+      k[u] = xf(probe[u] ? ids[j] : 0);
+      const unsigned k32 = (unsigned)k[u];
+      const unsigned slot = (k32 * 0x9E3779B1u) >> (32 - 13);
+      if (probe[u]) {
+        if (cache[slot] == k32) probe[u] = false;
+        else cache[slot] = k32;
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < kPerThread; ++u) word[u] = probe[u] ? __ldcg(&dir[k[u] >> 5].x) : 0xffffffffu;
+#pragma unroll
+    for (int u = 0; u < kPerThread; ++u) {
+      const unsigned bit = 1u << (k[u] & 31);
+      if (probe[u] && !(word[u] & bit)) atomicOr(&dir[k[u] >> 5].x, bit);
+    }
+  });
+}
+
+__global__ void __launch_bounds__(kTmaThreads) loc_rank_tma_kernel(const uint64_t* __restrict__ index, size_t n,
+                                                                   KeyXform xf, const uint2* __restrict__ dir,
+                                                                   uint32_t* __restrict__ out, uint32_t* cnt_out) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  uint64_t* stage = reinterpret_cast<uint64_t*>(smem);
+  uint64_t* bar = stage + (size_t)kTmaStages * kTileIds;
+  id_ring_run(index, n, stage, bar, [&](const uint64_t* ids, size_t base, unsigned cnt) {
+    uint64_t k[kPerThread];
+    uint2 e[kPerThread];
+#pragma unroll
+    for (int u = 0; u < kPerThread; ++u) {
+      const unsigned j = u * kTmaThreads + threadIdx.x;
+      k[u] = xf(j < cnt ? ids[j] : 0);
+      e[u] = __ldg(dir + (k[u] >> 5));
+    }
+#pragma unroll
+    for (int u = 0; u < kPerThread; ++u) {
+      const unsigned j = u * kTmaThreads + threadIdx.x;
+      if (j < cnt) {
+        const unsigned r = e[u].y + __popc(e[u].x & ((1u << (k[u] & 31)) - 1u));
+        out[base + j] = r;
+        if (cnt_out) atomicAdd(cnt_out + r, 1u);
+      }
+    }
+  });
 }
 
 int localize_direct(whContext* ctx, const LocInput& in, uint64_t* d_uniq, uint32_t* d_cnt,
@@ -85,14 +230,26 @@ int localize_direct(whContext* ctx, const LocInput& in, uint64_t* d_uniq, uint32
   WH_TRY(ctx->scan_tmp.reserve(div_up(words, kScanTile) * sizeof(unsigned) + 256));
   const size_t n = in.nnz;
   const unsigned grid = (unsigned)std::min<size_t>(div_up(n ? n : 1, 256), (size_t)ctx->num_sms * 16);
-  if (n) {
+  // TMA path: 16-byte aligned ids whose last tile may be read up to the next 16-byte boundary
+  // (an even entry count, or at least one spare id of readable memory behind an odd one)
+  const bool tma = n >= 2 && ((uintptr_t)in.index & 15) == 0 && (n & 1) == 0;
+  const size_t ring_smem = (size_t)kTmaStages * kTileIds * 8 + kTmaStages * 8;
+  static bool attr = false;
+  if (!attr) {
+    WH_CUDA(cudaFuncSetAttribute(loc_mark_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(ring_smem + kMarkCache * 4)));
+    WH_CUDA(cudaFuncSetAttribute(loc_rank_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ring_smem));
+    attr = true;
+  }
+  const unsigned tgrid = (unsigned)std::min<size_t>(div_up(n ? n : 1, kTileIds), (size_t)ctx->num_sms * 2);
+  if (n && tma) {
+    WH_LAUNCH(loc_mark_tma_kernel, tgrid, kTmaThreads, ring_smem + kMarkCache * 4, ctx->stream, in.index, n, in.xf, dir);
+  } else if (n) {
     // Warm-up slice: a small launch sets the presence bits of the features that occur in most
-    // rows. Without it every thread of the first full wave sees such a bit still clear and they
-    // all fire an atomicOr at the same word (~64k same-address atomics, ~40 us, measured).
+    // rows, so that the full wave does not fire one atomicOr per thread at the same words.
     const size_t head = std::min<size_t>(n, 65536);
     WH_LAUNCH(loc_mark_kernel, (unsigned)div_up(head, 1024), 256, 0, ctx->stream, in.index, head, in.xf, dir);
     if (n > head) {
-      const unsigned g2 = (unsigned)std::min<size_t>(div_up(n - head, 256), (size_t)ctx->num_sms * 16);
+      const unsigned g2 = (unsigned)std::min<size_t>(div_up(n - head, 256), (size_t)ctx->num_sms * 6);
       WH_LAUNCH(loc_mark_kernel, g2, 256, 0, ctx->stream, in.index + head, n - head, in.xf, dir);
     }
   }
@@ -101,7 +258,12 @@ int localize_direct(whContext* ctx, const LocInput& in, uint64_t* d_uniq, uint32
                         d_nuniq));
   WH_PROF(ctx, "loc_dir_scan");
   if (d_cnt && n) WH_CUDA(cudaMemsetAsync(d_cnt, 0, std::min<uint64_t>(n, in.xf.max_key) * 4, ctx->stream));
-  if (n) WH_LAUNCH(loc_rank_kernel, grid, 256, 0, ctx->stream, in.index, n, in.xf, dir, d_index, d_cnt);
+  // (rank stays on the plain kernel: its ids come back from L2, and more resident threads keep more
+  //  directory gathers in flight -- measured 20 us vs 24 us for the TMA-fed variant)
+  static int rank_tma = -1;
+  if (rank_tma < 0) { const char* e = getenv("WH_RANK_TMA"); rank_tma = e ? atoi(e) : 0; }
+  if (n && tma && rank_tma) WH_LAUNCH(loc_rank_tma_kernel, tgrid, kTmaThreads, ring_smem, ctx->stream, in.index, n, in.xf, dir, d_index, d_cnt);
+  else if (n) WH_LAUNCH(loc_rank_kernel, grid, 256, 0, ctx->stream, in.index, n, in.xf, dir, d_index, d_cnt);
   WH_PROF(ctx, "loc_rank");
   WH_CUDA(cudaMemsetAsync(dir, 0, words * sizeof(uint2), ctx->stream));
   WH_PROF(ctx, "loc_dir_clear");

@@ -189,7 +189,7 @@ __global__ void fixed_finish_kernel(long long* acc, size_t n, const FixedScale* 
 
 unsigned acc_copies() {
   static int c = -1;
-  if (c < 0) { const char* e = getenv("WH_ACC_COPIES"); c = e ? atoi(e) : 1; if (c < 1 || c > (int)kAccCopies || (c & (c - 1))) c = 1; }
+  if (c < 0) { const char* e = getenv("WH_ACC_COPIES"); c = e ? atoi(e) : (int)kAccCopies; if (c < 1 || c > (int)kAccCopies || (c & (c - 1))) c = 1; }
   return (unsigned)c;
 }
 
@@ -219,8 +219,9 @@ int spmv_trans_accumulate_launch(whContext* ctx, size_t rows, size_t nnz, const 
                                  long long* acc, FixedScale* fs, unsigned copies, size_t stride) {
   WH_TRY(fixed_prepare(ctx, fs, x, rows, value, nnz));
   const unsigned grid = (unsigned)div_up(rows, kRowsPerBlock);
-  static int mode = -1;   // WH_TRANS_MODE=0: one atomic per entry; 1 (default): merged within the warp
-  if (mode < 0) { const char* e = getenv("WH_TRANS_MODE"); mode = e ? atoi(e) : 1; }
+  static int mode = -1;   // WH_TRANS_MODE=0 (default): one atomic per entry; 1: merged within the warp first
+                          // (measured: merging costs more instructions than the atomics it saves)
+  if (mode < 0) { const char* e = getenv("WH_TRANS_MODE"); mode = e ? atoi(e) : 0; }
   if (value) {
     const size_t smem = kTileCap * 8;
     static bool attr = false;
