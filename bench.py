@@ -73,7 +73,9 @@ def run_reference(args):
     import multiprocessing as mp
     cores = os.cpu_count() or 2
     nprocs = args.cpu_procs or max(1, min(32, cores // 2))
-    rows = args.rows
+    # bounded sample: ~3.5 us per row per worker on this class of host; keep K+W steps within ~2 minutes
+    budget_rows = int(120.0 / max(1, args.steps + args.warmup) / 3.5e-6)
+    rows = max(2000, min(args.rows, budget_rows))
     ctx = mp.get_context("fork")
     q, go = ctx.Queue(), ctx.Event()
     procs = [ctx.Process(target=_ref_worker, args=(r, nprocs, rows, 2, args.warmup, args.steps, q, go))
@@ -97,8 +99,9 @@ def run_reference(args):
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": WORKLOAD, "rows_per_minibatch": rows, "max_key": MAX_KEY},
         "cpu_baseline": {"value": value, "unit": "examples/s", "cores": min(cores, 2 * nprocs), "kind": kind,
-                         "sample": "%d worker+server pairs x %d minibatches of %d rows each, nt=2 per worker, "
-                                   "in-process ps stand-in (no network, no serialisation)" % (nprocs, args.steps, rows)},
+                         "sample": "%d worker+server pairs x %d minibatches of %d rows each (of the workload's %d), "
+                                   "nt=2 per worker, in-process ps stand-in (no network, no serialisation)"
+                                   % (nprocs, args.steps, rows, args.rows)},
         "e2e": {"value": value, "unit": "examples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -186,8 +189,19 @@ def run_ours(args):
     ctx = capi.Context(local)
     stream = torch.cuda.current_stream()
     ctx.set_stream(stream.cuda_stream)
-    srv = capi.Server(ctx, capi.ALGO_FTRL, FTRL["l1"], FTRL["l2"], FTRL["eta"], FTRL["beta"], 0, MAX_KEY)
-    wk = capi.Worker(ctx, srv, capi.LOSS_LOGIT, MAX_KEY, depth=args.depth)
+    if world == 1:
+        # worker and the one server share the GPU: the lane pipeline (minibatches in flight)
+        srv = capi.Server(ctx, capi.ALGO_FTRL, FTRL["l1"], FTRL["l2"], FTRL["eta"], FTRL["beta"], 0, MAX_KEY)
+        wk = capi.Worker(ctx, srv, capi.LOSS_LOGIT, MAX_KEY, depth=args.depth)
+        sw = None
+    else:
+        # rank g = worker g + server g of the key range [g*max_key/S, (g+1)*max_key/S): pull and push
+        # are all-to-all-v exchanges over NCCL (wormhole_b200/dist.py); weak scaling, one stream per GPU
+        from wormhole_b200.dist import DeviceShard, ShardedKV, ShardedWorker, key_range
+        kb, ke = key_range(rank, world, MAX_KEY)
+        srv = capi.Server(ctx, capi.ALGO_FTRL, FTRL["l1"], FTRL["l2"], FTRL["eta"], FTRL["beta"], kb, ke)
+        wk = capi.Worker(ctx, None, capi.LOSS_LOGIT, MAX_KEY)
+        sw = ShardedWorker(ctx, wk, ShardedKV(DeviceShard(srv), MAX_KEY, device=torch.device("cuda", local)))
 
     # the minibatch pool: distinct minibatches, resident in HBM (device leg) and in pinned host
     # memory (e2e leg). pool_n x ~32 MB exceeds the 126 MB L2, so every step streams from HBM.
@@ -215,6 +229,10 @@ def run_ours(args):
         torch.cuda.synchronize()
 
     def run(blocks, mem, first, count):
+        if sw is not None:
+            for i in range(count):
+                sw.process_minibatch(blocks[(first + i) % pool_n], True, mem, N)
+            return
         # up to `depth` minibatches in flight (conf max_concurrency); every one is waited for,
         # so its progress numbers have reached the host before the clock stops
         pending = []
@@ -256,7 +274,10 @@ def run_ours(args):
     import ctypes as C
     lib.wh_profile_enable(ctx.h, 1)
     for i in range(min(args.steps, 50)):
-        wk.process_minibatch(dev[i % pool_n], True, capi.WH_DEVICE)
+        if sw is not None:
+            sw.process_minibatch(dev[i % pool_n], True, capi.WH_DEVICE, N)
+        else:
+            wk.process_minibatch(dev[i % pool_n], True, capi.WH_DEVICE)
     segs = []
     for i in range(lib.wh_profile_count(ctx.h)):
         name, ms, cnt = C.c_char_p(), C.c_double(), C.c_uint64()
@@ -285,7 +306,7 @@ def run_ours(args):
                        "max_key": MAX_KEY, "unique_keys_per_row_r": round(r, 4), "pool_minibatches": pool_n,
                        "l2_policy": "inputs larger than L2 (pool of %d distinct minibatches, %.0f MB)" % (pool_n, pool_n * N * 8 / 1e6),
                        "parallelism": "key-range shards x%d" % world, "updater": FTRL,
-                       "minibatches_in_flight": args.depth},
+                       "minibatches_in_flight": args.depth if world == 1 else 1},
             "e2e": {"value": e2e, "unit": "examples/s", "h2d_bytes_per_step": N * 8 + (rows + 1) * 8 + rows * 4,
                     "d2h_bytes_per_step": 72 + 16},
             "gpu_launches": int(launches),
@@ -298,8 +319,13 @@ def run_ours(args):
                               "frac_of_hbm_peak": value * bytes_per_ex / (world * pk["hbm_gbs"] * 1e9)},
             "kernel_ms": {n: round(ms, 5) for n, ms in segs},
         }
-        # CPU baseline on a bounded sample (subprocess: no fork after CUDA init)
+        # CPU baseline on a bounded sample, rank 0 at N=1 only (subprocess: no fork after CUDA init)
+        if world > 1:
+            line["cpu_baseline"] = None
+            print(json.dumps(line))
         try:
+            if world > 1:
+                raise StopIteration
             out = subprocess.run([sys.executable, os.path.abspath(__file__), "--impl", "reference", "--steps", "4",
                                   "--warmup", "1", "--cpu-procs", "1", "--rows", str(rows)],
                                  capture_output=True, text=True, timeout=600,
@@ -307,10 +333,13 @@ def run_ours(args):
             cb = json.loads(out.stdout.strip().splitlines()[-1])["cpu_baseline"]
             cb["sample"] = "1 worker (nt=2) + 1 server, 4 minibatches of %d rows after 1 warm-up" % rows
             line["cpu_baseline"] = cb
+        except StopIteration:
+            pass
         except Exception as e:  # noqa: BLE001
             line["cpu_baseline"] = {"value": None, "unit": "examples/s", "cores": 0, "kind": "port",
                                     "sample": "failed: %r" % (e,)}
-        print(json.dumps(line))
+        if world == 1:
+            print(json.dumps(line))
     wk.close(); srv.close(); ctx.close()
     if world > 1:
         dist.destroy_process_group()

@@ -222,6 +222,16 @@ WH_API int wh_worker_destroy(whWorker* w);
 WH_API int wh_worker_submit(whWorker* w, const whRowBlock* blk, int mem, size_t nnz, int train,
                             uint64_t* ticket);
 WH_API int wh_worker_wait(whWorker* w, uint64_t ticket, double* prog);
+/* ProcessMinibatch split at its ZPull (learn/linear/async_sgd.h:246-247 | :257-286), for servers that
+ * live elsewhere (key-range shards on other GPUs; the worker may be created with server = NULL).
+ * begin: Localize; returns a DEVICE pointer to the ascending unique keys (valid until the next begin)
+ * and their number -- the key list of the pull and the push. Synchronises once to learn the number.
+ * finish: the pull callback -- Init / Evaluate / CalcGrad with the pulled weights d_weights[num_uniq]
+ * (device); the gradient is written to d_grads[num_uniq] (device) for the caller's push. prog[5]
+ * (new_w) is 0: the servers own that count (wh_server_nnz_w). */
+WH_API int wh_worker_begin(whWorker* w, const whRowBlock* blk, int mem, size_t nnz, const uint64_t** d_uniq,
+                           size_t* num_uniq);
+WH_API int wh_worker_finish(whWorker* w, const float* d_weights, float* d_grads, int train, double* prog);
 /* AsgdWorker::ProcessMinibatch, learn/linear/async_sgd.h:240-288: Localize -> ZPull ->
  * Init/Evaluate -> (train) CalcGrad -> ZPush. prog[6] as in wh_linear_loss, with new_w the
  * server's change of |w|_0 for this minibatch. Synchronous. */

@@ -1,0 +1,112 @@
+"""Key-range sharded push/pull on real GPUs. World size 1 runs on any GPU box; the 2-rank NCCL test
+needs two GPUs (gpurun --gpus 2) and is skipped otherwise."""
+import os
+import socket
+
+import numpy as np
+import pytest
+
+from tests.util import random_block
+
+pytestmark = pytest.mark.gpu
+MAX_KEY = 1000003
+L1, L2, ETA, BETA = 0.5, 0.1, 0.1, 1.0
+STEPS = 4
+
+
+def minibatch(rank, step):
+    rng = np.random.default_rng(7000 + 1000 * rank + step)
+    return random_block(rng, 3000, 12, 20000, with_value=(step % 2 == 1), empty_rows=False)
+
+
+def test_world_of_one_equals_the_local_worker():
+    """begin -> ShardedKV.pull -> finish -> ShardedKV.push on one GPU == wh_worker_process_minibatch."""
+    import torch
+    from wormhole_b200 import capi
+    from wormhole_b200.dist import DeviceShard, ShardedKV, ShardedWorker
+    ctx = capi.Context(0)
+    ctx.set_stream(torch.cuda.current_stream().cuda_stream)
+    states, progs = [], []
+    for sharded in (False, True):
+        srv = capi.Server(ctx, capi.ALGO_FTRL, L1, L2, ETA, BETA, 0, MAX_KEY)
+        if sharded:
+            wk = capi.Worker(ctx, None, capi.LOSS_LOGIT, MAX_KEY)
+            sw = ShardedWorker(ctx, wk, ShardedKV(DeviceShard(srv), MAX_KEY, device=torch.device("cuda", 0)))
+            out = [sw.process_minibatch(minibatch(0, s)) for s in range(STEPS)]
+        else:
+            wk = capi.Worker(ctx, srv, capi.LOSS_LOGIT, MAX_KEY)
+            out = [wk.process_minibatch(minibatch(0, s)) for s in range(STEPS)]
+        torch.cuda.synchronize()
+        keys = np.unique(np.concatenate([minibatch(0, s).index % np.uint64(MAX_KEY) for s in range(STEPS)]))
+        states.append(srv.get_state(keys)); progs.append(np.array(out)[:, :5])
+        nnz = srv.nnz_w()
+        assert nnz == int((states[-1][0] != 0).sum())
+        wk.close(); srv.close()
+    assert np.array_equal(progs[0], progs[1])
+    for a, b in zip(states[0], states[1]):
+        assert np.array_equal(a, b)
+    ctx.close()
+
+
+def _rank_main(rank, world, port_no, out_dir):
+    import torch
+    import torch.distributed as dist
+    from wormhole_b200 import capi
+    from wormhole_b200.dist import DeviceShard, ShardedKV, ShardedWorker, key_range
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port_no)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    ctx = capi.Context(rank)
+    ctx.set_stream(torch.cuda.current_stream().cuda_stream)
+    b, e = key_range(rank, world, MAX_KEY)
+    srv = capi.Server(ctx, capi.ALGO_SGD, L1, L2, ETA, BETA, b, e)
+    wk = capi.Worker(ctx, None, capi.LOSS_LOGIT, MAX_KEY)
+    sw = ShardedWorker(ctx, wk, ShardedKV(DeviceShard(srv), MAX_KEY, device=torch.device("cuda", rank)))
+    for s in range(STEPS):
+        sw.process_minibatch(minibatch(rank, s))
+    torch.cuda.synchronize()
+    keys = np.arange(b, e, dtype=np.uint64)
+    w, _, _ = srv.get_state(keys)
+    np.savez(os.path.join(out_dir, "rank%d.npz" % rank), w=w, t=srv.sgd_t(), nnz=srv.nnz_w())
+    dist.barrier()
+    wk.close(); srv.close(); ctx.close()
+    dist.destroy_process_group()
+
+
+def test_two_gpus_match_the_cpu_simulation(tmp_path):
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs (gpurun --gpus 2)")
+    import torch.multiprocessing as mp
+    from oracle import oracle as O
+    from wormhole_b200.dist import key_range
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port_no = s.getsockname()[1]; s.close()
+    world = 2
+    mp.spawn(_rank_main, args=(world, port_no, str(tmp_path)), nprocs=world, join=True)
+    # the same message order on the CPU checker: pulls see the model as of the previous step, pushes
+    # are applied per (owner, source) in ascending source order, SGD's t advances per push message
+    chk = O.best()
+    bounds = [key_range(r, world, MAX_KEY)[0] for r in range(world)] + [MAX_KEY]
+    W = np.zeros(MAX_KEY, np.float32)
+    t = [1] * world
+    for step in range(STEPS):
+        msgs = []
+        for r in range(world):
+            D = chk.localize(minibatch(r, step), MAX_KEY)
+            keys = D.uniq.astype(np.int64)
+            _, grad = chk.linear_loss(O.LOSS_LOGIT, D, W[keys], 2)
+            msgs.append((keys, grad, np.searchsorted(keys, bounds)))
+        for sidx in range(world):
+            for r in range(world):
+                keys, grad, cut = msgs[r]
+                sl = slice(cut[sidx], cut[sidx + 1])
+                w = W[keys[sl]].copy()
+                _, t[sidx] = chk.handle_push(O.ALGO_SGD, L1, L2, ETA, BETA, grad[sl].copy(), w, None, None, t[sidx])
+                W[keys[sl]] = w
+    for r in range(world):
+        got = np.load(tmp_path / ("rank%d.npz" % r))
+        b, e = key_range(r, world, MAX_KEY)
+        assert int(got["t"]) == t[r] == 1 + world * STEPS
+        err = np.abs(got["w"] - W[b:e])
+        assert np.all(err <= 1e-5 * np.maximum(np.abs(W[b:e]), 1.0)), float(err.max())
+        assert abs(int(got["nnz"]) - int((W[b:e] != 0).sum())) <= 2

@@ -242,6 +242,14 @@ class Server:
         keys, grads = np.ascontiguousarray(keys, np.uint64), _f32(grads)
         _check(lib().wh_server_push(self.h, _ptr(keys), C.c_size_t(len(keys)), C.c_int(WH_HOST), _ptr(grads)))
 
+    def pull_dev(self, keys_ptr, n, vals_ptr):
+        """One pull message on device arrays (addresses); enqueued on the context's stream."""
+        _check(lib().wh_server_pull(self.h, C.c_void_p(keys_ptr), C.c_size_t(n), C.c_int(WH_DEVICE), C.c_void_p(vals_ptr)))
+
+    def push_dev(self, keys_ptr, n, grads_ptr):
+        """One push message on device arrays (addresses); enqueued on the context's stream."""
+        _check(lib().wh_server_push(self.h, C.c_void_p(keys_ptr), C.c_size_t(n), C.c_int(WH_DEVICE), C.c_void_p(grads_ptr)))
+
     def nnz_w(self):
         out = C.c_int64()
         _check(lib().wh_server_nnz_w(self.h, C.byref(out)))
@@ -274,8 +282,8 @@ class Worker:
     def __init__(self, ctx, server, loss=LOSS_LOGIT, max_key=NO_MAX_KEY, depth=1):
         self.ctx, self.server, self.depth = ctx, server, depth
         self.h = C.c_void_p()
-        _check(lib().wh_worker_create_ex(ctx.h, server.h, C.c_int(loss), C.c_uint64(max_key), C.c_int(depth),
-                                         C.byref(self.h)))
+        _check(lib().wh_worker_create_ex(ctx.h, server.h if server is not None else None, C.c_int(loss),
+                                         C.c_uint64(max_key), C.c_int(depth), C.byref(self.h)))
         self._keep = {}
 
     def submit(self, blk, train=True, mem=WH_HOST, nnz=0):
@@ -285,6 +293,20 @@ class Worker:
         _check(lib().wh_worker_submit(self.h, C.byref(rb), C.c_int(mem), C.c_size_t(nnz), C.c_int(train), C.byref(t)))
         self._keep[t.value] = blk   # the arrays must outlive the call
         return t.value
+
+    def begin(self, blk, mem=WH_HOST, nnz=0):
+        """First half of ProcessMinibatch (Localize). -> (device address of the ascending unique keys, U)."""
+        p, n = C.c_void_p(), C.c_size_t()
+        rb = _rowblock(blk)
+        self._begun = blk
+        _check(lib().wh_worker_begin(self.h, C.byref(rb), C.c_int(mem), C.c_size_t(nnz), C.byref(p), C.byref(n)))
+        return (p.value or 0), n.value
+
+    def finish(self, weights_ptr, grads_ptr, train=True):
+        """The pull callback: Init / Evaluate / CalcGrad with the pulled weights (device addresses)."""
+        prog = np.zeros(6, np.float64)
+        _check(lib().wh_worker_finish(self.h, C.c_void_p(weights_ptr), C.c_void_p(grads_ptr), C.c_int(train), _ptr(prog)))
+        return prog
 
     def wait(self, ticket):
         prog = np.zeros(6, np.float64)

@@ -239,6 +239,15 @@ int spmv_trans_accumulate_launch(whContext* ctx, size_t rows, size_t nnz, const 
   return WH_OK;
 }
 
+// Accumulator -> fp32 (and clear), for callers that ran spmv_trans_accumulate_launch themselves.
+int fixed_finish_launch(whContext* ctx, long long* acc, size_t n, const FixedScale* fs, float* y, float mul,
+                        unsigned copies, size_t stride) {
+  if (n == 0) return WH_OK;
+  const unsigned g2 = (unsigned)std::min<size_t>(div_up(n, 256), (size_t)ctx->num_sms * 8);
+  WH_LAUNCH(fixed_finish_kernel, g2, 256, 0, ctx->stream, acc, n, fs, 0.f, (const float*)nullptr, y, mul, copies, stride);
+  return WH_OK;
+}
+
 int spmv_trans_times_launch(whContext* ctx, size_t rows, size_t nnz, const size_t* offset,
                             const uint32_t* index, const float* value, const float* x, float* y,
                             size_t ysize, long long* acc, FixedScale* fs, float mul, unsigned copies) {

@@ -23,6 +23,8 @@ namespace wh {
 int spmv_trans_accumulate_launch(whContext* ctx, size_t rows, size_t nnz, const size_t* offset,
                                  const uint32_t* index, const float* value, const float* x,
                                  long long* acc, FixedScale* fs, unsigned copies, size_t stride);
+int fixed_finish_launch(whContext* ctx, long long* acc, size_t n, const FixedScale* fs, float* y, float mul,
+                        unsigned copies, size_t stride);
 constexpr int kMaxDepth = 8;
 
 struct Lane {
@@ -34,6 +36,10 @@ struct Lane {
   char* pinned = nullptr;    // 512 B of the worker's pinned block
   bool busy = false, train = false;
   size_t rows = 0;
+  // state between wh_worker_begin and wh_worker_finish
+  bool b_open = false;
+  size_t b_nnz = 0, b_nuniq = 0;
+  const size_t* b_offset = nullptr; const float* b_value = nullptr; const float* b_label = nullptr;
   unsigned long long ticket = 0;
 };
 }  // namespace wh
@@ -93,8 +99,8 @@ static int lane_init(whWorker* w, int i) {
 extern "C" {
 
 int wh_worker_create_ex(whContext* ctx, whServer* server, int loss, uint64_t max_key, int depth, whWorker** out) {
-  WH_REQUIRE(ctx && server && out, "wh_worker_create: NULL argument");
-  WH_REQUIRE(server->ctx == ctx, "wh_worker_create: server lives on another context");
+  WH_REQUIRE(ctx && out, "wh_worker_create: NULL argument");
+  WH_REQUIRE(server == nullptr || server->ctx == ctx, "wh_worker_create: server lives on another context");
   WH_REQUIRE(loss == WH_LOSS_LOGIT || loss == WH_LOSS_SQUARE_HINGE,
              "wh_worker_create: unknown loss type %d (SQUARE is unimplemented in the reference, learn/linear/loss.h:163-180)", loss);
   WH_REQUIRE(max_key != 0, "wh_worker_create: max_key must be positive");
@@ -132,6 +138,7 @@ int wh_worker_wait(whWorker* w, uint64_t ticket, double* prog);
 
 int wh_worker_submit(whWorker* w, const whRowBlock* blk, int mem, size_t nnz, int train, uint64_t* ticket) {
   WH_REQUIRE(w && blk && ticket, "wh_worker_submit: NULL argument");
+  WH_REQUIRE(w->server != nullptr, "wh_worker_submit: this worker has no local server; use wh_worker_begin / wh_worker_finish");
   WH_REQUIRE(mem == WH_HOST || mem == WH_DEVICE, "wh_worker_submit: bad mem %d", mem);
   whContext* ctx = w->ctx;
   whServer* s = w->server;
@@ -251,11 +258,105 @@ int wh_worker_wait(whWorker* w, uint64_t ticket, double* prog) {
   return WH_OK;
 }
 
+// ---- the two halves around ZPull, for servers that live elsewhere (key-range shards on other GPUs)
+
+int wh_worker_begin(whWorker* w, const whRowBlock* blk, int mem, size_t nnz, const uint64_t** d_uniq, size_t* num_uniq) {
+  WH_REQUIRE(w && blk && d_uniq && num_uniq, "wh_worker_begin: NULL argument");
+  WH_REQUIRE(mem == WH_HOST || mem == WH_DEVICE, "wh_worker_begin: bad mem %d", mem);
+  WH_REQUIRE(w->next_wait == w->next_ticket, "wh_worker_begin: minibatches submitted earlier are still in flight");
+  whContext* ctx = w->ctx;
+  DeviceGuard g(ctx->device);
+  const size_t rows = blk->size;
+  WH_REQUIRE(rows > 0 && blk->offset && blk->index && blk->label, "wh_worker_begin: empty block or NULL offset/index/label");
+  Lane& l = w->lane[0];
+  whContext* cx = &l.cx;
+  cx->prof.on = ctx->prof.on;
+  size_t n = nnz;
+  if (mem == WH_HOST) n = blk->offset[rows];
+  else if (n == 0) {
+    WH_CUDA(cudaMemcpyAsync(l.pinned + 384, blk->offset + rows, sizeof(size_t), cudaMemcpyDeviceToHost, cx->stream));
+    WH_CUDA(cudaStreamSynchronize(cx->stream));
+    n = *reinterpret_cast<size_t*>(l.pinned + 384);
+  }
+  WH_REQUIRE(n > 0 && n < (size_t)UINT32_MAX, "wh_worker_begin: %zu entries", n);
+  const uint64_t* d_index;
+  WH_TRY(to_device(cx, l.in_index, blk->index, n, mem, &d_index));
+  WH_TRY(to_device(cx, l.in_offset, blk->offset, rows + 1, mem, &l.b_offset));
+  WH_TRY(to_device(cx, l.in_value, blk->value, n, mem, &l.b_value));
+  WH_TRY(to_device(cx, l.in_label, blk->label, rows, mem, &l.b_label));
+  const size_t ucap = (size_t)std::min<uint64_t>(n, w->max_key);
+  WH_TRY(l.uniq.reserve(ucap * 8)); WH_TRY(l.index.reserve(n * 4));
+  WH_TRY(l.xw.reserve(rows * 4)); WH_TRY(l.dual.reserve(rows * 4));
+  unsigned* d_nuniq = l.scal.as<unsigned>();
+  WH_TRY(prof_begin(cx));
+  LocInput in{d_index, n, make_xform(w->max_key)};
+  if (direct_supported(w->max_key)) WH_TRY(localize_direct(cx, in, l.uniq.as<uint64_t>(), nullptr, l.index.as<uint32_t>(), d_nuniq));
+  else WH_TRY(localize_sort(cx, in, l.uniq.as<uint64_t>(), nullptr, l.index.as<uint32_t>(), d_nuniq));
+  WH_CUDA(cudaMemcpyAsync(l.pinned + 384, d_nuniq, sizeof(unsigned), cudaMemcpyDeviceToHost, cx->stream));
+  WH_CUDA(cudaStreamSynchronize(cx->stream));
+  l.rows = rows; l.b_nnz = n; l.b_nuniq = *reinterpret_cast<unsigned*>(l.pinned + 384);
+  l.b_open = true;
+  *d_uniq = l.uniq.as<uint64_t>();
+  *num_uniq = l.b_nuniq;
+  return WH_OK;
+}
+
+int wh_worker_finish(whWorker* w, const float* d_weights, float* d_grads, int train, double* prog) {
+  WH_REQUIRE(w && prog, "wh_worker_finish: NULL argument");
+  Lane& l = w->lane[0];
+  WH_REQUIRE(l.b_open, "wh_worker_finish: no minibatch begun");
+  WH_REQUIRE(l.b_nuniq == 0 || d_weights, "wh_worker_finish: weights are NULL");
+  WH_REQUIRE(!train || l.b_nuniq == 0 || d_grads, "wh_worker_finish: training needs a gradient buffer");
+  whContext* ctx = w->ctx;
+  DeviceGuard g(ctx->device);
+  whContext* cx = &l.cx;
+  l.b_open = false;
+  const size_t rows = l.rows, n = l.b_nnz, U = l.b_nuniq;
+  FixedScale* fs = reinterpret_cast<FixedScale*>(l.scal.as<char>() + 256);
+  EvalOut* d_eval = reinterpret_cast<EvalOut*>(l.scal.as<char>() + 512);
+  WH_PROF(cx, "pull_exchange");
+  WH_CUDA(cudaMemsetAsync(l.xw.p, 0, rows * 4, cx->stream));
+  WH_TRY(spmv_times_launch(cx, rows, l.b_offset, l.index.as<uint32_t>(), l.b_value, d_weights, l.xw.as<float>()));
+  WH_PROF(cx, "spmv_times");
+  WH_TRY(loss_forward_launch(cx, w->loss, rows, l.b_label, l.xw.as<float>(), train ? l.dual.as<float>() : nullptr, d_eval, 0));
+  WH_PROF(cx, "loss_forward");
+  WH_CUDA(cudaEventRecord(l.ev_fork, cx->stream));
+  WH_CUDA(cudaStreamWaitEvent(l.ax.stream, l.ev_fork, 0));
+  WH_TRY(auc_launch(&l.ax, rows, l.b_label, l.xw.as<float>(), d_eval));
+  WH_CUDA(cudaEventRecord(l.ev_auc, l.ax.stream));
+  if (train && U) {
+    long long* acc;
+    WH_TRY(ensure_acc(cx, U, &acc));
+    WH_TRY(spmv_trans_accumulate_launch(cx, rows, n, l.b_offset, l.index.as<uint32_t>(), l.b_value, l.dual.as<float>(), acc, fs, acc_copies(), U));
+    WH_PROF(cx, "spmv_trans");
+    WH_TRY(fixed_finish_launch(cx, acc, U, fs, d_grads, w->loss == WH_LOSS_SQUARE_HINGE ? -2.f : 1.f, acc_copies(), U));
+    WH_PROF(cx, "grad_finish");
+  }
+  WH_CUDA(cudaStreamWaitEvent(cx->stream, l.ev_auc, 0));
+  if (cx->prof.on) WH_TRY(prof_mark(cx, "auc_tail"));
+  WH_CUDA(cudaMemcpyAsync(l.pinned, d_eval, sizeof(EvalOut), cudaMemcpyDeviceToHost, cx->stream));
+  WH_CUDA(cudaStreamSynchronize(cx->stream));
+  if (cx->prof.on) {
+    WH_TRY(prof_collect(cx));
+    for (auto& a : cx->prof.acc) {
+      Profiler::Acc* t = nullptr;
+      for (auto& x : ctx->prof.acc) if (x.name == a.name) { t = &x; break; }
+      if (!t) { ctx->prof.acc.push_back(Profiler::Acc()); t = &ctx->prof.acc.back(); t->name = a.name; }
+      t->ms += a.ms; t->count += a.count;
+    }
+    cx->prof.acc.clear();
+  }
+  EvalHost h = eval_finish(*reinterpret_cast<const EvalOut*>(l.pinned), rows);
+  prog[0] = h.objv; prog[1] = h.acc; prog[2] = h.auc; prog[3] = 1; prog[4] = (double)rows; prog[5] = 0;
+  return WH_OK;
+}
+
 int wh_worker_process_minibatch(whWorker* w, const whRowBlock* blk, int mem, int train, double* prog) {
   WH_REQUIRE(w && blk && prog, "wh_worker_process_minibatch: NULL argument");
   for (int i = 0; i < 6; ++i) prog[i] = 0;
   if (blk->size == 0) return WH_OK;
   WH_REQUIRE(w->next_wait == w->next_ticket, "wh_worker_process_minibatch: minibatches submitted earlier are still in flight");
+  WH_REQUIRE(w->server != nullptr, "wh_worker_process_minibatch: this worker has no local server; use wh_worker_begin / wh_worker_finish");
   uint64_t t = 0;
   WH_TRY(wh_worker_submit(w, blk, mem, 0, train, &t));
   return wh_worker_wait(w, t, prog);

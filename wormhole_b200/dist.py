@@ -1,0 +1,131 @@
+"""Key-range sharded push / pull across the GPUs of one box: the ps-lite part of the path.
+
+In the reference every worker cuts its SORTED unique key list into contiguous slices, one per
+server, and sends each slice to the server that owns that key range (ps::KVWorker::ZPull / ZPush,
+call sites learn/linear/async_sgd.h:277-278,287; ps-lite itself is not vendored). Here rank g is
+both worker g (its own minibatch stream) and server g, owner of the transformed keys in
+[floor(g*max_key/S), floor((g+1)*max_key/S)). One pull = all-to-all-v of key slices, a Handle::Pull
+per received key on the owner, all-to-all-v of the weights back. One push = all-to-all-v of the
+gradients (the key slices of the pull are reused: the reference's KEY_CACHING filter,
+learn/linear/async_sgd.h:295-297), then on each owner one push message PER SOURCE RANK applied in
+ascending source order -- every (worker, minibatch) gradient is its own handle update, as in the
+asynchronous parameter server; nothing is summed across workers.
+
+Only torch.distributed is used for the exchange (NCCL over NVLink on GPUs, gloo in the CPU tests);
+the shard itself is anything with pull(keys)->weights and push(keys, grads): the CUDA shard
+(DeviceShard below) in production, a CPU stand-in in the world_size-2 gloo tests.
+"""
+import torch
+import torch.distributed as dist
+
+
+def key_range(rank, world, max_key):
+    """[begin, end) of the transformed keys that server `rank` of `world` owns."""
+    return (rank * max_key) // world, ((rank + 1) * max_key) // world
+
+
+def range_boundaries(world, max_key, device):
+    """The world+1 range boundaries as an int64 tensor (max_key <= 2^62 so they fit)."""
+    return torch.tensor([(r * max_key) // world for r in range(world + 1)], dtype=torch.int64, device=device)
+
+
+class DeviceShard:
+    """Adapter: a capi.Server (CUDA shard) behind the pull / push interface ShardedKV expects."""
+
+    def __init__(self, server):
+        self.server = server
+
+    def pull(self, keys):
+        vals = torch.empty(keys.numel(), dtype=torch.float32, device=keys.device)
+        if keys.numel():
+            self.server.pull_dev(keys.data_ptr(), keys.numel(), vals.data_ptr())
+        return vals
+
+    def push(self, keys, grads):
+        # an empty slice is still a push message for this server: SGDHandle::Start advances t
+        # (learn/linear/async_sgd.h:85-90); wh_server_push handles n == 0 that way
+        self.server.push_dev(keys.data_ptr() if keys.numel() else 0, keys.numel(),
+                             grads.data_ptr() if grads.numel() else 0)
+
+
+class ShardedKV:
+    """ZPull / ZPush of one worker against `world` key-range shards (one per rank)."""
+
+    def __init__(self, shard, max_key, group=None, device=None):
+        self.shard, self.max_key, self.group = shard, max_key, group
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.device = device if device is not None else torch.device("cpu")
+        self.bounds = range_boundaries(self.world, max_key, self.device)
+        self._cache = None   # (send_counts, recv_counts, recv_keys) of the last pull
+
+    def _split(self, keys):
+        """Entries of the ascending key list per destination shard."""
+        cut = torch.searchsorted(keys, self.bounds)          # keys are int64 views of values < 2^62
+        return (cut[1:] - cut[:-1]).tolist()                 # host sync: the split sizes
+
+    def _a2a(self, out, inp, out_split, in_split):
+        if self.world == 1:
+            out.copy_(inp)
+        else:
+            dist.all_to_all_single(out, inp, out_split, in_split, group=self.group)
+
+    def pull(self, keys):
+        """keys: ascending unique transformed keys (int64 tensor). Returns their weights (float32)."""
+        send = self._split(keys)
+        if self.world == 1:
+            recv = list(send)
+        else:
+            s = torch.tensor(send, dtype=torch.int64, device=self.device)
+            r = torch.empty_like(s)
+            dist.all_to_all_single(r, s, group=self.group)
+            recv = r.tolist()
+        recv_keys = torch.empty(sum(recv), dtype=torch.int64, device=self.device)
+        self._a2a(recv_keys, keys, recv, send)
+        # one pull message per source; Handle::Pull is stateless, so serve them as one batch
+        recv_vals = self.shard.pull(recv_keys)
+        vals = torch.empty(keys.numel(), dtype=torch.float32, device=self.device)
+        self._a2a(vals, recv_vals, send, recv)
+        self._cache = (send, recv, recv_keys)
+        return vals
+
+    def push(self, grads):
+        """grads: one float per key of the last pull. Applied on the owners, one message per source."""
+        send, recv, recv_keys = self._cache
+        recv_grads = torch.empty(sum(recv), dtype=torch.float32, device=self.device)
+        self._a2a(recv_grads, grads, recv, send)
+        o = 0
+        for src in range(self.world):           # ascending source rank: one valid async interleaving
+            n = recv[src]
+            self.shard.push(recv_keys[o:o + n], recv_grads[o:o + n])
+            o += n
+
+
+class ShardedWorker:
+    """AsgdWorker::ProcessMinibatch on rank g of a key-range sharded job (CUDA path):
+    wh_worker_begin (Localize) -> ShardedKV.pull -> wh_worker_finish (Init/Evaluate/CalcGrad) ->
+    ShardedKV.push."""
+
+    def __init__(self, ctx, worker, kv):
+        self.ctx, self.worker, self.kv = ctx, worker, kv
+
+    def process_minibatch(self, blk, train=True, mem=0, nnz=0):
+        ptr, U = self.worker.begin(blk, mem, nnz)
+        keys = _wrap_device_i64(ptr, U, self.kv.device)
+        w = self.kv.pull(keys)
+        grads = torch.empty(U, dtype=torch.float32, device=self.kv.device)
+        prog = self.worker.finish(w.data_ptr() if U else 0, grads.data_ptr() if U else 0, train)
+        if train:
+            self.kv.push(grads)
+        return prog
+
+
+def _wrap_device_i64(ptr, n, device):
+    """A torch int64 view of n uint64 keys at a raw device address (keys < 2^63 by construction)."""
+    if n == 0:
+        return torch.empty(0, dtype=torch.int64, device=device)
+
+    class _Arr:
+        __cuda_array_interface__ = {"shape": (n,), "typestr": "<i8", "data": (ptr, False), "version": 2}
+
+    return torch.as_tensor(_Arr(), device=device)
