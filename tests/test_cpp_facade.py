@@ -1,0 +1,101 @@
+"""The C++ host facade (wormhole_b200/host: dmlc::Localizer, SpMV, SpMM, BinClassEval, CreateLoss,
+ps::KVWorker, AsgdServer, AsgdWorker) compiled with g++ against the C-ABI library and run on the GPU;
+its outputs are compared with the CPU checker exactly as the ctypes path's are. The CPU part checks
+that the headers compile and link (no GPU needed for that)."""
+import os
+import struct
+import subprocess
+
+import numpy as np
+import pytest
+
+from tests.util import random_block
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+MAX_KEY = 2 ** 20
+CONF = 'algo = FTRL\nloss = LOGIT\nlambda_l1 = .5   # comment\nlambda_l2 = .1\nlr_eta = .1\nlr_beta = 1\nmax_concurrency = 1\n'
+
+
+def build_binary(tmp):
+    from wormhole_b200 import build
+    build.build()
+    exe = os.path.join(str(tmp), "facade_test")
+    cmd = ["/usr/bin/g++", "-std=c++14", "-O1", "-Wall", "-I" + os.path.join(ROOT, "include"),
+           "-I" + os.path.join(ROOT, "wormhole_b200", "host"), os.path.join(ROOT, "tests", "cpp", "facade_test.cc"),
+           "-o", exe, "-L" + os.path.join(ROOT, "wormhole_b200"), "-lwormhole_b200",
+           "-Wl,-rpath," + os.path.join(ROOT, "wormhole_b200"), "-L/usr/local/cuda/lib64", "-lcudart"]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    return exe
+
+
+def test_facade_headers_compile_and_link(tmp_path):
+    assert os.path.exists(build_binary(tmp_path))
+
+
+def put(f, a):
+    f.write(struct.pack("<Q", len(a)))
+    f.write(np.ascontiguousarray(a).tobytes())
+
+
+def get(f, dtype):
+    n, = struct.unpack("<Q", f.read(8))
+    return np.frombuffer(f.read(n * np.dtype(dtype).itemsize), dtype=dtype).copy()
+
+
+@pytest.mark.gpu
+def test_facade_matches_the_checker(tmp_path, checker):
+    from oracle import oracle as O
+    exe = build_binary(tmp_path)
+    rng = np.random.default_rng(77)
+    blks = [random_block(rng, 3000, 14, 30000, with_value=(m % 2 == 1), empty_rows=False) for m in range(4)]
+    fin, fout, fconf = (str(tmp_path / n) for n in ("in.bin", "out.bin", "conf.txt"))
+    with open(fin, "wb") as f:
+        put(f, np.array([MAX_KEY, len(blks)], np.uint64))
+        for b in blks:
+            put(f, b.offset); put(f, b.index)
+            put(f, b.value if b.value is not None else np.zeros(0, np.float32)); put(f, b.label)
+    open(fconf, "w").write(CONF)
+    r = subprocess.run([exe, fin, fout, fconf], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout + r.stderr
+
+    D = checker.localize(blks[0], MAX_KEY)
+    U = len(D.uniq)
+    with open(fout, "rb") as f:
+        assert np.array_equal(get(f, np.uint64), D.uniq)
+        assert np.array_equal(get(f, np.uint32), D.cnt)
+        assert np.array_equal(get(f, np.uint64), D.offset)
+        assert np.array_equal(get(f, np.uint32), D.index)
+        val = (np.float32(0.01) * ((np.arange(U, dtype=np.uint64) * np.uint64(2654435761)) % np.uint64(97)).astype(np.float32)
+               - np.float32(0.4)).astype(np.float32)
+        d = (np.float32(0.001) * (np.arange(D.rows) % 1000).astype(np.float32) - np.float32(0.5)).astype(np.float32)
+        xw, g = get(f, np.float32), get(f, np.float32)
+        assert np.array_equal(xw, checker.spmv_times(D, val))
+        gw = checker.spmv_trans_times(D, d, U)
+        assert np.linalg.norm(g.astype(np.float64) - gw) <= 1e-5 * np.linalg.norm(gw.astype(np.float64))
+        prog, grad = get(f, np.float64), get(f, np.float32)
+        pc, gc = checker.linear_loss(O.LOSS_LOGIT, D, val, 2)
+        assert prog[1] == pc[1] and prog[4] == pc[4] and abs(prog[0] - pc[0]) <= 1e-4 * abs(pc[0])
+        assert np.linalg.norm(grad.astype(np.float64) - gc) <= 1e-5 * np.linalg.norm(gc.astype(np.float64))
+        ev = get(f, np.float32)
+        ec = checker.bin_eval(D.label, xw, 2)
+        assert abs(ev[0] - ec["auc"]) <= 1e-3 and ev[1] == ec["acc"] and abs(ev[2] - ec["logit_objv"]) <= 1e-4 * ec["logit_objv"]
+        dim = 4
+        V = (np.float32(0.001) * (np.arange(U * dim) % 613).astype(np.float32) - np.float32(0.3)).astype(np.float32)
+        xv, gv = get(f, np.float32), get(f, np.float32)
+        xvc = checker.spmm_times(D, V, dim)
+        assert np.array_equal(xv, xvc)
+        gvc = checker.spmm_trans_times(D, xvc, U * dim, dim)
+        assert np.linalg.norm(gv.astype(np.float64) - gvc) <= 1e-5 * np.linalg.norm(gvc.astype(np.float64))
+        # the whole path: AsgdWorker::ProcessMinibatch over 4 minibatches
+        progs = get(f, np.float64).reshape(-1, 6)
+        keys, w, z, cg, nnz = get(f, np.uint64), get(f, np.float32), get(f, np.float32), get(f, np.float32), get(f, np.int64)
+    job = checker.linear_create(O.ALGO_FTRL, O.LOSS_LOGIT, 0.5, 0.1, 0.1, 1.0, MAX_KEY)
+    pcs = np.array([checker.linear_minibatch(job, b) for b in blks])
+    ck, cw, cz, ccg = checker.linear_model(job)
+    assert np.array_equal(keys, ck)
+    assert np.array_equal(progs[:, 1], pcs[:, 1]) and np.array_equal(progs[:, 4], pcs[:, 4])
+    assert np.all(np.abs(progs[:, 0] - pcs[:, 0]) <= 1e-4 * np.abs(pcs[:, 0]))
+    for a, b in ((w, cw), (z, cz), (cg, ccg)):
+        assert np.all(np.abs(a - b) <= 1e-5 * np.maximum(np.abs(b), 1.0))
+    assert abs(int(nnz[0]) - int((cw != 0).sum())) <= 2 and progs[:, 5].sum() == nnz[0]
