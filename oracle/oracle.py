@@ -138,7 +138,61 @@ class _Base:
         self._f("linear_destroy")(job)
 
 
-class Port(_Base):
+class _DifactoMixin:
+    """DiFacto: learn/difacto/loss.h and learn/difacto/async_sgd.h (same calls on both checkers)."""
+
+    def _dl(self):
+        raise NotImplementedError
+
+    def difacto_loss(self, D, model, model_siz, dim, nt=2, clip=0.0, norm=0.0, want_grad=True):
+        """Loss(data, model, model_siz, conf); Evaluate; CalcGrad -> (prog[8], grad or None)."""
+        L, pre = self._dl()
+        model = _f32(model)
+        siz = np.ascontiguousarray(model_siz, np.int32)
+        prog = np.zeros(8, np.float64)
+        grad = np.zeros(len(model), np.float32) if want_grad else None
+        getattr(L, pre + "difacto_loss")(
+            C.c_size_t(D.rows), _p(D.offset), _p(D.index), _p(D.value), _p(D.label), _p(model),
+            C.c_size_t(len(model)), _p(siz), C.c_size_t(len(siz)), C.c_int(dim), C.c_int(nt), C.c_float(clip),
+            C.c_float(0.0), C.c_float(norm), _p(prog), _p(grad))
+        return prog, grad
+
+    def difacto_create(self, l1=1.0, l2=0.0, eta=.01, beta=1.0, l1_shrk=True, dim=0, threshold=0, v_l2=0.0,
+                       v_eta=None, v_beta=None, init_scale=.01, clip=0.0, norm=0.0, nt=2, max_key=NO_MAX_KEY,
+                       seed=0):
+        L, pre = self._dl()
+        f = getattr(L, pre + "difacto_create")
+        f.restype = C.c_void_p
+        return C.c_void_p(f(C.c_float(l1), C.c_float(l2), C.c_float(eta), C.c_float(beta), C.c_int(l1_shrk),
+                            C.c_int(dim), C.c_int(threshold), C.c_float(v_l2), C.c_int(v_eta is not None),
+                            C.c_float(v_eta or 0), C.c_int(v_beta is not None), C.c_float(v_beta or 0),
+                            C.c_float(init_scale), C.c_float(0.0), C.c_float(clip), C.c_float(norm), C.c_int(nt),
+                            C.c_uint64(max_key), C.c_uint(seed)))
+
+    def difacto_minibatch(self, job, blk, train=True, data_pass=0):
+        L, pre = self._dl()
+        prog = np.zeros(8, np.float64)
+        getattr(L, pre + "difacto_minibatch")(job, _p(blk.index), _p(blk.offset), _p(blk.value), _p(blk.label),
+                                              C.c_size_t(blk.rows), C.c_int(train), C.c_int(data_pass), _p(prog))
+        return prog
+
+    def difacto_model(self, job, dim):
+        """-> keys, fea_cnt, size, w[n, dim+1] = {w0, V}, cg[n, dim+2] = {sqc_grad_0, z_0, sqc_grad_V}"""
+        L, pre = self._dl()
+        f = getattr(L, pre + "difacto_model_size")
+        f.restype = C.c_size_t
+        n = f(job)
+        keys = np.zeros(n, np.uint64); cnt = np.zeros(n, np.uint32); size = np.zeros(n, np.int32)
+        w = np.zeros((n, dim + 1), np.float32); cg = np.zeros((n, dim + 2), np.float32)
+        getattr(L, pre + "difacto_model_get")(job, C.c_int(dim), _p(keys), _p(cnt), _p(size), _p(w), _p(cg))
+        return keys, cnt, size, w, cg
+
+    def difacto_destroy(self, job):
+        L, pre = self._dl()
+        getattr(L, pre + "difacto_destroy")(job)
+
+
+class Port(_Base, _DifactoMixin):
     """The plain-C restatement (always available; built on demand)."""
     pre = "orc_"
     kind = "port"
@@ -153,6 +207,9 @@ class Port(_Base):
         L.orc_remap.restype = C.c_void_p
         for n in ("orc_auc", "orc_accuracy", "orc_logit_objv", "orc_logloss"):
             getattr(L, n).restype = C.c_float
+
+    def _dl(self):
+        return self.L, "orc_"
 
     def localize(self, blk, max_key=NO_MAX_KEY, nt=2, float_cnt=False):
         h = self.L.orc_localize(_p(blk.index), _p(blk.offset), _p(blk.value), _p(blk.label),
@@ -212,7 +269,7 @@ class Port(_Base):
         return (prog, grad, xw, dual) if want_xw else (prog, grad)
 
 
-class Ref(_Base):
+class Ref(_Base, _DifactoMixin):
     """The reference's own headers (oracle/_ref). Raises FileNotFoundError if absent."""
     pre = "ref_"
     kind = "reference"
@@ -232,6 +289,11 @@ class Ref(_Base):
 
     def num_procs(self):
         return int(self.L.ref_num_procs())
+
+    def _dl(self):
+        if not hasattr(self, "_LD"):
+            self._LD = C.CDLL(os.path.join(_HERE, "_ref", "libwh_ref_difacto.so"))
+        return self._LD, "ref_"
 
     def localize(self, blk, max_key=NO_MAX_KEY, nt=2, float_cnt=False):
         h = self.L.ref_localize(_p(blk.index), _p(blk.offset), _p(blk.value), _p(blk.label),

@@ -155,3 +155,53 @@ def test_full_job(port, ref, algo, loss):
     for x, y in zip(ma, mb):
         assert np.array_equal(x, y)
     port.linear_destroy(jobs[0]); ref.linear_destroy(jobs[1])
+
+
+# ------------------------------------------------------------------ DiFacto ------------------
+
+def make_model(rng, U, dim, frac_v=0.4, frac_absent=0.05):
+    """A pulled payload: per key 0 (absent), 1 (w only) or dim+1 (w, V) floats, concatenated."""
+    r = rng.random(U)
+    siz = np.where(r < frac_absent, 0, np.where(r < frac_absent + frac_v, dim + 1, 1)).astype(np.int32)
+    if dim == 0:
+        siz = np.where(siz > 1, 1, siz).astype(np.int32)
+    model = (rng.standard_normal(int(siz.sum())) * 0.2).astype(np.float32)
+    return model, siz
+
+
+@pytest.mark.parametrize("with_value", [False, True])
+@pytest.mark.parametrize("dim", [0, 1, 5, 16])
+def test_difacto_loss(port, ref, with_value, dim):
+    rng = np.random.default_rng(8)
+    blk = random_block(rng, 700, 20, 2500, with_value, empty_rows=True)
+    D = ref.localize(blk, 2 ** 24)
+    model, siz = make_model(rng, len(D.uniq), dim)
+    for nt, clip, norm in [(1, 0.0, 0.0), (2, 0.05, 0.0), (2, 0.0, 1.0)]:
+        pa, ga = port.difacto_loss(D, model, siz, dim, nt, clip, norm)
+        pb, gb = ref.difacto_loss(D, model, siz, dim, nt, clip, norm)
+        pa[1] = pb[1] if abs(pa[1] - pb[1]) < 5e-3 else pa[1]    # AUC: tie order of equal scores
+        assert np.array_equal(pa, pb), (pa, pb)
+        assert np.array_equal(ga, gb)
+
+
+@pytest.mark.parametrize("dim,l1_shrk", [(0, True), (4, True), (4, False), (16, True)])
+def test_difacto_full_job(port, ref, dim, l1_shrk):
+    """AsyncWorker::ProcessMinibatch + AsyncServer (count push on pass 0, ZVPull, ZVPush) vs the port."""
+    rng = np.random.default_rng(9)
+    kw = dict(l1=0.3, l2=0.01, eta=0.05, beta=1.0, l1_shrk=l1_shrk, dim=dim, threshold=3, v_l2=1e-4,
+              v_eta=0.02, init_scale=0.01, max_key=2 ** 20, seed=123)
+    blks = [random_block(rng, 500, 12, 1500, with_value=(m % 2 == 1), empty_rows=False) for m in range(4)]
+    # V is initialised from the process-global glibc rand(): each job runs alone, from the same seed
+    models, progs = [], []
+    for o in (port, ref):
+        j = o.difacto_create(**kw)
+        pr = [o.difacto_minibatch(j, blk, True, dp) for dp in range(2) for blk in blks]
+        models.append(o.difacto_model(j, dim)); progs.append(np.array(pr))
+        o.difacto_destroy(j)
+    pa, pb = progs
+    pa[:, 1] = pb[:, 1]          # AUC with equal scores: pinned elsewhere
+    assert np.array_equal(pa, pb)
+    for x, y in zip(models[0], models[1]):
+        assert np.array_equal(x, y)
+    if dim:
+        assert (models[0][2] == dim + 1).any(), "the test should exercise embeddings"
