@@ -238,6 +238,52 @@ WH_API int wh_worker_finish(whWorker* w, const float* d_weights, float* d_grads,
 WH_API int wh_worker_process_minibatch(whWorker* w, const whRowBlock* blk, int mem, int train,
                                        double* prog);
 
+/* ---- (5) DiFacto: factorization machine on the same path -------------------------------- */
+typedef struct whDifacto whDifacto; /* AsyncServer shard + AsyncWorker pipeline on one GPU */
+
+/* The conf keys AsyncServer / AsyncWorker / Loss read (learn/difacto/config.proto:6-167,
+ * learn/difacto/async_sgd.h:302-327,344-357, learn/difacto/loss.h:28-40). */
+typedef struct {
+  float lambda_l1, lambda_l2;   /* w */
+  float lr_eta, lr_beta;        /* w: alpha, beta of the FTRL-style UpdateW */
+  int l1_shrk;                  /* conf.l1_shrk(): pull / grow embeddings only where w != 0 */
+  int dim;                      /* embedding(0).dim(); 0 = no embedding */
+  int threshold;                /* embedding(0).threshold(): grow V once fea_cnt > threshold */
+  float v_lambda_l2;            /* embedding(0).lambda_l2() */
+  int v_has_lr_eta;  float v_lr_eta;    /* embedding(0).lr_eta(), falls back to lr_eta when absent */
+  int v_has_lr_beta; float v_lr_beta;
+  float init_scale;             /* V starts uniform in [-init_scale, init_scale] */
+  float grad_clipping, grad_normalization;
+  float dropout;                /* must be 0: the reference draws it from rand() on the worker */
+  uint64_t key_begin, key_end;  /* the shard's key range (dense) */
+  uint64_t max_key;             /* ps::FLAGS_max_key */
+  uint64_t seed;                /* V init without an init stream: hash of (seed, key, j) */
+} whDifactoConfig;
+
+WH_API int wh_difacto_create(whContext* ctx, const whDifactoConfig* conf, whDifacto** out);
+WH_API int wh_difacto_destroy(whDifacto* d);
+/* The reference initialises a new embedding with glibc rand() in server arrival order
+ * (learn/difacto/async_sgd.h:254). To reproduce a reference run, hand over the next n values of that
+ * rand() sequence (host ints, after the same srand): the i-th embedding float created from now on
+ * uses the i-th value. Without a stream V is initialised from a hash of (seed, key, j). */
+WH_API int wh_difacto_set_init_stream(whDifacto* d, const int* rand_values, size_t n);
+/* AsyncWorker::ProcessMinibatch, learn/difacto/async_sgd.h:363-425: Localize with counts ->
+ * (train, data_pass 0, dim > 0: count push, cmd = kPushFeaCnt) -> ZVPull -> Loss::Evaluate ->
+ * Loss::CalcGrad -> ZVPush. prog[8] = {objv, auc, objv_w, copc(0), count, new_ex, new_w, new_V}
+ * (learn/difacto/progress.h:28-36). Synchronous. */
+WH_API int wh_difacto_process_minibatch(whDifacto* d, const whRowBlock* blk, int mem, int train, int data_pass,
+                                        double* prog);
+/* Entry fields of the given keys (host arrays): fea_cnt[n], size[n] (1 or dim+1), w[n*(dim+1)] =
+ * {w0, V}, cg[n*(dim+2)] = {sqc_grad_0, z_0, sqc_grad_V}; rows are zero beyond the entry's size. */
+WH_API int wh_difacto_get_state(whDifacto* d, const uint64_t* keys, size_t n, uint32_t* fea_cnt, int* size,
+                                float* w, float* cg);
+/* difacto::Loss<float>(data, model, model_siz, conf); Evaluate; CalcGrad (learn/difacto/loss.h:24-158).
+ * model is the ZVPull payload: model_siz[k] in {0, 1, dim+1} floats per key, concatenated; grad (NULL =
+ * evaluate only) has the same layout. Host arrays. prog[8] as above. */
+WH_API int wh_difacto_loss(whContext* ctx, const whLocalBlock* D, const float* model, size_t model_len,
+                           const int* model_siz, size_t nkeys, int dim, float grad_clipping,
+                           float grad_normalization, double* prog, float* grad);
+
 #ifdef __cplusplus
 }
 #endif

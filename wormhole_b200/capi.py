@@ -63,7 +63,7 @@ def lib():
             getattr(L, n).restype = C.c_size_t
             getattr(L, n).argtypes = [C.c_void_p]
         for n in ("wh_batch_has_value", "wh_batch_has_label", "wh_batch_destroy", "wh_destroy",
-                  "wh_sync", "wh_server_destroy", "wh_worker_destroy", "wh_server_sgd_t"):
+                  "wh_sync", "wh_server_destroy", "wh_worker_destroy", "wh_server_sgd_t", "wh_difacto_destroy"):
             getattr(L, n).argtypes = [C.c_void_p]
         _lib = L
     return _lib
@@ -273,6 +273,63 @@ class Server:
     def close(self):
         if self.h:
             lib().wh_server_destroy(self.h)
+            self.h = None
+
+
+class _DifactoConfig(C.Structure):
+    _fields_ = [("lambda_l1", C.c_float), ("lambda_l2", C.c_float), ("lr_eta", C.c_float), ("lr_beta", C.c_float),
+                ("l1_shrk", C.c_int), ("dim", C.c_int), ("threshold", C.c_int), ("v_lambda_l2", C.c_float),
+                ("v_has_lr_eta", C.c_int), ("v_lr_eta", C.c_float), ("v_has_lr_beta", C.c_int), ("v_lr_beta", C.c_float),
+                ("init_scale", C.c_float), ("grad_clipping", C.c_float), ("grad_normalization", C.c_float),
+                ("dropout", C.c_float), ("key_begin", C.c_uint64), ("key_end", C.c_uint64), ("max_key", C.c_uint64),
+                ("seed", C.c_uint64)]
+
+
+def difacto_loss(ctx, D, model, model_siz, dim, clip=0.0, norm=0.0, want_grad=True):
+    """difacto::Loss(data, model, model_siz, conf); Evaluate; CalcGrad -> (prog[8], grad or None)."""
+    model = _f32(model)
+    siz = np.ascontiguousarray(model_siz, np.int32)
+    prog = np.zeros(8, np.float64)
+    grad = np.zeros(len(model), np.float32) if want_grad else None
+    lb = _localblock(D)
+    _check(lib().wh_difacto_loss(ctx.h, C.byref(lb), _ptr(model), C.c_size_t(len(model)), _ptr(siz), C.c_size_t(len(siz)),
+                                 C.c_int(dim), C.c_float(clip), C.c_float(norm), _ptr(prog), _ptr(grad)))
+    return prog, grad
+
+
+class Difacto:
+    """AsyncServer + AsyncWorker of learn/difacto/async_sgd.h on one GPU."""
+
+    def __init__(self, ctx, l1=1.0, l2=0.0, eta=.01, beta=1.0, l1_shrk=True, dim=0, threshold=0, v_l2=0.0, v_eta=None,
+                 v_beta=None, init_scale=.01, clip=0.0, norm=0.0, max_key=2 ** 24, key_begin=0, key_end=None, seed=0):
+        self.ctx, self.dim = ctx, dim
+        cfg = _DifactoConfig(l1, l2, eta, beta, int(l1_shrk), dim, threshold, v_l2, int(v_eta is not None), v_eta or 0.0,
+                             int(v_beta is not None), v_beta or 0.0, init_scale, clip, norm, 0.0, key_begin,
+                             key_end if key_end is not None else max_key, max_key, seed)
+        self.h = C.c_void_p()
+        _check(lib().wh_difacto_create(ctx.h, C.byref(cfg), C.byref(self.h)))
+
+    def set_init_stream(self, rand_values):
+        v = np.ascontiguousarray(rand_values, np.int32)
+        _check(lib().wh_difacto_set_init_stream(self.h, _ptr(v), C.c_size_t(len(v))))
+
+    def process_minibatch(self, blk, train=True, data_pass=0, mem=WH_HOST):
+        prog = np.zeros(8, np.float64)
+        rb = _rowblock(blk)
+        _check(lib().wh_difacto_process_minibatch(self.h, C.byref(rb), C.c_int(mem), C.c_int(train), C.c_int(data_pass), _ptr(prog)))
+        return prog
+
+    def get_state(self, keys):
+        keys = np.ascontiguousarray(keys, np.uint64)
+        n, dim = len(keys), self.dim
+        cnt = np.zeros(n, np.uint32); size = np.zeros(n, np.int32)
+        w = np.zeros((n, dim + 1), np.float32); cg = np.zeros((n, dim + 2), np.float32)
+        _check(lib().wh_difacto_get_state(self.h, _ptr(keys), C.c_size_t(n), _ptr(cnt), _ptr(size), _ptr(w), _ptr(cg)))
+        return cnt, size, w, cg
+
+    def close(self):
+        if self.h:
+            lib().wh_difacto_destroy(self.h)
             self.h = None
 
 

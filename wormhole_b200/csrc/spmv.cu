@@ -93,6 +93,7 @@ __global__ void fixed_scale_kernel(FixedScale* fs, size_t nnz, int has_val) {
   float mx = __uint_as_float(fs->maxx_bits);
   float mv = has_val ? __uint_as_float(fs->maxv_bits) : 1.f;
   double m = (double)mx * (double)mv;
+  if (has_val == 2) m *= (double)mv;   // terms x * val^2 (DiFacto's (X.*X)' p)
   int e = 0;
   if (m > 0.0 && isfinite(m)) {
     int em; frexp(m, &em);                    // m < 2^em
@@ -203,13 +204,13 @@ int ensure_acc(whContext* ctx, size_t n, long long** out) {
   return WH_OK;
 }
 
-static int fixed_prepare(whContext* ctx, FixedScale* fs, const float* x, size_t nx, const float* value,
-                         size_t nnz) {
+int fixed_prepare(whContext* ctx, FixedScale* fs, const float* x, size_t nx, const float* value,
+                  size_t nnz, int vpow) {
   const unsigned cap = (unsigned)ctx->num_sms * 8;
   WH_LAUNCH(fixed_reset_kernel, 1, 1, 0, ctx->stream, fs);
   WH_LAUNCH(absmax_kernel, (unsigned)std::min<size_t>(div_up(nx ? nx : 1, 256), cap), 256, 0, ctx->stream, x, nx, &fs->maxx_bits);
   if (value) WH_LAUNCH(absmax_kernel, (unsigned)std::min<size_t>(div_up(nnz ? nnz : 1, 256), cap), 256, 0, ctx->stream, value, nnz, &fs->maxv_bits);
-  WH_LAUNCH(fixed_scale_kernel, 1, 1, 0, ctx->stream, fs, nnz, value ? 1 : 0);
+  WH_LAUNCH(fixed_scale_kernel, 1, 1, 0, ctx->stream, fs, nnz, value ? vpow : 0);
   return WH_OK;
 }
 
@@ -217,7 +218,7 @@ static int fixed_prepare(whContext* ctx, FixedScale* fs, const float* x, size_t 
 int spmv_trans_accumulate_launch(whContext* ctx, size_t rows, size_t nnz, const size_t* offset,
                                  const uint32_t* index, const float* value, const float* x,
                                  long long* acc, FixedScale* fs, unsigned copies, size_t stride) {
-  WH_TRY(fixed_prepare(ctx, fs, x, rows, value, nnz));
+  WH_TRY(fixed_prepare(ctx, fs, x, rows, value, nnz, 1));
   const unsigned grid = (unsigned)div_up(rows, kRowsPerBlock);
   static int mode = -1;   // WH_TRANS_MODE=0 (default): one atomic per entry; 1: merged within the warp first
                           // (measured: merging costs more instructions than the atomics it saves)
@@ -308,7 +309,7 @@ int spmm_trans_times_launch(whContext* ctx, size_t rows, size_t nnz, const size_
                             const float* z, float* y, size_t ysize, int dim, long long* acc,
                             FixedScale* fs) {
   if (ysize == 0 || dim <= 0) return WH_OK;
-  WH_TRY(fixed_prepare(ctx, fs, x, rows * dim, value, nnz));
+  WH_TRY(fixed_prepare(ctx, fs, x, rows * dim, value, nnz, 1));
   if (rows) WH_LAUNCH(spmm_trans_kernel, (unsigned)div_up(rows * dim, 256), 256, 0, ctx->stream, rows, offset, index, value, x, dim, acc, fs);
   const unsigned g2 = (unsigned)std::min<size_t>(div_up(ysize, 256), (size_t)ctx->num_sms * 8);
   WH_LAUNCH(fixed_finish_kernel, g2, 256, 0, ctx->stream, acc, ysize, fs, p, (z && p != 0.f) ? z : (const float*)nullptr, y, 1.f, 1u, ysize);

@@ -41,6 +41,8 @@ int spmm_trans_times_launch(whContext* ctx, size_t rows, size_t nnz, const size_
                             const uint32_t* index, const float* value, const float* x, float p,
                             const float* z, float* y, size_t ysize, int dim, long long* acc,
                             FixedScale* fs);
+// Chooses the fixed-point scale for terms x * value^vpow (max|x|, max|value| reductions + one tiny kernel).
+int fixed_prepare(whContext* ctx, FixedScale* fs, const float* x, size_t nx, const float* value, size_t nnz, int vpow);
 // A whLocalBlock resolved to device pointers.
 struct DevLocal {
   size_t rows = 0, nnz = 0;
