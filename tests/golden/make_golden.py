@@ -142,6 +142,29 @@ def main():
         out[name + "_conf"] = np.array([algo, loss, max_key], dtype=np.uint64)
         ref.linear_destroy(job)
     np.savez_compressed(os.path.join(HERE, "golden_agaricus.npz"), **out)
+    # --- DiFacto (learn/difacto): the loss on a ZVPull-shaped payload, and the guide's demo.conf
+    # (embedding dim 5, threshold 5) on agaricus for two passes, 1 worker + 1 server
+    from tests.test_oracle_vs_ref import make_model
+    out = {}
+    blk = random_block(rng, 400, 15, 900, True)
+    D = ref.localize(blk, 2 ** 24)
+    pack_loc("l_", D, out); out["l_label"] = D.label
+    for dim in (0, 5):
+        model, siz = make_model(rng, len(D.uniq), dim)
+        prog, grad = ref.difacto_loss(D, model, siz, dim, 2, 0.0, 0.0)
+        out["l%d_model" % dim], out["l%d_siz" % dim], out["l%d_prog" % dim], out["l%d_grad" % dim] = model, siz, prog, grad
+    kw = dict(l1=1.0, l2=0.0, eta=.01, beta=1.0, l1_shrk=True, dim=5, threshold=5, v_l2=0.0, init_scale=.01,
+              max_key=2 ** 20, seed=7)
+    job = ref.difacto_create(**kw)
+    progs = [ref.difacto_minibatch(job, ag.slice(b, min(ag.rows, b + 1000)), True, dp)
+             for dp in range(2) for b in range(0, ag.rows, 1000)]
+    keys, cnt, size, w, cg = ref.difacto_model(job, 5)
+    ref.difacto_destroy(job)
+    out["ag_prog"], out["ag_keys"], out["ag_cnt"], out["ag_size"], out["ag_w"], out["ag_cg"] = np.array(progs), keys, cnt, size, w, cg
+    import ctypes
+    libc = ctypes.CDLL("libc.so.6"); libc.srand(ctypes.c_uint(7))
+    out["ag_rand"] = np.array([libc.rand() for _ in range(4096)], np.int32)   # the rand() values V was drawn from
+    np.savez_compressed(os.path.join(HERE, "golden_difacto.npz"), **out)
     for f in sorted(os.listdir(HERE)):
         if f.endswith(".npz"):
             print(f, os.path.getsize(os.path.join(HERE, f)))

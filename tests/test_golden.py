@@ -202,3 +202,59 @@ def test_gpu_agaricus_epoch_matches_golden(gpu):
         for a, b in ((w, g[name + "_w"]), (z, g[name + "_z"]), (cg, g[name + "_cg"])):
             assert np.all(np.abs(a - b) <= 1e-5 * np.maximum(np.abs(b), 1.0))
         wk.close(); srv.close()
+
+
+# ------------------------------------------------------------------ DiFacto ------------------
+
+DFC_KW = dict(l1=1.0, l2=0.0, eta=.01, beta=1.0, l1_shrk=True, dim=5, threshold=5, v_l2=0.0, init_scale=.01)
+
+
+def test_port_difacto_matches_golden(port):
+    g = load("golden_difacto.npz")
+    D = get_local(g, "l_")
+    for dim in (0, 5):
+        prog, grad = port.difacto_loss(D, g["l%d_model" % dim], g["l%d_siz" % dim], dim, 2)
+        want = g["l%d_prog" % dim].copy()
+        assert abs(prog[1] - want[1]) < 5e-3
+        prog[1] = want[1]
+        assert np.array_equal(prog, want) and np.array_equal(grad, g["l%d_grad" % dim])
+    ag = agaricus()
+    job = port.difacto_create(max_key=2 ** 20, seed=7, **DFC_KW)
+    progs = np.array([port.difacto_minibatch(job, ag.slice(b, min(ag.rows, b + 1000)), True, dp)
+                      for dp in range(2) for b in range(0, ag.rows, 1000)])
+    keys, cnt, size, w, cg = port.difacto_model(job, 5)
+    port.difacto_destroy(job)
+    cols = [0, 2, 3, 4, 5, 6, 7]
+    assert np.array_equal(progs[:, cols], g["ag_prog"][:, cols])
+    for a, b in ((keys, g["ag_keys"]), (cnt, g["ag_cnt"]), (size, g["ag_size"]), (w, g["ag_w"]), (cg, g["ag_cg"])):
+        assert np.array_equal(a, b)
+    assert (size == 6).any()
+
+
+@pytest.mark.gpu
+def test_gpu_difacto_matches_golden(gpu):
+    from wormhole_b200 import capi
+    g = load("golden_difacto.npz")
+    D = get_local(g, "l_")
+    for dim in (0, 5):
+        prog, grad = capi.difacto_loss(gpu, D, g["l%d_model" % dim], g["l%d_siz" % dim], dim)
+        want, gw = g["l%d_prog" % dim], g["l%d_grad" % dim]
+        assert abs(prog[0] - want[0]) <= 1e-4 * abs(want[0]) and abs(prog[2] - want[2]) <= 1e-4 * abs(want[2])
+        assert np.linalg.norm(grad.astype(np.float64) - gw) <= 2e-5 * np.linalg.norm(gw.astype(np.float64))
+    ag = agaricus()
+    d = capi.Difacto(gpu, max_key=2 ** 20, **DFC_KW)
+    d.set_init_stream(g["ag_rand"])
+    progs = np.array([d.process_minibatch(ag.slice(b, min(ag.rows, b + 1000)), True, dp)
+                      for dp in range(2) for b in range(0, ag.rows, 1000)])
+    cnt, size, w, cg = d.get_state(g["ag_keys"])
+    d.close()
+    want = g["ag_prog"]
+    assert np.array_equal(progs[:, 4:], want[:, 4:])            # count, new_ex, new_w, new_V
+    assert np.array_equal(cnt, g["ag_cnt"]) and np.array_equal(size, g["ag_size"])
+    fin = np.isfinite(want[:, 0])
+    assert np.array_equal(np.isfinite(progs[:, 0]), fin)
+    assert abs(progs[fin, 0].sum() / progs[fin, 5].sum() - want[fin, 0].sum() / want[fin, 5].sum()) <= 1e-4
+    # 14 dependent updates with a 5-dim interaction term: per-step rounding differences (summation order of
+    # X' p) compound, so the end-of-run state is held to 2e-4; single steps are held to 2e-5 in test_gpu_difacto.py
+    for a, b in ((w, g["ag_w"]), (cg, g["ag_cg"])):
+        assert np.all(np.abs(a - b) <= 2e-4 * np.maximum(np.abs(b), 1.0))
