@@ -197,13 +197,24 @@ def run_ours(args):
         wk = capi.Worker(ctx, srv, capi.LOSS_LOGIT, MAX_KEY, depth=args.depth)
         sw = None
     else:
-        # rank g = worker g + server g of the key range [g*max_key/S, (g+1)*max_key/S): pull and push
-        # are all-to-all-v exchanges over NCCL (wormhole_b200/dist.py); weak scaling, one stream per GPU
+        # rank g = worker g + server g of the key range [g*max_key/S, (g+1)*max_key/S). Default: every rank maps
+        # the other ranks' shards over NVLink (CUDA IPC); pull gathers from the owning GPU, push runs in S turns
+        # with stream-ordered barriers (server.cu). --exchange nccl: all-to-all-v of (key, weight) / (key, grad)
+        # messages through torch.distributed instead (wormhole_b200/dist.py). Weak scaling.
         from wormhole_b200.dist import DeviceShard, ShardedKV, ShardedWorker, key_range
         kb, ke = key_range(rank, world, MAX_KEY)
         srv = capi.Server(ctx, capi.ALGO_FTRL, FTRL["l1"], FTRL["l2"], FTRL["eta"], FTRL["beta"], kb, ke)
-        wk = capi.Worker(ctx, None, capi.LOSS_LOGIT, MAX_KEY)
-        sw = ShardedWorker(ctx, wk, ShardedKV(DeviceShard(srv), MAX_KEY, device=torch.device("cuda", local)))
+        if args.exchange == "p2p":
+            handles = [None] * world
+            dist.all_gather_object(handles, srv.ipc_export())
+            srv.ipc_attach(rank, world, MAX_KEY, handles)
+            dist.barrier()
+            args.depth = 1
+            wk = capi.Worker(ctx, srv, capi.LOSS_LOGIT, MAX_KEY, depth=1)
+            sw = None
+        else:
+            wk = capi.Worker(ctx, None, capi.LOSS_LOGIT, MAX_KEY)
+            sw = ShardedWorker(ctx, wk, ShardedKV(DeviceShard(srv), MAX_KEY, device=torch.device("cuda", local)))
 
     # the minibatch pool: distinct minibatches, resident in HBM (device leg) and in pinned host
     # memory (e2e leg). pool_n x ~32 MB exceeds the 126 MB L2, so every step streams from HBM.
@@ -307,7 +318,7 @@ def run_ours(args):
             "config": {"workload": WORKLOAD, "rows_per_minibatch": rows, "nnz_per_minibatch": N,
                        "max_key": MAX_KEY, "unique_keys_per_row_r": round(r, 4), "pool_minibatches": pool_n,
                        "l2_policy": "inputs larger than L2 (pool of %d distinct minibatches, %.0f MB)" % (pool_n, pool_n * N * 8 / 1e6),
-                       "parallelism": "key-range shards x%d" % world, "updater": FTRL,
+                       "parallelism": "key-range shards x%d" % world + ("" if world == 1 else " (" + args.exchange + ")"), "updater": FTRL,
                        "minibatches_in_flight": args.depth if world == 1 else 1},
             "e2e": {"value": e2e, "unit": "examples/s", "h2d_bytes_per_step": N * 8 + (rows + 1) * 8 + rows * 4,
                     "d2h_bytes_per_step": 72 + 16},
@@ -355,6 +366,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--rows", type=int, default=ROWS)
     ap.add_argument("--pool", type=int, default=8, help="distinct minibatches kept resident")
+    ap.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"], help="N>1: how pull/push reach the owning GPU")
     ap.add_argument("--depth", type=int, default=3, help="minibatches in flight (conf max_concurrency)")
     ap.add_argument("--cpu-procs", type=int, default=0, help="reference arm: worker+server pairs (0 = cores/2)")
     args = ap.parse_args()

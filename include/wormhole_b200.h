@@ -200,6 +200,17 @@ WH_API int wh_server_set_state(whServer* s, const uint64_t* keys, size_t n, int 
                                const float* z, const float* sq_cum_grad);
 /* SGDHandle::t (learn/linear/async_sgd.h:100). */
 WH_API int wh_server_sgd_t(const whServer* s);
+/* Key-range shards on several GPUs of one box (one process per GPU). ps-lite gives server g an even slice of
+ * [0, max_key) and routes each worker's key slices to it over ZeroMQ; here every rank maps every other rank's
+ * shard over NVLink (CUDA IPC) and the pull / push kernels of a worker address the owning GPU directly.
+ * export: fills WH_IPC_HANDLE_BYTES bytes that the caller passes to the other ranks by any means.
+ * attach: `handles` = the exports of ranks 0..world-1 concatenated; this shard must have been created with the
+ * range [rank*max_key/world, (rank+1)*max_key/world). Afterwards a worker created on this server runs the sharded
+ * ProcessMinibatch: gather from the owners, barrier, then `world` push turns (turn k updates shard (rank+k)%world)
+ * with stream-ordered barriers in between; every rank must process the same number of minibatches. */
+#define WH_IPC_HANDLE_BYTES 192
+WH_API int wh_server_ipc_export(whServer* s, void* handle);
+WH_API int wh_server_ipc_attach(whServer* s, int rank, int world, uint64_t max_key, const void* handles);
 
 /* ---- the per-minibatch pipeline --------------------------------------------------------- */
 /* AsgdWorker, learn/linear/async_sgd.h:229-305, bound to one server shard that owns every key

@@ -110,3 +110,77 @@ def test_two_gpus_match_the_cpu_simulation(tmp_path):
         err = np.abs(got["w"] - W[b:e])
         assert np.all(err <= 1e-5 * np.maximum(np.abs(W[b:e]), 1.0)), float(err.max())
         assert abs(int(got["nnz"]) - int((W[b:e] != 0).sum())) <= 2
+
+
+# ---- shards mapped over NVLink (CUDA IPC): no message exchange, push in turns ---------------------
+
+def _p2p_rank_main(rank, world, port_no, out_dir, algo):
+    import torch
+    import torch.distributed as dist
+    from wormhole_b200 import capi
+    from wormhole_b200.dist import key_range
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port_no)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("gloo", rank=rank, world_size=world)      # only to pass the 192-byte handles around
+    ctx = capi.Context(rank)
+    b, e = key_range(rank, world, MAX_KEY)
+    srv = capi.Server(ctx, algo, L1, L2, ETA, BETA, b, e)
+    handles = [None] * world
+    dist.all_gather_object(handles, srv.ipc_export())
+    srv.ipc_attach(rank, world, MAX_KEY, handles)
+    dist.barrier()
+    wk = capi.Worker(ctx, srv, capi.LOSS_LOGIT, MAX_KEY)
+    progs = [wk.process_minibatch(minibatch(rank, s)) for s in range(STEPS)]
+    dist.barrier()
+    keys = np.arange(b, e, dtype=np.uint64)
+    w, z, cg = srv.get_state(keys)
+    np.savez(os.path.join(out_dir, "p2p%d.npz" % rank), w=w, z=z, cg=cg, t=srv.sgd_t(), nnz=srv.nnz_w(), prog=np.array(progs))
+    dist.barrier()
+    wk.close(); srv.close(); ctx.close()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("algo_name", ["FTRL", "SGD"])
+def test_two_gpus_peer_mapped_shards(tmp_path, algo_name):
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs (gpurun --gpus 2)")
+    import torch.multiprocessing as mp
+    from oracle import oracle as O
+    from wormhole_b200 import capi
+    from wormhole_b200.dist import key_range
+    algo = {"FTRL": capi.ALGO_FTRL, "SGD": capi.ALGO_SGD}[algo_name]
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port_no = s.getsockname()[1]; s.close()
+    world = 2
+    mp.spawn(_p2p_rank_main, args=(world, port_no, str(tmp_path), algo), nprocs=world, join=True)
+    # CPU checker, same order: all pulls of a step see the model as of the previous step; shard s then takes
+    # the pushes of sources s, s-1, ... (mod world), one handle update each
+    chk = O.best()
+    bounds = [key_range(r, world, MAX_KEY)[0] for r in range(world)] + [MAX_KEY]
+    W, Z, CG = (np.zeros(MAX_KEY, np.float32) for _ in range(3))
+    t = [1] * world
+    for step in range(STEPS):
+        msgs = []
+        for r in range(world):
+            D = chk.localize(minibatch(r, step), MAX_KEY)
+            keys = D.uniq.astype(np.int64)
+            _, grad = chk.linear_loss(O.LOSS_LOGIT, D, W[keys], 2)
+            msgs.append((keys, grad, np.searchsorted(keys, bounds)))
+        for sidx in range(world):
+            for k in range(world):
+                keys, grad, cut = msgs[(sidx - k) % world]
+                sl = slice(cut[sidx], cut[sidx + 1])
+                w, z, cg = W[keys[sl]].copy(), Z[keys[sl]].copy(), CG[keys[sl]].copy()
+                _, t[sidx] = chk.handle_push(algo, L1, L2, ETA, BETA, grad[sl].copy(), w, z, cg, t[sidx])
+                W[keys[sl]], Z[keys[sl]], CG[keys[sl]] = w, z, cg
+    for r in range(world):
+        got = np.load(tmp_path / ("p2p%d.npz" % r))
+        b, e = key_range(r, world, MAX_KEY)
+        if algo == capi.ALGO_SGD:
+            assert int(got["t"]) == t[r] == 1 + world * STEPS
+        for name, ref in (("w", W), ("z", Z), ("cg", CG)):
+            if algo == capi.ALGO_SGD and name != "w":
+                continue
+            err = np.abs(got[name] - ref[b:e])
+            assert np.all(err <= 1e-5 * np.maximum(np.abs(ref[b:e]), 1.0)), (name, float(err.max()))
+        assert abs(int(got["nnz"]) - int((W[b:e] != 0).sum())) <= 2

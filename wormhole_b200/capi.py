@@ -250,6 +250,18 @@ class Server:
         """One push message on device arrays (addresses); enqueued on the context's stream."""
         _check(lib().wh_server_push(self.h, C.c_void_p(keys_ptr), C.c_size_t(n), C.c_int(WH_DEVICE), C.c_void_p(grads_ptr)))
 
+    def ipc_export(self):
+        """The bytes other ranks need to map this shard (wh_server_ipc_export)."""
+        buf = C.create_string_buffer(192)
+        _check(lib().wh_server_ipc_export(self.h, buf))
+        return buf.raw
+
+    def ipc_attach(self, rank, world, max_key, handles):
+        """handles: the ipc_export() bytes of ranks 0..world-1, in rank order."""
+        blob = b"".join(handles)
+        assert len(blob) == 192 * world
+        _check(lib().wh_server_ipc_attach(self.h, C.c_int(rank), C.c_int(world), C.c_uint64(max_key), blob))
+
     def nnz_w(self):
         out = C.c_int64()
         _check(lib().wh_server_nnz_w(self.h, C.byref(out)))

@@ -167,6 +167,124 @@ int server_push_acc_launch(whServer* s, cudaStream_t stream, const uint64_t* key
   return WH_OK;
 }
 
+
+// ---------------------------------------------------------------- shards on several GPUs --
+// Rank g is worker g and server g (key range [bounds[g], bounds[g+1])). Instead of exchanging
+// (key, value) messages, every rank maps every other rank's table (CUDA IPC; loads, stores and atomics
+// go over NVLink) and runs the handle itself:
+//   pull        one gather per key straight from the owner's table;
+//   push        in `world` turns; in turn k rank r applies its gradients to shard (r + k) % world, so
+//               each shard has exactly one writer at a time and every (worker, minibatch) gradient is
+//               its own handle update, as in the reference's asynchronous server. Shard s receives its
+//               sources in the order s, s-1, ..., s+1 (mod world);
+//   barrier     between pull and the first turn and after every turn: a one-block kernel that announces
+//               an epoch in every peer's flag array and waits for all peers' announcements. It is
+//               stream-ordered -- no host synchronisation anywhere in the exchange.
+
+__device__ __forceinline__ int shard_of(const ShardMap& m, uint64_t k) {
+  int g = 0;
+#pragma unroll
+  for (int i = 1; i < kMaxShards; ++i) g += (i < m.world && k >= m.bounds[i]) ? 1 : 0;
+  return g;
+}
+
+__global__ void __launch_bounds__(256)
+server_pull_sharded_kernel(int algo, ShardMap m, uint64_t max_key, const uint64_t* __restrict__ keys, size_t n,
+                           const unsigned* d_n, float* __restrict__ vals, long long* counters) {
+  if (d_n) n = *d_n;
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int bad = 0;
+  if (i < n) {
+    const uint64_t k = keys[i];
+    if (k < max_key) {
+      const int g = shard_of(m, k);
+      const uint64_t s = k - m.bounds[g];
+      const void* table = m.table[g];
+      float w;
+      if (algo == WH_ALGO_FTRL) w = *reinterpret_cast<const volatile float*>(reinterpret_cast<const float4*>(table) + s);
+      else if (algo == WH_ALGO_ADAGRAD) w = *reinterpret_cast<const volatile float*>(reinterpret_cast<const float2*>(table) + s);
+      else w = *(reinterpret_cast<const volatile float*>(table) + s);
+      vals[i] = w;
+    } else { vals[i] = 0.f; bad = 1; }
+  }
+  commit_counters(counters, 0, bad);
+}
+
+__global__ void __launch_bounds__(256)
+server_push_turn_kernel(HandleParams h, ShardMap m, int target, const uint64_t* __restrict__ keys, size_t n,
+                        const unsigned* d_n, long long* acc, const FixedScale* fs, float mul, unsigned copies,
+                        size_t stride) {
+  if (d_n) n = *d_n;
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int delta = 0;
+  if (i < n) {
+    const uint64_t k = keys[i];
+    if (k >= m.bounds[target] && k < m.bounds[target + 1]) {
+      long long a = 0;
+      for (unsigned c = 0; c < copies; ++c) { a += acc[c * stride + i]; acc[c * stride + i] = 0; }
+      const float g = (float)((double)a * fs->inv) * mul;
+      delta = handle_push(h, m.table[target], k - m.bounds[target], g);
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) delta += __shfl_xor_sync(0xffffffffu, delta, o);
+  if ((threadIdx.x & 31) == 0 && delta)
+    atomicAdd_system(reinterpret_cast<unsigned long long*>(m.counters[target]), (unsigned long long)(long long)delta);
+}
+
+// All-rank rendezvous. flags[g][r] lives on GPU g and is written by rank r only.
+__global__ void shard_barrier_kernel(ShardMap m, unsigned long long epoch, long long* counters) {
+  const int t = threadIdx.x;
+  __threadfence_system();   // everything this GPU wrote to its peers before the barrier is visible first
+  if (t < m.world) {
+    volatile unsigned long long* out = m.flags[t] + m.rank;
+    *out = epoch;
+    __threadfence_system();
+    const volatile unsigned long long* in = m.flags[m.rank] + t;
+    const long long t0 = clock64();
+    while (*in < epoch) {
+      if (clock64() - t0 > 20000000000ll) {   // ~10 s: a peer is gone; report instead of hanging the GPU
+        atomicAdd(reinterpret_cast<unsigned long long*>(counters + 2), 1ull);
+        break;
+      }
+    }
+  }
+  __threadfence_system();
+}
+
+int server_pull_sharded_launch(whServer* s, cudaStream_t stream, const uint64_t* keys, size_t n, const unsigned* d_n, float* vals) {
+  if (n == 0) return WH_OK;
+  WH_LAUNCH(server_pull_sharded_kernel, (unsigned)div_up(n, 256), 256, 0, stream, s->algo, s->map,
+            s->map.bounds[s->map.world], keys, n, d_n, vals, s->counters.as<long long>());
+  return WH_OK;
+}
+
+int server_push_turn_launch(whServer* s, cudaStream_t stream, int turn, const uint64_t* keys, size_t n, const unsigned* d_n,
+                            long long* acc, const FixedScale* fs, float mul, unsigned copies, size_t stride) {
+  const int target = (s->map.rank + turn) % s->map.world;
+  HandleParams h;
+  h.algo = s->algo; h.l1 = s->l1; h.l2 = s->l2; h.alpha = s->alpha; h.beta = s->beta;
+  h.key_begin = s->map.bounds[target]; h.key_end = s->map.bounds[target + 1];
+  h.eta_sgd = 0.f;
+  if (s->algo == WH_ALGO_SGD) {
+    // SGDHandle::t of the target shard when this message arrives: it has seen `world` messages per earlier
+    // step and `turn` messages in this one (learn/linear/async_sgd.h:85-90)
+    const unsigned long long t = 1ull + s->steps * (unsigned long long)s->map.world + (unsigned long long)turn;
+    h.eta_sgd = (s->beta + sqrtf((float)t)) / s->alpha;
+  }
+  if (n == 0) return WH_OK;
+  WH_LAUNCH(server_push_turn_kernel, (unsigned)div_up(n, 256), 256, 0, stream, h, s->map, target, keys, n, d_n, acc, fs,
+            mul, copies, stride);
+  return WH_OK;
+}
+
+int server_barrier_launch(whServer* s, cudaStream_t stream) {
+  if (s->map.world <= 1) return WH_OK;
+  s->epoch++;
+  WH_LAUNCH(shard_barrier_kernel, 1, 32, 0, stream, s->map, s->epoch, s->counters.as<long long>());
+  return WH_OK;
+}
+
 }  // namespace wh
 
 using namespace wh;
@@ -204,9 +322,15 @@ int wh_server_create(whContext* ctx, const whServerConfig* c, whServer** out) {
   const size_t esz = c->algo == WH_ALGO_FTRL ? 16 : (c->algo == WH_ALGO_ADAGRAD ? 8 : 4);
   int r = s->table.reserve(s->entries() * esz);
   if (r == WH_OK) r = s->counters.reserve(64);
+  if (r == WH_OK) r = s->flags.reserve(kMaxShards * 8);
   if (r != WH_OK) { delete s; return r; }
   WH_CUDA(cudaMemsetAsync(s->table.p, 0, s->table.cap, ctx->stream));  // entries default to 0 (:72,108-109,146-148)
   WH_CUDA(cudaMemsetAsync(s->counters.p, 0, 64, ctx->stream));
+  WH_CUDA(cudaMemsetAsync(s->flags.p, 0, kMaxShards * 8, ctx->stream));
+  s->map.world = 1; s->map.rank = 0;
+  s->map.bounds[0] = c->key_begin; s->map.bounds[1] = c->key_end;
+  s->map.table[0] = s->table.p; s->map.counters[0] = s->counters.as<long long>();
+  s->map.flags[0] = s->flags.as<unsigned long long>();
   *out = s;
   return WH_OK;
 }
@@ -215,7 +339,8 @@ int wh_server_destroy(whServer* s) {
   if (!s) return WH_OK;
   DeviceGuard g(s->ctx->device);
   cudaStreamSynchronize(s->ctx->stream);
-  s->table.release(); s->counters.release();
+  for (void* p : s->peer_base) if (p) cudaIpcCloseMemHandle(p);
+  s->table.release(); s->counters.release(); s->flags.release();
   delete s;
   return WH_OK;
 }
@@ -286,6 +411,49 @@ int wh_server_set_state(whServer* s, const uint64_t* keys, size_t n, int mem, co
   WH_REQUIRE(s && (n == 0 || keys), "wh_server_set_state: NULL argument");
   return state_io(s, keys, n, mem, nullptr, nullptr, nullptr, w, z, cg, 1);
 }
-int wh_server_sgd_t(const whServer* s) { return s ? s->t : 0; }
+int wh_server_sgd_t(const whServer* s) {
+  if (!s) return 0;
+  if (s->map.world > 1) return (int)(1 + s->steps * (unsigned long long)s->map.world);   // lock-step shards
+  return s->t;
+}
+
+int wh_server_ipc_export(whServer* s, void* handle) {
+  WH_REQUIRE(s && handle, "wh_server_ipc_export: NULL argument");
+  DeviceGuard g(s->ctx->device);
+  WH_CUDA(cudaStreamSynchronize(s->ctx->stream));
+  cudaIpcMemHandle_t* h = reinterpret_cast<cudaIpcMemHandle_t*>(handle);
+  WH_CUDA(cudaIpcGetMemHandle(&h[0], s->table.p));
+  WH_CUDA(cudaIpcGetMemHandle(&h[1], s->counters.p));
+  WH_CUDA(cudaIpcGetMemHandle(&h[2], s->flags.p));
+  return WH_OK;
+}
+
+int wh_server_ipc_attach(whServer* s, int rank, int world, uint64_t max_key, const void* handles) {
+  WH_REQUIRE(s && handles, "wh_server_ipc_attach: NULL argument");
+  WH_REQUIRE(world >= 1 && world <= kMaxShards && rank >= 0 && rank < world, "wh_server_ipc_attach: rank %d of %d", rank, world);
+  WH_REQUIRE(s->map.world == 1, "wh_server_ipc_attach: already attached");
+  const uint64_t b = (uint64_t)(((unsigned __int128)rank * max_key) / world), e = (uint64_t)(((unsigned __int128)(rank + 1) * max_key) / world);
+  WH_REQUIRE(s->key_begin == b && s->key_end == e, "wh_server_ipc_attach: this shard holds [%llu, %llu) but rank %d of %d owns [%llu, %llu)",
+             (unsigned long long)s->key_begin, (unsigned long long)s->key_end, rank, world, (unsigned long long)b, (unsigned long long)e);
+  DeviceGuard g(s->ctx->device);
+  const cudaIpcMemHandle_t* h = reinterpret_cast<const cudaIpcMemHandle_t*>(handles);
+  ShardMap m;
+  m.world = world; m.rank = rank;
+  for (int r = 0; r <= world; ++r) m.bounds[r] = (uint64_t)(((unsigned __int128)r * max_key) / world);
+  for (int r = 0; r < world; ++r) {
+    if (r == rank) {
+      m.table[r] = s->table.p; m.counters[r] = s->counters.as<long long>(); m.flags[r] = s->flags.as<unsigned long long>();
+      continue;
+    }
+    void* p[3] = {nullptr, nullptr, nullptr};
+    for (int j = 0; j < 3; ++j) {
+      WH_CUDA(cudaIpcOpenMemHandle(&p[j], h[3 * r + j], cudaIpcMemLazyEnablePeerAccess));
+      s->peer_base[3 * r + j] = p[j];
+    }
+    m.table[r] = p[0]; m.counters[r] = static_cast<long long*>(p[1]); m.flags[r] = static_cast<unsigned long long*>(p[2]);
+  }
+  s->map = m;
+  return WH_OK;
+}
 
 }  // extern "C"

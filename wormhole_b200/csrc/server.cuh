@@ -3,8 +3,26 @@
 #include "common.cuh"
 #include "spmv.cuh"
 
+namespace wh {
+constexpr int kMaxShards = 8;
+// The shards of one box as seen from one GPU: every rank's table / counters / barrier flags are mapped
+// into this process (CUDA IPC over NVLink), so a kernel can address any shard directly.
+struct ShardMap {
+  int world = 1, rank = 0;
+  uint64_t bounds[kMaxShards + 1] = {0};          // shard g owns keys [bounds[g], bounds[g+1])
+  void* table[kMaxShards] = {nullptr};
+  long long* counters[kMaxShards] = {nullptr};
+  unsigned long long* flags[kMaxShards] = {nullptr};   // flags[g][r]: last barrier epoch rank r announced to rank g
+};
+}  // namespace wh
+
 struct whServer {
   whContext* ctx = nullptr;
+  wh::ShardMap map;                 // world == 1: just this shard
+  wh::DevBuf flags;                 // this rank's barrier flags (kMaxShards x u64)
+  unsigned long long epoch = 0;     // barriers issued so far (all ranks in lock step)
+  unsigned long long steps = 0;     // training minibatches pushed so far (SGD: t of every shard follows from it)
+  void* peer_base[3 * wh::kMaxShards] = {nullptr};   // pointers opened with cudaIpcOpenMemHandle
   int algo = WH_ALGO_FTRL;
   float l1 = 1.f, l2 = 0.f;
   float alpha = 0.1f, beta = 1.f;   // ISGDHandle defaults, learn/linear/async_sgd.h:49
@@ -21,6 +39,12 @@ int server_pull_launch(whServer* s, cudaStream_t stream, const uint64_t* keys, s
 int server_push_launch(whServer* s, cudaStream_t stream, const uint64_t* keys, size_t n, const unsigned* d_n, const float* grads);
 // Gradients still in the fixed-point accumulator of the transposed product: converts, clears the
 // accumulator and applies the update in one pass (no fp32 gradient array in between).
+// Multi-shard versions (world > 1): pull gathers every key from the GPU that owns it; push_turn applies this
+// worker's gradients to ONE shard, (rank + turn) % world; barrier is a stream-ordered rendezvous of all ranks.
+int server_pull_sharded_launch(whServer* s, cudaStream_t stream, const uint64_t* keys, size_t n, const unsigned* d_n, float* vals);
+int server_push_turn_launch(whServer* s, cudaStream_t stream, int turn, const uint64_t* keys, size_t n, const unsigned* d_n,
+                            long long* acc, const FixedScale* fs, float mul, unsigned copies, size_t stride);
+int server_barrier_launch(whServer* s, cudaStream_t stream);
 int server_push_acc_launch(whServer* s, cudaStream_t stream, const uint64_t* keys, size_t n, const unsigned* d_n, long long* acc,
                            const FixedScale* fs, float mul, unsigned copies, size_t stride);
 }  // namespace wh

@@ -146,6 +146,7 @@ int wh_worker_submit(whWorker* w, const whRowBlock* blk, int mem, size_t nnz, in
   const size_t rows = blk->size;
   WH_REQUIRE(rows > 0, "wh_worker_submit: empty minibatch");
   WH_REQUIRE(blk->offset && blk->index && blk->label, "wh_worker_submit: offset/index/label is NULL");
+  WH_REQUIRE(s->map.world == 1 || w->depth == 1, "wh_worker_submit: key-range shards on several GPUs run one minibatch at a time per rank (depth 1)");
   Lane& l = w->lane[w->next_ticket % w->depth];
   if (l.busy) {  // the lane's previous minibatch has not been collected: results would be lost
     set_error("wh_worker_submit: %d minibatches already in flight; wh_worker_wait the oldest first", w->depth);
@@ -186,7 +187,14 @@ int wh_worker_submit(whWorker* w, const whRowBlock* blk, int mem, size_t nnz, in
   else WH_TRY(localize_sort(cx, in, l.uniq.as<uint64_t>(), nullptr, l.index.as<uint32_t>(), d_nuniq));
   // ZPull: one Handle::Pull per unique key, after every earlier push
   if (w->have_pushed) WH_CUDA(cudaStreamWaitEvent(cx->stream, w->ev_pushed, 0));
-  WH_TRY(server_pull_launch(s, cx->stream, l.uniq.as<uint64_t>(), ucap, d_nuniq, l.w.as<float>()));
+  const bool sharded = s->map.world > 1;
+  if (sharded) {
+    // gather straight from the GPUs that own the keys; nobody may start pushing before everyone has pulled
+    WH_TRY(server_pull_sharded_launch(s, cx->stream, l.uniq.as<uint64_t>(), ucap, d_nuniq, l.w.as<float>()));
+    WH_TRY(server_barrier_launch(s, cx->stream));
+  } else {
+    WH_TRY(server_pull_launch(s, cx->stream, l.uniq.as<uint64_t>(), ucap, d_nuniq, l.w.as<float>()));
+  }
   WH_PROF(cx, "pull");
   // Init: Xw
   WH_CUDA(cudaMemsetAsync(l.xw.p, 0, rows * 4, cx->stream));
@@ -204,11 +212,19 @@ int wh_worker_submit(whWorker* w, const whRowBlock* blk, int mem, size_t nnz, in
     // CalcGrad: X^T dual into the fixed-point accumulator; ZPush: convert + update in one pass
     WH_TRY(spmv_trans_accumulate_launch(cx, rows, n, d_offset, l.index.as<uint32_t>(), d_value, l.dual.as<float>(), acc, fs, acc_copies(), ucap));
     WH_PROF(cx, "spmv_trans");
-    WH_TRY(server_push_acc_launch(s, cx->stream, l.uniq.as<uint64_t>(), ucap, d_nuniq, acc, fs,
-                                  w->loss == WH_LOSS_SQUARE_HINGE ? -2.f : 1.f, acc_copies(), ucap));
+    const float mul = w->loss == WH_LOSS_SQUARE_HINGE ? -2.f : 1.f;
+    if (sharded) {
+      for (int turn = 0; turn < s->map.world; ++turn) {   // turn k: this rank is the only writer of shard (rank+k)%world
+        WH_TRY(server_push_turn_launch(s, cx->stream, turn, l.uniq.as<uint64_t>(), ucap, d_nuniq, acc, fs, mul, acc_copies(), ucap));
+        WH_TRY(server_barrier_launch(s, cx->stream));
+      }
+      s->steps++;
+    } else {
+      WH_TRY(server_push_acc_launch(s, cx->stream, l.uniq.as<uint64_t>(), ucap, d_nuniq, acc, fs, mul, acc_copies(), ucap));
+    }
     WH_PROF(cx, "push");
   }
-  WH_CUDA(cudaMemcpyAsync(l.pinned + 256, s->counters.p, 16, cudaMemcpyDeviceToHost, cx->stream));
+  WH_CUDA(cudaMemcpyAsync(l.pinned + 256, s->counters.p, 24, cudaMemcpyDeviceToHost, cx->stream));
   WH_CUDA(cudaEventRecord(w->ev_pushed, cx->stream));
   w->have_pushed = true;
   // join the AUC branch, then the progress read-back
@@ -245,6 +261,11 @@ int wh_worker_wait(whWorker* w, uint64_t ticket, double* prog) {
     l.cx.prof.acc.clear();
   }
   const long long* cnt = reinterpret_cast<const long long*>(l.pinned + 256);
+  if (cnt[2]) {
+    WH_CUDA(cudaMemsetAsync(s->counters.as<long long>() + 2, 0, 8, l.cx.stream));
+    set_error("wh_worker: a barrier between the GPUs of this job timed out (%lld times): a rank is missing or behind", cnt[2]);
+    return WH_ERR_CUDA;
+  }
   if (cnt[1]) {
     WH_CUDA(cudaMemsetAsync(s->counters.as<long long>() + 1, 0, 8, l.cx.stream));
     set_error("wh_worker: %lld keys fall outside the server's range [%llu, %llu)", cnt[1],
