@@ -209,8 +209,9 @@ def run_ours(args):
             dist.all_gather_object(handles, srv.ipc_export())
             srv.ipc_attach(rank, world, MAX_KEY, handles)
             dist.barrier()
-            args.depth = 1
-            wk = capi.Worker(ctx, srv, capi.LOSS_LOGIT, MAX_KEY, depth=1)
+            # lanes still apply: every server interaction of a rank is chained through one CUDA event, so the
+            # barriers keep one global order; localize / staging / AUC of the next minibatch overlap
+            wk = capi.Worker(ctx, srv, capi.LOSS_LOGIT, MAX_KEY, depth=args.depth)
             sw = None
         else:
             wk = capi.Worker(ctx, None, capi.LOSS_LOGIT, MAX_KEY)
@@ -319,7 +320,7 @@ def run_ours(args):
                        "max_key": MAX_KEY, "unique_keys_per_row_r": round(r, 4), "pool_minibatches": pool_n,
                        "l2_policy": "inputs larger than L2 (pool of %d distinct minibatches, %.0f MB)" % (pool_n, pool_n * N * 8 / 1e6),
                        "parallelism": "key-range shards x%d" % world + ("" if world == 1 else " (" + args.exchange + ")"), "updater": FTRL,
-                       "minibatches_in_flight": args.depth if world == 1 else 1},
+                       "minibatches_in_flight": args.depth if (world == 1 or args.exchange == "p2p") else 1},
             "e2e": {"value": e2e, "unit": "examples/s", "h2d_bytes_per_step": N * 8 + (rows + 1) * 8 + rows * 4,
                     "d2h_bytes_per_step": 72 + 16},
             "gpu_launches": int(launches),

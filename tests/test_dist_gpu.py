@@ -129,8 +129,14 @@ def _p2p_rank_main(rank, world, port_no, out_dir, algo):
     dist.all_gather_object(handles, srv.ipc_export())
     srv.ipc_attach(rank, world, MAX_KEY, handles)
     dist.barrier()
-    wk = capi.Worker(ctx, srv, capi.LOSS_LOGIT, MAX_KEY)
-    progs = [wk.process_minibatch(minibatch(rank, s)) for s in range(STEPS)]
+    depth = 2 if algo == capi.ALGO_FTRL else 1       # FTRL case: two minibatches in flight per rank
+    wk = capi.Worker(ctx, srv, capi.LOSS_LOGIT, MAX_KEY, depth=depth)
+    progs, pending = [], []
+    for s in range(STEPS):
+        if len(pending) == depth:
+            progs.append(wk.wait(pending.pop(0)))
+        pending.append(wk.submit(minibatch(rank, s)))
+    progs += [wk.wait(t) for t in pending]
     dist.barrier()
     keys = np.arange(b, e, dtype=np.uint64)
     w, z, cg = srv.get_state(keys)

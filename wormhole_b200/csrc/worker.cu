@@ -146,7 +146,6 @@ int wh_worker_submit(whWorker* w, const whRowBlock* blk, int mem, size_t nnz, in
   const size_t rows = blk->size;
   WH_REQUIRE(rows > 0, "wh_worker_submit: empty minibatch");
   WH_REQUIRE(blk->offset && blk->index && blk->label, "wh_worker_submit: offset/index/label is NULL");
-  WH_REQUIRE(s->map.world == 1 || w->depth == 1, "wh_worker_submit: key-range shards on several GPUs run one minibatch at a time per rank (depth 1)");
   Lane& l = w->lane[w->next_ticket % w->depth];
   if (l.busy) {  // the lane's previous minibatch has not been collected: results would be lost
     set_error("wh_worker_submit: %d minibatches already in flight; wh_worker_wait the oldest first", w->depth);
