@@ -162,6 +162,7 @@ def segment_bytes(name, N, B, U, words):
         "loc_dir_clear": 8 * words,
         "pull": U * (8 + 4 + 4),                        # key read, weight gathered, weight written
         "spmv_times": 4 * N + 8 * B + 4 * B + 4 * U,    # local ids, offsets, Xw written, w gathered
+        "spmv_loss": 4 * N + 8 * B + 12 * B + 4 * U,    # the same pass + label read, dual written
         "loss_forward": 12 * B,                         # label, Xw read; dual written
         "auc": 8 * B,                                   # label, Xw read
         "spmv_trans": 4 * N + 8 * B + 4 * B + 8 * U,    # local ids, offsets, dual, accumulators

@@ -19,8 +19,6 @@
 
 namespace wh {
 
-__device__ __forceinline__ float exp_rn(float a) { return (float)exp((double)a); }
-__device__ __forceinline__ float log_rn(float a) { return (float)log((double)a); }
 
 __global__ void eval_reset_kernel(EvalOut* out) {
   out->objv = 0; out->logloss = 0; out->correct = 0; out->npos = 0; out->ngroups = 0;
@@ -38,16 +36,9 @@ loss_forward_kernel(int loss, size_t rows, const float* __restrict__ label, cons
   unsigned correct = 0;
   if (i < rows) {
     const float lab = label[i], p = xw[i];
-    const float y = lab > 0 ? 1.f : -1.f;
-    if (loss == WH_LOSS_LOGIT) {
-      if (dual) dual[i] = -y / (1.f + exp_rn(y * p));
-      objv = (double)log_rn(1.f + exp_rn(-y * p));
-    } else {  // WH_LOSS_SQUARE_HINGE, as written in the reference (active when the margin is > 1)
-      if (dual) dual[i] = y * ((y * p > 1.0f) ? 1.f : 0.f);
-      float t = fmaxf(1.f - y * p, 0.f);
-      objv = (double)(t * t);
-    }
-    correct = ((lab > 0 && p > 0.f) || (lab <= 0 && p <= 0.f)) ? 1u : 0u;
+    float dl;
+    loss_row(loss, lab, p, &dl, &objv, &correct);
+    if (dual) dual[i] = dl;
     if (want_logloss) {
       float yy = lab > 0 ? 1.f : 0.f;
       float q = 1.f / (1.f + exp_rn(-p));
@@ -76,18 +67,34 @@ loss_forward_kernel(int loss, size_t rows, const float* __restrict__ label, cons
 
 __global__ void __launch_bounds__(256)
 loss_reduce_kernel(unsigned nparts, const double* part_objv, const double* part_ll,
-                   const unsigned* part_correct, EvalOut* out) {
+                   const unsigned* part_correct, EvalOut* out, FixedScale* fs, float fs_scale, double fs_inv) {
   __shared__ double s_o[256], s_l[256];
   __shared__ unsigned long long s_c[256];
   double o = 0, l = 0; unsigned long long c = 0;
-  for (unsigned i = threadIdx.x; i < nparts; i += 256) { o += part_objv[i]; l += part_ll[i]; c += part_correct[i]; }
+  for (unsigned i = threadIdx.x; i < nparts; i += 256) { o += part_objv[i]; if (part_ll) l += part_ll[i]; c += part_correct[i]; }
   s_o[threadIdx.x] = o; s_l[threadIdx.x] = l; s_c[threadIdx.x] = c;
   __syncthreads();
   for (int s = 128; s > 0; s >>= 1) {
     if (threadIdx.x < s) { s_o[threadIdx.x] += s_o[threadIdx.x + s]; s_l[threadIdx.x] += s_l[threadIdx.x + s]; s_c[threadIdx.x] += s_c[threadIdx.x + s]; }
     __syncthreads();
   }
-  if (threadIdx.x == 0) { out->objv = s_o[0]; out->logloss = s_l[0]; out->correct = s_c[0]; }
+  if (threadIdx.x == 0) {
+    out->objv = s_o[0]; out->logloss = s_l[0]; out->correct = s_c[0];
+    out->npos = 0; out->ngroups = 0; out->area_lo = 0; out->ties = 0;   // the AUC kernel adds into these
+    if (fs) { fs->scale = fs_scale; fs->inv = fs_inv; }
+  }
+}
+
+int loss_reduce_launch(whContext* ctx, unsigned nparts, const double* po, const double* pl, const unsigned* pc,
+                       EvalOut* out, FixedScale* fs, size_t nnz) {
+  float sc = 1.f; double inv = 1.0;
+  if (fs) {   // terms bounded by 1 in magnitude: nnz * 1 * 2^e < 2^62 (same rule as fixed_scale_kernel)
+    int en = 0; while (en < 64 && ((unsigned long long)(nnz | 1) >> en)) ++en;
+    const int e = 61 - 1 - en;
+    sc = ldexpf(1.f, e); inv = ldexp(1.0, -e);
+  }
+  WH_LAUNCH(loss_reduce_kernel, 1, 256, 0, ctx->stream, nparts, po, pl, pc, out, fs, sc, inv);
+  return WH_OK;
 }
 
 int loss_forward_launch(whContext* ctx, int loss, size_t rows, const float* label, const float* xw,
@@ -100,7 +107,7 @@ int loss_forward_launch(whContext* ctx, int loss, size_t rows, const float* labe
   double* pl = po + nb;
   unsigned* pc = reinterpret_cast<unsigned*>(pl + nb);
   WH_LAUNCH(loss_forward_kernel, nb, 256, 0, ctx->stream, loss, rows, label, xw, dual, po, pl, pc, want_logloss);
-  WH_LAUNCH(loss_reduce_kernel, 1, 256, 0, ctx->stream, nb, po, pl, pc, out);
+  WH_LAUNCH(loss_reduce_kernel, 1, 256, 0, ctx->stream, nb, po, pl, pc, out, (FixedScale*)nullptr, 1.f, 1.0);
   return WH_OK;
 }
 

@@ -24,6 +24,36 @@ int auc_launch(whContext* ctx, size_t rows, const float* label, const float* xw,
 // the multi-launch radix-sort variant (any size); auc_launch uses it beyond 2^20 examples
 int auc_launch_multiblock(whContext* ctx, size_t rows, const float* label, const float* xw, EvalOut* out);
 
+#ifdef __CUDACC__
+// exp / log in fp64 rounded to fp32: the correctly rounded fp32 result in all but ~1e-9 of cases (what glibc's
+// expf / logf deliver on the reference's side)
+__device__ __forceinline__ float exp_rn(float a) { return (float)exp((double)a); }
+__device__ __forceinline__ float log_rn(float a) { return (float)log((double)a); }
+// One example: learn/linear/loss.h:109-113 (logit dual), :145-149 (squared hinge dual, as written: active when
+// the margin is > 1), :131-138 and binary_class_evaluation.h:66-74 (objective terms), :40-51 (accuracy).
+__device__ __forceinline__ void loss_row(int loss, float lab, float p, float* dual, double* objv, unsigned* correct) {
+  const float y = lab > 0 ? 1.f : -1.f;
+  if (loss == WH_LOSS_LOGIT) {
+    *dual = -y / (1.f + exp_rn(y * p));
+    *objv = (double)log_rn(1.f + exp_rn(-y * p));
+  } else {
+    *dual = y * ((y * p > 1.0f) ? 1.f : 0.f);
+    const float t = fmaxf(1.f - y * p, 0.f);
+    *objv = (double)(t * t);
+  }
+  *correct = ((lab > 0 && p > 0.f) || (lab <= 0 && p <= 0.f)) ? 1u : 0u;
+}
+#endif
+
+// Xw, the dual and the objective / accuracy partial sums in ONE pass over the rows (SpMV::Times with the loss as
+// its epilogue), then the one-block reduction. With fs != NULL the reduction also writes the fixed-point scale for
+// the transposed product that follows, for |dual| <= 1 and binary features (no max-reduction kernels needed).
+int spmv_loss_launch(whContext* ctx, int loss, size_t rows, size_t nnz, const size_t* offset, const uint32_t* index,
+                     const float* value, const float* label, const float* w, float* xw, float* dual, EvalOut* out,
+                     struct FixedScale* fs);
+int loss_reduce_launch(whContext* ctx, unsigned nparts, const double* po, const double* pl, const unsigned* pc,
+                       EvalOut* out, struct FixedScale* fs, size_t nnz);
+
 // Host-side closing arithmetic of binary_class_evaluation.h:36-38 and :49-50.
 struct EvalHost { double auc, auc_lo, auc_hi, acc, objv, logloss; };
 EvalHost eval_finish(const EvalOut& e, size_t rows);

@@ -1,6 +1,7 @@
 // Pieces (2) and (5): SpMV::Times / TransTimes and SpMM::Times / TransTimes. See spmv.cuh.
 #include <stdlib.h>
 
+#include "loss.cuh"
 #include "spmv.cuh"
 
 namespace wh {
@@ -60,6 +61,79 @@ spmv_times_kernel(size_t rows, const size_t* __restrict__ offset, const uint32_t
     for (size_t j = b; j < e; ++j) { float g = __ldg(x + index[j]); if (HAS_VAL) g *= value[j]; acc += g; }
   }
   y[r] = acc;
+}
+
+
+// SpMV::Times with the loss as its epilogue (learn/linear/loss.h:32-39 Init, then the per-example part of
+// Evaluate and CalcGrad): the thread that has just summed row i turns Xw[i] into dual[i] and adds the row's
+// objective term and accuracy flag to the block's partial sums. Same summation order as spmv_times_kernel.
+template <bool HAS_VAL>
+__global__ void __launch_bounds__(kRowsPerBlock)
+spmv_loss_kernel(int loss, size_t rows, const size_t* __restrict__ offset, const uint32_t* __restrict__ index,
+                 const float* __restrict__ value, const float* __restrict__ label, const float* __restrict__ x,
+                 float* __restrict__ y, float* __restrict__ dual, double* part_objv, unsigned* part_correct) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  __shared__ size_t s_off[kRowsPerBlock + 1];
+  __shared__ double s_o[kRowsPerBlock / 32];
+  __shared__ unsigned s_c[kRowsPerBlock / 32];
+  uint32_t* s_idx = reinterpret_cast<uint32_t*>(smem);
+  float* s_val = reinterpret_cast<float*>(smem + sizeof(uint32_t) * kTileCap);
+  const bool staged = stage_rows<HAS_VAL>(rows, offset, index, value, s_off, s_idx, s_val);
+  const size_t r = (size_t)blockIdx.x * kRowsPerBlock + threadIdx.x;
+  double objv = 0;
+  unsigned correct = 0;
+  if (r < rows) {
+    const size_t b = s_off[threadIdx.x], e = s_off[threadIdx.x + 1];
+    float acc = 0.f;
+    if (staged) {
+      const unsigned lb = (unsigned)(b - s_off[0]), le = (unsigned)(e - s_off[0]);
+      unsigned j = lb;
+      for (; j + 4 <= le; j += 4) {
+        float g0 = __ldg(x + s_idx[j]), g1 = __ldg(x + s_idx[j + 1]);
+        float g2 = __ldg(x + s_idx[j + 2]), g3 = __ldg(x + s_idx[j + 3]);
+        if (HAS_VAL) { g0 *= s_val[j]; g1 *= s_val[j + 1]; g2 *= s_val[j + 2]; g3 *= s_val[j + 3]; }
+        acc += g0; acc += g1; acc += g2; acc += g3;
+      }
+      for (; j < le; ++j) { float g = __ldg(x + s_idx[j]); if (HAS_VAL) g *= s_val[j]; acc += g; }
+    } else {
+      for (size_t j = b; j < e; ++j) { float g = __ldg(x + index[j]); if (HAS_VAL) g *= value[j]; acc += g; }
+    }
+    y[r] = acc;   // rows without entries: Xw_ starts zeroed in ScalarLoss::Init (vector::resize)
+    float dl;
+    loss_row(loss, label[r], acc, &dl, &objv, &correct);
+    if (dual) dual[r] = dl;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    objv += __shfl_down_sync(0xffffffffu, objv, o);
+    correct += __shfl_down_sync(0xffffffffu, correct, o);
+  }
+  if ((threadIdx.x & 31) == 0) { s_o[threadIdx.x >> 5] = objv; s_c[threadIdx.x >> 5] = correct; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double o = 0; unsigned c = 0;
+    for (int w = 0; w < kRowsPerBlock / 32; ++w) { o += s_o[w]; c += s_c[w]; }
+    part_objv[blockIdx.x] = o; part_correct[blockIdx.x] = c;
+  }
+}
+
+int spmv_loss_launch(whContext* ctx, int loss, size_t rows, size_t nnz, const size_t* offset, const uint32_t* index,
+                     const float* value, const float* label, const float* w, float* xw, float* dual, EvalOut* out,
+                     FixedScale* fs) {
+  if (rows == 0) return loss_reduce_launch(ctx, 0, nullptr, nullptr, nullptr, out, fs, nnz);
+  const unsigned grid = (unsigned)div_up(rows, kRowsPerBlock);
+  WH_TRY(ctx->stage[7].reserve((size_t)grid * 16 + 64));
+  double* po = ctx->stage[7].as<double>();
+  unsigned* pc = reinterpret_cast<unsigned*>(po + grid);
+  if (value) {
+    const size_t smem = kTileCap * 8;
+    static bool attr = false;
+    if (!attr) { WH_CUDA(cudaFuncSetAttribute(spmv_loss_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); attr = true; }
+    WH_LAUNCH(spmv_loss_kernel<true>, grid, kRowsPerBlock, smem, ctx->stream, loss, rows, offset, index, value, label, w, xw, dual, po, pc);
+  } else {
+    WH_LAUNCH(spmv_loss_kernel<false>, grid, kRowsPerBlock, kTileCap * 4, ctx->stream, loss, rows, offset, index, value, label, w, xw, dual, po, pc);
+  }
+  return loss_reduce_launch(ctx, grid, po, nullptr, pc, out, fs, nnz);
 }
 
 int spmv_times_launch(whContext* ctx, size_t rows, const size_t* offset, const uint32_t* index,
@@ -217,8 +291,8 @@ int fixed_prepare(whContext* ctx, FixedScale* fs, const float* x, size_t nx, con
 // Scale selection + accumulation only; the caller converts (fixed_finish or the fused push).
 int spmv_trans_accumulate_launch(whContext* ctx, size_t rows, size_t nnz, const size_t* offset,
                                  const uint32_t* index, const float* value, const float* x,
-                                 long long* acc, FixedScale* fs, unsigned copies, size_t stride) {
-  WH_TRY(fixed_prepare(ctx, fs, x, rows, value, nnz, 1));
+                                 long long* acc, FixedScale* fs, unsigned copies, size_t stride, bool scale_ready) {
+  if (!scale_ready) WH_TRY(fixed_prepare(ctx, fs, x, rows, value, nnz, 1));
   const unsigned grid = (unsigned)div_up(rows, kRowsPerBlock);
   static int mode = -1;   // WH_TRANS_MODE=0 (default): one atomic per entry; 1: merged within the warp first
                           // (measured: merging costs more instructions than the atomics it saves)
@@ -253,7 +327,7 @@ int spmv_trans_times_launch(whContext* ctx, size_t rows, size_t nnz, const size_
                             const uint32_t* index, const float* value, const float* x, float* y,
                             size_t ysize, long long* acc, FixedScale* fs, float mul, unsigned copies) {
   if (ysize == 0) return WH_OK;
-  WH_TRY(spmv_trans_accumulate_launch(ctx, rows, nnz, offset, index, value, x, acc, fs, copies, ysize));
+  WH_TRY(spmv_trans_accumulate_launch(ctx, rows, nnz, offset, index, value, x, acc, fs, copies, ysize, false));
   const unsigned g2 = (unsigned)std::min<size_t>(div_up(ysize, 256), (size_t)ctx->num_sms * 8);
   WH_LAUNCH(fixed_finish_kernel, g2, 256, 0, ctx->stream, acc, ysize, fs, 0.f, (const float*)nullptr, y, mul, copies, ysize);
   return WH_OK;

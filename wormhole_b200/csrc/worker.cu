@@ -22,7 +22,7 @@
 namespace wh {
 int spmv_trans_accumulate_launch(whContext* ctx, size_t rows, size_t nnz, const size_t* offset,
                                  const uint32_t* index, const float* value, const float* x,
-                                 long long* acc, FixedScale* fs, unsigned copies, size_t stride);
+                                 long long* acc, FixedScale* fs, unsigned copies, size_t stride, bool scale_ready = false);
 int fixed_finish_launch(whContext* ctx, long long* acc, size_t n, const FixedScale* fs, float* y, float mul,
                         unsigned copies, size_t stride);
 constexpr int kMaxDepth = 8;
@@ -195,13 +195,12 @@ int wh_worker_submit(whWorker* w, const whRowBlock* blk, int mem, size_t nnz, in
     WH_TRY(server_pull_launch(s, cx->stream, l.uniq.as<uint64_t>(), ucap, d_nuniq, l.w.as<float>()));
   }
   WH_PROF(cx, "pull");
-  // Init: Xw
-  WH_CUDA(cudaMemsetAsync(l.xw.p, 0, rows * 4, cx->stream));
-  WH_TRY(spmv_times_launch(cx, rows, d_offset, l.index.as<uint32_t>(), d_value, l.w.as<float>(), l.xw.as<float>()));
-  WH_PROF(cx, "spmv_times");
-  // Evaluate (+ the dual of CalcGrad, which falls out of the same pass)
-  WH_TRY(loss_forward_launch(cx, w->loss, rows, d_label, l.xw.as<float>(), train ? l.dual.as<float>() : nullptr, d_eval, 0));
-  WH_PROF(cx, "loss_forward");
+  // Init (Xw), the per-example part of Evaluate, and the dual of CalcGrad: one pass over the rows. With
+  // binary features |dual| <= 1 bounds every term of X^T dual, so the fixed-point scale is known up front.
+  const bool scale_ready = d_value == nullptr;
+  WH_TRY(spmv_loss_launch(cx, w->loss, rows, n, d_offset, l.index.as<uint32_t>(), d_value, d_label, l.w.as<float>(),
+                          l.xw.as<float>(), train ? l.dual.as<float>() : nullptr, d_eval, (train && scale_ready) ? fs : nullptr));
+  WH_PROF(cx, "spmv_loss");
   // AUC on the side stream (nothing downstream of it but the progress numbers)
   WH_CUDA(cudaEventRecord(l.ev_fork, cx->stream));
   WH_CUDA(cudaStreamWaitEvent(l.ax.stream, l.ev_fork, 0));
@@ -209,7 +208,7 @@ int wh_worker_submit(whWorker* w, const whRowBlock* blk, int mem, size_t nnz, in
   WH_CUDA(cudaEventRecord(l.ev_auc, l.ax.stream));
   if (train) {
     // CalcGrad: X^T dual into the fixed-point accumulator; ZPush: convert + update in one pass
-    WH_TRY(spmv_trans_accumulate_launch(cx, rows, n, d_offset, l.index.as<uint32_t>(), d_value, l.dual.as<float>(), acc, fs, acc_copies(), ucap));
+    WH_TRY(spmv_trans_accumulate_launch(cx, rows, n, d_offset, l.index.as<uint32_t>(), d_value, l.dual.as<float>(), acc, fs, acc_copies(), ucap, scale_ready));
     WH_PROF(cx, "spmv_trans");
     const float mul = w->loss == WH_LOSS_SQUARE_HINGE ? -2.f : 1.f;
     if (sharded) {
