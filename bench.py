@@ -213,6 +213,10 @@ def run_ours(args):
             # lanes still apply: every server interaction of a rank is chained through one CUDA event, so the
             # barriers keep one global order; localize / staging / AUC of the next minibatch overlap
             wk = capi.Worker(ctx, srv, capi.LOSS_LOGIT, MAX_KEY, depth=args.depth)
+            boxes = [None] * world
+            dist.all_gather_object(boxes, wk.ipc_export(min(rows * NNZ_PER_ROW, MAX_KEY)))
+            wk.ipc_attach(boxes)
+            dist.barrier()
             sw = None
         else:
             wk = capi.Worker(ctx, None, capi.LOSS_LOGIT, MAX_KEY)

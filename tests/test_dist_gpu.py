@@ -114,7 +114,7 @@ def test_two_gpus_match_the_cpu_simulation(tmp_path):
 
 # ---- shards mapped over NVLink (CUDA IPC): no message exchange, push in turns ---------------------
 
-def _p2p_rank_main(rank, world, port_no, out_dir, algo):
+def _p2p_rank_main(rank, world, port_no, out_dir, algo, owner_push):
     import torch
     import torch.distributed as dist
     from wormhole_b200 import capi
@@ -131,6 +131,11 @@ def _p2p_rank_main(rank, world, port_no, out_dir, algo):
     dist.barrier()
     depth = 2 if algo == capi.ALGO_FTRL else 1       # FTRL case: two minibatches in flight per rank
     wk = capi.Worker(ctx, srv, capi.LOSS_LOGIT, MAX_KEY, depth=depth)
+    if owner_push:      # outboxes: the owners read each source's slice and apply it (2 barriers per step)
+        boxes = [None] * world
+        dist.all_gather_object(boxes, wk.ipc_export(3000 * 12))
+        wk.ipc_attach(boxes)
+        dist.barrier()
     progs, pending = [], []
     for s in range(STEPS):
         if len(pending) == depth:
@@ -146,8 +151,9 @@ def _p2p_rank_main(rank, world, port_no, out_dir, algo):
     dist.destroy_process_group()
 
 
+@pytest.mark.parametrize("owner_push", [False, True])
 @pytest.mark.parametrize("algo_name", ["FTRL", "SGD"])
-def test_two_gpus_peer_mapped_shards(tmp_path, algo_name):
+def test_two_gpus_peer_mapped_shards(tmp_path, algo_name, owner_push):
     import torch
     if torch.cuda.device_count() < 2:
         pytest.skip("needs two GPUs (gpurun --gpus 2)")
@@ -158,9 +164,10 @@ def test_two_gpus_peer_mapped_shards(tmp_path, algo_name):
     algo = {"FTRL": capi.ALGO_FTRL, "SGD": capi.ALGO_SGD}[algo_name]
     s = socket.socket(); s.bind(("127.0.0.1", 0)); port_no = s.getsockname()[1]; s.close()
     world = 2
-    mp.spawn(_p2p_rank_main, args=(world, port_no, str(tmp_path), algo), nprocs=world, join=True)
+    mp.spawn(_p2p_rank_main, args=(world, port_no, str(tmp_path), algo, owner_push), nprocs=world, join=True)
     # CPU checker, same order: all pulls of a step see the model as of the previous step; shard s then takes
-    # the pushes of sources s, s-1, ... (mod world), one handle update each
+    # the pushes one handle update each -- of sources s, s-1, ... (mod world) when the workers push in turns, of
+    # sources 0, 1, ... when the owners read the workers' outboxes
     chk = O.best()
     bounds = [key_range(r, world, MAX_KEY)[0] for r in range(world)] + [MAX_KEY]
     W, Z, CG = (np.zeros(MAX_KEY, np.float32) for _ in range(3))
@@ -174,7 +181,7 @@ def test_two_gpus_peer_mapped_shards(tmp_path, algo_name):
             msgs.append((keys, grad, np.searchsorted(keys, bounds)))
         for sidx in range(world):
             for k in range(world):
-                keys, grad, cut = msgs[(sidx - k) % world]
+                keys, grad, cut = msgs[k if owner_push else (sidx - k) % world]
                 sl = slice(cut[sidx], cut[sidx + 1])
                 w, z, cg = W[keys[sl]].copy(), Z[keys[sl]].copy(), CG[keys[sl]].copy()
                 _, t[sidx] = chk.handle_push(algo, L1, L2, ETA, BETA, grad[sl].copy(), w, z, cg, t[sidx])

@@ -363,6 +363,14 @@ class Worker:
         self._keep[t.value] = blk   # the arrays must outlive the call
         return t.value
 
+    def ipc_export(self, max_uniq):
+        buf = C.create_string_buffer(64 * self.depth)
+        _check(lib().wh_worker_ipc_export(self.h, C.c_size_t(max_uniq), buf))
+        return buf.raw
+
+    def ipc_attach(self, handles):
+        _check(lib().wh_worker_ipc_attach(self.h, b"".join(handles)))
+
     def begin(self, blk, mem=WH_HOST, nnz=0):
         """First half of ProcessMinibatch (Localize). -> (device address of the ascending unique keys, U)."""
         p, n = C.c_void_p(), C.c_size_t()

@@ -252,6 +252,51 @@ __global__ void shard_barrier_kernel(ShardMap m, unsigned long long epoch, long 
   __threadfence_system();
 }
 
+static HandleParams make_params(whServer* s, bool start_push);
+
+// A worker's outbox: {header: U at word 0, slice cuts at words 4..4+world} | keys[cap] | grads[cap].
+// The owner of a key range applies, for one source rank, the slice of that rank's (key, gradient) list that
+// falls into its range -- read directly from the source GPU's memory. One launch per source, in ascending
+// source order: each is one push message for this shard's handle.
+__global__ void __launch_bounds__(256)
+server_apply_from_kernel(HandleParams h, void* table, const unsigned char* outbox, size_t cap, int me, long long* counters) {
+  const volatile unsigned* hdr = reinterpret_cast<const volatile unsigned*>(outbox);
+  const unsigned lo = hdr[4 + me], hi = hdr[4 + me + 1];
+  const uint64_t* keys = reinterpret_cast<const uint64_t*>(outbox + 256);
+  const float* grads = reinterpret_cast<const float*>(outbox + 256 + cap * 8);
+  int delta = 0, bad = 0;
+  for (size_t i = lo + (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += (size_t)gridDim.x * blockDim.x) {
+    const uint64_t k = keys[i];
+    if (k >= h.key_begin && k < h.key_end) delta += handle_push(h, table, k - h.key_begin, grads[i]);
+    else bad = 1;
+  }
+  commit_counters(counters, delta, bad);
+}
+
+// cuts[g] = first position in the ascending key list whose key is >= bounds[g]
+__global__ void outbox_cuts_kernel(unsigned char* outbox, ShardMap m) {
+  unsigned* hdr = reinterpret_cast<unsigned*>(outbox);
+  const uint64_t* keys = reinterpret_cast<const uint64_t*>(outbox + 256);
+  const unsigned U = hdr[0];
+  const int g = threadIdx.x;
+  if (g > m.world) return;
+  unsigned lo = 0, hi = U;
+  const uint64_t b = m.bounds[g];
+  while (lo < hi) { unsigned mid = (lo + hi) >> 1; if (keys[mid] < b) lo = mid + 1; else hi = mid; }
+  hdr[4 + g] = (g == m.world) ? U : lo;
+}
+
+int server_apply_from_launch(whServer* s, cudaStream_t stream, const unsigned char* outbox, size_t cap) {
+  HandleParams h = make_params(s, true);   // one push message: SGD's t advances even for an empty slice
+  WH_LAUNCH(server_apply_from_kernel, (unsigned)(s->ctx->num_sms * 2), 256, 0, stream, h, s->table.p, outbox, cap,
+            s->map.rank, s->counters.as<long long>());
+  return WH_OK;
+}
+int outbox_cuts_launch(whServer* s, cudaStream_t stream, unsigned char* outbox) {
+  WH_LAUNCH(outbox_cuts_kernel, 1, 32, 0, stream, outbox, s->map);
+  return WH_OK;
+}
+
 int server_pull_sharded_launch(whServer* s, cudaStream_t stream, const uint64_t* keys, size_t n, const unsigned* d_n, float* vals) {
   if (n == 0) return WH_OK;
   WH_LAUNCH(server_pull_sharded_kernel, (unsigned)div_up(n, 256), 256, 0, stream, s->algo, s->map,

@@ -45,6 +45,9 @@ int server_pull_sharded_launch(whServer* s, cudaStream_t stream, const uint64_t*
 int server_push_turn_launch(whServer* s, cudaStream_t stream, int turn, const uint64_t* keys, size_t n, const unsigned* d_n,
                             long long* acc, const FixedScale* fs, float mul, unsigned copies, size_t stride);
 int server_barrier_launch(whServer* s, cudaStream_t stream);
+// owner-side application of one source rank's outbox slice; cuts of an outbox for all destinations
+int server_apply_from_launch(whServer* s, cudaStream_t stream, const unsigned char* outbox, size_t cap);
+int outbox_cuts_launch(whServer* s, cudaStream_t stream, unsigned char* outbox);
 int server_push_acc_launch(whServer* s, cudaStream_t stream, const uint64_t* keys, size_t n, const unsigned* d_n, long long* acc,
                            const FixedScale* fs, float mul, unsigned copies, size_t stride);
 }  // namespace wh

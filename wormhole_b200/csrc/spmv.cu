@@ -252,7 +252,8 @@ spmv_trans_agg_kernel(size_t rows, const size_t* __restrict__ offset, const uint
 // y = fixed-point sum back to fp32 (+ p*z for SpMM); clears the accumulator for the next call.
 __global__ void fixed_finish_kernel(long long* acc, size_t n, const FixedScale* __restrict__ fs,
                                     float p, const float* __restrict__ z, float* __restrict__ y,
-                                    float mul, unsigned copies, size_t stride) {
+                                    float mul, unsigned copies, size_t stride, const unsigned* d_n) {
+  if (d_n) n = *d_n;   // the count may live on the device (number of unique keys of a minibatch)
   const double inv = fs->inv;
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
     long long a = 0;
@@ -316,10 +317,10 @@ int spmv_trans_accumulate_launch(whContext* ctx, size_t rows, size_t nnz, const 
 
 // Accumulator -> fp32 (and clear), for callers that ran spmv_trans_accumulate_launch themselves.
 int fixed_finish_launch(whContext* ctx, long long* acc, size_t n, const FixedScale* fs, float* y, float mul,
-                        unsigned copies, size_t stride) {
+                        unsigned copies, size_t stride, const unsigned* d_n) {
   if (n == 0) return WH_OK;
   const unsigned g2 = (unsigned)std::min<size_t>(div_up(n, 256), (size_t)ctx->num_sms * 8);
-  WH_LAUNCH(fixed_finish_kernel, g2, 256, 0, ctx->stream, acc, n, fs, 0.f, (const float*)nullptr, y, mul, copies, stride);
+  WH_LAUNCH(fixed_finish_kernel, g2, 256, 0, ctx->stream, acc, n, fs, 0.f, (const float*)nullptr, y, mul, copies, stride, d_n);
   return WH_OK;
 }
 
@@ -329,7 +330,7 @@ int spmv_trans_times_launch(whContext* ctx, size_t rows, size_t nnz, const size_
   if (ysize == 0) return WH_OK;
   WH_TRY(spmv_trans_accumulate_launch(ctx, rows, nnz, offset, index, value, x, acc, fs, copies, ysize, false));
   const unsigned g2 = (unsigned)std::min<size_t>(div_up(ysize, 256), (size_t)ctx->num_sms * 8);
-  WH_LAUNCH(fixed_finish_kernel, g2, 256, 0, ctx->stream, acc, ysize, fs, 0.f, (const float*)nullptr, y, mul, copies, ysize);
+  WH_LAUNCH(fixed_finish_kernel, g2, 256, 0, ctx->stream, acc, ysize, fs, 0.f, (const float*)nullptr, y, mul, copies, ysize, (const unsigned*)nullptr);
   return WH_OK;
 }
 
@@ -386,7 +387,7 @@ int spmm_trans_times_launch(whContext* ctx, size_t rows, size_t nnz, const size_
   WH_TRY(fixed_prepare(ctx, fs, x, rows * dim, value, nnz, 1));
   if (rows) WH_LAUNCH(spmm_trans_kernel, (unsigned)div_up(rows * dim, 256), 256, 0, ctx->stream, rows, offset, index, value, x, dim, acc, fs);
   const unsigned g2 = (unsigned)std::min<size_t>(div_up(ysize, 256), (size_t)ctx->num_sms * 8);
-  WH_LAUNCH(fixed_finish_kernel, g2, 256, 0, ctx->stream, acc, ysize, fs, p, (z && p != 0.f) ? z : (const float*)nullptr, y, 1.f, 1u, ysize);
+  WH_LAUNCH(fixed_finish_kernel, g2, 256, 0, ctx->stream, acc, ysize, fs, p, (z && p != 0.f) ? z : (const float*)nullptr, y, 1.f, 1u, ysize, (const unsigned*)nullptr);
   return WH_OK;
 }
 

@@ -24,7 +24,7 @@ int spmv_trans_accumulate_launch(whContext* ctx, size_t rows, size_t nnz, const 
                                  const uint32_t* index, const float* value, const float* x,
                                  long long* acc, FixedScale* fs, unsigned copies, size_t stride, bool scale_ready = false);
 int fixed_finish_launch(whContext* ctx, long long* acc, size_t n, const FixedScale* fs, float* y, float mul,
-                        unsigned copies, size_t stride);
+                        unsigned copies, size_t stride, const unsigned* d_n = nullptr);
 constexpr int kMaxDepth = 8;
 
 struct Lane {
@@ -34,6 +34,7 @@ struct Lane {
   DevBuf in_index, in_offset, in_value, in_label;   // staged host input
   DevBuf uniq, index, w, xw, dual, scal;
   char* pinned = nullptr;    // 512 B of the worker's pinned block
+  DevBuf outbox;             // sharded jobs: {U, cuts | keys | grads}, mapped by every peer
   bool busy = false, train = false;
   size_t rows = 0;
   // state between wh_worker_begin and wh_worker_finish
@@ -54,6 +55,10 @@ struct whWorker {
   wh::PinnedBuf pinned;
   cudaEvent_t ev_pushed = nullptr;   // completion of the most recent push (or evaluation pull)
   bool have_pushed = false;
+  // sharded jobs: every rank's lane outboxes, [rank][lane] (own ones included); 0 capacity = not attached
+  size_t outbox_cap = 0;
+  unsigned char* peer_outbox[wh::kMaxShards][wh::kMaxDepth] = {{nullptr}};
+  void* opened[wh::kMaxShards * wh::kMaxDepth] = {nullptr};
   unsigned long long next_ticket = 1, next_wait = 1;
   long long seen_new_w = 0;
 };
@@ -62,7 +67,7 @@ using namespace wh;
 
 static void lane_release(Lane& l) {
   for (DevBuf* b : {&l.in_index, &l.in_offset, &l.in_value, &l.in_label, &l.uniq, &l.index, &l.w, &l.xw, &l.dual,
-                    &l.scal, &l.cx.directory, &l.cx.scan_tmp, &l.cx.acc, &l.cx.small, &l.ax.scan_tmp, &l.ax.small})
+                    &l.scal, &l.outbox, &l.cx.directory, &l.cx.scan_tmp, &l.cx.acc, &l.cx.small, &l.ax.scan_tmp, &l.ax.small})
     b->release();
   for (auto& b : l.cx.sort_tmp) b.release();
   for (auto& b : l.ax.sort_tmp) b.release();
@@ -127,6 +132,7 @@ int wh_worker_destroy(whWorker* w) {
     cudaStreamSynchronize(w->lane[i].cx.stream);
     cudaStreamSynchronize(w->lane[i].ax.stream);
   }
+  for (void* p : w->opened) if (p) cudaIpcCloseMemHandle(p);
   for (int i = 0; i < w->depth; ++i) lane_release(w->lane[i]);
   if (w->ev_pushed) cudaEventDestroy(w->ev_pushed);
   w->pinned.release();
@@ -171,9 +177,15 @@ int wh_worker_submit(whWorker* w, const whRowBlock* blk, int mem, size_t nnz, in
   WH_TRY(to_device(cx, l.in_label, blk->label, rows, mem, &d_label));
 
   const size_t ucap = (size_t)std::min<uint64_t>(n, w->max_key);
-  WH_TRY(l.uniq.reserve(ucap * 8)); WH_TRY(l.index.reserve(n * 4)); WH_TRY(l.w.reserve(ucap * 4));
+  const bool outboxed = w->outbox_cap != 0 && s->map.world > 1;
+  WH_REQUIRE(!outboxed || ucap <= w->outbox_cap, "wh_worker_submit: %zu possible unique keys exceed the outbox capacity %zu given to wh_worker_ipc_export",
+             ucap, w->outbox_cap);
+  if (!outboxed) WH_TRY(l.uniq.reserve(ucap * 8));
+  WH_TRY(l.index.reserve(n * 4)); WH_TRY(l.w.reserve(ucap * 4));
   WH_TRY(l.xw.reserve(rows * 4)); WH_TRY(l.dual.reserve(rows * 4));
-  unsigned* d_nuniq = l.scal.as<unsigned>();
+  // sharded jobs keep the key list, its count and the gradients in the lane's outbox, where the owners read them
+  uint64_t* uniq = outboxed ? reinterpret_cast<uint64_t*>(l.outbox.as<unsigned char>() + 256) : l.uniq.as<uint64_t>();
+  unsigned* d_nuniq = outboxed ? l.outbox.as<unsigned>() : l.scal.as<unsigned>();
   FixedScale* fs = reinterpret_cast<FixedScale*>(l.scal.as<char>() + 256);
   EvalOut* d_eval = reinterpret_cast<EvalOut*>(l.scal.as<char>() + 512);
   long long* acc = nullptr;
@@ -182,17 +194,18 @@ int wh_worker_submit(whWorker* w, const whRowBlock* blk, int mem, size_t nnz, in
   WH_TRY(prof_begin(cx));
   // Localize
   LocInput in{d_index, n, make_xform(w->max_key)};
-  if (direct) WH_TRY(localize_direct(cx, in, l.uniq.as<uint64_t>(), nullptr, l.index.as<uint32_t>(), d_nuniq));
-  else WH_TRY(localize_sort(cx, in, l.uniq.as<uint64_t>(), nullptr, l.index.as<uint32_t>(), d_nuniq));
+  if (direct) WH_TRY(localize_direct(cx, in, uniq, nullptr, l.index.as<uint32_t>(), d_nuniq));
+  else WH_TRY(localize_sort(cx, in, uniq, nullptr, l.index.as<uint32_t>(), d_nuniq));
+  if (outboxed) WH_TRY(outbox_cuts_launch(s, cx->stream, l.outbox.as<unsigned char>()));
   // ZPull: one Handle::Pull per unique key, after every earlier push
   if (w->have_pushed) WH_CUDA(cudaStreamWaitEvent(cx->stream, w->ev_pushed, 0));
   const bool sharded = s->map.world > 1;
   if (sharded) {
     // gather straight from the GPUs that own the keys; nobody may start pushing before everyone has pulled
-    WH_TRY(server_pull_sharded_launch(s, cx->stream, l.uniq.as<uint64_t>(), ucap, d_nuniq, l.w.as<float>()));
-    WH_TRY(server_barrier_launch(s, cx->stream));
+    WH_TRY(server_pull_sharded_launch(s, cx->stream, uniq, ucap, d_nuniq, l.w.as<float>()));
+    if (!outboxed || !train) WH_TRY(server_barrier_launch(s, cx->stream));
   } else {
-    WH_TRY(server_pull_launch(s, cx->stream, l.uniq.as<uint64_t>(), ucap, d_nuniq, l.w.as<float>()));
+    WH_TRY(server_pull_launch(s, cx->stream, uniq, ucap, d_nuniq, l.w.as<float>()));
   }
   WH_PROF(cx, "pull");
   // Init (Xw), the per-example part of Evaluate, and the dual of CalcGrad: one pass over the rows. With
@@ -211,14 +224,26 @@ int wh_worker_submit(whWorker* w, const whRowBlock* blk, int mem, size_t nnz, in
     WH_TRY(spmv_trans_accumulate_launch(cx, rows, n, d_offset, l.index.as<uint32_t>(), d_value, l.dual.as<float>(), acc, fs, acc_copies(), ucap, scale_ready));
     WH_PROF(cx, "spmv_trans");
     const float mul = w->loss == WH_LOSS_SQUARE_HINGE ? -2.f : 1.f;
-    if (sharded) {
+    if (outboxed) {
+      // owners apply: gradients go to the outbox as fp32; once every rank has pulled and filled its outbox
+      // (barrier), each owner walks the source ranks in ascending order -- one push message each -- reading its
+      // slice straight from the source GPU; a second barrier keeps outboxes and tables stable until all are done
+      float* ob_grads = reinterpret_cast<float*>(l.outbox.as<unsigned char>() + 256 + w->outbox_cap * 8);
+      WH_TRY(fixed_finish_launch(cx, acc, ucap, fs, ob_grads, mul, acc_copies(), ucap, d_nuniq));
+      WH_TRY(server_barrier_launch(s, cx->stream));
+      const int lane_idx = (int)(&l - w->lane);
+      for (int src = 0; src < s->map.world; ++src)
+        WH_TRY(server_apply_from_launch(s, cx->stream, w->peer_outbox[src][lane_idx], w->outbox_cap));
+      WH_TRY(server_barrier_launch(s, cx->stream));
+      s->steps++;
+    } else if (sharded) {
       for (int turn = 0; turn < s->map.world; ++turn) {   // turn k: this rank is the only writer of shard (rank+k)%world
-        WH_TRY(server_push_turn_launch(s, cx->stream, turn, l.uniq.as<uint64_t>(), ucap, d_nuniq, acc, fs, mul, acc_copies(), ucap));
+        WH_TRY(server_push_turn_launch(s, cx->stream, turn, uniq, ucap, d_nuniq, acc, fs, mul, acc_copies(), ucap));
         WH_TRY(server_barrier_launch(s, cx->stream));
       }
       s->steps++;
     } else {
-      WH_TRY(server_push_acc_launch(s, cx->stream, l.uniq.as<uint64_t>(), ucap, d_nuniq, acc, fs, mul, acc_copies(), ucap));
+      WH_TRY(server_push_acc_launch(s, cx->stream, uniq, ucap, d_nuniq, acc, fs, mul, acc_copies(), ucap));
     }
     WH_PROF(cx, "push");
   }
@@ -274,6 +299,42 @@ int wh_worker_wait(whWorker* w, uint64_t ticket, double* prog) {
   prog[0] = h.objv; prog[1] = h.acc; prog[2] = h.auc; prog[3] = 1; prog[4] = (double)l.rows;
   prog[5] = (double)(cnt[0] - w->seen_new_w);
   w->seen_new_w = cnt[0];
+  return WH_OK;
+}
+
+// ---- outboxes of a sharded job -----------------------------------------------------------------------
+
+int wh_worker_ipc_export(whWorker* w, size_t max_uniq, void* handles) {
+  WH_REQUIRE(w && handles && max_uniq > 0, "wh_worker_ipc_export: bad argument");
+  WH_REQUIRE(w->server && w->outbox_cap == 0, "wh_worker_ipc_export: needs a worker with a local server, once");
+  DeviceGuard g(w->ctx->device);
+  cudaIpcMemHandle_t* h = reinterpret_cast<cudaIpcMemHandle_t*>(handles);
+  for (int i = 0; i < w->depth; ++i) {
+    Lane& l = w->lane[i];
+    WH_TRY(l.outbox.reserve(256 + max_uniq * 12));
+    WH_CUDA(cudaMemsetAsync(l.outbox.p, 0, 256, w->ctx->stream));
+    WH_CUDA(cudaIpcGetMemHandle(&h[i], l.outbox.p));
+  }
+  WH_CUDA(cudaStreamSynchronize(w->ctx->stream));
+  w->outbox_cap = max_uniq;
+  return WH_OK;
+}
+
+int wh_worker_ipc_attach(whWorker* w, const void* handles) {
+  WH_REQUIRE(w && handles && w->server, "wh_worker_ipc_attach: bad argument");
+  WH_REQUIRE(w->outbox_cap != 0, "wh_worker_ipc_attach: call wh_worker_ipc_export first");
+  const ShardMap& m = w->server->map;
+  WH_REQUIRE(m.world > 1, "wh_worker_ipc_attach: attach the server to its peers first (wh_server_ipc_attach)");
+  DeviceGuard g(w->ctx->device);
+  const cudaIpcMemHandle_t* h = reinterpret_cast<const cudaIpcMemHandle_t*>(handles);
+  for (int r = 0; r < m.world; ++r)
+    for (int i = 0; i < w->depth; ++i) {
+      if (r == m.rank) { w->peer_outbox[r][i] = w->lane[i].outbox.as<unsigned char>(); continue; }
+      void* p = nullptr;
+      WH_CUDA(cudaIpcOpenMemHandle(&p, h[r * w->depth + i], cudaIpcMemLazyEnablePeerAccess));
+      w->opened[r * kMaxDepth + i] = p;
+      w->peer_outbox[r][i] = static_cast<unsigned char*>(p);
+    }
   return WH_OK;
 }
 
