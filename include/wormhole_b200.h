@@ -198,6 +198,13 @@ WH_API int wh_server_get_state(whServer* s, const uint64_t* keys, size_t n, int 
                                float* sq_cum_grad);
 WH_API int wh_server_set_state(whServer* s, const uint64_t* keys, size_t n, int mem, const float* w,
                                const float* z, const float* sq_cum_grad);
+/* AsgdServer::SaveModel / LoadModel (learn/linear/async_sgd.h:215-223 -> KVStore::Save/Load -> Entry::Save/Load,
+ * :59-66): one {uint64 key, float w} record per entry with w != 0, ascending keys (ps-lite's own record framing is
+ * not in the reference tree). The caller names the file as IterServer::ModelName does
+ * (<model_out>[_iter-k]_part-<rank>, learn/solver/iter_solver.h:115-119). Load restores w only and counts it in
+ * |w|_0, as TLoad does; optimizer state is not checkpointed by the reference either. */
+WH_API int wh_server_save(whServer* s, const char* path);
+WH_API int wh_server_load(whServer* s, const char* path);
 /* SGDHandle::t (learn/linear/async_sgd.h:100). */
 WH_API int wh_server_sgd_t(const whServer* s);
 /* Key-range shards on several GPUs of one box (one process per GPU). ps-lite gives server g an even slice of
@@ -247,6 +254,9 @@ WH_API int wh_worker_wait(whWorker* w, uint64_t ticket, double* prog);
  * rank's outbox that falls into its key range and applies it as one push message. */
 WH_API int wh_worker_ipc_export(whWorker* w, size_t max_uniq, void* handles);
 WH_API int wh_worker_ipc_attach(whWorker* w, const void* handles);
+/* The PRED workload (learn/linear/async_sgd.h:263-265 -> ScalarLoss::Predict, learn/linear/loss.h:55-63): Localize,
+ * ZPull, Xw; out[rows] (host) receives 1/(1+exp(-Xw)) if prob_predict else Xw. Needs a local, unsharded server. */
+WH_API int wh_worker_predict(whWorker* w, const whRowBlock* blk, int mem, int prob_predict, float* out);
 WH_API int wh_worker_begin(whWorker* w, const whRowBlock* blk, int mem, size_t nnz, const uint64_t** d_uniq,
                            size_t* num_uniq);
 WH_API int wh_worker_finish(whWorker* w, const float* d_weights, float* d_grads, int train, double* prog);

@@ -250,6 +250,13 @@ class Server:
         """One push message on device arrays (addresses); enqueued on the context's stream."""
         _check(lib().wh_server_push(self.h, C.c_void_p(keys_ptr), C.c_size_t(n), C.c_int(WH_DEVICE), C.c_void_p(grads_ptr)))
 
+    def save(self, path):
+        """AsgdServer::SaveModel: {key, w} records of the non-zero weights."""
+        _check(lib().wh_server_save(self.h, path.encode()))
+
+    def load(self, path):
+        _check(lib().wh_server_load(self.h, path.encode()))
+
     def ipc_export(self):
         """The bytes other ranks need to map this shard (wh_server_ipc_export)."""
         buf = C.create_string_buffer(192)
@@ -362,6 +369,13 @@ class Worker:
         _check(lib().wh_worker_submit(self.h, C.byref(rb), C.c_int(mem), C.c_size_t(nnz), C.c_int(train), C.byref(t)))
         self._keep[t.value] = blk   # the arrays must outlive the call
         return t.value
+
+    def predict(self, blk, prob_predict=True, mem=WH_HOST):
+        """The PRED workload: one prediction per row (sigmoid of Xw if prob_predict)."""
+        out = np.zeros(blk.rows, np.float32)
+        rb = _rowblock(blk)
+        _check(lib().wh_worker_predict(self.h, C.byref(rb), C.c_int(mem), C.c_int(prob_predict), _ptr(out)))
+        return out
 
     def ipc_export(self, max_uniq):
         buf = C.create_string_buffer(64 * self.depth)

@@ -6,6 +6,9 @@
 // 16 B (FTRL) / 8 B (AdaGrad) / 4 B (SGD) so that a key costs one vector load and one store.
 // All fp32 steps are single IEEE operations (-fmad=false; sqrtf and '/' are correctly rounded),
 // so given the same gradient the new state is bit-identical to the reference's.
+#include <vector>
+
+#include "scan.cuh"
 #include "server.cuh"
 
 namespace wh {
@@ -334,6 +337,27 @@ int server_barrier_launch(whServer* s, cudaStream_t stream) {
   return WH_OK;
 }
 
+
+// ---- model files (the train -> save -> load -> predict loop) ------------------------------------------
+// Entries save only w, and entries with w == 0 are skipped (SGDEntry/AdaGradEntry/FTRLEntry::Save and ::Empty,
+// learn/linear/async_sgd.h:59-66,73-75,111-113,150-152). The record framing of ps-lite's KVStore::Save is
+// not in the reference tree; this library writes {uint64 key, float w} records in ascending key order.
+struct NonZero {
+  const void* table; int algo;
+  __device__ float w(size_t i) const {
+    if (algo == WH_ALGO_FTRL) return reinterpret_cast<const float4*>(table)[i].x;
+    if (algo == WH_ALGO_ADAGRAD) return reinterpret_cast<const float2*>(table)[i].x;
+    return reinterpret_cast<const float*>(table)[i];
+  }
+  __device__ unsigned operator()(size_t i) const { return w(i) != 0.f ? 1u : 0u; }
+};
+struct DumpOut {
+  NonZero nz; uint64_t key_begin; uint64_t* keys; float* ws;
+  __device__ void operator()(size_t i, unsigned v, unsigned prefix) const {
+    if (v) { keys[prefix] = key_begin + i; ws[prefix] = nz.w(i); }
+  }
+};
+
 }  // namespace wh
 
 using namespace wh;
@@ -464,6 +488,48 @@ int wh_server_sgd_t(const whServer* s) {
   if (!s) return 0;
   if (s->map.world > 1) return (int)(1 + s->steps * (unsigned long long)s->map.world);   // lock-step shards
   return s->t;
+}
+
+
+int wh_server_save(whServer* s, const char* path) {
+  WH_REQUIRE(s && path, "wh_server_save: NULL argument");
+  whContext* ctx = s->ctx;
+  DeviceGuard g(ctx->device);
+  int64_t nnz = 0;
+  WH_TRY(wh_server_nnz_w(s, &nnz));
+  const size_t n = s->entries(), cap = (size_t)(nnz > 0 ? nnz : 0) + 1;
+  WH_TRY(ctx->stage[0].reserve(cap * 8)); WH_TRY(ctx->stage[1].reserve(cap * 4));
+  WH_TRY(ctx->scan_tmp.reserve(div_up(n, kScanTile) * sizeof(unsigned) + 256));
+  unsigned* total = ctx->small.as<unsigned>() + 64;
+  NonZero nz{s->table.p, s->algo};
+  WH_TRY(scan_and_apply<unsigned>(ctx, nz, DumpOut{nz, s->key_begin, ctx->stage[0].as<uint64_t>(), ctx->stage[1].as<float>()},
+                                  n, ctx->scan_tmp.as<unsigned>(), total));
+  std::vector<uint64_t> keys(cap);
+  std::vector<float> ws(cap);
+  unsigned cnt = 0;
+  WH_CUDA(cudaMemcpyAsync(&cnt, total, 4, cudaMemcpyDeviceToHost, ctx->stream));
+  WH_CUDA(cudaMemcpyAsync(keys.data(), ctx->stage[0].p, cap * 8, cudaMemcpyDeviceToHost, ctx->stream));
+  WH_CUDA(cudaMemcpyAsync(ws.data(), ctx->stage[1].p, cap * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  WH_CUDA(cudaStreamSynchronize(ctx->stream));
+  WH_REQUIRE((int64_t)cnt == nnz, "wh_server_save: %u non-zero weights found but |w|_0 counter says %lld", cnt, (long long)nnz);
+  FILE* f = fopen(path, "wb");
+  WH_REQUIRE(f != nullptr, "wh_server_save: cannot open %s", path);
+  for (unsigned i = 0; i < cnt; ++i) { fwrite(&keys[i], 8, 1, f); fwrite(&ws[i], 4, 1, f); }
+  fclose(f);
+  return WH_OK;
+}
+
+int wh_server_load(whServer* s, const char* path) {
+  WH_REQUIRE(s && path, "wh_server_load: NULL argument");
+  FILE* f = fopen(path, "rb");
+  WH_REQUIRE(f != nullptr, "wh_server_load: cannot open %s", path);
+  std::vector<uint64_t> keys; std::vector<float> ws;
+  uint64_t k; float w;
+  while (fread(&k, 8, 1, f) == 1 && fread(&w, 4, 1, f) == 1) { keys.push_back(k); ws.push_back(w); }
+  fclose(f);
+  // TLoad: only w is read back, and Update(w, 0) counts it (learn/linear/async_sgd.h:59-62); z and
+  // sq_cum_grad of a loaded entry stay at their defaults, as in the reference
+  return wh_server_set_state(s, keys.data(), keys.size(), WH_HOST, ws.data(), nullptr, nullptr);
 }
 
 int wh_server_ipc_export(whServer* s, void* handle) {

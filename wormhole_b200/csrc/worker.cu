@@ -302,6 +302,52 @@ int wh_worker_wait(whWorker* w, uint64_t ticket, double* prog) {
   return WH_OK;
 }
 
+__global__ void predict_kernel(size_t n, float* xw, int prob) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  // learn/linear/loss.h:59: 1.0 / (1.0 + exp(-p)) with p a float: fp32 exp, the rest in double, printed as text
+  if (i < n && prob) xw[i] = (float)(1.0 / (1.0 + (double)exp_rn(-xw[i])));
+}
+
+int wh_worker_predict(whWorker* w, const whRowBlock* blk, int mem, int prob, float* out) {
+  WH_REQUIRE(w && blk && out, "wh_worker_predict: NULL argument");
+  WH_REQUIRE(w->server && w->server->map.world == 1, "wh_worker_predict: needs a local, unsharded server");
+  WH_REQUIRE(w->next_wait == w->next_ticket, "wh_worker_predict: minibatches are still in flight");
+  whContext* ctx = w->ctx;
+  DeviceGuard g(ctx->device);
+  const size_t rows = blk->size;
+  if (rows == 0) return WH_OK;
+  WH_REQUIRE(blk->offset && blk->index, "wh_worker_predict: offset/index is NULL");
+  Lane& l = w->lane[0];
+  whContext* cx = &l.cx;
+  size_t n;
+  if (mem == WH_HOST) n = blk->offset[rows];
+  else {
+    WH_CUDA(cudaMemcpyAsync(l.pinned + 384, blk->offset + rows, sizeof(size_t), cudaMemcpyDeviceToHost, cx->stream));
+    WH_CUDA(cudaStreamSynchronize(cx->stream));
+    n = *reinterpret_cast<size_t*>(l.pinned + 384);
+  }
+  WH_TRY(l.xw.reserve(rows * 4));
+  WH_CUDA(cudaMemsetAsync(l.xw.p, 0, rows * 4, cx->stream));
+  if (n > 0) {
+    const uint64_t* d_index; const size_t* d_offset; const float* d_value;
+    WH_TRY(to_device(cx, l.in_index, blk->index, n, mem, &d_index));
+    WH_TRY(to_device(cx, l.in_offset, blk->offset, rows + 1, mem, &d_offset));
+    WH_TRY(to_device(cx, l.in_value, blk->value, n, mem, &d_value));
+    const size_t ucap = (size_t)std::min<uint64_t>(n, w->max_key);
+    WH_TRY(l.uniq.reserve(ucap * 8)); WH_TRY(l.index.reserve(n * 4)); WH_TRY(l.w.reserve(ucap * 4));
+    unsigned* d_nuniq = l.scal.as<unsigned>();
+    LocInput in{d_index, n, make_xform(w->max_key)};
+    if (direct_supported(w->max_key)) WH_TRY(localize_direct(cx, in, l.uniq.as<uint64_t>(), nullptr, l.index.as<uint32_t>(), d_nuniq));
+    else WH_TRY(localize_sort(cx, in, l.uniq.as<uint64_t>(), nullptr, l.index.as<uint32_t>(), d_nuniq));
+    WH_TRY(server_pull_launch(w->server, cx->stream, l.uniq.as<uint64_t>(), ucap, d_nuniq, l.w.as<float>()));
+    WH_TRY(spmv_times_launch(cx, rows, d_offset, l.index.as<uint32_t>(), d_value, l.w.as<float>(), l.xw.as<float>()));
+  }
+  WH_LAUNCH(predict_kernel, (unsigned)div_up(rows, 256), 256, 0, cx->stream, rows, l.xw.as<float>(), prob);
+  WH_CUDA(cudaMemcpyAsync(out, l.xw.p, rows * 4, cudaMemcpyDeviceToHost, cx->stream));
+  WH_CUDA(cudaStreamSynchronize(cx->stream));
+  return WH_OK;
+}
+
 // ---- outboxes of a sharded job -----------------------------------------------------------------------
 
 int wh_worker_ipc_export(whWorker* w, size_t max_uniq, void* handles) {
