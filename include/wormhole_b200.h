@@ -180,6 +180,9 @@ typedef struct {
   float lr_beta;
   uint64_t key_begin;      /* this shard owns transformed keys in [key_begin, key_end) */
   uint64_t key_end;        /* dense direct-addressed table: key_end - key_begin entries */
+  uint64_t hash_slots;     /* 0: dense. Else an open-addressing table of this many slots (power of two) for
+                              un-hashed 64-bit keys -- ps::FLAGS_max_key at its default, keys = nibble-reversed
+                              ids spread over the whole 64-bit range; key_begin / key_end still bound the range */
 } whServerConfig;
 
 /* AsgdServer::CreateServer<Entry,Handle>, learn/linear/async_sgd.h:200-213. */

@@ -179,9 +179,11 @@ def test_gpu_agaricus_epoch_matches_golden(gpu):
     from wormhole_b200 import capi
     g = load("golden_agaricus.npz")
     ag = agaricus()
-    for name in ("ftrl_hashed", "adagrad_hinge", "sgd_logit"):
+    for name in ("ftrl_default", "ftrl_hashed", "adagrad_hinge", "sgd_logit"):
         algo, loss, max_key = (int(x) for x in g[name + "_conf"])
-        srv = capi.Server(gpu, algo, 1.0, 0.0, None, None, 0, max_key)
+        # "ftrl_default" is the guide's demo.conf as shipped: ps::FLAGS_max_key at its default, so the keys are
+        # nibble-reversed 64-bit ids -> the radix-sort localizer and the open-addressing shard
+        srv = capi.Server(gpu, algo, 1.0, 0.0, None, None, 0, max_key, hash_slots=(1 << 16) if max_key == capi.NO_MAX_KEY else 0)
         wk = capi.Worker(gpu, srv, loss, max_key)
         progs = np.array([wk.process_minibatch(ag.slice(b, min(ag.rows, b + 1000))) for b in range(0, ag.rows, 1000)])
         want = g[name + "_prog"]

@@ -362,3 +362,27 @@ def test_minibatches_in_flight_equal_sequential(gpu):
     assert np.array_equal(progs[0], progs[1])
     for a, b in zip(states[0], states[1]):
         assert np.array_equal(a, b)
+
+
+def test_unhashed_64bit_keys_end_to_end(gpu, checker):
+    """ps::FLAGS_max_key at its default (learn/base/localizer.h:116-121): nibble-reversed ids over the whole
+    64-bit range, radix-sort localizer, open-addressing shard; including a table that has to probe a lot."""
+    from tests.util import wide_ids
+    rng = np.random.default_rng(54)
+    pool = wide_ids(rng, 3000)                       # 3000 distinct 64-bit feature ids
+    job = checker.linear_create(capi.ALGO_FTRL, capi.LOSS_LOGIT, 0.5, 0.1, 0.1, 1.0, capi.NO_MAX_KEY)
+    srv = capi.Server(gpu, capi.ALGO_FTRL, 0.5, 0.1, 0.1, 1.0, 0, capi.NO_MAX_KEY, hash_slots=4096)   # 73 % full
+    wk = capi.Worker(gpu, srv, capi.LOSS_LOGIT, capi.NO_MAX_KEY)
+    for m in range(5):
+        nnz = rng.integers(1, 15, 2000)
+        off = np.zeros(2001, np.uint64); off[1:] = np.cumsum(nnz)
+        blk = RowBlock(off, pool[rng.integers(0, len(pool), int(off[-1]))], None, (rng.random(2000) < 0.4).astype(np.float32))
+        pg, pc = wk.process_minibatch(blk), checker.linear_minibatch(job, blk)
+        assert pg[1] == pc[1] and abs(pg[0] - pc[0]) <= 1e-4 * abs(pc[0]) and abs(pg[5] - pc[5]) <= 1
+    keys, w, z, cg = checker.linear_model(job)
+    weights_close(srv.get_state(keys), (w, z, cg))
+    assert np.array_equal(srv.pull(np.array([12345], np.uint64)), [0.0])      # a key never seen: default entry
+    with pytest.raises(capi.WormholeError):                                     # more keys than slots: reported
+        small = capi.Server(gpu, capi.ALGO_SGD, 0, 0, 0.1, 1.0, 0, capi.NO_MAX_KEY, hash_slots=16)
+        small.push(pool[:100], np.ones(100, np.float32))
+    wk.close(); srv.close(); checker.linear_destroy(job)

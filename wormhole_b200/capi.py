@@ -39,7 +39,8 @@ class _LocalBlock(C.Structure):
 class _ServerConfig(C.Structure):
     _fields_ = [("algo", C.c_int), ("lambda_l1", C.c_float), ("lambda_l2", C.c_float),
                 ("has_lr_eta", C.c_int), ("lr_eta", C.c_float), ("has_lr_beta", C.c_int),
-                ("lr_beta", C.c_float), ("key_begin", C.c_uint64), ("key_end", C.c_uint64)]
+                ("lr_beta", C.c_float), ("key_begin", C.c_uint64), ("key_end", C.c_uint64),
+                ("hash_slots", C.c_uint64)]
 
 
 _lib = None
@@ -224,10 +225,10 @@ class Server:
     learn/linear/async_sgd.h:83-213). eta / beta None = key absent from the conf."""
 
     def __init__(self, ctx, algo=ALGO_FTRL, l1=1.0, l2=0.0, eta=None, beta=None, key_begin=0,
-                 key_end=2 ** 24):
+                 key_end=2 ** 24, hash_slots=0):
         self.ctx = ctx
         cfg = _ServerConfig(algo, l1, l2, int(eta is not None), eta or 0.0, int(beta is not None),
-                            beta or 0.0, key_begin, key_end)
+                            beta or 0.0, key_begin, key_end, hash_slots)
         self.h = C.c_void_p()
         _check(lib().wh_server_create(ctx.h, C.byref(cfg), C.byref(self.h)))
         self.algo = algo

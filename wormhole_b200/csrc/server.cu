@@ -6,6 +6,7 @@
 // 16 B (FTRL) / 8 B (AdaGrad) / 4 B (SGD) so that a key costs one vector load and one store.
 // All fp32 steps are single IEEE operations (-fmad=false; sqrtf and '/' are correctly rounded),
 // so given the same gradient the new state is bit-identical to the reference's.
+#include <algorithm>
 #include <vector>
 
 #include "scan.cuh"
@@ -24,7 +25,38 @@ struct HandleParams {
   float l1, l2, alpha, beta;
   float eta_sgd;            // SGDHandle::eta for this push message
   uint64_t key_begin, key_end;
+  // un-hashed 64-bit keys (ps::FLAGS_max_key at its default): open addressing instead of direct addressing
+  unsigned long long* hkeys;   // NULL = dense shard; else one key per slot, kEmptyKey = free
+  uint64_t hmask;              // slots - 1 (a power of two)
 };
+constexpr unsigned long long kEmptyKey = ~0ull;
+
+__device__ __forceinline__ uint64_t hash_mix(uint64_t x) {
+  x ^= x >> 33; x *= 0xff51afd7ed558ccdULL; x ^= x >> 33; x *= 0xc4ceb9fe1a85ec53ULL; x ^= x >> 33; return x;
+}
+// Where does key k live? insert = true claims a free slot for a key not seen before (entries are zero by
+// default, as ps-lite's store default-constructs on first touch); insert = false leaves absent keys absent.
+// Returns false if the key is outside the shard / the table is full (counted as a bad key by the caller).
+__device__ __forceinline__ bool find_slot(const HandleParams& h, uint64_t k, bool insert, uint64_t* slot, bool* present) {
+  *present = true;
+  if (h.hkeys == nullptr) {
+    if (k < h.key_begin || k >= h.key_end) return false;
+    *slot = k - h.key_begin;
+    return true;
+  }
+  if (k == kEmptyKey) return false;
+  uint64_t i = hash_mix(k) & h.hmask;
+  for (uint64_t probes = 0; probes <= h.hmask; ++probes, i = (i + 1) & h.hmask) {
+    unsigned long long cur = h.hkeys[i];
+    if (cur == k) { *slot = i; return true; }
+    if (cur == kEmptyKey) {
+      if (!insert) { *present = false; *slot = i; return true; }
+      cur = atomicCAS(h.hkeys + i, kEmptyKey, (unsigned long long)k);
+      if (cur == kEmptyKey || cur == k) { *slot = i; return true; }
+    }
+  }
+  return false;
+}
 
 // One key of one push message. Returns the change of |w|_0 (learn/linear/async_sgd.h:35-41).
 __device__ __forceinline__ int handle_push(const HandleParams& h, void* table, uint64_t slot, float g) {
@@ -85,8 +117,9 @@ server_push_kernel(HandleParams h, void* table, const uint64_t* __restrict__ key
     } else {
       g = grads[i];
     }
-    uint64_t k = keys[i];
-    if (k >= h.key_begin && k < h.key_end) delta = handle_push(h, table, k - h.key_begin, g);
+    uint64_t k = keys[i], slot;
+    bool present;
+    if (find_slot(h, k, true, &slot, &present)) delta = handle_push(h, table, slot, g);
     else bad = 1;
   }
   commit_counters(counters, delta, bad);
@@ -94,18 +127,20 @@ server_push_kernel(HandleParams h, void* table, const uint64_t* __restrict__ key
 
 // learn/linear/async_sgd.h:97-99,137-139,177-179: send[0] = w
 __global__ void __launch_bounds__(256)
-server_pull_kernel(int algo, const void* table, uint64_t key_begin, uint64_t key_end,
+server_pull_kernel(HandleParams h, const void* table,
                    const uint64_t* __restrict__ keys, size_t n, const unsigned* d_n,
                    float* __restrict__ vals, long long* counters) {
   if (d_n) n = *d_n;
   const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   int bad = 0;
   if (i < n) {
-    uint64_t k = keys[i];
-    if (k >= key_begin && k < key_end) {
-      const uint64_t s = k - key_begin;
+    uint64_t k = keys[i], s;
+    bool present;
+    const int algo = h.algo;
+    if (find_slot(h, k, false, &s, &present)) {
       float w;
-      if (algo == WH_ALGO_FTRL) w = __ldg(reinterpret_cast<const float*>(reinterpret_cast<const float4*>(table) + s));
+      if (!present) w = 0.f;
+      else if (algo == WH_ALGO_FTRL) w = __ldg(reinterpret_cast<const float*>(reinterpret_cast<const float4*>(table) + s));
       else if (algo == WH_ALGO_ADAGRAD) w = __ldg(reinterpret_cast<const float*>(reinterpret_cast<const float2*>(table) + s));
       else w = __ldg(reinterpret_cast<const float*>(table) + s);
       vals[i] = w;
@@ -114,15 +149,17 @@ server_pull_kernel(int algo, const void* table, uint64_t key_begin, uint64_t key
   commit_counters(counters, 0, bad);
 }
 
-__global__ void server_state_kernel(int algo, void* table, uint64_t key_begin, uint64_t key_end,
+__global__ void server_state_kernel(HandleParams h, void* table,
                                     const uint64_t* __restrict__ keys, size_t n, float* w, float* z,
                                     float* cg, const float* sw, const float* sz, const float* scg,
                                     int set, long long* counters) {
   const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
-  uint64_t k = keys[i];
-  if (k < key_begin || k >= key_end) { atomicAdd(reinterpret_cast<unsigned long long*>(counters + 1), 1ull); return; }
-  const uint64_t s = k - key_begin;
+  uint64_t k = keys[i], s;
+  bool present;
+  const int algo = h.algo;
+  if (!find_slot(h, k, set != 0, &s, &present)) { atomicAdd(reinterpret_cast<unsigned long long*>(counters + 1), 1ull); return; }
+  if (!present) { if (w) w[i] = 0.f; if (z) z[i] = 0.f; if (cg) cg[i] = 0.f; return; }
   float vw, vz = 0.f, vc = 0.f;
   if (algo == WH_ALGO_FTRL) { float4 v = reinterpret_cast<float4*>(table)[s]; vw = v.x; vz = v.y; vc = v.z; }
   else if (algo == WH_ALGO_ADAGRAD) { float2 v = reinterpret_cast<float2*>(table)[s]; vw = v.x; vc = v.y; }
@@ -140,6 +177,7 @@ static HandleParams make_params(whServer* s, bool start_push) {
   HandleParams h;
   h.algo = s->algo; h.l1 = s->l1; h.l2 = s->l2; h.alpha = s->alpha; h.beta = s->beta;
   h.key_begin = s->key_begin; h.key_end = s->key_end;
+  h.hkeys = s->hkeys.as<unsigned long long>(); h.hmask = s->hslots ? s->hslots - 1 : 0;
   h.eta_sgd = 0.f;
   if (start_push && s->algo == WH_ALGO_SGD) {  // SGDHandle::Start, async_sgd.h:85-90
     h.eta_sgd = (s->beta + sqrtf((float)s->t)) / s->alpha;
@@ -150,8 +188,8 @@ static HandleParams make_params(whServer* s, bool start_push) {
 
 int server_pull_launch(whServer* s, cudaStream_t stream, const uint64_t* keys, size_t n, const unsigned* d_n, float* vals) {
   if (n == 0) return WH_OK;
-  WH_LAUNCH(server_pull_kernel, (unsigned)div_up(n, 256), 256, 0, stream, s->algo, s->table.p,
-            s->key_begin, s->key_end, keys, n, d_n, vals, s->counters.as<long long>());
+  WH_LAUNCH(server_pull_kernel, (unsigned)div_up(n, 256), 256, 0, stream, make_params(s, false), s->table.p,
+            keys, n, d_n, vals, s->counters.as<long long>());
   return WH_OK;
 }
 int server_push_launch(whServer* s, cudaStream_t stream, const uint64_t* keys, size_t n, const unsigned* d_n, const float* grads) {
@@ -317,6 +355,7 @@ int server_push_turn_launch(whServer* s, cudaStream_t stream, int turn, const ui
   HandleParams h;
   h.algo = s->algo; h.l1 = s->l1; h.l2 = s->l2; h.alpha = s->alpha; h.beta = s->beta;
   h.key_begin = s->map.bounds[target]; h.key_end = s->map.bounds[target + 1];
+  h.hkeys = nullptr; h.hmask = 0;
   h.eta_sgd = 0.f;
   if (s->algo == WH_ALGO_SGD) {
     // SGDHandle::t of the target shard when this message arrives: it has seen `world` messages per earlier
@@ -352,9 +391,9 @@ struct NonZero {
   __device__ unsigned operator()(size_t i) const { return w(i) != 0.f ? 1u : 0u; }
 };
 struct DumpOut {
-  NonZero nz; uint64_t key_begin; uint64_t* keys; float* ws;
+  NonZero nz; uint64_t key_begin; const unsigned long long* hkeys; uint64_t* keys; float* ws;
   __device__ void operator()(size_t i, unsigned v, unsigned prefix) const {
-    if (v) { keys[prefix] = key_begin + i; ws[prefix] = nz.w(i); }
+    if (v) { keys[prefix] = hkeys ? hkeys[i] : key_begin + i; ws[prefix] = nz.w(i); }
   }
 };
 
@@ -384,8 +423,10 @@ int wh_server_create(whContext* ctx, const whServerConfig* c, whServer** out) {
              "wh_server_create: unknown algo: %d", c->algo);
   WH_REQUIRE(c->lambda_l1 >= 0 && c->lambda_l2 >= 0, "wh_server_create: lambda must be >= 0 (learn/linear/penalty.h:15,19)");
   WH_REQUIRE(c->key_end > c->key_begin, "wh_server_create: empty key range");
-  WH_REQUIRE(c->key_end - c->key_begin <= (1ull << 32), "wh_server_create: dense shard of %llu keys is too large",
+  WH_REQUIRE(c->hash_slots != 0 || c->key_end - c->key_begin <= (1ull << 32),
+             "wh_server_create: a dense shard of %llu keys is too large; give hash_slots for un-hashed 64-bit keys",
              (unsigned long long)(c->key_end - c->key_begin));
+  WH_REQUIRE((c->hash_slots & (c->hash_slots - 1)) == 0 && c->hash_slots <= (1ull << 32), "wh_server_create: hash_slots must be a power of two <= 2^32");
   DeviceGuard g(ctx->device);
   whServer* s = new whServer();
   s->ctx = ctx; s->algo = c->algo; s->l1 = c->lambda_l1; s->l2 = c->lambda_l2;
@@ -393,13 +434,16 @@ int wh_server_create(whContext* ctx, const whServerConfig* c, whServer** out) {
   if (c->has_lr_beta) s->beta = c->lr_beta;
   s->key_begin = c->key_begin; s->key_end = c->key_end;
   const size_t esz = c->algo == WH_ALGO_FTRL ? 16 : (c->algo == WH_ALGO_ADAGRAD ? 8 : 4);
+  s->hslots = c->hash_slots;
   int r = s->table.reserve(s->entries() * esz);
+  if (r == WH_OK && s->hslots) r = s->hkeys.reserve(s->hslots * 8);
   if (r == WH_OK) r = s->counters.reserve(64);
   if (r == WH_OK) r = s->flags.reserve(kMaxShards * 8);
   if (r != WH_OK) { delete s; return r; }
   WH_CUDA(cudaMemsetAsync(s->table.p, 0, s->table.cap, ctx->stream));  // entries default to 0 (:72,108-109,146-148)
   WH_CUDA(cudaMemsetAsync(s->counters.p, 0, 64, ctx->stream));
   WH_CUDA(cudaMemsetAsync(s->flags.p, 0, kMaxShards * 8, ctx->stream));
+  if (s->hslots) WH_CUDA(cudaMemsetAsync(s->hkeys.p, 0xff, s->hslots * 8, ctx->stream));
   s->map.world = 1; s->map.rank = 0;
   s->map.bounds[0] = c->key_begin; s->map.bounds[1] = c->key_end;
   s->map.table[0] = s->table.p; s->map.counters[0] = s->counters.as<long long>();
@@ -413,7 +457,7 @@ int wh_server_destroy(whServer* s) {
   DeviceGuard g(s->ctx->device);
   cudaStreamSynchronize(s->ctx->stream);
   for (void* p : s->peer_base) if (p) cudaIpcCloseMemHandle(p);
-  s->table.release(); s->counters.release(); s->flags.release();
+  s->table.release(); s->counters.release(); s->flags.release(); s->hkeys.release();
   delete s;
   return WH_OK;
 }
@@ -466,8 +510,7 @@ static int state_io(whServer* s, const uint64_t* keys, size_t n, int mem, float*
   WH_TRY(to_device(ctx, ctx->stage[4], sw, n, mem, &dsw));
   WH_TRY(to_device(ctx, ctx->stage[5], sz, n, mem, &dsz));
   WH_TRY(to_device(ctx, ctx->stage[6], scg, n, mem, &dsc));
-  WH_LAUNCH(server_state_kernel, (unsigned)div_up(n, 256), 256, 0, ctx->stream, s->algo, s->table.p, s->key_begin,
-            s->key_end, dk, n, dw, dz, dc, dsw, dsz, dsc, set, s->counters.as<long long>());
+  WH_LAUNCH(server_state_kernel, (unsigned)div_up(n, 256), 256, 0, ctx->stream, make_params(s, false), s->table.p, dk, n, dw, dz, dc, dsw, dsz, dsc, set, s->counters.as<long long>());
   WH_TRY(out_commit(ctx, w, dw, n, mem));
   WH_TRY(out_commit(ctx, z, dz, n, mem));
   WH_TRY(out_commit(ctx, cg, dc, n, mem));
@@ -502,7 +545,7 @@ int wh_server_save(whServer* s, const char* path) {
   WH_TRY(ctx->scan_tmp.reserve(div_up(n, kScanTile) * sizeof(unsigned) + 256));
   unsigned* total = ctx->small.as<unsigned>() + 64;
   NonZero nz{s->table.p, s->algo};
-  WH_TRY(scan_and_apply<unsigned>(ctx, nz, DumpOut{nz, s->key_begin, ctx->stage[0].as<uint64_t>(), ctx->stage[1].as<float>()},
+  WH_TRY(scan_and_apply<unsigned>(ctx, nz, DumpOut{nz, s->key_begin, s->hkeys.as<unsigned long long>(), ctx->stage[0].as<uint64_t>(), ctx->stage[1].as<float>()},
                                   n, ctx->scan_tmp.as<unsigned>(), total));
   std::vector<uint64_t> keys(cap);
   std::vector<float> ws(cap);
@@ -512,9 +555,12 @@ int wh_server_save(whServer* s, const char* path) {
   WH_CUDA(cudaMemcpyAsync(ws.data(), ctx->stage[1].p, cap * 4, cudaMemcpyDeviceToHost, ctx->stream));
   WH_CUDA(cudaStreamSynchronize(ctx->stream));
   WH_REQUIRE((int64_t)cnt == nnz, "wh_server_save: %u non-zero weights found but |w|_0 counter says %lld", cnt, (long long)nnz);
+  std::vector<unsigned> order(cnt);
+  for (unsigned i = 0; i < cnt; ++i) order[i] = i;
+  if (s->hslots) std::sort(order.begin(), order.end(), [&](unsigned a, unsigned b) { return keys[a] < keys[b]; });  // slot order -> key order
   FILE* f = fopen(path, "wb");
   WH_REQUIRE(f != nullptr, "wh_server_save: cannot open %s", path);
-  for (unsigned i = 0; i < cnt; ++i) { fwrite(&keys[i], 8, 1, f); fwrite(&ws[i], 4, 1, f); }
+  for (unsigned i = 0; i < cnt; ++i) { fwrite(&keys[order[i]], 8, 1, f); fwrite(&ws[order[i]], 4, 1, f); }
   fclose(f);
   return WH_OK;
 }
@@ -547,6 +593,7 @@ int wh_server_ipc_attach(whServer* s, int rank, int world, uint64_t max_key, con
   WH_REQUIRE(s && handles, "wh_server_ipc_attach: NULL argument");
   WH_REQUIRE(world >= 1 && world <= kMaxShards && rank >= 0 && rank < world, "wh_server_ipc_attach: rank %d of %d", rank, world);
   WH_REQUIRE(s->map.world == 1, "wh_server_ipc_attach: already attached");
+  WH_REQUIRE(s->hslots == 0, "wh_server_ipc_attach: key-range shards over several GPUs need a hashed key space (dense shards)");
   const uint64_t b = (uint64_t)(((unsigned __int128)rank * max_key) / world), e = (uint64_t)(((unsigned __int128)(rank + 1) * max_key) / world);
   WH_REQUIRE(s->key_begin == b && s->key_end == e, "wh_server_ipc_attach: this shard holds [%llu, %llu) but rank %d of %d owns [%llu, %llu)",
              (unsigned long long)s->key_begin, (unsigned long long)s->key_end, rank, world, (unsigned long long)b, (unsigned long long)e);

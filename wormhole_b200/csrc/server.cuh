@@ -30,7 +30,9 @@ struct whServer {
   int t = 1;                        // SGDHandle::t, learn/linear/async_sgd.h:100
   wh::DevBuf table;                 // FTRL: float4 {w, z, sq_cum_grad, 0}; AdaGrad: float2 {w, sq_cum_grad}; SGD: float w
   wh::DevBuf counters;              // [0] new_w (long long), [1] out-of-range keys seen
-  size_t entries() const { return (size_t)(key_end - key_begin); }
+  wh::DevBuf hkeys;                 // hash shard: the key held by each slot (all ones = free)
+  uint64_t hslots = 0;              // 0 = dense shard
+  size_t entries() const { return hslots ? (size_t)hslots : (size_t)(key_end - key_begin); }
 };
 
 namespace wh {

@@ -23,7 +23,8 @@ using FeaID = ps::Key;
 /// otherwise, :49,205-206). Owns the keys [key_begin, key_end) of the transformed key space.
 class AsgdServer {
  public:
-  explicit AsgdServer(const Config& conf, uint64_t key_begin = 0, uint64_t key_end = 0) : conf_(conf) {
+  explicit AsgdServer(const Config& conf, uint64_t key_begin = 0, uint64_t key_end = 0, uint64_t hash_slots = 1ull << 24)
+      : conf_(conf) {
     whServerConfig c;
     c.algo = conf.algo();
     c.lambda_l1 = conf.lambda_l1(); c.lambda_l2 = conf.lambda_l2();
@@ -31,10 +32,8 @@ class AsgdServer {
     c.has_lr_beta = conf.has_lr_beta(); c.lr_beta = conf.lr_beta();
     c.key_begin = key_begin;
     c.key_end = key_end ? key_end : ps::FLAGS_max_key;
-    if (c.key_end - c.key_begin > (1ull << 32)) {
-      fprintf(stderr, "[FATAL] AsgdServer: the dense GPU shard needs a hashed key space (set ps::FLAGS_max_key)\n");
-      abort();
-    }
+    // hashed key space: dense shard. Default ps::FLAGS_max_key (all ones): 64-bit keys, open-addressing shard
+    c.hash_slots = (c.key_end - c.key_begin > (1ull << 32)) ? hash_slots : 0;
     WH_CHECK(wh_server_create(wh::Ctx(), &c, &server_));
   }
   ~AsgdServer() { wh_server_destroy(server_); }
