@@ -106,9 +106,10 @@ server_push_kernel(HandleParams h, void* table, const uint64_t* __restrict__ key
                    const unsigned* d_n, const float* __restrict__ grads, long long* acc,
                    const FixedScale* fs, float mul, long long* counters, unsigned copies, size_t stride) {
   if (d_n) n = *d_n;
-  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   int delta = 0, bad = 0;
-  if (i < n) {
+  // grid-stride: the launch is sized for the number of SMs, not for the upper bound of n (which is only known
+  // on the device and is ~15x smaller than the bound at Criteo shape)
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
     float g;
     if (FROM_ACC) {
       long long a = 0;
@@ -119,7 +120,7 @@ server_push_kernel(HandleParams h, void* table, const uint64_t* __restrict__ key
     }
     uint64_t k = keys[i], slot;
     bool present;
-    if (find_slot(h, k, true, &slot, &present)) delta = handle_push(h, table, slot, g);
+    if (find_slot(h, k, true, &slot, &present)) delta += handle_push(h, table, slot, g);
     else bad = 1;
   }
   commit_counters(counters, delta, bad);
@@ -131,9 +132,8 @@ server_pull_kernel(HandleParams h, const void* table,
                    const uint64_t* __restrict__ keys, size_t n, const unsigned* d_n,
                    float* __restrict__ vals, long long* counters) {
   if (d_n) n = *d_n;
-  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   int bad = 0;
-  if (i < n) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
     uint64_t k = keys[i], s;
     bool present;
     const int algo = h.algo;
@@ -188,14 +188,14 @@ static HandleParams make_params(whServer* s, bool start_push) {
 
 int server_pull_launch(whServer* s, cudaStream_t stream, const uint64_t* keys, size_t n, const unsigned* d_n, float* vals) {
   if (n == 0) return WH_OK;
-  WH_LAUNCH(server_pull_kernel, (unsigned)div_up(n, 256), 256, 0, stream, make_params(s, false), s->table.p,
+  WH_LAUNCH(server_pull_kernel, (unsigned)std::min<size_t>(div_up(n, 256), (size_t)s->ctx->num_sms * 8), 256, 0, stream, make_params(s, false), s->table.p,
             keys, n, d_n, vals, s->counters.as<long long>());
   return WH_OK;
 }
 int server_push_launch(whServer* s, cudaStream_t stream, const uint64_t* keys, size_t n, const unsigned* d_n, const float* grads) {
   HandleParams h = make_params(s, true);  // Start() runs even for an empty message
   if (n == 0) return WH_OK;
-  WH_LAUNCH(server_push_kernel<false>, (unsigned)div_up(n, 256), 256, 0, stream, h, s->table.p, keys, n,
+  WH_LAUNCH(server_push_kernel<false>, (unsigned)std::min<size_t>(div_up(n, 256), (size_t)s->ctx->num_sms * 8), 256, 0, stream, h, s->table.p, keys, n,
             d_n, grads, (long long*)nullptr, (const FixedScale*)nullptr, 1.f, s->counters.as<long long>(), 1u, (size_t)0);
   return WH_OK;
 }
@@ -203,7 +203,7 @@ int server_push_acc_launch(whServer* s, cudaStream_t stream, const uint64_t* key
                            const FixedScale* fs, float mul, unsigned copies, size_t stride) {
   HandleParams h = make_params(s, true);
   if (n == 0) return WH_OK;
-  WH_LAUNCH(server_push_kernel<true>, (unsigned)div_up(n, 256), 256, 0, stream, h, s->table.p, keys, n,
+  WH_LAUNCH(server_push_kernel<true>, (unsigned)std::min<size_t>(div_up(n, 256), (size_t)s->ctx->num_sms * 8), 256, 0, stream, h, s->table.p, keys, n,
             d_n, (const float*)nullptr, acc, fs, mul, s->counters.as<long long>(), copies, stride);
   return WH_OK;
 }
