@@ -283,6 +283,8 @@ def run_ours(args):
         return ms, wall, capi.kernel_launches() - l0
 
     sampler = ClockSampler(local)
+    if args.max_delay and world == 1:
+        wk.set_max_delay(args.max_delay)
     ms_dev, _, launches = timed(dev, capi.WH_DEVICE, args.steps, args.warmup)
     ms_e2e, wall_e2e, _ = timed(host, capi.WH_HOST, args.steps, max(3, args.warmup // 2))
     ms_e2e = max(ms_e2e, 1e3 * wall_e2e)  # host-side staging is part of the end-to-end time
@@ -314,6 +316,15 @@ def run_ours(args):
         top = max(chain, key=lambda s: s[1]) if chain else ("none", 0.0)
         top_bytes = segment_bytes(top[0], N, rows, uniq_per_mb, words)
         achieved = top_bytes / (top[1] * 1e-3) / 1e9 if top[1] > 0 else 0.0
+        # DRAM bytes per launch of that kernel from the committed ncu --set full capture (profiles/), or null
+        traffic = None
+        try:
+            tr = json.load(open(os.path.join(ROOT, "profiles", "r1_c_traffic.json")))
+            kname = {"spmv_trans": "spmv_trans_kernel<0>", "push": "server_push_kernel<1>", "spmv_loss": "spmv_loss_kernel<0>",
+                     "loc_mark": "loc_mark_tma_kernel", "loc_rank": "loc_rank_kernel", "pull": "server_pull_kernel"}.get(top[0])
+            traffic = tr.get(kname) if (rows == ROWS and world == 1) else None
+        except Exception:
+            pass
         bytes_per_ex = NNZ_PER_ROW * 8 + 12 + r * (8 + 2 * 12)
         value = world * rows * args.steps / (ms_dev * 1e-3)
         e2e = world * rows * args.steps / (ms_e2e * 1e-3)
@@ -325,13 +336,14 @@ def run_ours(args):
                        "max_key": MAX_KEY, "unique_keys_per_row_r": round(r, 4), "pool_minibatches": pool_n,
                        "l2_policy": "inputs larger than L2 (pool of %d distinct minibatches, %.0f MB)" % (pool_n, pool_n * N * 8 / 1e6),
                        "parallelism": "key-range shards x%d" % world + ("" if world == 1 else " (" + args.exchange + ")"), "updater": FTRL,
-                       "minibatches_in_flight": args.depth if (world == 1 or args.exchange == "p2p") else 1},
+                       "minibatches_in_flight": args.depth if (world == 1 or args.exchange == "p2p") else 1,
+                       "max_delay": args.max_delay if world == 1 else 0},
             "e2e": {"value": e2e, "unit": "examples/s", "h2d_bytes_per_step": N * 8 + (rows + 1) * 8 + rows * 4,
                     "d2h_bytes_per_step": 72 + 16},
             "gpu_launches": int(launches),
             "clocks": sampler.summary(),
             "roofline": {"bound": "hbm", "kernel": top[0], "achieved": achieved, "peak": pk["hbm_gbs"],
-                         "peak_kind": pk_kind, "unit": "GB/s", "frac": achieved / pk["hbm_gbs"], "traffic": None,
+                         "peak_kind": pk_kind, "unit": "GB/s", "frac": achieved / pk["hbm_gbs"], "traffic": traffic,
                          "kernel_ms": top[1], "kernel_share_of_step": top[1] / total_seg,
                          "kernel_algorithmic_bytes": top_bytes},
             "step_roofline": {"bytes_per_example": bytes_per_ex,
@@ -373,6 +385,7 @@ def main():
     ap.add_argument("--rows", type=int, default=ROWS)
     ap.add_argument("--pool", type=int, default=8, help="distinct minibatches kept resident")
     ap.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"], help="N>1: how pull/push reach the owning GPU")
+    ap.add_argument("--max-delay", type=int, default=0, help="bounded staleness of pulls (0 = sequential semantics)")
     ap.add_argument("--depth", type=int, default=3, help="minibatches in flight (conf max_concurrency)")
     ap.add_argument("--cpu-procs", type=int, default=0, help="reference arm: worker+server pairs (0 = cores/2)")
     args = ap.parse_args()

@@ -363,6 +363,9 @@ class Worker:
                                          C.c_uint64(max_key), C.c_int(depth), C.byref(self.h)))
         self._keep = {}
 
+    def set_max_delay(self, d):
+        _check(lib().wh_worker_set_max_delay(self.h, C.c_int(d)))
+
     def submit(self, blk, train=True, mem=WH_HOST, nnz=0):
         """Enqueue one minibatch (up to `depth` in flight); returns a ticket for wait()."""
         t = C.c_uint64()

@@ -53,8 +53,9 @@ struct whWorker {
   int depth = 1;
   wh::Lane lane[wh::kMaxDepth];
   wh::PinnedBuf pinned;
-  cudaEvent_t ev_pushed = nullptr;   // completion of the most recent push (or evaluation pull)
-  bool have_pushed = false;
+  // ev_pushed[t % ring]: completion of minibatch t's push (or, for evaluation, of its pull)
+  cudaEvent_t ev_pushed[wh::kMaxDepth + 1] = {nullptr};
+  int max_delay = 0;                 // pull(t) waits for push(t - 1 - max_delay); pushes stay in order
   // sharded jobs: every rank's lane outboxes, [rank][lane] (own ones included); 0 capacity = not attached
   size_t outbox_cap = 0;
   unsigned char* peer_outbox[wh::kMaxShards][wh::kMaxDepth] = {{nullptr}};
@@ -115,7 +116,8 @@ int wh_worker_create_ex(whContext* ctx, whServer* server, int loss, uint64_t max
   w->ctx = ctx; w->server = server; w->loss = loss; w->max_key = max_key; w->depth = depth;
   int r = w->pinned.reserve(512 * kMaxDepth);
   for (int i = 0; r == WH_OK && i < depth; ++i) r = lane_init(w, i);
-  if (r == WH_OK && cudaEventCreateWithFlags(&w->ev_pushed, cudaEventDisableTiming) != cudaSuccess) r = WH_ERR_CUDA;
+  for (int i = 0; r == WH_OK && i <= kMaxDepth; ++i)
+    if (cudaEventCreateWithFlags(&w->ev_pushed[i], cudaEventDisableTiming) != cudaSuccess) r = WH_ERR_CUDA;
   if (r != WH_OK) { for (int i = 0; i < depth; ++i) lane_release(w->lane[i]); w->pinned.release(); delete w; return r; }
   *out = w;
   return WH_OK;
@@ -134,13 +136,21 @@ int wh_worker_destroy(whWorker* w) {
   }
   for (void* p : w->opened) if (p) cudaIpcCloseMemHandle(p);
   for (int i = 0; i < w->depth; ++i) lane_release(w->lane[i]);
-  if (w->ev_pushed) cudaEventDestroy(w->ev_pushed);
+  for (auto e : w->ev_pushed) if (e) cudaEventDestroy(e);
   w->pinned.release();
   delete w;
   return WH_OK;
 }
 
 int wh_worker_wait(whWorker* w, uint64_t ticket, double* prog);
+
+int wh_worker_set_max_delay(whWorker* w, int max_delay) {
+  WH_REQUIRE(w && max_delay >= 0 && max_delay < w->depth, "wh_worker_set_max_delay: needs 0 <= max_delay < depth");
+  WH_REQUIRE(w->next_wait == w->next_ticket, "wh_worker_set_max_delay: minibatches are in flight");
+  WH_REQUIRE(max_delay == 0 || !w->server || w->server->map.world == 1, "wh_worker_set_max_delay: sharded jobs keep max_delay 0 (their barriers assume one order)");
+  w->max_delay = max_delay;
+  return WH_OK;
+}
 
 int wh_worker_submit(whWorker* w, const whRowBlock* blk, int mem, size_t nnz, int train, uint64_t* ticket) {
   WH_REQUIRE(w && blk && ticket, "wh_worker_submit: NULL argument");
@@ -198,7 +208,11 @@ int wh_worker_submit(whWorker* w, const whRowBlock* blk, int mem, size_t nnz, in
   else WH_TRY(localize_sort(cx, in, uniq, nullptr, l.index.as<uint32_t>(), d_nuniq));
   if (outboxed) WH_TRY(outbox_cuts_launch(s, cx->stream, l.outbox.as<unsigned char>()));
   // ZPull: one Handle::Pull per unique key, after every earlier push
-  if (w->have_pushed) WH_CUDA(cudaStreamWaitEvent(cx->stream, w->ev_pushed, 0));
+  const unsigned long long tk = w->next_ticket;       // this minibatch's ticket (1, 2, ...)
+  const int ring = kMaxDepth + 1;
+  // bounded staleness (the reference's max_concurrency > 1 lets a worker pull before its earlier pushes have
+  // landed): with max_delay = d the pull of minibatch t waits for the push of minibatch t - 1 - d only
+  if (tk > 1ull + (unsigned)w->max_delay) WH_CUDA(cudaStreamWaitEvent(cx->stream, w->ev_pushed[(tk - 1 - w->max_delay) % ring], 0));
   const bool sharded = s->map.world > 1;
   if (sharded) {
     // gather straight from the GPUs that own the keys; nobody may start pushing before everyone has pulled
@@ -224,6 +238,8 @@ int wh_worker_submit(whWorker* w, const whRowBlock* blk, int mem, size_t nnz, in
     WH_TRY(spmv_trans_accumulate_launch(cx, rows, n, d_offset, l.index.as<uint32_t>(), d_value, l.dual.as<float>(), acc, fs, acc_copies(), ucap, scale_ready));
     WH_PROF(cx, "spmv_trans");
     const float mul = w->loss == WH_LOSS_SQUARE_HINGE ? -2.f : 1.f;
+    // pushes are applied one message at a time, in ticket order (two push kernels on one key would tear an entry)
+    if (w->max_delay > 0 && tk > 1) WH_CUDA(cudaStreamWaitEvent(cx->stream, w->ev_pushed[(tk - 1) % ring], 0));
     if (outboxed) {
       // owners apply: gradients go to the outbox as fp32; once every rank has pulled and filled its outbox
       // (barrier), each owner walks the source ranks in ascending order -- one push message each -- reading its
@@ -248,8 +264,7 @@ int wh_worker_submit(whWorker* w, const whRowBlock* blk, int mem, size_t nnz, in
     WH_PROF(cx, "push");
   }
   WH_CUDA(cudaMemcpyAsync(l.pinned + 256, s->counters.p, 24, cudaMemcpyDeviceToHost, cx->stream));
-  WH_CUDA(cudaEventRecord(w->ev_pushed, cx->stream));
-  w->have_pushed = true;
+  WH_CUDA(cudaEventRecord(w->ev_pushed[tk % ring], cx->stream));
   // join the AUC branch, then the progress read-back
   WH_CUDA(cudaStreamWaitEvent(cx->stream, l.ev_auc, 0));
   if (cx->prof.on) WH_TRY(prof_mark(cx, "auc_tail"));
