@@ -275,6 +275,34 @@ WH_API int wh_worker_finish(whWorker* w, const float* d_weights, float* d_grads,
 WH_API int wh_worker_process_minibatch(whWorker* w, const whRowBlock* blk, int mem, int train,
                                        double* prog);
 
+/* ---- (4b) the reader in front of the path ------------------------------- */
+/* Text formats of MinibatchIter (learn/base/minibatch_iter.h:44-59). "crb" (lz4 + recordio) and "adfea" are not built. */
+enum { WH_FMT_LIBSVM = 0, WH_FMT_CRITEO = 1, WH_FMT_CRITEO_TEST = 2 };
+typedef struct whRows whRows; /* a device-resident dmlc::data::RowBlockContainer<uint64_t> */
+/* ParseNext of one chunk of text (whole lines; host or device memory, < 4 GiB) on the GPU:
+ *   criteo / criteo_test  CriteoParser::ParseNext, learn/base/criteo_parser.h:38-89: label, 13 integer fields and 26
+ *                         8-byte categorical fields, tab separated; index = CityHash64(field) >> 10 | field_no << 54.
+ *   libsvm                dmlc-core's LibSVMParser (un-vendored): `label index[:value] ...`, numbers as atof / strtoull.
+ * Where the reference would read past the end of a line or CHECK-fail (short lines, categorical fields that are not
+ * 8 bytes) the call fails with WH_ERR_INVALID and names the line; numeric literals that cannot be converted exactly
+ * with one double operation (> 15 digits or |exponent| > 22) are refused rather than rounded differently. */
+WH_API int wh_parse_text(whContext* ctx, int format, const char* text, size_t len, int mem, whRows** out);
+/* RowBlockContainer: Clear / Push(RowBlock slice) / Push(Row) / GetBlock, as MinibatchIter::Next uses them
+ * (learn/base/minibatch_iter.h:74-147). append takes rows [begin, begin+n) of src, or the n rows listed in the HOST
+ * array row_ids (the shuffled order rdp_[i], :102-110). drop_unit_values is the all-ones rule (:116-118).
+ * view yields DEVICE pointers, ready for wh_worker_submit(..., WH_DEVICE, wh_rows_nnz(r), ...). */
+WH_API int wh_rows_create(whContext* ctx, whRows** out);
+WH_API void wh_rows_destroy(whRows* r);
+WH_API int wh_rows_clear(whRows* r);
+WH_API int wh_rows_append(whContext* ctx, whRows* dst, const whRows* src, size_t begin, size_t n, const uint32_t* row_ids);
+WH_API int wh_rows_drop_unit_values(whContext* ctx, whRows* r);
+WH_API size_t wh_rows_size(const whRows* r);
+WH_API size_t wh_rows_nnz(const whRows* r);
+WH_API int wh_rows_has_value(const whRows* r);
+WH_API int wh_rows_view(const whRows* r, whRowBlock* view);
+/* to host arrays (NULL = skip): offset[size+1], label[size], index[nnz], value[nnz] */
+WH_API int wh_rows_copy(whContext* ctx, const whRows* r, size_t* offset, float* label, uint64_t* index, float* value);
+
 /* ---- (5) DiFacto: factorization machine on the same path -------------------------------- */
 typedef struct whDifacto whDifacto; /* AsyncServer shard + AsyncWorker pipeline on one GPU */
 

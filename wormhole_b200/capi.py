@@ -420,3 +420,99 @@ class Worker:
         if self.h:
             lib().wh_worker_destroy(self.h)
             self.h = None
+
+
+FMT = {"libsvm": 0, "criteo": 1, "criteo_test": 2}
+
+
+class Rows:
+    """A device-resident RowBlockContainer<uint64_t> (whRows): the product of wh_parse_text and the
+    container MinibatchIter assembles minibatches in. Duck-types the block argument of Worker.submit
+    (rows / offset / label / index / value are DEVICE addresses; pass mem=WH_DEVICE, nnz=self.nnz)."""
+
+    class _DevPtr:
+        def __init__(self, p):
+            self.p = p
+
+        def data_ptr(self):
+            return self.p
+
+    def __init__(self, ctx, handle=None):
+        self.ctx = ctx
+        if handle is None:
+            handle = C.c_void_p()
+            _check(lib().wh_rows_create(ctx.h, C.byref(handle)))
+        self.h = handle
+
+    @property
+    def rows(self):
+        L = lib()
+        L.wh_rows_size.restype = C.c_size_t
+        return int(L.wh_rows_size(self.h))
+
+    @property
+    def nnz(self):
+        L = lib()
+        L.wh_rows_nnz.restype = C.c_size_t
+        return int(L.wh_rows_nnz(self.h))
+
+    @property
+    def has_value(self):
+        return bool(lib().wh_rows_has_value(self.h))
+
+    def _view(self):
+        v = _RowBlock()
+        _check(lib().wh_rows_view(self.h, C.byref(v)))
+        return v
+
+    offset = property(lambda self: Rows._DevPtr(self._view().offset))
+    label = property(lambda self: Rows._DevPtr(self._view().label))
+    index = property(lambda self: Rows._DevPtr(self._view().index))
+    value = property(lambda self: Rows._DevPtr(self._view().value) if self.has_value else None)
+
+    def clear(self):
+        _check(lib().wh_rows_clear(self.h))
+
+    def append(self, src, begin=0, n=None, row_ids=None):
+        if row_ids is not None:
+            ids = np.ascontiguousarray(row_ids, dtype=np.uint32)
+            _check(lib().wh_rows_append(self.ctx.h, self.h, src.h, C.c_size_t(0), C.c_size_t(len(ids)), _ptr(ids)))
+        else:
+            n = src.rows - begin if n is None else n
+            _check(lib().wh_rows_append(self.ctx.h, self.h, src.h, C.c_size_t(begin), C.c_size_t(n), None))
+
+    def drop_unit_values(self):
+        _check(lib().wh_rows_drop_unit_values(self.ctx.h, self.h))
+
+    def labels(self):
+        lab = np.empty(self.rows, np.float32)
+        _check(lib().wh_rows_copy(self.ctx.h, self.h, None, _ptr(lab), None, None))
+        return lab
+
+    def to_host(self):
+        """-> RowBlock on the host (tests, debugging)."""
+        rows, nnz = self.rows, self.nnz
+        off, lab, idx = np.empty(rows + 1, np.uint64), np.empty(rows, np.float32), np.empty(nnz, np.uint64)
+        val = np.empty(nnz, np.float32) if self.has_value else None
+        _check(lib().wh_rows_copy(self.ctx.h, self.h, _ptr(off), _ptr(lab), _ptr(idx), _ptr(val)))
+        return RowBlock(off, idx, val, lab)
+
+    def close(self):
+        if self.h:
+            lib().wh_rows_destroy(self.h)
+            self.h = None
+
+    __del__ = close
+
+
+def parse_text(ctx, fmt, text, mem=WH_HOST, length=None):
+    """wh_parse_text: one chunk of whole lines -> Rows. text: bytes (host) or a device address with `length`."""
+    h = C.c_void_p()
+    if mem == WH_HOST:
+        buf = (C.c_char * len(text)).from_buffer_copy(text) if not isinstance(text, np.ndarray) else None
+        p = C.cast(buf, C.c_void_p) if buf is not None else _ptr(text)
+        n = len(text)
+    else:
+        p, n = C.c_void_p(int(text)), int(length)
+    _check(lib().wh_parse_text(ctx.h, FMT[fmt], p, C.c_size_t(n), mem, C.byref(h)))
+    return Rows(ctx, h)
