@@ -285,7 +285,9 @@ typedef struct whRows whRows; /* a device-resident dmlc::data::RowBlockContainer
  *   libsvm                dmlc-core's LibSVMParser (un-vendored): `label index[:value] ...`, numbers as atof / strtoull.
  * Where the reference would read past the end of a line or CHECK-fail (short lines, categorical fields that are not
  * 8 bytes) the call fails with WH_ERR_INVALID and names the line; numeric literals that cannot be converted exactly
- * with one double operation (> 15 digits or |exponent| > 22) are refused rather than rounded differently. */
+ * with one double operation (> 15 digits or |exponent| > 22) are refused rather than rounded differently.
+ * *out == NULL on entry: a new container is returned; otherwise that container is cleared and refilled, reusing
+ * its device buffers (no allocation in steady state). */
 WH_API int wh_parse_text(whContext* ctx, int format, const char* text, size_t len, int mem, whRows** out);
 /* RowBlockContainer: Clear / Push(RowBlock slice) / Push(Row) / GetBlock, as MinibatchIter::Next uses them
  * (learn/base/minibatch_iter.h:74-147). append takes rows [begin, begin+n) of src, or the n rows listed in the HOST

@@ -499,15 +499,19 @@ class Rows:
 
     def close(self):
         if self.h:
-            lib().wh_rows_destroy(self.h)
+            try:
+                lib().wh_rows_destroy(self.h)
+            except TypeError:        # interpreter shutdown: the module globals are already gone
+                pass
             self.h = None
 
     __del__ = close
 
 
-def parse_text(ctx, fmt, text, mem=WH_HOST, length=None):
-    """wh_parse_text: one chunk of whole lines -> Rows. text: bytes (host) or a device address with `length`."""
-    h = C.c_void_p()
+def parse_text(ctx, fmt, text, mem=WH_HOST, length=None, into=None):
+    """wh_parse_text: one chunk of whole lines -> Rows. text: bytes / numpy uint8 (host) or a device address with
+    `length`. into: a Rows to refill (its buffers are reused) instead of creating one."""
+    h = C.c_void_p() if into is None else into.h
     if mem == WH_HOST:
         buf = (C.c_char * len(text)).from_buffer_copy(text) if not isinstance(text, np.ndarray) else None
         p = C.cast(buf, C.c_void_p) if buf is not None else _ptr(text)
@@ -515,4 +519,4 @@ def parse_text(ctx, fmt, text, mem=WH_HOST, length=None):
     else:
         p, n = C.c_void_p(int(text)), int(length)
     _check(lib().wh_parse_text(ctx.h, FMT[fmt], p, C.c_size_t(n), mem, C.byref(h)))
-    return Rows(ctx, h)
+    return Rows(ctx, h) if into is None else into

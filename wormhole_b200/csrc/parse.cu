@@ -70,9 +70,9 @@ __device__ uint64_t cityhash64_short(const char* s, int len) {
 // digits at all give 0, as strtod does. The value is formed as M * 10^e with ONE correctly rounded double
 // operation, which equals strtod whenever M < 2^53 and |e| <= 22; literals outside that range, and inf / nan /
 // hex floats, set *bad (the call then fails instead of returning a differently rounded number).
+__constant__ double kP10[23] = {1e0, 1e1, 1e2, 1e3, 1e4, 1e5, 1e6, 1e7, 1e8, 1e9, 1e10, 1e11,
+                                1e12, 1e13, 1e14, 1e15, 1e16, 1e17, 1e18, 1e19, 1e20, 1e21, 1e22};
 __device__ double parse_number(const char* p, const char* end, int* bad) {
-  const double p10[23] = {1e0, 1e1, 1e2, 1e3, 1e4, 1e5, 1e6, 1e7, 1e8, 1e9, 1e10, 1e11,
-                          1e12, 1e13, 1e14, 1e15, 1e16, 1e17, 1e18, 1e19, 1e20, 1e21, 1e22};
   while (p != end && (is_blank(*p) || *p == '\v' || *p == '\f')) ++p;
   bool neg = false;
   if (p != end && (*p == '-' || *p == '+')) { neg = *p == '-'; ++p; }
@@ -108,7 +108,7 @@ __device__ double parse_number(const char* p, const char* end, int* bad) {
   double r;
   if (m == 0) r = 0;
   else if (big || m >= (1ULL << 53) || e > 22 || e < -22) { *bad = 1; return 0; }
-  else r = e >= 0 ? (double)m * p10[e] : (double)m / p10[-e];
+  else r = e >= 0 ? (double)m * kP10[e] : (double)m / kP10[-e];
   return neg ? -r : r;
 }
 
@@ -147,12 +147,33 @@ __device__ __forceinline__ void report(unsigned long long* err, int code, size_t
 }
 
 // ---- Criteo (learn/base/criteo_parser.h:47-87), one thread per line ----------------------------------------
-__global__ void __launch_bounds__(128) criteo_lines_kernel(const char* text, size_t len, const uint32_t* starts,
-                                                           size_t lines, int is_train, float* label, unsigned* cnt,
-                                                           uint64_t* tmp, unsigned long long* err) {
-  const size_t r = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+// A block owns kCriteoLPB consecutive lines = one contiguous span of text, which it first copies to shared memory
+// with coalesced 16-byte loads (a thread walking its line in global memory would touch a different 128-byte line
+// of the cache than each of its 31 neighbours on every byte). Spans beyond the buffer are parsed in place.
+constexpr int kCriteoLPB = 128;
+constexpr int kCriteoSpan = 56 * 1024;   // bytes of text staged per block (average Criteo line: ~230 bytes)
+__global__ void __launch_bounds__(kCriteoLPB) criteo_lines_kernel(const char* text, size_t len, const uint32_t* starts,
+                                                                  size_t lines, int is_train, float* label, unsigned* cnt,
+                                                                  uint64_t* tmp, unsigned long long* err) {
+  extern __shared__ uint4 stage[];
+  const size_t l0 = (size_t)blockIdx.x * kCriteoLPB;
+  const size_t r = l0 + threadIdx.x;
+  const size_t g0 = starts[l0], g1 = l0 + kCriteoLPB < lines ? starts[l0 + kCriteoLPB] : len;
+  const size_t a0 = g0 & ~(size_t)15;                       // 16-byte aligned start of the copy
+  const char* base = text;                                  // address of text byte 0 in the space we parse from
+  const bool aligned = ((uintptr_t)text & 15) == 0;
+  if (aligned && g1 - a0 <= (size_t)kCriteoSpan) {
+    const size_t n16 = (g1 - a0 + 15) / 16;
+    const uint4* src = reinterpret_cast<const uint4*>(text + a0);
+    for (size_t k = threadIdx.x; k < n16; k += kCriteoLPB) {
+      if (a0 + 16 * k + 16 <= len) stage[k] = __ldg(src + k);
+      else for (size_t b = a0 + 16 * k; b < len; ++b) reinterpret_cast<char*>(stage)[b - a0] = text[b];   // the text's last bytes
+    }
+    __syncthreads();
+    base = reinterpret_cast<const char*>(stage) - a0;
+  }
   if (r >= lines) return;
-  const char *p = text + starts[r], *end = text + len;
+  const char *p = base + starts[r], *end = base + len;
   const char* lend = line_end(p, end);
   uint64_t* out = tmp + r * kCriteoMax;
   unsigned n = 0;
@@ -198,16 +219,20 @@ struct CntFlag {
   const unsigned* cnt;
   __device__ unsigned operator()(size_t i) const { return cnt[i]; }
 };
-struct CompactCriteo {
-  const uint64_t* tmp;
-  uint64_t* index;
+struct EmitOffset {
   size_t* offset;
-  __device__ void operator()(size_t r, unsigned v, unsigned prefix) const {
-    offset[r + 1] = (size_t)prefix + v;
-    const uint64_t* s = tmp + r * kCriteoMax;
-    for (unsigned k = 0; k < v; ++k) index[prefix + k] = s[k];
-  }
+  __device__ void operator()(size_t r, unsigned v, unsigned prefix) const { offset[r + 1] = (size_t)prefix + v; }
 };
+// one warp moves one line's strip (<= 39 ids, contiguous on both sides) to its place in the CSR
+__global__ void __launch_bounds__(256) compact_criteo_kernel(const uint64_t* tmp, const size_t* offset, size_t lines,
+                                                             uint64_t* index) {
+  const size_t r = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const unsigned lane = threadIdx.x & 31;
+  if (r >= lines) return;
+  const size_t o = offset[r], n = offset[r + 1] - o;
+  const uint64_t* s = tmp + r * kCriteoMax;
+  for (size_t k = lane; k < n; k += 32) index[o + k] = s[k];
+}
 
 // ---- libsvm, one thread per line ---------------------------------------------------------------------------
 // value of the scan: (1 << 32 | tokens) for a line that holds a row, 0 for a blank one
@@ -417,9 +442,11 @@ int wh_parse_text(whContext* ctx, int format, const char* text, size_t len, int 
   WH_REQUIRE(len < (1ULL << 32), "wh_parse_text: a chunk is at most 4 GiB - 1 bytes (got %zu)", len);
   DeviceGuard g(ctx->device);
   cudaStream_t st = ctx->stream;
-  whRows* r = nullptr;
-  WH_TRY(wh_rows_create(ctx, &r));
-  struct Guard { whRows* r; ~Guard() { if (r) wh_rows_destroy(r); } } guard{r};
+  // *out == NULL: a new container; otherwise the caller's container is cleared and refilled (its buffers are reused)
+  whRows* r = *out;
+  const bool fresh = r == nullptr;
+  if (fresh) WH_TRY(wh_rows_create(ctx, &r)); else WH_TRY(wh_rows_clear(r));
+  struct Guard { whRows* r; ~Guard() { if (r) wh_rows_destroy(r); } } guard{fresh ? r : nullptr};
   if (len == 0) { guard.r = nullptr; *out = r; return WH_OK; }
 
   const char* d_text = nullptr;
@@ -482,12 +509,15 @@ int wh_parse_text(whContext* ctx, int format, const char* text, size_t len, int 
     WH_TRY(ctx->stage[4].reserve((size_t)nbl * sizeof(unsigned)));
     unsigned* cnt = ctx->stage[3].as<unsigned>();
     uint64_t* tmp = ctx->stage[2].as<uint64_t>();
-    WH_LAUNCH(criteo_lines_kernel, (unsigned)div_up(lines, 128), 128, 0, st, d_text, len, starts, lines,
+    // > 48 KiB of dynamic shared memory needs the opt-in (per device, so repeated; it is a host-side table write)
+    WH_CUDA(cudaFuncSetAttribute(criteo_lines_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kCriteoSpan + 16));
+    WH_LAUNCH(criteo_lines_kernel, (unsigned)div_up(lines, kCriteoLPB), kCriteoLPB, kCriteoSpan + 16, st, d_text, len, starts, lines,
               format == WH_FMT_CRITEO ? 1 : 0, r->label.as<float>(), cnt, tmp, d_u64 + 3);
     unsigned* d_nnz = ctx->small.as<unsigned>() + 1;
-    WH_TRY((scan_and_apply<unsigned, CntFlag, CompactCriteo>(
-        ctx, CntFlag{cnt}, CompactCriteo{tmp, r->index.as<uint64_t>(), r->offset.as<size_t>()}, lines,
-        ctx->stage[4].as<unsigned>(), d_nnz)));
+    WH_TRY((scan_and_apply<unsigned, CntFlag, EmitOffset>(ctx, CntFlag{cnt}, EmitOffset{r->offset.as<size_t>()}, lines,
+                                                          ctx->stage[4].as<unsigned>(), d_nnz)));
+    WH_LAUNCH(compact_criteo_kernel, (unsigned)div_up(lines * 32, 256), 256, 0, st, tmp, r->offset.as<size_t>(), lines,
+              r->index.as<uint64_t>());
     WH_CUDA(cudaMemcpyAsync(hp, d_u64 + 3, 8, cudaMemcpyDeviceToHost, st));
     WH_CUDA(cudaMemcpyAsync(hp + 1, d_nnz, 4, cudaMemcpyDeviceToHost, st));
     WH_CUDA(cudaStreamSynchronize(st));

@@ -93,3 +93,19 @@ def kdd_minibatch(m, rows=1000000, seed=43, bias=-2.0):
     p = 1.0 / (1.0 + np.exp(-score))
     label = (_uniform(seed, m, rows, 4) < p).astype(np.float32)
     return RowBlock(offset, ids, None, label)
+
+
+def criteo_text_minibatch(m, rows=100000, seed=42):
+    """Minibatch m of the Criteo-shape stream as TEXT in the dataset's own schema (learn/base/criteo_parser.h:17-21):
+    the same per-field Zipf ranks as criteo_minibatch, written as decimal integers (13 fields) and 8 hex digits
+    (26 fields), tab separated, `label` first; labels are Bernoulli(0.25). Used to feed the GPU reader."""
+    F = CRITEO_FIELDS
+    u = _uniform(seed, m, rows * F, 1).reshape(rows, F)
+    cols = [np.where(_uniform(seed, m, rows, 2) < 0.25, "1", "0")]
+    for f in range(F):
+        r = _zipf_rank(u[:, f], CRITEO_CARD[f], 1.1).astype(np.uint64)
+        cols.append(np.char.mod("%d" if f < 13 else "%08x", r))
+    lines = cols[0]
+    for c in cols[1:]:
+        lines = np.char.add(np.char.add(lines, "\t"), c)
+    return ("\n".join(lines.tolist()) + "\n").encode()
