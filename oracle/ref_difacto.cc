@@ -126,3 +126,17 @@ REF_API void ref_difacto_model_get(void* h, int dim, uint64_t* keys, uint32_t* f
 REF_API void ref_difacto_destroy(void* h) {
   Job* j = (Job*)h; delete j->worker; delete j->server; delete j->store; delete j;
 }
+
+// learn/difacto/progress.h:14-30 through the reference's own struct (8 values; carries ttl_ex, nnz_w, nnz_V).
+REF_API int ref_difacto_progress_row(const double* data8, double* carry3, char* out, int cap) {
+  dmlc::difacto::Progress p;
+  p.data.assign(data8, data8 + 8);
+  p.ttl_ex = carry3[0]; p.nnz_w = carry3[1]; p.nnz_V = carry3[2];
+  std::string s = p.PrintStr();
+  carry3[0] = p.ttl_ex; carry3[1] = p.nnz_w; carry3[2] = p.nnz_V;
+  snprintf(out, cap, "%s", s.c_str());
+  return (int)s.size();
+}
+REF_API int ref_difacto_progress_head(char* out, int cap) {
+  return snprintf(out, cap, "%s", dmlc::difacto::Progress::HeadStr().c_str());
+}

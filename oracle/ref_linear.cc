@@ -281,3 +281,18 @@ REF_API void ref_linear_destroy(void* h) {
   delete j->worker; delete j->server; delete j->store; delete j;
 }
 REF_API int ref_num_procs(void) { return omp_get_num_procs(); }
+
+// learn/linear/progress.h:14-27 through the reference's own struct: one table row for the merged progress
+// `data6`, carrying ttl_ex / nnz_w across calls. Returns the length written to out (0 = "no progress").
+REF_API int ref_linear_progress_row(const double* data6, double* ttl_ex, double* nnz_w, char* out, int cap) {
+  dmlc::linear::Progress p;
+  p.data.assign(data6, data6 + 6);
+  p.ttl_ex = *ttl_ex; p.nnz_w = *nnz_w;
+  std::string s = p.PrintStr();
+  *ttl_ex = p.ttl_ex; *nnz_w = p.nnz_w;
+  snprintf(out, cap, "%s", s.c_str());
+  return (int)s.size();
+}
+REF_API int ref_linear_progress_head(char* out, int cap) {
+  return snprintf(out, cap, "%s", dmlc::linear::Progress::HeadStr().c_str());
+}

@@ -1,0 +1,59 @@
+"""Host logic of the scheduler mirror, CPU only: conf parsing the way arg_parser.h + protobuf text
+format read it, and the progress-table rows against rows printed by the reference's own Progress structs
+(tests/golden/golden_progress.json, made by tests/golden/make_progress_golden.py through oracle/_ref)."""
+import io
+import json
+import os
+
+from wormhole_b200.solver import Config, DifactoProgress, DifactoStop, Progress, match_files
+
+G = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "golden_progress.json")))
+
+
+def test_linear_progress_rows_equal_the_reference():
+    assert Progress.HeadStr() == G["linear"]["head"]
+    p = Progress()
+    for v, want in zip(G["linear"]["in"], G["linear"]["rows"]):
+        p.data = list(v)
+        assert p.PrintStr() == want
+
+
+def test_difacto_progress_rows_equal_the_reference():
+    assert DifactoProgress.HeadStr() == G["difacto"]["head"]
+    p = DifactoProgress()
+    for v, want in zip(G["difacto"]["in"], G["difacto"]["rows"]):
+        p.data = list(v)
+        assert p.PrintStr() == want
+
+
+def test_demo_conf_and_argument_overrides():
+    demo = '# demo conf\n\ntrain_data = "learn/data/agaricus.txt.train"\nval_data = "learn/data/agaricus.txt.test"\n' \
+           'model_out = "./agaricus_model"\nmax_data_pass = 3\n'                 # learn/linear/guide/demo.conf
+    c = Config(demo)
+    assert c.train_data == "learn/data/agaricus.txt.train" and c.max_data_pass == 3 and c.model_out == "./agaricus_model"
+    assert c.algo == "FTRL" and c.minibatch == 1000 and c.rand_shuffle == 10 and c.max_concurrency == 2   # defaults
+    assert not c.has("lr_eta") and c.lr_eta == 0.01
+    c.merge("lr_eta=.1 algo=ADAGRAD train_data='a=b.txt' minibatch: 500")         # '=' kept inside quotes
+    assert c.has("lr_eta") and abs(c.lr_eta - 0.1) < 1e-7 and c.algo == "ADAGRAD" and c.train_data == "a=b.txt"
+    assert c.minibatch == 500
+    try:
+        Config("no_such_key = 1")
+        assert False
+    except Exception as e:
+        assert "unknown field" in str(e)
+
+
+def test_match_files(tmp_path):
+    for n in ("part-0", "part-1", "other"):
+        (tmp_path / n).write_text("x")
+    assert [os.path.basename(f) for f in match_files(str(tmp_path / "part-.*"))] == ["part-0", "part-1"]
+    assert match_files(str(tmp_path / "other")) == [str(tmp_path / "other")]
+
+
+def test_difacto_stop_rule():
+    out = io.StringIO()
+    s = DifactoStop(early_stop=True, min_objv_decr=1e-3, max_objv=2.0, out=out)
+    assert not s(500.0, 1000, True) and s(2500.0, 1000, True)         # training: objective above max_objv
+    assert not s(600.0, 1000, False)                                   # 100 -> 0.6
+    assert not s(590.0, 1000, False)                                   # improved by 0.01
+    assert s(589.9, 1000, False) and "minimal requirement" in out.getvalue()
