@@ -166,6 +166,7 @@ def segment_bytes(name, N, B, U, words):
         "loss_forward": 12 * B,                         # label, Xw read; dual written
         "auc": 8 * B,                                   # label, Xw read
         "spmv_trans": 4 * N + 8 * B + 4 * B + 8 * U,    # local ids, offsets, dual, accumulators
+        "spmv_fused": 4 * N + 8 * B + 8 * B + 4 * U + 8 * U,  # forward + backward in one launch: local ids once, offsets, label, Xw, w, accumulators
         "push": U * (8 + 8 + 2 * s),                    # key, accumulator, state read + written
     }.get(name, 0)
 
@@ -320,7 +321,7 @@ def run_ours(args):
         traffic = None
         try:
             tr = json.load(open(os.path.join(ROOT, "profiles", "r1_c_traffic.json")))
-            kname = {"spmv_trans": "spmv_trans_kernel<0>", "push": "server_push_kernel<1>", "spmv_loss": "spmv_loss_kernel<0>",
+            kname = {"spmv_fused": "spmv_fused_hot_kernel", "spmv_trans": "spmv_trans_kernel<0>", "push": "server_push_kernel<1>", "spmv_loss": "spmv_loss_kernel<0>",
                      "loc_mark": "loc_mark_tma_kernel", "loc_rank": "loc_rank_kernel", "pull": "server_pull_kernel"}.get(top[0])
             traffic = tr.get(kname) if (rows == ROWS and world == 1) else None
         except Exception:

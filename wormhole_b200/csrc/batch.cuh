@@ -35,5 +35,10 @@ int localize_direct(whContext* ctx, const LocInput& in, uint64_t* d_uniq, uint32
 int localize_sort(whContext* ctx, const LocInput& in, uint64_t* d_uniq, uint32_t* d_cnt,
                   uint32_t* d_index, unsigned* d_nuniq);
 bool direct_supported(uint64_t max_key);
+struct HotView;
+// Direct localizer with the worker's hot-key table (hot.cuh): d_codes[i] = kHotFlag | slot for table keys, the rank
+// otherwise; also fills hot.rank for this minibatch. Needs a 16-byte aligned id array with an even entry count.
+int localize_direct_hot(whContext* ctx, const LocInput& in, const HotView& hot, uint64_t* d_uniq, uint32_t* d_codes,
+                        unsigned* d_nuniq);
 
 }  // namespace wh

@@ -13,7 +13,12 @@
 //          radix sort of (key, position), run-length heads -> ranks, scatter by position.
 #include <stdlib.h>
 
+#include <algorithm>
+#include <numeric>
+#include <vector>
+
 #include "batch.cuh"
+#include "hot.cuh"
 #include "scan.cuh"
 
 namespace wh {
@@ -268,6 +273,148 @@ int localize_direct(whContext* ctx, const LocInput& in, uint64_t* d_uniq, uint32
   WH_CUDA(cudaMemsetAsync(dir, 0, words * sizeof(uint2), ctx->stream));
   WH_PROF(ctx, "loc_dir_clear");
   return WH_OK;
+}
+
+// ------------------------------------------------------------------ direct, with hot keys --
+// See hot.cuh. Same directory, same scan, same ascending key list; entries of table keys never touch the
+// directory (one shared-memory probe instead of an L2 access in mark and in rank) and come out as codes.
+
+constexpr int kHotMarkThreads = kTmaThreads;
+constexpr unsigned kColdCode = 0x7fffffffu;   // "not a table key": the rank pass replaces it
+__global__ void __launch_bounds__(kTmaThreads) loc_mark_hot_kernel(const uint64_t* __restrict__ index, size_t n,
+                                                                   KeyXform xf, uint2* dir, HotView hot,
+                                                                   uint32_t* __restrict__ codes) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  uint64_t* stage = reinterpret_cast<uint64_t*>(smem);
+  uint64_t* bar = stage + (size_t)kTmaStages * kTileIds;
+  static_assert(kTmaStages % 2 == 0, "the tag table behind the barriers must stay 16-byte aligned");
+  uint4* s_tags = reinterpret_cast<uint4*>(bar + kTmaStages);
+  unsigned char* s_present = reinterpret_cast<unsigned char*>(s_tags + kHotBuckets);
+  hot_load_tags(s_tags, hot.tags);
+  for (int i = threadIdx.x; i < kHotSlots / 4; i += blockDim.x) reinterpret_cast<unsigned*>(s_present)[i] = 0u;
+  // (id_ring_run starts with a __syncthreads)
+  id_ring_run(index, n, stage, bar, [&](const uint64_t* ids, size_t base, unsigned cnt) {
+    uint64_t k[kPerThread];
+    unsigned word[kPerThread];
+    bool probe[kPerThread];
+#pragma unroll
+    for (int u = 0; u < kPerThread; ++u) {
+      const unsigned j = u * kTmaThreads + threadIdx.x;
+      probe[u] = j < cnt;
+      k[u] = xf(probe[u] ? ids[j] : 0);
+      if (probe[u]) {
+        const int slot = hot_probe(s_tags, (unsigned)k[u]);
+        codes[base + j] = slot >= 0 ? (kHotFlag | (unsigned)slot) : kColdCode;   // the entry's code is known here
+        if (slot >= 0) { s_present[slot] = 1; probe[u] = false; }   // same-value byte stores: no atomics needed
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < kPerThread; ++u) word[u] = probe[u] ? __ldcg(&dir[k[u] >> 5].x) : 0xffffffffu;
+#pragma unroll
+    for (int u = 0; u < kPerThread; ++u) {
+      const unsigned bit = 1u << (k[u] & 31);
+      if (probe[u] && !(word[u] & bit)) atomicOr(&dir[k[u] >> 5].x, bit);
+    }
+  });
+  __syncthreads();
+  for (int i = threadIdx.x; i < kHotSlots; i += blockDim.x) if (s_present[i]) hot.present[i] = 1u;
+}
+
+// table keys that occur in this minibatch enter the directory like any other key (kHotSlots threads; folding
+// this into the mark kernel's tail -- last block, or per-block test-and-set -- cost 15-25 us of serial latency)
+__global__ void hot_present_kernel(HotView hot, uint2* dir) {
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= kHotSlots || !hot.present[p]) return;
+  const unsigned k = reinterpret_cast<const unsigned*>(hot.tags)[p];
+  atomicOr(&dir[k >> 5].x, 1u << (k & 31));
+}
+// after the scan: the rank of every table key that is present; resets the presence flags for the next minibatch
+__device__ __forceinline__ void hot_rank_slot(const HotView& hot, const uint2* __restrict__ dir, int p) {
+  unsigned r = kHotNone;
+  if (hot.present[p]) {
+    const unsigned k = reinterpret_cast<const unsigned*>(hot.tags)[p];
+    const uint2 e = dir[k >> 5];
+    r = e.y + __popc(e.x & ((1u << (k & 31)) - 1u));
+    hot.present[p] = 0u;
+  }
+  hot.rank[p] = r;
+}
+
+// rank pass: only entries that are not table keys still need their key and the directory
+__global__ void __launch_bounds__(256) loc_rank_cold_kernel(const uint64_t* __restrict__ index, size_t n, KeyXform xf,
+                                                            const uint2* __restrict__ dir, uint32_t* __restrict__ codes,
+                                                            HotView hot) {
+  // (the blocks also rank the table keys, a slice each: nothing in this launch reads hot.rank)
+  {
+    const int per = (kHotSlots + (int)gridDim.x - 1) / (int)gridDim.x;
+    const int lo = (int)blockIdx.x * per, hi = min(kHotSlots, lo + per);
+    for (int p = lo + (int)threadIdx.x; p < hi; p += (int)blockDim.x) hot_rank_slot(hot, dir, p);
+  }
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  for (size_t i0 = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i0 < n; i0 += stride * kLocIlp) {
+    uint32_t c[kLocIlp];
+    uint64_t k[kLocIlp];
+    uint2 e[kLocIlp];
+#pragma unroll
+    for (int u = 0; u < kLocIlp; ++u) { const size_t i = i0 + u * stride; c[u] = i < n ? ld_stream_u32(codes + i) : 0u; }
+#pragma unroll
+    for (int u = 0; u < kLocIlp; ++u) if (c[u] == kColdCode) k[u] = ld_stream_u64(index + i0 + u * stride);
+#pragma unroll
+    for (int u = 0; u < kLocIlp; ++u) if (c[u] == kColdCode) { k[u] = xf(k[u]); e[u] = __ldg(dir + (k[u] >> 5)); }
+#pragma unroll
+    for (int u = 0; u < kLocIlp; ++u)
+      if (c[u] == kColdCode) codes[i0 + u * stride] = e[u].y + __popc(e[u].x & ((1u << (k[u] & 31)) - 1u));
+  }
+}
+
+int localize_direct_hot(whContext* ctx, const LocInput& in, const HotView& hot, uint64_t* d_uniq, uint32_t* d_codes,
+                        unsigned* d_nuniq) {
+  const size_t words = div_up(in.xf.max_key, 32);
+  if (ctx->directory.cap < words * sizeof(uint2) || ctx->directory_words < words) {
+    WH_TRY(ctx->directory.reserve(words * sizeof(uint2)));
+    WH_CUDA(cudaMemsetAsync(ctx->directory.p, 0, ctx->directory.cap, ctx->stream));
+    ctx->directory_words = ctx->directory.cap / sizeof(uint2);
+  }
+  uint2* dir = ctx->directory.as<uint2>();
+  WH_TRY(ctx->scan_tmp.reserve(div_up(words, kScanTile) * sizeof(unsigned) + 256));
+  const size_t n = in.nnz;
+  const bool tma = n >= 2 && ((uintptr_t)in.index & 15) == 0 && (n & 1) == 0;
+  WH_REQUIRE(tma, "localize_direct_hot: the id array must be 16-byte aligned with an even entry count");
+  const size_t mark_smem = (size_t)kTmaStages * kTileIds * 8 + kTmaStages * 8 + kHotSlots * 4 + kHotSlots;
+  WH_CUDA(cudaFuncSetAttribute(loc_mark_hot_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)mark_smem));
+  const unsigned tgrid = (unsigned)std::min<size_t>(div_up(n, kTileIds), (size_t)ctx->num_sms * 2);
+  WH_LAUNCH(loc_mark_hot_kernel, tgrid, kTmaThreads, mark_smem, ctx->stream, in.index, n, in.xf, dir, hot, d_codes);
+  WH_LAUNCH(hot_present_kernel, kHotSlots / 256, 256, 0, ctx->stream, hot, dir);
+  WH_PROF(ctx, "loc_mark");
+  WH_TRY(scan_and_apply<unsigned>(ctx, DirPopc{dir}, DirEmit{dir, d_uniq}, words, ctx->scan_tmp.as<unsigned>(), d_nuniq));
+  WH_PROF(ctx, "loc_dir_scan");
+  const unsigned rgrid = (unsigned)std::min<size_t>(div_up(n, 256 * kLocIlp), (size_t)ctx->num_sms * 8);
+  WH_LAUNCH(loc_rank_cold_kernel, rgrid, 256, 0, ctx->stream, in.index, n, in.xf, dir, d_codes, hot);
+  WH_PROF(ctx, "loc_rank");
+  WH_CUDA(cudaMemsetAsync(dir, 0, words * sizeof(uint2), ctx->stream));
+  WH_PROF(ctx, "loc_dir_clear");
+  return WH_OK;
+}
+
+// Most frequent keys first; a key whose bucket is already full is left out (it simply stays an ordinary key).
+int hot_build_image(const uint64_t* keys, const uint32_t* counts, size_t n, uint32_t* image) {
+  std::fill(image, image + kHotSlots, kHotEmpty);
+  std::vector<uint32_t> order(n);
+  std::iota(order.begin(), order.end(), 0u);
+  const size_t want = std::min<size_t>(n, kHotSlots / 2);          // half-full table: few buckets overflow
+  std::partial_sort(order.begin(), order.begin() + want, order.end(), [&](uint32_t a, uint32_t b) {
+    return counts[a] != counts[b] ? counts[a] > counts[b] : keys[a] < keys[b];
+  });
+  int placed = 0;
+  for (size_t i = 0; i < want; ++i) {
+    const uint64_t k = keys[order[i]];
+    if (counts[order[i]] < 2 || k >= kDirectMaxKey) continue;
+    const unsigned k32 = (unsigned)k;
+    const unsigned b = (k32 * 0x9E3779B1u) >> (32 - 11);
+    for (int w = 0; w < kHotWays; ++w)
+      if (image[b * kHotWays + w] == kHotEmpty) { image[b * kHotWays + w] = k32; ++placed; break; }
+  }
+  return placed;
 }
 
 // --------------------------------------------------------------------------------- sort --

@@ -88,11 +88,7 @@ loss_reduce_kernel(unsigned nparts, const double* part_objv, const double* part_
 int loss_reduce_launch(whContext* ctx, unsigned nparts, const double* po, const double* pl, const unsigned* pc,
                        EvalOut* out, FixedScale* fs, size_t nnz) {
   float sc = 1.f; double inv = 1.0;
-  if (fs) {   // terms bounded by 1 in magnitude: nnz * 1 * 2^e < 2^62 (same rule as fixed_scale_kernel)
-    int en = 0; while (en < 64 && ((unsigned long long)(nnz | 1) >> en)) ++en;
-    const int e = 61 - 1 - en;
-    sc = ldexpf(1.f, e); inv = ldexp(1.0, -e);
-  }
+  if (fs) unit_terms_scale(nnz, &sc, &inv);
   WH_LAUNCH(loss_reduce_kernel, 1, 256, 0, ctx->stream, nparts, po, pl, pc, out, fs, sc, inv);
   return WH_OK;
 }

@@ -50,7 +50,7 @@ __device__ __forceinline__ void loss_row(int loss, float lab, float p, float* du
 // the transposed product that follows, for |dual| <= 1 and binary features (no max-reduction kernels needed).
 int spmv_loss_launch(whContext* ctx, int loss, size_t rows, size_t nnz, const size_t* offset, const uint32_t* index,
                      const float* value, const float* label, const float* w, float* xw, float* dual, EvalOut* out,
-                     struct FixedScale* fs);
+                     struct FixedScale* fs, const float* hot_w = nullptr);   // hot_w: index holds codes (hot.cuh)
 int loss_reduce_launch(whContext* ctx, unsigned nparts, const double* po, const double* pl, const unsigned* pc,
                        EvalOut* out, struct FixedScale* fs, size_t nnz);
 

@@ -109,18 +109,22 @@ server_push_kernel(HandleParams h, void* table, const uint64_t* __restrict__ key
   int delta = 0, bad = 0;
   // grid-stride: the launch is sized for the number of SMs, not for the upper bound of n (which is only known
   // on the device and is ~15x smaller than the bound at Criteo shape)
+  const size_t entry_bytes = h.algo == WH_ALGO_FTRL ? 16 : (h.algo == WH_ALGO_ADAGRAD ? 8 : 4);
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const uint64_t k = keys[i];
+    uint64_t slot;
+    bool present;
+    const bool ok = find_slot(h, k, true, &slot, &present);
+    // start the entry's trip from DRAM now, so that it overlaps the accumulator loads instead of following them
+    if (ok) asm volatile("prefetch.global.L2 [%0];" ::"l"(reinterpret_cast<const char*>(table) + slot * entry_bytes));
     float g;
     if (FROM_ACC) {
-      long long a = 0;
-      for (unsigned c = 0; c < copies; ++c) { a += acc[c * stride + i]; acc[c * stride + i] = 0; }
+      const long long a = sum_and_clear_replicas(acc, copies, stride, i);
       g = (float)((double)a * fs->inv) * mul;
     } else {
       g = grads[i];
     }
-    uint64_t k = keys[i], slot;
-    bool present;
-    if (find_slot(h, k, true, &slot, &present)) delta += handle_push(h, table, slot, g);
+    if (ok) delta += handle_push(h, table, slot, g);
     else bad = 1;
   }
   commit_counters(counters, delta, bad);
@@ -261,8 +265,9 @@ server_push_turn_kernel(HandleParams h, ShardMap m, int target, const uint64_t* 
   if (i < n) {
     const uint64_t k = keys[i];
     if (k >= m.bounds[target] && k < m.bounds[target + 1]) {
-      long long a = 0;
-      for (unsigned c = 0; c < copies; ++c) { a += acc[c * stride + i]; acc[c * stride + i] = 0; }
+      // all replicas first, then the clears: interleaved, every load waits for the one before it (the
+      // stores may alias), and a thread pays `copies` memory latencies in a row
+      long long a = sum_and_clear_replicas(acc, copies, stride, i);
       const float g = (float)((double)a * fs->inv) * mul;
       delta = handle_push(h, m.table[target], k - m.bounds[target], g);
     }

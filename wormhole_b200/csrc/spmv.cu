@@ -1,6 +1,7 @@
 // Pieces (2) and (5): SpMV::Times / TransTimes and SpMM::Times / TransTimes. See spmv.cuh.
 #include <stdlib.h>
 
+#include "hot.cuh"
 #include "loss.cuh"
 #include "spmv.cuh"
 
@@ -67,11 +68,20 @@ spmv_times_kernel(size_t rows, const size_t* __restrict__ offset, const uint32_t
 // SpMV::Times with the loss as its epilogue (learn/linear/loss.h:32-39 Init, then the per-example part of
 // Evaluate and CalcGrad): the thread that has just summed row i turns Xw[i] into dual[i] and adds the row's
 // objective term and accuracy flag to the block's partial sums. Same summation order as spmv_times_kernel.
-template <bool HAS_VAL>
+// HOT: index holds codes (hot.cuh): kHotFlag | slot reads the slot-indexed weight array (32 KB, L1 resident).
+template <bool HOT>
+__device__ __forceinline__ float gather_w(const float* __restrict__ x, const float* __restrict__ hot_w, uint32_t code) {
+  // one load from a selected address: no divergent branch around two loads
+  const float* p = (HOT && (code & kHotFlag)) ? hot_w + (code & (kHotSlots - 1)) : x + code;
+  return __ldg(p);
+}
+
+template <bool HAS_VAL, bool HOT>
 __global__ void __launch_bounds__(kRowsPerBlock)
 spmv_loss_kernel(int loss, size_t rows, const size_t* __restrict__ offset, const uint32_t* __restrict__ index,
                  const float* __restrict__ value, const float* __restrict__ label, const float* __restrict__ x,
-                 float* __restrict__ y, float* __restrict__ dual, double* part_objv, unsigned* part_correct) {
+                 float* __restrict__ y, float* __restrict__ dual, double* part_objv, unsigned* part_correct,
+                 const float* __restrict__ hot_w) {
   extern __shared__ __align__(16) unsigned char smem[];
   __shared__ size_t s_off[kRowsPerBlock + 1];
   __shared__ double s_o[kRowsPerBlock / 32];
@@ -89,14 +99,14 @@ spmv_loss_kernel(int loss, size_t rows, const size_t* __restrict__ offset, const
       const unsigned lb = (unsigned)(b - s_off[0]), le = (unsigned)(e - s_off[0]);
       unsigned j = lb;
       for (; j + 4 <= le; j += 4) {
-        float g0 = __ldg(x + s_idx[j]), g1 = __ldg(x + s_idx[j + 1]);
-        float g2 = __ldg(x + s_idx[j + 2]), g3 = __ldg(x + s_idx[j + 3]);
+        float g0 = gather_w<HOT>(x, hot_w, s_idx[j]), g1 = gather_w<HOT>(x, hot_w, s_idx[j + 1]);
+        float g2 = gather_w<HOT>(x, hot_w, s_idx[j + 2]), g3 = gather_w<HOT>(x, hot_w, s_idx[j + 3]);
         if (HAS_VAL) { g0 *= s_val[j]; g1 *= s_val[j + 1]; g2 *= s_val[j + 2]; g3 *= s_val[j + 3]; }
         acc += g0; acc += g1; acc += g2; acc += g3;
       }
-      for (; j < le; ++j) { float g = __ldg(x + s_idx[j]); if (HAS_VAL) g *= s_val[j]; acc += g; }
+      for (; j < le; ++j) { float g = gather_w<HOT>(x, hot_w, s_idx[j]); if (HAS_VAL) g *= s_val[j]; acc += g; }
     } else {
-      for (size_t j = b; j < e; ++j) { float g = __ldg(x + index[j]); if (HAS_VAL) g *= value[j]; acc += g; }
+      for (size_t j = b; j < e; ++j) { float g = gather_w<HOT>(x, hot_w, index[j]); if (HAS_VAL) g *= value[j]; acc += g; }
     }
     y[r] = acc;   // rows without entries: Xw_ starts zeroed in ScalarLoss::Init (vector::resize)
     float dl;
@@ -119,7 +129,7 @@ spmv_loss_kernel(int loss, size_t rows, const size_t* __restrict__ offset, const
 
 int spmv_loss_launch(whContext* ctx, int loss, size_t rows, size_t nnz, const size_t* offset, const uint32_t* index,
                      const float* value, const float* label, const float* w, float* xw, float* dual, EvalOut* out,
-                     FixedScale* fs) {
+                     FixedScale* fs, const float* hot_w) {
   if (rows == 0) return loss_reduce_launch(ctx, 0, nullptr, nullptr, nullptr, out, fs, nnz);
   const unsigned grid = (unsigned)div_up(rows, kRowsPerBlock);
   WH_TRY(ctx->stage[7].reserve((size_t)grid * 16 + 64));
@@ -127,11 +137,13 @@ int spmv_loss_launch(whContext* ctx, int loss, size_t rows, size_t nnz, const si
   unsigned* pc = reinterpret_cast<unsigned*>(po + grid);
   if (value) {
     const size_t smem = kTileCap * 8;
-    static bool attr = false;
-    if (!attr) { WH_CUDA(cudaFuncSetAttribute(spmv_loss_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); attr = true; }
-    WH_LAUNCH(spmv_loss_kernel<true>, grid, kRowsPerBlock, smem, ctx->stream, loss, rows, offset, index, value, label, w, xw, dual, po, pc);
+    WH_CUDA(cudaFuncSetAttribute(spmv_loss_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    WH_CUDA(cudaFuncSetAttribute(spmv_loss_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    if (hot_w) WH_LAUNCH((spmv_loss_kernel<true, true>), grid, kRowsPerBlock, smem, ctx->stream, loss, rows, offset, index, value, label, w, xw, dual, po, pc, hot_w);
+    else WH_LAUNCH((spmv_loss_kernel<true, false>), grid, kRowsPerBlock, smem, ctx->stream, loss, rows, offset, index, value, label, w, xw, dual, po, pc, hot_w);
   } else {
-    WH_LAUNCH(spmv_loss_kernel<false>, grid, kRowsPerBlock, kTileCap * 4, ctx->stream, loss, rows, offset, index, value, label, w, xw, dual, po, pc);
+    if (hot_w) WH_LAUNCH((spmv_loss_kernel<false, true>), grid, kRowsPerBlock, kTileCap * 4, ctx->stream, loss, rows, offset, index, value, label, w, xw, dual, po, pc, hot_w);
+    else WH_LAUNCH((spmv_loss_kernel<false, false>), grid, kRowsPerBlock, kTileCap * 4, ctx->stream, loss, rows, offset, index, value, label, w, xw, dual, po, pc, hot_w);
   }
   return loss_reduce_launch(ctx, grid, po, nullptr, pc, out, fs, nnz);
 }
@@ -256,8 +268,7 @@ __global__ void fixed_finish_kernel(long long* acc, size_t n, const FixedScale* 
   if (d_n) n = *d_n;   // the count may live on the device (number of unique keys of a minibatch)
   const double inv = fs->inv;
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
-    long long a = 0;
-    for (unsigned c = 0; c < copies; ++c) { a += acc[c * stride + i]; acc[c * stride + i] = 0; }
+    const long long a = sum_and_clear_replicas(acc, copies, stride, i);
     float s = (float)((double)a * inv) * mul;
     y[i] = z ? z[i] * p + s : s;
   }
@@ -332,6 +343,148 @@ int spmv_trans_times_launch(whContext* ctx, size_t rows, size_t nnz, const size_
   const unsigned g2 = (unsigned)std::min<size_t>(div_up(ysize, 256), (size_t)ctx->num_sms * 8);
   WH_LAUNCH(fixed_finish_kernel, g2, 256, 0, ctx->stream, acc, ysize, fs, 0.f, (const float*)nullptr, y, mul, copies, ysize, (const unsigned*)nullptr);
   return WH_OK;
+}
+
+// ------------------------------------------------------- forward + backward with hot keys --
+// hot.cuh. One launch does ScalarLoss::Init (Xw), the per-example part of Evaluate, the dual, and X^T dual for
+// binary features: the thread that summed row i turns Xw[i] into dual[i] and then walks the same (still staged)
+// codes a second time. One block per SM owns a contiguous band of rows, so that the entries of table keys can be
+// added up in a 64 KB shared-memory accumulator and leave the SM once per block instead of once per entry:
+// lanes of a warp holding the same slot merge first (ballot match + hardware warp reductions), the group's
+// leader adds to shared memory, everything else goes to the global fixed-point accumulators as before.
+__global__ void hot_w_kernel(HotView hot, const float* __restrict__ w) {
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= kHotSlots) return;
+  const unsigned r = hot.rank[p];
+  hot.w[p] = r == kHotNone ? 0.f : __ldg(w + r);
+}
+// weight of a code: table keys from shared memory, the rest from the pulled array (generic load, one address)
+__device__ __forceinline__ float gather_sw(const float* __restrict__ w, const float* s_w, uint32_t code) {
+  const float* p = (code & kHotFlag) ? s_w + (code & (kHotSlots - 1)) : w + code;
+  return *p;
+}
+// 64-bit add in shared memory out of two native 32-bit atomics. (atomicAdd on a 64-bit shared word compiles to a
+// compare-and-swap spin loop, ATOMS.CAST.SPIN, which collapsed under the table's contention: 600 instructions
+// per warp step.) The low word's returned old value tells this add whether IT wrapped; the carry rides on the
+// high word's add. Every wrap is carried exactly once, so the 64-bit sum is exact whatever the interleaving.
+__device__ __forceinline__ void smem_add_i64(long long* slot, long long v) {
+  unsigned* p = reinterpret_cast<unsigned*>(slot);
+  const unsigned lo = (unsigned)(unsigned long long)v, hi = (unsigned)((unsigned long long)v >> 32);
+  const unsigned old = atomicAdd(p, lo);
+  const unsigned carry = (old + lo) < old ? 1u : 0u;
+  if (hi + carry != 0u) atomicAdd(p + 1, hi + carry);
+}
+
+__global__ void __launch_bounds__(1024)
+spmv_fused_hot_kernel(int loss, size_t rows, unsigned rows_per_block, unsigned stage_cap,
+                      const size_t* __restrict__ offset, const uint32_t* __restrict__ codes,
+                      const float* __restrict__ label, const float* __restrict__ w, HotView hot,
+                      float* __restrict__ y, float* __restrict__ dual, double* part_objv, unsigned* part_correct,
+                      long long* acc, float scale, unsigned copies, size_t stride) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  long long* s_acc = reinterpret_cast<long long*>(smem);                       // kHotSlots
+  float* s_w = reinterpret_cast<float*>(s_acc + kHotSlots);                    // kHotSlots: the table keys' weights
+  size_t* s_off = reinterpret_cast<size_t*>(s_w + kHotSlots);                  // rows_per_block + 1
+  uint32_t* s_idx = reinterpret_cast<uint32_t*>(s_off + rows_per_block + 1);   // stage_cap
+  __shared__ double s_o[32];
+  __shared__ unsigned s_c[32];
+  // the table keys' pulled weights: slot -> rank of the key in this minibatch -> w
+  for (int i = threadIdx.x; i < kHotSlots; i += blockDim.x) {
+    s_acc[i] = 0;
+    const unsigned rk = __ldg(hot.rank + i);
+    s_w[i] = rk == kHotNone ? 0.f : __ldg(w + rk);
+  }
+  const size_t r0 = (size_t)blockIdx.x * rows_per_block;
+  for (unsigned t = threadIdx.x; t <= rows_per_block; t += blockDim.x) s_off[t] = offset[min(r0 + t, rows)];
+  __syncthreads();
+  const size_t begin = s_off[0];
+  const size_t cnt = s_off[rows_per_block] - begin;
+  const bool staged = cnt <= (size_t)stage_cap;
+  if (staged) for (unsigned i = threadIdx.x; i < (unsigned)cnt; i += blockDim.x) s_idx[i] = ld_stream_u32(codes + begin + i);
+  __syncthreads();
+  const uint32_t* idx = staged ? s_idx : codes + begin;   // generic pointer: shared or global
+  const size_t r = r0 + threadIdx.x;
+  const bool live = threadIdx.x < rows_per_block && r < rows;
+  const unsigned lb = live ? (unsigned)(s_off[threadIdx.x] - begin) : 0u;
+  const unsigned len = live ? (unsigned)(s_off[threadIdx.x + 1] - s_off[threadIdx.x]) : 0u;
+  // forward: sequential fp32 in CSR order, four gathers in flight
+  double objv = 0;
+  unsigned correct = 0;
+  float dl = 0.f;
+  if (live) {
+    float sum = 0.f;
+    unsigned j = 0;
+    for (; j + 4 <= len; j += 4) {
+      const float g0 = gather_sw(w, s_w, idx[lb + j]), g1 = gather_sw(w, s_w, idx[lb + j + 1]);
+      const float g2 = gather_sw(w, s_w, idx[lb + j + 2]), g3 = gather_sw(w, s_w, idx[lb + j + 3]);
+      sum += g0; sum += g1; sum += g2; sum += g3;
+    }
+    for (; j < len; ++j) sum += gather_sw(w, s_w, idx[lb + j]);
+    y[r] = sum;
+    loss_row(loss, label[r], sum, &dl, &objv, &correct);
+    if (dual) dual[r] = dl;
+  }
+  // backward: every entry of row i contributes dual[i] (binary features), in fixed point
+  const long long q = __float2ll_rn(dl * scale);
+  long long* gacc = acc + (size_t)(blockIdx.x & (copies - 1)) * stride;
+  const unsigned maxlen = __reduce_max_sync(0xffffffffu, len);
+  const unsigned lane = threadIdx.x & 31;
+  for (unsigned j = 0; j < maxlen; ++j) {
+    const bool valid = j < len;
+    const uint32_t c = valid ? idx[lb + j] : 0u;
+    const bool is_hot = valid && (c & kHotFlag);
+    if (valid && !is_hot) atomicAdd(reinterpret_cast<unsigned long long*>(gacc + c), (unsigned long long)q);
+    // table keys: straight into shared memory. Lanes of a warp on the same slot are serialised by the hardware
+    // inside ONE native atomic; merging them in software first (ballot match + masked warp reductions) cost 600
+    // instructions per warp step, because reductions over lane masks that differ within the warp run mask by mask.
+    if (is_hot) smem_add_i64(s_acc + (c & (kHotSlots - 1)), q);
+  }
+  // objective / accuracy partial sums of the block
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    objv += __shfl_down_sync(0xffffffffu, objv, o);
+    correct += __shfl_down_sync(0xffffffffu, correct, o);
+  }
+  if (lane == 0) { s_o[threadIdx.x >> 5] = objv; s_c[threadIdx.x >> 5] = correct; }
+  __syncthreads();   // also: every shared-memory sum of the block is in
+  if (threadIdx.x == 0) {
+    double o = 0; unsigned cc = 0;
+    for (unsigned k = 0; k < (blockDim.x + 31) / 32; ++k) { o += s_o[k]; cc += s_c[k]; }
+    part_objv[blockIdx.x] = o; part_correct[blockIdx.x] = cc;
+  }
+  // the block's sums of the table keys join the ordinary accumulators at their keys' ranks
+  for (int i = threadIdx.x; i < kHotSlots; i += blockDim.x) {
+    const long long v = s_acc[i];
+    if (v != 0) atomicAdd(reinterpret_cast<unsigned long long*>(gacc + __ldg(hot.rank + i)), (unsigned long long)v);
+  }
+}
+
+int hot_w_launch(whContext* ctx, const HotView& hot, const float* w) {
+  WH_LAUNCH(hot_w_kernel, kHotSlots / 256, 256, 0, ctx->stream, hot, w);
+  return WH_OK;
+}
+
+// Binary features, codes from localize_direct_hot, acc all zero on entry. Leaves Xw in xw, the dual in dual (may
+// be NULL), the evaluation partials in `out`, X^T dual in acc (fixed point, scale written to fs for the push).
+int spmv_fused_hot_launch(whContext* ctx, int loss, size_t rows, size_t nnz, const size_t* offset, const uint32_t* codes,
+                          const float* label, const float* w, const HotView& hot, float* xw, float* dual, EvalOut* out,
+                          FixedScale* fs, long long* acc, unsigned copies, size_t stride) {
+  // one block per SM if the rows allow it; a thread per row
+  unsigned rpb = (unsigned)align_up(div_up(rows, (size_t)ctx->num_sms), 32);
+  rpb = std::max(32u, std::min(rpb, 1024u));
+  const unsigned grid = (unsigned)div_up(rows, rpb);
+  const size_t fixed = (size_t)kHotSlots * 12 + ((size_t)rpb + 1) * 8;
+  const size_t budget = 220 * 1024;
+  const unsigned cap = (unsigned)((budget - fixed) / 4);
+  WH_CUDA(cudaFuncSetAttribute(spmv_fused_hot_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)budget));
+  WH_TRY(ctx->stage[7].reserve((size_t)grid * 16 + 64));
+  double* po = ctx->stage[7].as<double>();
+  unsigned* pc = reinterpret_cast<unsigned*>(po + grid);
+  float sc; double inv;
+  unit_terms_scale(nnz, &sc, &inv);
+  WH_LAUNCH(spmv_fused_hot_kernel, grid, rpb, budget, ctx->stream, loss, rows, rpb, cap, offset, codes, label, w, hot, xw,
+            dual, po, pc, acc, sc, copies, stride);
+  return loss_reduce_launch(ctx, grid, po, nullptr, pc, out, fs, nnz);
 }
 
 // --------------------------------------------------------------------------------- SpMM --

@@ -14,6 +14,8 @@
 // (bit-reproducible run to run) and differs from the reference only by the reference's own
 // fp32 accumulation rounding (tests bound it by 1e-5 of the sum of |terms|).
 #pragma once
+#include <math.h>
+
 #include "common.cuh"
 
 namespace wh {
@@ -21,12 +23,44 @@ namespace wh {
 // replicas of the accumulator array that blocks spread their atomics over (power of two)
 constexpr unsigned kAccCopies = 8;   // upper bound; acc_copies() picks the count in use
 unsigned acc_copies();
+#ifdef __CUDACC__
+// Sum of one output's accumulator replicas, clearing them for the next minibatch. All replicas are loaded
+// first, then cleared: interleaved, every load waits for the one before it (the stores may alias) and a
+// thread pays `copies` memory latencies in a row.
+__device__ __forceinline__ long long sum_and_clear_replicas(long long* acc, unsigned copies, size_t stride, size_t i) {
+  long long v[kAccCopies];
+#pragma unroll
+  for (unsigned c = 0; c < kAccCopies; ++c) v[c] = c < copies ? __ldcg(acc + c * stride + i) : 0;
+  long long a = 0;
+#pragma unroll
+  for (unsigned c = 0; c < kAccCopies; ++c) a += v[c];
+#pragma unroll
+  for (unsigned c = 0; c < kAccCopies; ++c) if (c < copies) acc[c * stride + i] = 0;
+  return a;
+}
+#endif
 
 struct FixedScale {
   float scale;     // 2^e
   double inv;      // 2^-e
   unsigned maxx_bits, maxv_bits;  // float bit patterns of max|x|, max|val| (atomicMax targets)
 };
+
+// Fixed-point scale for terms bounded by 1 in magnitude: nnz * 1 * 2^e < 2^62 (the rule of fixed_scale_kernel,
+// evaluated on the host when the bound is known up front: binary features, |dual| <= 1).
+static inline void unit_terms_scale(size_t nnz, float* scale, double* inv) {
+  int en = 0;
+  while (en < 64 && ((unsigned long long)(nnz | 1) >> en)) ++en;
+  const int e = 61 - 1 - en;
+  *scale = ldexpf(1.f, e);
+  *inv = ldexp(1.0, -e);
+}
+struct HotView;
+struct EvalOut;
+int hot_w_launch(whContext* ctx, const HotView& hot, const float* w);
+int spmv_fused_hot_launch(whContext* ctx, int loss, size_t rows, size_t nnz, const size_t* offset, const uint32_t* codes,
+                          const float* label, const float* w, const HotView& hot, float* xw, float* dual, EvalOut* out,
+                          FixedScale* fs, long long* acc, unsigned copies, size_t stride);
 
 int spmv_times_launch(whContext* ctx, size_t rows, const size_t* offset, const uint32_t* index,
                       const float* value, const float* x, float* y);

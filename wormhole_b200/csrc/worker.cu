@@ -14,7 +14,12 @@
 // (max_concurrency = 1, the configuration parity is judged in), while staging, localize and AUC
 // of neighbouring minibatches run side by side. AUC, which nothing downstream depends on, runs on
 // a side stream of the lane.
+#include <stdlib.h>
+
+#include <vector>
+
 #include "batch.cuh"
+#include "hot.cuh"
 #include "loss.cuh"
 #include "server.cuh"
 #include "spmv.cuh"
@@ -35,6 +40,7 @@ struct Lane {
   DevBuf uniq, index, w, xw, dual, scal;
   char* pinned = nullptr;    // 512 B of the worker's pinned block
   DevBuf outbox;             // sharded jobs: {U, cuts | keys | grads}, mapped by every peer
+  DevBuf hot;                // hot-key state of the lane (hot.cuh): present | rank | w (kHotSlots each) | block counter
   bool busy = false, train = false;
   size_t rows = 0;
   // state between wh_worker_begin and wh_worker_finish
@@ -62,13 +68,17 @@ struct whWorker {
   void* opened[wh::kMaxShards * wh::kMaxDepth] = {nullptr};
   unsigned long long next_ticket = 1, next_wait = 1;
   long long seen_new_w = 0;
+  // hot keys (hot.cuh): the table image shared by the lanes; built from a census of the first eligible minibatch
+  wh::DevBuf hot_tags;
+  bool hot_enabled = true, hot_tried = false, hot_ready = false;
+  int hot_keys = 0;
 };
 
 using namespace wh;
 
 static void lane_release(Lane& l) {
   for (DevBuf* b : {&l.in_index, &l.in_offset, &l.in_value, &l.in_label, &l.uniq, &l.index, &l.w, &l.xw, &l.dual,
-                    &l.scal, &l.outbox, &l.cx.directory, &l.cx.scan_tmp, &l.cx.acc, &l.cx.small, &l.ax.scan_tmp, &l.ax.small})
+                    &l.scal, &l.outbox, &l.hot, &l.cx.directory, &l.cx.scan_tmp, &l.cx.acc, &l.cx.small, &l.ax.scan_tmp, &l.ax.small})
     b->release();
   for (auto& b : l.cx.sort_tmp) b.release();
   for (auto& b : l.ax.sort_tmp) b.release();
@@ -96,9 +106,48 @@ static int lane_init(whWorker* w, int i) {
   WH_CUDA(cudaEventCreateWithFlags(&l.ev_auc, cudaEventDisableTiming));
   WH_CUDA(cudaEventCreateWithFlags(&l.ev_done, cudaEventDisableTiming));
   WH_TRY(l.scal.reserve(4096));
+  WH_TRY(l.hot.reserve((size_t)kHotSlots * (4 + 4 + 4 + 8)));
+  WH_CUDA(cudaMemsetAsync(l.hot.p, 0, (size_t)kHotSlots * (4 + 4 + 4 + 8), l.cx.stream));
   WH_TRY(l.cx.small.reserve(1 << 14));
   WH_TRY(l.ax.small.reserve(1 << 14));
   l.pinned = w->pinned.as<char>() + 512 * i;
+  return WH_OK;
+}
+
+static HotView lane_hot_view(const whWorker* w, Lane& l) {
+  HotView v;
+  v.tags = w->hot_tags.as<uint4>();
+  v.present = l.hot.as<unsigned>();
+  v.rank = v.present + kHotSlots;
+  v.w = reinterpret_cast<float*>(v.rank + kHotSlots);
+  v.done = reinterpret_cast<unsigned*>(v.w + kHotSlots);
+  return v;
+}
+
+// Census of one minibatch: localize it with counts, bring (key, count) to the host, pick the table. Runs once per
+// worker, synchronously; its only product is the table image (a cache hint -- results never depend on it).
+static int hot_census(whWorker* w, Lane& l, const LocInput& in, size_t ucap) {
+  whContext* cx = &l.cx;
+  w->hot_tried = true;
+  DevBuf keys, cnt, idx;
+  struct Free { DevBuf *a, *b, *c; ~Free() { a->release(); b->release(); c->release(); } } guard{&keys, &cnt, &idx};
+  WH_TRY(keys.reserve(ucap * 8)); WH_TRY(cnt.reserve(ucap * 4)); WH_TRY(idx.reserve(in.nnz * 4));
+  unsigned* d_n = l.scal.as<unsigned>() + 16;
+  WH_TRY(localize_direct(cx, in, keys.as<uint64_t>(), cnt.as<uint32_t>(), idx.as<uint32_t>(), d_n));
+  unsigned U = 0;
+  WH_CUDA(cudaMemcpyAsync(&U, d_n, 4, cudaMemcpyDeviceToHost, cx->stream));
+  WH_CUDA(cudaStreamSynchronize(cx->stream));
+  std::vector<uint64_t> hk(U);
+  std::vector<uint32_t> hc(U), image(kHotSlots);
+  if (U) {
+    WH_CUDA(cudaMemcpy(hk.data(), keys.p, (size_t)U * 8, cudaMemcpyDeviceToHost));
+    WH_CUDA(cudaMemcpy(hc.data(), cnt.p, (size_t)U * 4, cudaMemcpyDeviceToHost));
+  }
+  w->hot_keys = hot_build_image(hk.data(), hc.data(), U, image.data());
+  if (w->hot_keys < 64) return WH_OK;            // nothing repeats enough to be worth a table
+  WH_TRY(w->hot_tags.reserve((size_t)kHotSlots * 4));
+  WH_CUDA(cudaMemcpy(w->hot_tags.p, image.data(), (size_t)kHotSlots * 4, cudaMemcpyHostToDevice));
+  w->hot_ready = true;
   return WH_OK;
 }
 
@@ -114,6 +163,7 @@ int wh_worker_create_ex(whContext* ctx, whServer* server, int loss, uint64_t max
   DeviceGuard g(ctx->device);
   whWorker* w = new whWorker();
   w->ctx = ctx; w->server = server; w->loss = loss; w->max_key = max_key; w->depth = depth;
+  { const char* e = getenv("WH_HOT"); w->hot_enabled = !(e && atoi(e) == 0); }   // WH_HOT=0: plain kernels only
   int r = w->pinned.reserve(512 * kMaxDepth);
   for (int i = 0; r == WH_OK && i < depth; ++i) r = lane_init(w, i);
   for (int i = 0; r == WH_OK && i <= kMaxDepth; ++i)
@@ -138,6 +188,7 @@ int wh_worker_destroy(whWorker* w) {
   for (int i = 0; i < w->depth; ++i) lane_release(w->lane[i]);
   for (auto e : w->ev_pushed) if (e) cudaEventDestroy(e);
   w->pinned.release();
+  w->hot_tags.release();
   delete w;
   return WH_OK;
 }
@@ -201,10 +252,17 @@ int wh_worker_submit(whWorker* w, const whRowBlock* blk, int mem, size_t nnz, in
   long long* acc = nullptr;
   if (train) WH_TRY(ensure_acc(cx, ucap, &acc));
 
+  LocInput in{d_index, n, make_xform(w->max_key)};
+  // hot keys (hot.cuh): binary features in a direct-addressed key space, ids the TMA ring can stream
+  const bool hot_ok = w->hot_enabled && direct && d_value == nullptr && n >= 2 && (n & 1) == 0 && ((uintptr_t)d_index & 15) == 0;
+  if (hot_ok && !w->hot_tried) WH_TRY(hot_census(w, l, in, ucap));
+  const bool hot = hot_ok && w->hot_ready;
+  const HotView hv = lane_hot_view(w, l);
+
   WH_TRY(prof_begin(cx));
   // Localize
-  LocInput in{d_index, n, make_xform(w->max_key)};
-  if (direct) WH_TRY(localize_direct(cx, in, uniq, nullptr, l.index.as<uint32_t>(), d_nuniq));
+  if (hot) WH_TRY(localize_direct_hot(cx, in, hv, uniq, l.index.as<uint32_t>(), d_nuniq));
+  else if (direct) WH_TRY(localize_direct(cx, in, uniq, nullptr, l.index.as<uint32_t>(), d_nuniq));
   else WH_TRY(localize_sort(cx, in, uniq, nullptr, l.index.as<uint32_t>(), d_nuniq));
   if (outboxed) WH_TRY(outbox_cuts_launch(s, cx->stream, l.outbox.as<unsigned char>()));
   // ZPull: one Handle::Pull per unique key, after every earlier push
@@ -225,9 +283,19 @@ int wh_worker_submit(whWorker* w, const whRowBlock* blk, int mem, size_t nnz, in
   // Init (Xw), the per-example part of Evaluate, and the dual of CalcGrad: one pass over the rows. With
   // binary features |dual| <= 1 bounds every term of X^T dual, so the fixed-point scale is known up front.
   const bool scale_ready = d_value == nullptr;
-  WH_TRY(spmv_loss_launch(cx, w->loss, rows, n, d_offset, l.index.as<uint32_t>(), d_value, d_label, l.w.as<float>(),
-                          l.xw.as<float>(), train ? l.dual.as<float>() : nullptr, d_eval, (train && scale_ready) ? fs : nullptr));
-  WH_PROF(cx, "spmv_loss");
+  const bool fused = hot && train;
+  if (hot && !fused) WH_TRY(hot_w_launch(cx, hv, l.w.as<float>()));   // evaluation: the slot-indexed weights for spmv_loss
+  if (fused) {
+    // ... and with the hot-key table the transposed product rides in the same launch (spmv.cu)
+    WH_TRY(spmv_fused_hot_launch(cx, w->loss, rows, n, d_offset, l.index.as<uint32_t>(), d_label, l.w.as<float>(), hv,
+                                 l.xw.as<float>(), nullptr, d_eval, fs, acc, acc_copies(), ucap));
+    WH_PROF(cx, "spmv_fused");
+  } else {
+    WH_TRY(spmv_loss_launch(cx, w->loss, rows, n, d_offset, l.index.as<uint32_t>(), d_value, d_label, l.w.as<float>(),
+                            l.xw.as<float>(), train ? l.dual.as<float>() : nullptr, d_eval,
+                            (train && scale_ready) ? fs : nullptr, hot ? hv.w : nullptr));
+    WH_PROF(cx, "spmv_loss");
+  }
   // AUC on the side stream (nothing downstream of it but the progress numbers)
   WH_CUDA(cudaEventRecord(l.ev_fork, cx->stream));
   WH_CUDA(cudaStreamWaitEvent(l.ax.stream, l.ev_fork, 0));
@@ -235,8 +303,10 @@ int wh_worker_submit(whWorker* w, const whRowBlock* blk, int mem, size_t nnz, in
   WH_CUDA(cudaEventRecord(l.ev_auc, l.ax.stream));
   if (train) {
     // CalcGrad: X^T dual into the fixed-point accumulator; ZPush: convert + update in one pass
-    WH_TRY(spmv_trans_accumulate_launch(cx, rows, n, d_offset, l.index.as<uint32_t>(), d_value, l.dual.as<float>(), acc, fs, acc_copies(), ucap, scale_ready));
-    WH_PROF(cx, "spmv_trans");
+    if (!fused) {
+      WH_TRY(spmv_trans_accumulate_launch(cx, rows, n, d_offset, l.index.as<uint32_t>(), d_value, l.dual.as<float>(), acc, fs, acc_copies(), ucap, scale_ready));
+      WH_PROF(cx, "spmv_trans");
+    }
     const float mul = w->loss == WH_LOSS_SQUARE_HINGE ? -2.f : 1.f;
     // pushes are applied one message at a time, in ticket order (two push kernels on one key would tear an entry)
     if (w->max_delay > 0 && tk > 1) WH_CUDA(cudaStreamWaitEvent(cx->stream, w->ev_pushed[(tk - 1) % ring], 0));
