@@ -122,7 +122,7 @@ __global__ void __launch_bounds__(256) loc_rank_kernel(const uint64_t* __restric
 // Tiles of 2048 ids (16 KB) stream into a 4-deep ring of shared-memory stages by cp.async.bulk; the
 // block's threads take 8 ids each from the stage that has landed. Requires a 16-byte aligned id
 // array (the plain kernels above remain for the unaligned case).
-constexpr int kTileIds = 2048, kTmaStages = 4, kTmaThreads = 256, kPerThread = kTileIds / kTmaThreads;
+constexpr int kTileIds = 2048, kTmaStages = 2, kTmaThreads = 256, kPerThread = kTileIds / kTmaThreads;
 
 struct IdRing {
   uint64_t* stage;   // kTmaStages * kTileIds ids
@@ -320,6 +320,49 @@ __global__ void __launch_bounds__(kTmaThreads) loc_mark_hot_kernel(const uint64_
   for (int i = threadIdx.x; i < kHotSlots; i += blockDim.x) if (s_present[i]) hot.present[i] = 1u;
 }
 
+// The same pass without the TMA ring: a plain grid-stride kernel whose only shared memory is the table (40 KB), so
+// that four times as many warps are resident to hide the directory probes of the entries that miss it.
+constexpr int kHotMarkPlainThreads = 512;
+__global__ void __launch_bounds__(kHotMarkPlainThreads) loc_mark_hot_plain_kernel(const uint64_t* __restrict__ index, size_t n,
+                                                                                  KeyXform xf, uint2* dir, HotView hot,
+                                                                                  uint32_t* __restrict__ codes) {
+  __shared__ uint4 s_tags[kHotBuckets];
+  __shared__ unsigned char s_present[kHotSlots];
+  hot_load_tags(s_tags, hot.tags);
+  for (int i = threadIdx.x; i < kHotSlots / 4; i += blockDim.x) reinterpret_cast<unsigned*>(s_present)[i] = 0u;
+  __syncthreads();
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  for (size_t i0 = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i0 < n; i0 += stride * kLocIlp) {
+    uint64_t k[kLocIlp];
+    unsigned word[kLocIlp];
+    bool probe[kLocIlp];
+#pragma unroll
+    for (int u = 0; u < kLocIlp; ++u) {
+      const size_t i = i0 + u * stride;
+      probe[u] = i < n;
+      k[u] = probe[u] ? ld_stream_u64(index + i) : 0;
+    }
+#pragma unroll
+    for (int u = 0; u < kLocIlp; ++u) {
+      k[u] = xf(k[u]);
+      if (probe[u]) {
+        const int slot = hot_probe(s_tags, (unsigned)k[u]);
+        codes[i0 + u * stride] = slot >= 0 ? (kHotFlag | (unsigned)slot) : kColdCode;
+        if (slot >= 0) { s_present[slot] = 1; probe[u] = false; }
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < kLocIlp; ++u) word[u] = probe[u] ? __ldcg(&dir[k[u] >> 5].x) : 0xffffffffu;
+#pragma unroll
+    for (int u = 0; u < kLocIlp; ++u) {
+      const unsigned bit = 1u << (k[u] & 31);
+      if (probe[u] && !(word[u] & bit)) atomicOr(&dir[k[u] >> 5].x, bit);
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < kHotSlots; i += blockDim.x) if (s_present[i]) hot.present[i] = 1u;
+}
+
 // table keys that occur in this minibatch enter the directory like any other key (kHotSlots threads; folding
 // this into the mark kernel's tail -- last block, or per-block test-and-set -- cost 15-25 us of serial latency)
 __global__ void hot_present_kernel(HotView hot, uint2* dir) {
@@ -382,8 +425,18 @@ int localize_direct_hot(whContext* ctx, const LocInput& in, const HotView& hot, 
   WH_REQUIRE(tma, "localize_direct_hot: the id array must be 16-byte aligned with an even entry count");
   const size_t mark_smem = (size_t)kTmaStages * kTileIds * 8 + kTmaStages * 8 + kHotSlots * 4 + kHotSlots;
   WH_CUDA(cudaFuncSetAttribute(loc_mark_hot_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)mark_smem));
-  const unsigned tgrid = (unsigned)std::min<size_t>(div_up(n, kTileIds), (size_t)ctx->num_sms * 2);
-  WH_LAUNCH(loc_mark_hot_kernel, tgrid, kTmaThreads, mark_smem, ctx->stream, in.index, n, in.xf, dir, hot, d_codes);
+  const unsigned tgrid = (unsigned)std::min<size_t>(div_up(n, kTileIds), (size_t)ctx->num_sms * 3);
+  // measured at the Criteo shape: plain kernel, 2 x 512 threads per SM 33.8 us; TMA ring (2 stages, 3 blocks per SM)
+  // 40.1 us -- with 78 % of the entries answered from shared memory the pass is bound by instruction issue, and
+  // the ring's extra shared memory only costs resident warps. WH_HOT_MARK_PLAIN=0 selects the ring.
+  static int plain = -1;
+  if (plain < 0) { const char* e = getenv("WH_HOT_MARK_PLAIN"); plain = e ? atoi(e) : 2; }
+  if (plain) {
+    const unsigned pg = (unsigned)std::min<size_t>(div_up(n, kHotMarkPlainThreads * kLocIlp), (size_t)ctx->num_sms * plain);
+    WH_LAUNCH(loc_mark_hot_plain_kernel, pg, kHotMarkPlainThreads, 0, ctx->stream, in.index, n, in.xf, dir, hot, d_codes);
+  } else {
+    WH_LAUNCH(loc_mark_hot_kernel, tgrid, kTmaThreads, mark_smem, ctx->stream, in.index, n, in.xf, dir, hot, d_codes);
+  }
   WH_LAUNCH(hot_present_kernel, kHotSlots / 256, 256, 0, ctx->stream, hot, dir);
   WH_PROF(ctx, "loc_mark");
   WH_TRY(scan_and_apply<unsigned>(ctx, DirPopc{dir}, DirEmit{dir, d_uniq}, words, ctx->scan_tmp.as<unsigned>(), d_nuniq));

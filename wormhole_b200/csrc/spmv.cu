@@ -10,6 +10,21 @@ namespace wh {
 constexpr int kRowsPerBlock = 128;   // one thread per row
 constexpr int kTileCap = 6144;       // staged entries per block (Criteo shape: 128 x 39 = 4992)
 
+// Coalesced copy of a run of 32-bit words into shared memory with kStageIlp loads in flight per thread. (A plain
+// "s[i] = g[i]" loop keeps ONE: every store waits for its load, and a thread that stages 39 words pays 39 memory
+// latencies in a row -- measured as 31 % of all stall samples of the fused kernel, on this one store.)
+constexpr int kStageIlp = 8;
+template <typename T>
+__device__ __forceinline__ void stage_run(T* s, const T* __restrict__ g, unsigned cnt) {
+  for (unsigned i0 = threadIdx.x; i0 < cnt; i0 += blockDim.x * kStageIlp) {
+    T v[kStageIlp];
+#pragma unroll
+    for (int u = 0; u < kStageIlp; ++u) { const unsigned i = i0 + u * blockDim.x; if (i < cnt) v[u] = __ldcs(g + i); }
+#pragma unroll
+    for (int u = 0; u < kStageIlp; ++u) { const unsigned i = i0 + u * blockDim.x; if (i < cnt) s[i] = v[u]; }
+  }
+}
+
 // Loads the offsets of this block's rows and, if the rows' entries fit, their index (and value)
 // run into shared memory with coalesced loads. Returns whether the run was staged.
 template <bool HAS_VAL>
@@ -24,10 +39,8 @@ __device__ __forceinline__ bool stage_rows(size_t rows, const size_t* __restrict
   const size_t cnt = s_off[kRowsPerBlock] - begin;
   const bool staged = cnt <= (size_t)kTileCap;
   if (staged) {
-    for (unsigned i = threadIdx.x; i < (unsigned)cnt; i += blockDim.x) {
-      s_idx[i] = ld_stream_u32(index + begin + i);
-      if (HAS_VAL) s_val[i] = __ldg(value + begin + i);
-    }
+    stage_run(s_idx, index + begin, (unsigned)cnt);
+    if (HAS_VAL) stage_run(s_val, value + begin, (unsigned)cnt);
   }
   __syncthreads();
   return staged;
@@ -389,10 +402,15 @@ spmv_fused_hot_kernel(int loss, size_t rows, unsigned rows_per_block, unsigned s
   __shared__ double s_o[32];
   __shared__ unsigned s_c[32];
   // the table keys' pulled weights: slot -> rank of the key in this minibatch -> w
-  for (int i = threadIdx.x; i < kHotSlots; i += blockDim.x) {
-    s_acc[i] = 0;
-    const unsigned rk = __ldg(hot.rank + i);
-    s_w[i] = rk == kHotNone ? 0.f : __ldg(w + rk);
+  for (int i0 = threadIdx.x; i0 < kHotSlots; i0 += blockDim.x * 4) {   // 4 rank -> weight chains in flight
+    unsigned rk[4];
+    float wv[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) { const int i = i0 + u * blockDim.x; rk[u] = i < kHotSlots ? __ldg(hot.rank + i) : kHotNone; }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) wv[u] = rk[u] == kHotNone ? 0.f : __ldg(w + rk[u]);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) { const int i = i0 + u * blockDim.x; if (i < kHotSlots) { s_acc[i] = 0; s_w[i] = wv[u]; } }
   }
   const size_t r0 = (size_t)blockIdx.x * rows_per_block;
   for (unsigned t = threadIdx.x; t <= rows_per_block; t += blockDim.x) s_off[t] = offset[min(r0 + t, rows)];
@@ -400,7 +418,7 @@ spmv_fused_hot_kernel(int loss, size_t rows, unsigned rows_per_block, unsigned s
   const size_t begin = s_off[0];
   const size_t cnt = s_off[rows_per_block] - begin;
   const bool staged = cnt <= (size_t)stage_cap;
-  if (staged) for (unsigned i = threadIdx.x; i < (unsigned)cnt; i += blockDim.x) s_idx[i] = ld_stream_u32(codes + begin + i);
+  if (staged) stage_run(s_idx, codes + begin, (unsigned)cnt);
   __syncthreads();
   const uint32_t* idx = staged ? s_idx : codes + begin;   // generic pointer: shared or global
   const size_t r = r0 + threadIdx.x;
@@ -429,9 +447,16 @@ spmv_fused_hot_kernel(int loss, size_t rows, unsigned rows_per_block, unsigned s
   long long* gacc = acc + (size_t)(blockIdx.x & (copies - 1)) * stride;
   const unsigned maxlen = __reduce_max_sync(0xffffffffu, len);
   const unsigned lane = threadIdx.x & 31;
+  // Skewed walk: at step j lane l is on entry (j + 2l) mod len of its row. With one thread per row and
+  // field-aligned rows, the unskewed walk has all 32 lanes on the SAME field at every step, whose popular value
+  // then repeats across the lanes -- up to 16 lanes on one accumulator, serialised inside the atomic. Skewed, the
+  // lanes of a step sit on 32 different fields (2 is coprime to the usual odd row length; 39 + 2 is odd, so the
+  // shared-memory reads of the codes stay conflict-free). Integer sums do not care about the order.
+  unsigned pos = len ? (2u * lane) % len : 0u;
   for (unsigned j = 0; j < maxlen; ++j) {
     const bool valid = j < len;
-    const uint32_t c = valid ? idx[lb + j] : 0u;
+    const uint32_t c = valid ? idx[lb + pos] : 0u;
+    if (++pos >= len) pos = 0u;
     const bool is_hot = valid && (c & kHotFlag);
     if (valid && !is_hot) atomicAdd(reinterpret_cast<unsigned long long*>(gacc + c), (unsigned long long)q);
     // table keys: straight into shared memory. Lanes of a warp on the same slot are serialised by the hardware
