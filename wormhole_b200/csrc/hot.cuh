@@ -9,7 +9,7 @@
 //     the host from a census of the worker's first minibatch and copied into shared memory by the kernels;
 //   * an entry whose key is in the table gets the CODE  kHotFlag | slot  instead of its rank as local index; the
 //     forward product reads its weight from a 32 KB slot-indexed array, the backward product adds it up in a
-//     shared-memory accumulator and flushes the block's sums once;
+//     shared-memory accumulator and flushes the block's sums once (spmv.cu, spmv_fused_hot_kernel);
 //   * everything else (presence bits, ranks, the ascending key list, pull, push) is as before, so the results do
 //     not depend on which keys are in the table -- it is a cache, not a model. Integer accumulation keeps the
 //     gradients bit-identical with and without it.
@@ -26,8 +26,7 @@ struct HotView {
   const uint4* tags;     // shared by the lanes: bucket b = tags[b] = 4 transformed keys (kHotEmpty = free way)
   unsigned* present;     // 1 if the slot's key occurs in the current minibatch (reset by hot_rank)
   unsigned* rank;        // rank of the slot's key in the current minibatch, kHotNone if absent
-  float* w;              // pulled weight of the slot's key
-  unsigned* done;        // block counter of the mark kernel (its last block folds `present` into the directory)
+  float* w;              // pulled weight of the slot's key (evaluation passes; the fused training kernel gathers its own)
 };
 
 #ifdef __CUDACC__

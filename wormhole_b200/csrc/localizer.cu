@@ -280,7 +280,8 @@ int localize_direct(whContext* ctx, const LocInput& in, uint64_t* d_uniq, uint32
 // directory (one shared-memory probe instead of an L2 access in mark and in rank) and come out as codes.
 
 constexpr int kHotMarkThreads = kTmaThreads;
-constexpr unsigned kColdCode = 0x7fffffffu;   // "not a table key": the rank pass replaces it
+// Entries that are not table keys leave the mark pass holding their transformed key (< 2^28, flag bit clear); the
+// rank pass turns it into the rank in place, so that it never has to read the 64-bit ids again.
 __global__ void __launch_bounds__(kTmaThreads) loc_mark_hot_kernel(const uint64_t* __restrict__ index, size_t n,
                                                                    KeyXform xf, uint2* dir, HotView hot,
                                                                    uint32_t* __restrict__ codes) {
@@ -304,7 +305,7 @@ __global__ void __launch_bounds__(kTmaThreads) loc_mark_hot_kernel(const uint64_
       k[u] = xf(probe[u] ? ids[j] : 0);
       if (probe[u]) {
         const int slot = hot_probe(s_tags, (unsigned)k[u]);
-        codes[base + j] = slot >= 0 ? (kHotFlag | (unsigned)slot) : kColdCode;   // the entry's code is known here
+        codes[base + j] = slot >= 0 ? (kHotFlag | (unsigned)slot) : (unsigned)k[u];   // code, or the key for the rank pass
         if (slot >= 0) { s_present[slot] = 1; probe[u] = false; }   // same-value byte stores: no atomics needed
       }
     }
@@ -347,7 +348,7 @@ __global__ void __launch_bounds__(kHotMarkPlainThreads) loc_mark_hot_plain_kerne
       k[u] = xf(k[u]);
       if (probe[u]) {
         const int slot = hot_probe(s_tags, (unsigned)k[u]);
-        codes[i0 + u * stride] = slot >= 0 ? (kHotFlag | (unsigned)slot) : kColdCode;
+        codes[i0 + u * stride] = slot >= 0 ? (kHotFlag | (unsigned)slot) : (unsigned)k[u];   // code, or the key for the rank pass
         if (slot >= 0) { s_present[slot] = 1; probe[u] = false; }
       }
     }
@@ -383,9 +384,8 @@ __device__ __forceinline__ void hot_rank_slot(const HotView& hot, const uint2* _
   hot.rank[p] = r;
 }
 
-// rank pass: only entries that are not table keys still need their key and the directory
-__global__ void __launch_bounds__(256) loc_rank_cold_kernel(const uint64_t* __restrict__ index, size_t n, KeyXform xf,
-                                                            const uint2* __restrict__ dir, uint32_t* __restrict__ codes,
+// rank pass: entries that are not table keys hold their key; the directory turns it into the rank
+__global__ void __launch_bounds__(256) loc_rank_cold_kernel(size_t n, const uint2* __restrict__ dir, uint32_t* __restrict__ codes,
                                                             HotView hot) {
   // (the blocks also rank the table keys, a slice each: nothing in this launch reads hot.rank)
   {
@@ -393,20 +393,18 @@ __global__ void __launch_bounds__(256) loc_rank_cold_kernel(const uint64_t* __re
     const int lo = (int)blockIdx.x * per, hi = min(kHotSlots, lo + per);
     for (int p = lo + (int)threadIdx.x; p < hi; p += (int)blockDim.x) hot_rank_slot(hot, dir, p);
   }
+  constexpr int kIlp = 8;
   const size_t stride = (size_t)gridDim.x * blockDim.x;
-  for (size_t i0 = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i0 < n; i0 += stride * kLocIlp) {
-    uint32_t c[kLocIlp];
-    uint64_t k[kLocIlp];
-    uint2 e[kLocIlp];
+  for (size_t i0 = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i0 < n; i0 += stride * kIlp) {
+    uint32_t c[kIlp];
+    uint2 e[kIlp];
 #pragma unroll
-    for (int u = 0; u < kLocIlp; ++u) { const size_t i = i0 + u * stride; c[u] = i < n ? ld_stream_u32(codes + i) : 0u; }
+    for (int u = 0; u < kIlp; ++u) { const size_t i = i0 + u * stride; c[u] = i < n ? ld_stream_u32(codes + i) : kHotFlag; }
 #pragma unroll
-    for (int u = 0; u < kLocIlp; ++u) if (c[u] == kColdCode) k[u] = ld_stream_u64(index + i0 + u * stride);
+    for (int u = 0; u < kIlp; ++u) if (!(c[u] & kHotFlag)) e[u] = __ldg(dir + (c[u] >> 5));
 #pragma unroll
-    for (int u = 0; u < kLocIlp; ++u) if (c[u] == kColdCode) { k[u] = xf(k[u]); e[u] = __ldg(dir + (k[u] >> 5)); }
-#pragma unroll
-    for (int u = 0; u < kLocIlp; ++u)
-      if (c[u] == kColdCode) codes[i0 + u * stride] = e[u].y + __popc(e[u].x & ((1u << (k[u] & 31)) - 1u));
+    for (int u = 0; u < kIlp; ++u)
+      if (!(c[u] & kHotFlag)) codes[i0 + u * stride] = e[u].y + __popc(e[u].x & ((1u << (c[u] & 31)) - 1u));
   }
 }
 
@@ -441,8 +439,8 @@ int localize_direct_hot(whContext* ctx, const LocInput& in, const HotView& hot, 
   WH_PROF(ctx, "loc_mark");
   WH_TRY(scan_and_apply<unsigned>(ctx, DirPopc{dir}, DirEmit{dir, d_uniq}, words, ctx->scan_tmp.as<unsigned>(), d_nuniq));
   WH_PROF(ctx, "loc_dir_scan");
-  const unsigned rgrid = (unsigned)std::min<size_t>(div_up(n, 256 * kLocIlp), (size_t)ctx->num_sms * 8);
-  WH_LAUNCH(loc_rank_cold_kernel, rgrid, 256, 0, ctx->stream, in.index, n, in.xf, dir, d_codes, hot);
+  const unsigned rgrid = (unsigned)std::min<size_t>(div_up(n, 256 * 8), (size_t)ctx->num_sms * 8);
+  WH_LAUNCH(loc_rank_cold_kernel, rgrid, 256, 0, ctx->stream, n, dir, d_codes, hot);
   WH_PROF(ctx, "loc_rank");
   WH_CUDA(cudaMemsetAsync(dir, 0, words * sizeof(uint2), ctx->stream));
   WH_PROF(ctx, "loc_dir_clear");

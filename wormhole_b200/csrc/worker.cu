@@ -40,7 +40,7 @@ struct Lane {
   DevBuf uniq, index, w, xw, dual, scal;
   char* pinned = nullptr;    // 512 B of the worker's pinned block
   DevBuf outbox;             // sharded jobs: {U, cuts | keys | grads}, mapped by every peer
-  DevBuf hot;                // hot-key state of the lane (hot.cuh): present | rank | w (kHotSlots each) | block counter
+  DevBuf hot;                // hot-key state of the lane (hot.cuh): present | rank | w, kHotSlots each
   bool busy = false, train = false;
   size_t rows = 0;
   // state between wh_worker_begin and wh_worker_finish
@@ -120,7 +120,6 @@ static HotView lane_hot_view(const whWorker* w, Lane& l) {
   v.present = l.hot.as<unsigned>();
   v.rank = v.present + kHotSlots;
   v.w = reinterpret_cast<float*>(v.rank + kHotSlots);
-  v.done = reinterpret_cast<unsigned*>(v.w + kHotSlots);
   return v;
 }
 
