@@ -190,13 +190,23 @@ def run_ours(args):
         sys.stderr.write("bench.py: --gpus %d but WORLD_SIZE=%d; using WORLD_SIZE\n" % (args.gpus, world))
 
     rows, pool_n = args.rows, args.pool
+    # parity-test configurations of BASELINE.json (configs[2..3]) can be timed with --algo / --loss / --shape; the
+    # bench line proper is the default (configs[1])
+    algo = {"ftrl": capi.ALGO_FTRL, "adagrad": capi.ALGO_ADAGRAD, "sgd": capi.ALGO_SGD}[args.algo]
+    loss = {"logit": capi.LOSS_LOGIT, "sqhinge": capi.LOSS_SQUARE_HINGE}[args.loss]
+    global MAX_KEY, WORKLOAD, NNZ_PER_ROW
+    if args.shape == "kdd":
+        MAX_KEY, NNZ_PER_ROW = synth.KDD_VOCAB, 11
+        rows = args.rows if args.rows != ROWS else 1000000
+    if (args.algo, args.loss, args.shape) != ("ftrl", "logit", "criteo"):
+        WORKLOAD = "synthetic %s-shape sparse LR, %s, %s loss, max_key %d, minibatch %d" % (args.shape, args.algo, args.loss, MAX_KEY, rows)
     ctx = capi.Context(local)
     stream = torch.cuda.current_stream()
     ctx.set_stream(stream.cuda_stream)
     if world == 1:
         # worker and the one server share the GPU: the lane pipeline (minibatches in flight)
-        srv = capi.Server(ctx, capi.ALGO_FTRL, FTRL["l1"], FTRL["l2"], FTRL["eta"], FTRL["beta"], 0, MAX_KEY)
-        wk = capi.Worker(ctx, srv, capi.LOSS_LOGIT, MAX_KEY, depth=args.depth)
+        srv = capi.Server(ctx, algo, FTRL["l1"], FTRL["l2"], FTRL["eta"], FTRL["beta"], 0, MAX_KEY)
+        wk = capi.Worker(ctx, srv, loss, MAX_KEY, depth=args.depth)
         sw = None
     else:
         # rank g = worker g + server g of the key range [g*max_key/S, (g+1)*max_key/S). Default: every rank maps
@@ -205,7 +215,7 @@ def run_ours(args):
         # messages through torch.distributed instead (wormhole_b200/dist.py). Weak scaling.
         from wormhole_b200.dist import DeviceShard, ShardedKV, ShardedWorker, key_range
         kb, ke = key_range(rank, world, MAX_KEY)
-        srv = capi.Server(ctx, capi.ALGO_FTRL, FTRL["l1"], FTRL["l2"], FTRL["eta"], FTRL["beta"], kb, ke)
+        srv = capi.Server(ctx, algo, FTRL["l1"], FTRL["l2"], FTRL["eta"], FTRL["beta"], kb, ke)
         if args.exchange == "p2p":
             handles = [None] * world
             dist.all_gather_object(handles, srv.ipc_export())
@@ -213,29 +223,30 @@ def run_ours(args):
             dist.barrier()
             # lanes still apply: every server interaction of a rank is chained through one CUDA event, so the
             # barriers keep one global order; localize / staging / AUC of the next minibatch overlap
-            wk = capi.Worker(ctx, srv, capi.LOSS_LOGIT, MAX_KEY, depth=args.depth)
+            wk = capi.Worker(ctx, srv, loss, MAX_KEY, depth=args.depth)
             boxes = [None] * world
-            dist.all_gather_object(boxes, wk.ipc_export(min(rows * NNZ_PER_ROW, MAX_KEY)))
+            dist.all_gather_object(boxes, wk.ipc_export(min(rows * NNZ_PER_ROW * (2 if args.shape == "kdd" else 1), MAX_KEY)))
             wk.ipc_attach(boxes)
             dist.barrier()
             sw = None
         else:
-            wk = capi.Worker(ctx, None, capi.LOSS_LOGIT, MAX_KEY)
+            wk = capi.Worker(ctx, None, loss, MAX_KEY)
             sw = ShardedWorker(ctx, wk, ShardedKV(DeviceShard(srv), MAX_KEY, device=torch.device("cuda", local)))
 
     # the minibatch pool: distinct minibatches, resident in HBM (device leg) and in pinned host
     # memory (e2e leg). pool_n x ~32 MB exceeds the 126 MB L2, so every step streams from HBM.
     host, dev = [], []
     for m in range(pool_n):
-        b = synth.criteo_minibatch(rank * 100000 + m, rows=rows)
+        b = synth.criteo_minibatch(rank * 100000 + m, rows=rows) if args.shape == "criteo" else synth.kdd_minibatch(rank * 100000 + m, rows=rows)
         h = type("B", (), {})()
         h.rows = b.rows
+        h.nnz = b.nnz
         h.offset = torch.from_numpy(b.offset.view(np.int64)).pin_memory()
         h.index = torch.from_numpy(b.index.view(np.int64)).pin_memory()
         h.label = torch.from_numpy(b.label).pin_memory()
         h.value = None
         d = type("B", (), {})()
-        d.rows = b.rows
+        d.rows, d.nnz = b.rows, b.nnz
         d.offset, d.index, d.label, d.value = h.offset.cuda(), h.index.cuda(), h.label.cuda(), None
         host.append(h); dev.append(d)
     N = int(host[0].offset[-1])
@@ -251,7 +262,7 @@ def run_ours(args):
     def run(blocks, mem, first, count):
         if sw is not None:
             for i in range(count):
-                sw.process_minibatch(blocks[(first + i) % pool_n], True, mem, N)
+                sw.process_minibatch(blocks[(first + i) % pool_n], True, mem, blocks[(first + i) % pool_n].nnz)
             return
         # up to `depth` minibatches in flight (conf max_concurrency); every one is waited for,
         # so its progress numbers have reached the host before the clock stops
@@ -260,7 +271,7 @@ def run_ours(args):
             if len(pending) == args.depth:
                 wk.wait(pending.pop(0))
             b = blocks[(first + i) % pool_n]
-            pending.append(wk.submit(b, True, mem, N))
+            pending.append(wk.submit(b, True, mem, b.nnz))
         for t in pending:
             wk.wait(t)
 
@@ -297,7 +308,7 @@ def run_ours(args):
     lib.wh_profile_enable(ctx.h, 1)
     for i in range(min(args.steps, 50)):
         if sw is not None:
-            sw.process_minibatch(dev[i % pool_n], True, capi.WH_DEVICE, N)
+            sw.process_minibatch(dev[i % pool_n], True, capi.WH_DEVICE, dev[i % pool_n].nnz)
         else:
             wk.process_minibatch(dev[i % pool_n], True, capi.WH_DEVICE)
     segs = []
@@ -358,6 +369,9 @@ def run_ours(args):
         try:
             if world > 1:
                 raise StopIteration
+            if (args.algo, args.loss, args.shape) != ("ftrl", "logit", "criteo"):
+                line["cpu_baseline"] = None     # the CPU arm times the bench configuration only
+                raise StopIteration
             out = subprocess.run([sys.executable, os.path.abspath(__file__), "--impl", "reference", "--steps", "4",
                                   "--warmup", "1", "--cpu-procs", "1", "--rows", str(rows)],
                                  capture_output=True, text=True, timeout=600,
@@ -388,6 +402,9 @@ def main():
     ap.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"], help="N>1: how pull/push reach the owning GPU")
     ap.add_argument("--max-delay", type=int, default=0, help="bounded staleness of pulls (0 = sequential semantics)")
     ap.add_argument("--depth", type=int, default=3, help="minibatches in flight (conf max_concurrency)")
+    ap.add_argument("--algo", default="ftrl", choices=["ftrl", "adagrad", "sgd"], help="updater (the bench line is ftrl)")
+    ap.add_argument("--loss", default="logit", choices=["logit", "sqhinge"])
+    ap.add_argument("--shape", default="criteo", choices=["criteo", "kdd"], help="kdd: ~11 nnz/row, 54.7 M ids, 1 M-row minibatches")
     ap.add_argument("--cpu-procs", type=int, default=0, help="reference arm: worker+server pairs (0 = cores/2)")
     args = ap.parse_args()
     if args.impl == "reference":

@@ -386,3 +386,37 @@ def test_unhashed_64bit_keys_end_to_end(gpu, checker):
         small = capi.Server(gpu, capi.ALGO_SGD, 0, 0, 0.1, 1.0, 0, capi.NO_MAX_KEY, hash_slots=16)
         small.push(pool[:100], np.ones(100, np.float32))
     wk.close(); srv.close(); checker.linear_destroy(job)
+
+
+def test_hot_key_table_changes_nothing(gpu, monkeypatch):
+    """The worker's hot-key table (csrc/hot.cuh) is a cache: with it (codes, fused forward/backward, shared-memory
+    accumulators) and without it (WH_HOT=0: ranks, separate kernels) the progress numbers and the model are
+    bit-identical -- the fixed-point gradient sums do not depend on where they were added up. Skewed ids, odd entry
+    counts, train and evaluation minibatches, every updater."""
+    rng = np.random.default_rng(55)
+    blks = []
+    for m in range(6):
+        rows = 3001 + m
+        nnz = rng.integers(1, 25, rows)
+        off = np.zeros(rows + 1, np.uint64); off[1:] = np.cumsum(nnz)
+        ids = (rng.zipf(1.3, int(off[-1])) % 50000).astype(np.uint64) * np.uint64(2654435761)   # power law, hashed
+        blks.append(RowBlock(off, ids, None, (rng.random(rows) < 0.3).astype(np.float32)))
+    for algo, loss in [(capi.ALGO_FTRL, capi.LOSS_LOGIT), (capi.ALGO_ADAGRAD, capi.LOSS_SQUARE_HINGE), (capi.ALGO_SGD, capi.LOSS_LOGIT)]:
+        res = []
+        for hot in ("1", "0"):
+            monkeypatch.setenv("WH_HOT", hot)
+            srv = capi.Server(gpu, algo, 0.5, 0.1, 0.1, 1.0, 0, 2 ** 22)
+            wk = capi.Worker(gpu, srv, loss, 2 ** 22, depth=2)
+            pend, out = [], []
+            for m, b in enumerate(blks):
+                if len(pend) == 2:
+                    out.append(wk.wait(pend.pop(0)))
+                pend.append(wk.submit(b, train=(m != 3)))
+            out += [wk.wait(t) for t in pend]
+            keys = np.unique(np.concatenate([b.index % np.uint64(2 ** 22) for b in blks]))
+            res.append((np.array(out), srv.get_state(keys), srv.nnz_w()))
+            wk.close(); srv.close()
+        assert np.array_equal(res[0][0], res[1][0])
+        for a, b in zip(res[0][1], res[1][1]):
+            assert np.array_equal(a, b)
+        assert res[0][2] == res[1][2]

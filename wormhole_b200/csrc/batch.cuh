@@ -37,7 +37,7 @@ int localize_sort(whContext* ctx, const LocInput& in, uint64_t* d_uniq, uint32_t
 bool direct_supported(uint64_t max_key);
 struct HotView;
 // Direct localizer with the worker's hot-key table (hot.cuh): d_codes[i] = kHotFlag | slot for table keys, the rank
-// otherwise; also fills hot.rank for this minibatch. Needs a 16-byte aligned id array with an even entry count.
+// otherwise; also fills hot.rank for this minibatch.
 int localize_direct_hot(whContext* ctx, const LocInput& in, const HotView& hot, uint64_t* d_uniq, uint32_t* d_codes,
                         unsigned* d_nuniq);
 

@@ -420,7 +420,6 @@ int localize_direct_hot(whContext* ctx, const LocInput& in, const HotView& hot, 
   WH_TRY(ctx->scan_tmp.reserve(div_up(words, kScanTile) * sizeof(unsigned) + 256));
   const size_t n = in.nnz;
   const bool tma = n >= 2 && ((uintptr_t)in.index & 15) == 0 && (n & 1) == 0;
-  WH_REQUIRE(tma, "localize_direct_hot: the id array must be 16-byte aligned with an even entry count");
   const size_t mark_smem = (size_t)kTmaStages * kTileIds * 8 + kTmaStages * 8 + kHotSlots * 4 + kHotSlots;
   WH_CUDA(cudaFuncSetAttribute(loc_mark_hot_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)mark_smem));
   const unsigned tgrid = (unsigned)std::min<size_t>(div_up(n, kTileIds), (size_t)ctx->num_sms * 3);
@@ -429,8 +428,8 @@ int localize_direct_hot(whContext* ctx, const LocInput& in, const HotView& hot, 
   // the ring's extra shared memory only costs resident warps. WH_HOT_MARK_PLAIN=0 selects the ring.
   static int plain = -1;
   if (plain < 0) { const char* e = getenv("WH_HOT_MARK_PLAIN"); plain = e ? atoi(e) : 2; }
-  if (plain) {
-    const unsigned pg = (unsigned)std::min<size_t>(div_up(n, kHotMarkPlainThreads * kLocIlp), (size_t)ctx->num_sms * plain);
+  if (plain || !tma) {   // (the ring needs 16-byte aligned ids and an even count)
+    const unsigned pg = (unsigned)std::min<size_t>(div_up(n, kHotMarkPlainThreads * kLocIlp), (size_t)ctx->num_sms * (plain ? plain : 2));
     WH_LAUNCH(loc_mark_hot_plain_kernel, pg, kHotMarkPlainThreads, 0, ctx->stream, in.index, n, in.xf, dir, hot, d_codes);
   } else {
     WH_LAUNCH(loc_mark_hot_kernel, tgrid, kTmaThreads, mark_smem, ctx->stream, in.index, n, in.xf, dir, hot, d_codes);

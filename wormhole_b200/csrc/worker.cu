@@ -252,8 +252,8 @@ int wh_worker_submit(whWorker* w, const whRowBlock* blk, int mem, size_t nnz, in
   if (train) WH_TRY(ensure_acc(cx, ucap, &acc));
 
   LocInput in{d_index, n, make_xform(w->max_key)};
-  // hot keys (hot.cuh): binary features in a direct-addressed key space, ids the TMA ring can stream
-  const bool hot_ok = w->hot_enabled && direct && d_value == nullptr && n >= 2 && (n & 1) == 0 && ((uintptr_t)d_index & 15) == 0;
+  // hot keys (hot.cuh): binary features in a direct-addressed key space
+  const bool hot_ok = w->hot_enabled && direct && d_value == nullptr;
   if (hot_ok && !w->hot_tried) WH_TRY(hot_census(w, l, in, ucap));
   const bool hot = hot_ok && w->hot_ready;
   const HotView hv = lane_hot_view(w, l);
