@@ -401,7 +401,7 @@ def main():
     ap.add_argument("--pool", type=int, default=8, help="distinct minibatches kept resident")
     ap.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"], help="N>1: how pull/push reach the owning GPU")
     ap.add_argument("--max-delay", type=int, default=0, help="bounded staleness of pulls (0 = sequential semantics)")
-    ap.add_argument("--depth", type=int, default=3, help="minibatches in flight (conf max_concurrency)")
+    ap.add_argument("--depth", type=int, default=4, help="minibatches in flight (conf max_concurrency)")
     ap.add_argument("--algo", default="ftrl", choices=["ftrl", "adagrad", "sgd"], help="updater (the bench line is ftrl)")
     ap.add_argument("--loss", default="logit", choices=["logit", "sqhinge"])
     ap.add_argument("--shape", default="criteo", choices=["criteo", "kdd"], help="kdd: ~11 nnz/row, 54.7 M ids, 1 M-row minibatches")

@@ -95,6 +95,8 @@ struct whContext {
   wh::DevBuf directory;      // direct-address localizer: {bits, prefix} per 32 keys
   size_t directory_words = 0;  // words currently known to be all-zero
   wh::DevBuf scan_tmp;       // block sums of the directory scan
+  wh::DevBuf scan_state;     // tile states of the one-launch scan (scan.cuh); zeroed when (re)allocated
+  unsigned scan_epoch = 0;   // call counter of scan_state
   wh::DevBuf sort_tmp[6];    // radix sort ping-pong + histograms
   wh::DevBuf acc;            // int64 fixed-point accumulators of the transposed products
   wh::DevBuf small;          // device scalars (counts, plans, metric partials)

@@ -93,6 +93,17 @@ struct DirEmit {
   }
 };
 
+// The directory scan in one launch (scan.cuh: decoupled look-back). The state buffer belongs to the context.
+static int dir_scan(whContext* ctx, uint2* dir, uint64_t* d_uniq, size_t words, unsigned* d_nuniq) {
+  const size_t need = scan_onepass_bytes(words);
+  if (ctx->scan_state.cap < need) {
+    WH_TRY(ctx->scan_state.reserve(need));
+    WH_CUDA(cudaMemsetAsync(ctx->scan_state.p, 0, ctx->scan_state.cap, ctx->stream));
+    ctx->scan_epoch = 0;
+  }
+  return scan_onepass(ctx, DirPopc{dir}, DirEmit{dir, d_uniq}, words, ctx->scan_state.p, &ctx->scan_epoch, d_nuniq);
+}
+
 // learn/base/localizer.h:179-194,210: local id = rank of the transformed key.
 __global__ void __launch_bounds__(256) loc_rank_kernel(const uint64_t* __restrict__ index, size_t n,
                                                        KeyXform xf, const uint2* __restrict__ dir,
@@ -259,8 +270,7 @@ int localize_direct(whContext* ctx, const LocInput& in, uint64_t* d_uniq, uint32
     }
   }
   WH_PROF(ctx, "loc_mark");
-  WH_TRY(scan_and_apply<unsigned>(ctx, DirPopc{dir}, DirEmit{dir, d_uniq}, words, ctx->scan_tmp.as<unsigned>(),
-                        d_nuniq));
+  WH_TRY(dir_scan(ctx, dir, d_uniq, words, d_nuniq));
   WH_PROF(ctx, "loc_dir_scan");
   if (d_cnt && n) WH_CUDA(cudaMemsetAsync(d_cnt, 0, std::min<uint64_t>(n, in.xf.max_key) * 4, ctx->stream));
   // (rank stays on the plain kernel: its ids come back from L2, and more resident threads keep more
@@ -409,7 +419,7 @@ __global__ void __launch_bounds__(256) loc_rank_cold_kernel(size_t n, const uint
 }
 
 int localize_direct_hot(whContext* ctx, const LocInput& in, const HotView& hot, uint64_t* d_uniq, uint32_t* d_codes,
-                        unsigned* d_nuniq) {
+                        unsigned* d_nuniq, bool clear_dir) {
   const size_t words = div_up(in.xf.max_key, 32);
   if (ctx->directory.cap < words * sizeof(uint2) || ctx->directory_words < words) {
     WH_TRY(ctx->directory.reserve(words * sizeof(uint2)));
@@ -436,13 +446,15 @@ int localize_direct_hot(whContext* ctx, const LocInput& in, const HotView& hot, 
   }
   WH_LAUNCH(hot_present_kernel, kHotSlots / 256, 256, 0, ctx->stream, hot, dir);
   WH_PROF(ctx, "loc_mark");
-  WH_TRY(scan_and_apply<unsigned>(ctx, DirPopc{dir}, DirEmit{dir, d_uniq}, words, ctx->scan_tmp.as<unsigned>(), d_nuniq));
+  WH_TRY(dir_scan(ctx, dir, d_uniq, words, d_nuniq));
   WH_PROF(ctx, "loc_dir_scan");
   const unsigned rgrid = (unsigned)std::min<size_t>(div_up(n, 256 * 8), (size_t)ctx->num_sms * 8);
   WH_LAUNCH(loc_rank_cold_kernel, rgrid, 256, 0, ctx->stream, n, dir, d_codes, hot);
   WH_PROF(ctx, "loc_rank");
-  WH_CUDA(cudaMemsetAsync(dir, 0, words * sizeof(uint2), ctx->stream));
-  WH_PROF(ctx, "loc_dir_clear");
+  if (clear_dir) {   // (otherwise the caller's next kernel clears it as a side job: spmv_fused_hot_launch)
+    WH_CUDA(cudaMemsetAsync(dir, 0, words * sizeof(uint2), ctx->stream));
+    WH_PROF(ctx, "loc_dir_clear");
+  }
   return WH_OK;
 }
 

@@ -91,4 +91,94 @@ int scan_and_apply(whContext* ctx, F f, G g, size_t n, T* sums, T* total) {
   return WH_OK;
 }
 
+// ---- the same scan in ONE launch (decoupled look-back) ------------------------------------------------------
+// Three launches of a few microseconds each are mostly launch latency when the input is a 4 MB directory. Here a
+// block takes a tile by ticket (so that every tile's predecessors are already running), publishes its tile sum,
+// looks back over its predecessors' published {aggregate | inclusive prefix} words until it meets a prefix, and
+// applies. State words carry an epoch, so nothing has to be cleared between calls:
+//   word = epoch << 42 | status << 40 | value (40 bits),  status 1 = tile aggregate, 2 = inclusive prefix.
+// 32-bit scanned values; totals must stay below 2^40.
+struct ScanState {
+  unsigned long long* word;   // one per tile
+  unsigned* ticket;           // self-resetting tile counter (atomicInc wraps at the tile count)
+  unsigned epoch;             // 1 .. 2^22-1, advanced per call by the host
+};
+__device__ __forceinline__ unsigned long long scan_ld(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+template <typename F, typename G>
+__global__ void __launch_bounds__(kScanThreads) scan_onepass_kernel(F f, G g, size_t n, ScanState st, unsigned ntiles,
+                                                                    unsigned* total) {
+  __shared__ unsigned s_tile;
+  __shared__ unsigned long long s_prefix;
+  if (threadIdx.x == 0) s_tile = atomicInc(st.ticket, ntiles - 1);
+  __syncthreads();
+  const unsigned tile = s_tile;
+  const size_t base = (size_t)tile * kScanTile + (size_t)threadIdx.x * kScanItems;
+  unsigned v[kScanItems], s = 0;
+#pragma unroll
+  for (int k = 0; k < kScanItems; ++k) { v[k] = (base + k < n) ? f(base + k) : 0u; s += v[k]; }
+  unsigned tot;
+  const unsigned excl = block_exclusive_scan<unsigned>(s, &tot);
+  const unsigned long long tag = (unsigned long long)st.epoch << 42;
+  if (threadIdx.x == 0) {
+    const unsigned long long w = tag | ((tile == 0 ? 2ull : 1ull) << 40) | tot;
+    atomicExch(st.word + tile, w);
+    if (tile == 0) s_prefix = 0;
+  }
+  if (tile != 0 && threadIdx.x < 32) {
+    unsigned long long sum = 0;
+    int j = (int)tile - 1 - (int)threadIdx.x;      // this lane's predecessor in the current window
+    while (true) {
+      unsigned long long w = 0;
+      bool have = j < 0;                            // before tile 0: contributes nothing, counts as a prefix
+      if (!have) {
+        do { w = scan_ld(st.word + j); } while ((w >> 42) != st.epoch);
+      }
+      const bool is_prefix = have || ((w >> 40) & 3ull) == 2ull;
+      const unsigned pm = __ballot_sync(0xffffffffu, is_prefix);
+      const int first = pm ? __ffs(pm) - 1 : 32;    // nearest predecessor that already knows its prefix
+      unsigned long long c = (!have && (int)threadIdx.x <= first) ? (w & ((1ull << 40) - 1)) : 0ull;
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+      sum += c;
+      if (pm) break;
+      j -= 32;
+    }
+    if (threadIdx.x == 0) {
+      s_prefix = sum;
+      __threadfence();
+      atomicExch(st.word + tile, tag | (2ull << 40) | (sum + tot));
+    }
+  }
+  __syncthreads();
+  unsigned run = (unsigned)s_prefix + excl;
+  if (threadIdx.x == 0 && tile == ntiles - 1 && total) *total = (unsigned)s_prefix + tot;
+#pragma unroll
+  for (int k = 0; k < kScanItems; ++k) {
+    if (base + k < n) g(base + k, v[k], run);
+    run += v[k];
+  }
+}
+
+// Host driver. `state` must hold scan_onepass_bytes(n) bytes that were zero when first used and are only ever
+// passed to this function; *epoch is the caller's call counter for that buffer.
+static inline size_t scan_onepass_bytes(size_t n) { return div_up(n ? n : 1, kScanTile) * 8 + 64; }
+template <typename F, typename G>
+int scan_onepass(whContext* ctx, F f, G g, size_t n, void* state, unsigned* epoch, unsigned* total) {
+  const unsigned nt = (unsigned)div_up(n ? n : 1, kScanTile);
+  if (++*epoch >= (1u << 22)) {   // epoch wrap: start over with a clean buffer
+    WH_CUDA(cudaMemsetAsync(state, 0, scan_onepass_bytes(n), ctx->stream));
+    *epoch = 1;
+  }
+  ScanState st;
+  st.ticket = reinterpret_cast<unsigned*>(state);
+  st.word = reinterpret_cast<unsigned long long*>(reinterpret_cast<char*>(state) + 64);
+  st.epoch = *epoch;
+  WH_LAUNCH((scan_onepass_kernel<F, G>), nt, kScanThreads, 0, ctx->stream, f, g, n, st, nt, total);
+  return WH_OK;
+}
+
 }  // namespace wh

@@ -393,7 +393,12 @@ spmv_fused_hot_kernel(int loss, size_t rows, unsigned rows_per_block, unsigned s
                       const size_t* __restrict__ offset, const uint32_t* __restrict__ codes,
                       const float* __restrict__ label, const float* __restrict__ w, HotView hot,
                       float* __restrict__ y, float* __restrict__ dual, double* part_objv, unsigned* part_correct,
-                      long long* acc, float scale, unsigned copies, size_t stride) {
+                      long long* acc, float scale, unsigned copies, size_t stride, uint4* dirty, size_t dirty16) {
+  // side job: the localizer's directory is no longer needed once the codes exist; every block zeroes a slice
+  {
+    const size_t per = (dirty16 + gridDim.x - 1) / gridDim.x, lo = (size_t)blockIdx.x * per, hi = min(dirty16, lo + per);
+    for (size_t i = lo + threadIdx.x; i < hi; i += blockDim.x) dirty[i] = make_uint4(0u, 0u, 0u, 0u);
+  }
   extern __shared__ __align__(16) unsigned char smem[];
   long long* s_acc = reinterpret_cast<long long*>(smem);                       // kHotSlots
   float* s_w = reinterpret_cast<float*>(s_acc + kHotSlots);                    // kHotSlots: the table keys' weights
@@ -493,13 +498,22 @@ int hot_w_launch(whContext* ctx, const HotView& hot, const float* w) {
 // be NULL), the evaluation partials in `out`, X^T dual in acc (fixed point, scale written to fs for the push).
 int spmv_fused_hot_launch(whContext* ctx, int loss, size_t rows, size_t nnz, const size_t* offset, const uint32_t* codes,
                           const float* label, const float* w, const HotView& hot, float* xw, float* dual, EvalOut* out,
-                          FixedScale* fs, long long* acc, unsigned copies, size_t stride) {
-  // one block per SM if the rows allow it; a thread per row
-  unsigned rpb = (unsigned)align_up(div_up(rows, (size_t)ctx->num_sms), 32);
+                          FixedScale* fs, long long* acc, unsigned copies, size_t stride, void* dirty, size_t dirty_bytes) {
+  // one block per SM if the rows allow it, a thread per row. A block needs a whole SM's shared memory, so a few SMs
+  // are left to the kernels of the neighbouring minibatches (the AUC cluster of the previous one holds 8 SMs for
+  // ~150 us): with a block for every SM the last blocks had to wait for a free SM and the launch took two waves.
+  static int spare = -1;
+  if (spare < 0) { const char* e = getenv("WH_FUSED_SPARE_SMS"); spare = e ? atoi(e) : 16; }
+  const size_t use_sms = (size_t)std::max(1, ctx->num_sms - spare);
+  unsigned rpb = (unsigned)align_up(div_up(rows, use_sms), 32);
   rpb = std::max(32u, std::min(rpb, 1024u));
+  const size_t budget = 220 * 1024;
+  // ... as long as the band's codes fit the staging buffer (average row length; a band that still overflows is
+  // walked in global memory): otherwise narrower bands and more blocks
+  const size_t avg_len = std::max<size_t>(1, div_up(nnz, rows));
+  while (rpb > 32 && (size_t)rpb * avg_len * 4 + (size_t)kHotSlots * 12 + ((size_t)rpb + 1) * 8 > budget) rpb -= 32;
   const unsigned grid = (unsigned)div_up(rows, rpb);
   const size_t fixed = (size_t)kHotSlots * 12 + ((size_t)rpb + 1) * 8;
-  const size_t budget = 220 * 1024;
   const unsigned cap = (unsigned)((budget - fixed) / 4);
   WH_CUDA(cudaFuncSetAttribute(spmv_fused_hot_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)budget));
   WH_TRY(ctx->stage[7].reserve((size_t)grid * 16 + 64));
@@ -508,7 +522,7 @@ int spmv_fused_hot_launch(whContext* ctx, int loss, size_t rows, size_t nnz, con
   float sc; double inv;
   unit_terms_scale(nnz, &sc, &inv);
   WH_LAUNCH(spmv_fused_hot_kernel, grid, rpb, budget, ctx->stream, loss, rows, rpb, cap, offset, codes, label, w, hot, xw,
-            dual, po, pc, acc, sc, copies, stride);
+            dual, po, pc, acc, sc, copies, stride, reinterpret_cast<uint4*>(dirty), dirty_bytes / 16);
   return loss_reduce_launch(ctx, grid, po, nullptr, pc, out, fs, nnz);
 }
 

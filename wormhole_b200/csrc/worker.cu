@@ -78,7 +78,7 @@ using namespace wh;
 
 static void lane_release(Lane& l) {
   for (DevBuf* b : {&l.in_index, &l.in_offset, &l.in_value, &l.in_label, &l.uniq, &l.index, &l.w, &l.xw, &l.dual,
-                    &l.scal, &l.outbox, &l.hot, &l.cx.directory, &l.cx.scan_tmp, &l.cx.acc, &l.cx.small, &l.ax.scan_tmp, &l.ax.small})
+                    &l.scal, &l.outbox, &l.hot, &l.cx.directory, &l.cx.scan_tmp, &l.cx.scan_state, &l.cx.acc, &l.cx.small, &l.ax.scan_tmp, &l.ax.small})
     b->release();
   for (auto& b : l.cx.sort_tmp) b.release();
   for (auto& b : l.ax.sort_tmp) b.release();
@@ -256,11 +256,12 @@ int wh_worker_submit(whWorker* w, const whRowBlock* blk, int mem, size_t nnz, in
   const bool hot_ok = w->hot_enabled && direct && d_value == nullptr;
   if (hot_ok && !w->hot_tried) WH_TRY(hot_census(w, l, in, ucap));
   const bool hot = hot_ok && w->hot_ready;
+  const bool fused = hot && train;    // forward + backward in one launch, which also zeroes the localizer's directory
   const HotView hv = lane_hot_view(w, l);
 
   WH_TRY(prof_begin(cx));
   // Localize
-  if (hot) WH_TRY(localize_direct_hot(cx, in, hv, uniq, l.index.as<uint32_t>(), d_nuniq));
+  if (hot) WH_TRY(localize_direct_hot(cx, in, hv, uniq, l.index.as<uint32_t>(), d_nuniq, !fused));
   else if (direct) WH_TRY(localize_direct(cx, in, uniq, nullptr, l.index.as<uint32_t>(), d_nuniq));
   else WH_TRY(localize_sort(cx, in, uniq, nullptr, l.index.as<uint32_t>(), d_nuniq));
   if (outboxed) WH_TRY(outbox_cuts_launch(s, cx->stream, l.outbox.as<unsigned char>()));
@@ -282,12 +283,12 @@ int wh_worker_submit(whWorker* w, const whRowBlock* blk, int mem, size_t nnz, in
   // Init (Xw), the per-example part of Evaluate, and the dual of CalcGrad: one pass over the rows. With
   // binary features |dual| <= 1 bounds every term of X^T dual, so the fixed-point scale is known up front.
   const bool scale_ready = d_value == nullptr;
-  const bool fused = hot && train;
   if (hot && !fused) WH_TRY(hot_w_launch(cx, hv, l.w.as<float>()));   // evaluation: the slot-indexed weights for spmv_loss
   if (fused) {
     // ... and with the hot-key table the transposed product rides in the same launch (spmv.cu)
     WH_TRY(spmv_fused_hot_launch(cx, w->loss, rows, n, d_offset, l.index.as<uint32_t>(), d_label, l.w.as<float>(), hv,
-                                 l.xw.as<float>(), nullptr, d_eval, fs, acc, acc_copies(), ucap));
+                                 l.xw.as<float>(), nullptr, d_eval, fs, acc, acc_copies(), ucap,
+                                 cx->directory.p, div_up(w->max_key, 32) * sizeof(uint2)));
     WH_PROF(cx, "spmv_fused");
   } else {
     WH_TRY(spmv_loss_launch(cx, w->loss, rows, n, d_offset, l.index.as<uint32_t>(), d_value, d_label, l.w.as<float>(),
