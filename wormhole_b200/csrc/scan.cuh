@@ -108,7 +108,7 @@ __device__ __forceinline__ unsigned long long scan_ld(const unsigned long long* 
   asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
   return v;
 }
-template <typename F, typename G>
+template <int ITEMS, typename F, typename G>
 __global__ void __launch_bounds__(kScanThreads) scan_onepass_kernel(F f, G g, size_t n, ScanState st, unsigned ntiles,
                                                                     unsigned* total) {
   __shared__ unsigned s_tile;
@@ -116,10 +116,10 @@ __global__ void __launch_bounds__(kScanThreads) scan_onepass_kernel(F f, G g, si
   if (threadIdx.x == 0) s_tile = atomicInc(st.ticket, ntiles - 1);
   __syncthreads();
   const unsigned tile = s_tile;
-  const size_t base = (size_t)tile * kScanTile + (size_t)threadIdx.x * kScanItems;
-  unsigned v[kScanItems], s = 0;
+  const size_t base = (size_t)tile * (kScanThreads * ITEMS) + (size_t)threadIdx.x * ITEMS;
+  unsigned v[ITEMS], s = 0;
 #pragma unroll
-  for (int k = 0; k < kScanItems; ++k) { v[k] = (base + k < n) ? f(base + k) : 0u; s += v[k]; }
+  for (int k = 0; k < ITEMS; ++k) { v[k] = (base + k < n) ? f(base + k) : 0u; s += v[k]; }
   unsigned tot;
   const unsigned excl = block_exclusive_scan<unsigned>(s, &tot);
   const unsigned long long tag = (unsigned long long)st.epoch << 42;
@@ -131,6 +131,8 @@ __global__ void __launch_bounds__(kScanThreads) scan_onepass_kernel(F f, G g, si
   if (tile != 0 && threadIdx.x < 32) {
     unsigned long long sum = 0;
     int j = (int)tile - 1 - (int)threadIdx.x;      // this lane's predecessor in the current window
+    // (fetching several windows per round trip was slower: words read early are still aggregates, read late
+    //  they are often prefixes that end the walk)
     while (true) {
       unsigned long long w = 0;
       bool have = j < 0;                            // before tile 0: contributes nothing, counts as a prefix
@@ -157,7 +159,7 @@ __global__ void __launch_bounds__(kScanThreads) scan_onepass_kernel(F f, G g, si
   unsigned run = (unsigned)s_prefix + excl;
   if (threadIdx.x == 0 && tile == ntiles - 1 && total) *total = (unsigned)s_prefix + tot;
 #pragma unroll
-  for (int k = 0; k < kScanItems; ++k) {
+  for (int k = 0; k < ITEMS; ++k) {
     if (base + k < n) g(base + k, v[k], run);
     run += v[k];
   }
@@ -165,10 +167,11 @@ __global__ void __launch_bounds__(kScanThreads) scan_onepass_kernel(F f, G g, si
 
 // Host driver. `state` must hold scan_onepass_bytes(n) bytes that were zero when first used and are only ever
 // passed to this function; *epoch is the caller's call counter for that buffer.
-static inline size_t scan_onepass_bytes(size_t n) { return div_up(n ? n : 1, kScanTile) * 8 + 64; }
+constexpr int kOnepassItems = 4;   // elements per thread: smaller tiles than the 3-launch scan, for more blocks in flight
+static inline size_t scan_onepass_bytes(size_t n) { return div_up(n ? n : 1, kScanThreads * kOnepassItems) * 8 + 64; }
 template <typename F, typename G>
 int scan_onepass(whContext* ctx, F f, G g, size_t n, void* state, unsigned* epoch, unsigned* total) {
-  const unsigned nt = (unsigned)div_up(n ? n : 1, kScanTile);
+  const unsigned nt = (unsigned)div_up(n ? n : 1, kScanThreads * kOnepassItems);
   if (++*epoch >= (1u << 22)) {   // epoch wrap: start over with a clean buffer
     WH_CUDA(cudaMemsetAsync(state, 0, scan_onepass_bytes(n), ctx->stream));
     *epoch = 1;
@@ -177,7 +180,7 @@ int scan_onepass(whContext* ctx, F f, G g, size_t n, void* state, unsigned* epoc
   st.ticket = reinterpret_cast<unsigned*>(state);
   st.word = reinterpret_cast<unsigned long long*>(reinterpret_cast<char*>(state) + 64);
   st.epoch = *epoch;
-  WH_LAUNCH((scan_onepass_kernel<F, G>), nt, kScanThreads, 0, ctx->stream, f, g, n, st, nt, total);
+  WH_LAUNCH((scan_onepass_kernel<kOnepassItems, F, G>), nt, kScanThreads, 0, ctx->stream, f, g, n, st, nt, total);
   return WH_OK;
 }
 

@@ -437,10 +437,12 @@ spmv_fused_hot_kernel(int loss, size_t rows, unsigned rows_per_block, unsigned s
   if (live) {
     float sum = 0.f;
     unsigned j = 0;
-    for (; j + 4 <= len; j += 4) {
-      const float g0 = gather_sw(w, s_w, idx[lb + j]), g1 = gather_sw(w, s_w, idx[lb + j + 1]);
-      const float g2 = gather_sw(w, s_w, idx[lb + j + 2]), g3 = gather_sw(w, s_w, idx[lb + j + 3]);
-      sum += g0; sum += g1; sum += g2; sum += g3;
+    for (; j + 8 <= len; j += 8) {   // eight gathers in flight, the adds stay in CSR order
+      float g[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) g[u] = gather_sw(w, s_w, idx[lb + j + u]);
+#pragma unroll
+      for (int u = 0; u < 8; ++u) sum += g[u];
     }
     for (; j < len; ++j) sum += gather_sw(w, s_w, idx[lb + j]);
     y[r] = sum;
