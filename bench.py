@@ -331,10 +331,12 @@ def run_ours(args):
         # DRAM bytes per launch of that kernel from the committed ncu --set full capture (profiles/), or null
         traffic = None
         try:
-            tr = json.load(open(os.path.join(ROOT, "profiles", "r1_c_traffic.json")))
-            kname = {"spmv_fused": "spmv_fused_hot_kernel", "spmv_trans": "spmv_trans_kernel<0>", "push": "server_push_kernel<1>", "spmv_loss": "spmv_loss_kernel<0>",
-                     "loc_mark": "loc_mark_tma_kernel", "loc_rank": "loc_rank_kernel", "pull": "server_pull_kernel"}.get(top[0])
-            traffic = tr.get(kname) if (rows == ROWS and world == 1) else None
+            tr = json.load(open(os.path.join(ROOT, "profiles", "r1_d_traffic.json")))
+            kname = {"spmv_fused": "spmv_fused_hot_kernel", "push": "server_push_kernel<1>", "loc_mark": "loc_mark_hot_plain_kernel",
+                     "loc_rank": "loc_rank_cold_kernel", "pull": "server_pull_kernel",
+                     "loc_dir_scan": "scan_onepass_kernel<DirPopc, DirEmit>"}.get(top[0])
+            default_cfg = rows == ROWS and world == 1 and (args.algo, args.loss, args.shape) == ("ftrl", "logit", "criteo")
+            traffic = tr.get(kname) if default_cfg else None
         except Exception:
             pass
         bytes_per_ex = NNZ_PER_ROW * 8 + 12 + r * (8 + 2 * 12)
