@@ -26,7 +26,46 @@ template <typename T> static std::vector<T> Get(FILE* f) {
   std::vector<T> v(n); if (n && fread(v.data(), sizeof(T), n, f) != n) v.clear(); return v;
 }
 
+// facade_test --reader file format mb_size shuf_buf neg_sampling seed max_key out.bin:
+// MinibatchIter over a text file; every minibatch is written out (host view) and trained on (device view).
+static int ReaderMode(int argc, char** argv) {
+  if (argc < 10) { fprintf(stderr, "usage: facade_test --reader file fmt mb shuf neg seed max_key out.bin\n"); return 2; }
+  const char* file = argv[2]; const char* fmt = argv[3];
+  const unsigned mb = (unsigned)atoi(argv[4]), shuf = (unsigned)atoi(argv[5]);
+  const float neg = (float)atof(argv[6]);
+  srand((unsigned)atoi(argv[7]));
+  ps::FLAGS_max_key = strtoull(argv[8], NULL, 10);
+  FILE* out = fopen(argv[9], "wb");
+  linear::Config conf; std::string err;
+  conf.ParseFromString("algo = FTRL\nlambda_l1 = .5\nlambda_l2 = .1\nlr_eta = .1\nlr_beta = 1\n", &err);
+  linear::AsgdServer server(conf);
+  linear::AsgdWorker worker(conf, &server);
+  std::vector<double> progs;
+  worker.reporter = [&](const linear::Progress& p) { progs.insert(progs.end(), p.data.begin(), p.data.end()); };
+  data::MinibatchIter<uint64_t> reader(file, 0, 1, fmt, mb, shuf, neg, 40000);
+  reader.BeforeFirst();
+  uint64_t n = 0;
+  while (reader.Next()) {
+    const RowBlock<uint64_t>& b = reader.Value();
+    const size_t nnz = b.offset[b.size];
+    Put(out, std::vector<size_t>(b.offset, b.offset + b.size + 1));
+    Put(out, std::vector<uint64_t>(b.index, b.index + nnz));
+    Put(out, b.value ? std::vector<float>(b.value, b.value + nnz) : std::vector<float>());
+    Put(out, std::vector<float>(b.label, b.label + b.size));
+    worker.ProcessMinibatch(reader.DeviceValue(), true);
+    ++n;
+  }
+  Put(out, std::vector<size_t>());   // end marker: an empty offset array
+  Put(out, progs);
+  std::vector<int64_t> tail = {server.nnz_w(), (int64_t)reader.BytesRead()};
+  Put(out, tail);
+  fclose(out);
+  printf("facade_test reader ok: %llu minibatches\n", (unsigned long long)n);
+  return 0;
+}
+
 int main(int argc, char** argv) {
+  if (argc > 1 && !strcmp(argv[1], "--reader")) return ReaderMode(argc, argv);
   if (argc < 4) { fprintf(stderr, "usage: facade_test in.bin out.bin conf.txt\n"); return 2; }
   FILE* in = fopen(argv[1], "rb"); FILE* out = fopen(argv[2], "wb");
   // conf in the reference's text format

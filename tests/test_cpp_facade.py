@@ -99,3 +99,41 @@ def test_facade_matches_the_checker(tmp_path, checker):
     for a, b in ((w, cw), (z, cz), (cg, ccg)):
         assert np.all(np.abs(a - b) <= 1e-5 * np.maximum(np.abs(b), 1.0))
     assert abs(int(nnz[0]) - int((cw != 0).sum())) <= 2 and progs[:, 5].sum() == nnz[0]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("fmt,shuf,neg", [("criteo", 0, 1.0), ("criteo", 900, 0.4), ("libsvm", 0, 1.0)])
+def test_cpp_minibatch_iter_and_device_minibatches(tmp_path, checker, fmt, shuf, neg):
+    """dmlc::data::MinibatchIter of the C++ facade (GPU reader) against the CPU assembly rule on the CPU parse of
+    the same text, same rand() seed; and AsgdWorker::ProcessMinibatch(DeviceMinibatch) against the checker."""
+    import ctypes
+    from oracle import oracle as O
+    from oracle.oracle_io import PortIO, minibatches
+    from tests.util import criteo_text, libsvm_text
+    exe = build_binary(tmp_path)
+    rng = np.random.default_rng(78)
+    text = criteo_text(rng, 2000) if fmt == "criteo" else libsvm_text(rng, 2000, with_value="values", key_space=2 ** 40)
+    f, fout = tmp_path / "data.txt", str(tmp_path / "reader.bin")
+    f.write_bytes(text)
+    r = subprocess.run([exe, "--reader", str(f), fmt, "300", str(shuf), str(neg), "9", str(MAX_KEY), fout],
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout + r.stderr
+    libc = ctypes.CDLL("libc.so.6")
+    libc.srand(9)
+    whole = PortIO().parse_criteo(text) if fmt == "criteo" else PortIO().parse_libsvm(text)
+    want = list(minibatches([whole], 300, shuf_buf=shuf, neg_sampling=neg, rand=libc.rand))
+    job = checker.linear_create(O.ALGO_FTRL, O.LOSS_LOGIT, 0.5, 0.1, 0.1, 1.0, MAX_KEY)
+    with open(fout, "rb") as fh:
+        for b in want:
+            assert np.array_equal(get(fh, np.uint64), b.offset)
+            assert np.array_equal(get(fh, np.uint64), b.index)
+            v = get(fh, np.float32)
+            assert (len(v) == 0) == (b.value is None) and (b.value is None or np.array_equal(v, b.value))
+            assert np.array_equal(get(fh, np.float32), b.label)
+        assert len(get(fh, np.uint64)) == 0                       # no further minibatch
+        progs = get(fh, np.float64).reshape(-1, 6)
+        nnz_w, bytes_read = get(fh, np.int64)
+    pcs = np.array([checker.linear_minibatch(job, b) for b in want])
+    assert np.array_equal(progs[:, 1], pcs[:, 1]) and np.array_equal(progs[:, 4], pcs[:, 4])
+    assert np.all(np.abs(progs[:, 0] - pcs[:, 0]) <= 1e-4 * np.abs(pcs[:, 0]))
+    assert bytes_read == len(text)

@@ -12,6 +12,7 @@
 #include "penalty.h"
 #include "progress.h"
 #include "ps.h"
+#include "base/minibatch_iter.h"
 
 namespace dmlc {
 namespace linear {
@@ -73,6 +74,14 @@ class AsgdWorker {
     rb.index = mb.index; rb.value = mb.value;
     Progress prog;
     WH_CHECK(wh_worker_process_minibatch(worker_, &rb, WH_HOST, train ? 1 : 0, prog.data.data()));
+    if (reporter) reporter(prog);
+  }
+  /// the same for a minibatch that already lives on the device (MinibatchIter::DeviceValue of the GPU reader)
+  void ProcessMinibatch(const data::DeviceMinibatch& mb, bool train = true) {
+    Progress prog;
+    uint64_t ticket = 0;
+    WH_CHECK(wh_worker_submit(worker_, &mb.blk, WH_DEVICE, mb.nnz, train ? 1 : 0, &ticket));
+    WH_CHECK(wh_worker_wait(worker_, ticket, prog.data.data()));
     if (reporter) reporter(prog);
   }
  private:
