@@ -48,6 +48,8 @@ int server_push_turn_launch(whServer* s, cudaStream_t stream, int turn, const ui
                             long long* acc, const FixedScale* fs, float mul, unsigned copies, size_t stride);
 int server_barrier_launch(whServer* s, cudaStream_t stream);
 // owner-side application of one source rank's outbox slice; cuts of an outbox for all destinations
+// all sources of one step in one cooperative launch (outboxes[src], src = 0..world-1, ascending source order)
+int server_apply_all_launch(whServer* s, cudaStream_t stream, unsigned char* const* outboxes, size_t cap);
 int server_apply_from_launch(whServer* s, cudaStream_t stream, const unsigned char* outbox, size_t cap);
 int outbox_cuts_launch(whServer* s, cudaStream_t stream, unsigned char* outbox);
 int server_push_acc_launch(whServer* s, cudaStream_t stream, const uint64_t* keys, size_t n, const unsigned* d_n, long long* acc,

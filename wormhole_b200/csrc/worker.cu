@@ -316,10 +316,19 @@ int wh_worker_submit(whWorker* w, const whRowBlock* blk, int mem, size_t nnz, in
       // slice straight from the source GPU; a second barrier keeps outboxes and tables stable until all are done
       float* ob_grads = reinterpret_cast<float*>(l.outbox.as<unsigned char>() + 256 + w->outbox_cap * 8);
       WH_TRY(fixed_finish_launch(cx, acc, ucap, fs, ob_grads, mul, acc_copies(), ucap, d_nuniq));
-      WH_TRY(server_barrier_launch(s, cx->stream));
       const int lane_idx = (int)(&l - w->lane);
-      for (int src = 0; src < s->map.world; ++src)
-        WH_TRY(server_apply_from_launch(s, cx->stream, w->peer_outbox[src][lane_idx], w->outbox_cap));
+      static int apply_all = -1;   // WH_APPLY_ALL=0: one launch per source (the older path)
+      if (apply_all < 0) { const char* e = getenv("WH_APPLY_ALL"); apply_all = e ? atoi(e) : 1; }
+      WH_TRY(server_barrier_launch(s, cx->stream));
+      if (apply_all) {
+        // the `world` messages in ascending source order in one cooperative launch
+        unsigned char* boxes[kMaxShards];
+        for (int src = 0; src < s->map.world; ++src) boxes[src] = w->peer_outbox[src][lane_idx];
+        WH_TRY(server_apply_all_launch(s, cx->stream, boxes, w->outbox_cap));
+      } else {
+        for (int src = 0; src < s->map.world; ++src)
+          WH_TRY(server_apply_from_launch(s, cx->stream, w->peer_outbox[src][lane_idx], w->outbox_cap));
+      }
       WH_TRY(server_barrier_launch(s, cx->stream));
       s->steps++;
     } else if (sharded) {
