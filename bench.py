@@ -295,7 +295,7 @@ def run_ours(args):
         return ms, wall, capi.kernel_launches() - l0
 
     sampler = ClockSampler(local)
-    if args.max_delay and world == 1:
+    if args.max_delay and (world == 1 or args.exchange == "p2p"):
         wk.set_max_delay(args.max_delay)
     ms_dev, _, launches = timed(dev, capi.WH_DEVICE, args.steps, args.warmup)
     ms_e2e, wall_e2e, _ = timed(host, capi.WH_HOST, args.steps, max(3, args.warmup // 2))
@@ -351,7 +351,7 @@ def run_ours(args):
                        "l2_policy": "inputs larger than L2 (pool of %d distinct minibatches, %.0f MB)" % (pool_n, pool_n * N * 8 / 1e6),
                        "parallelism": "key-range shards x%d" % world + ("" if world == 1 else " (" + args.exchange + ")"), "updater": FTRL,
                        "minibatches_in_flight": args.depth if (world == 1 or args.exchange == "p2p") else 1,
-                       "max_delay": args.max_delay if world == 1 else 0},
+                       "max_delay": args.max_delay if (world == 1 or args.exchange == "p2p") else 0},
             "e2e": {"value": e2e, "unit": "examples/s", "h2d_bytes_per_step": N * 8 + (rows + 1) * 8 + rows * 4,
                     "d2h_bytes_per_step": 72 + 16},
             "gpu_launches": int(launches),

@@ -244,7 +244,7 @@ WH_API int wh_worker_destroy(whWorker* w);
  * the configuration parity is judged in ("max_delay = 0"). d > 0: the pull of minibatch t only waits for the push
  * of minibatch t-1-d, as in the reference when max_concurrency minibatches are in flight and a pull overtakes the
  * worker's own earlier pushes (learn/solver/minibatch_solver.h:307-311); pushes are still applied in order.
- * Needs d < depth. */
+ * Needs d < depth. Sharded jobs: after wh_worker_ipc_attach only, and the same d on every rank. */
 WH_API int wh_worker_set_max_delay(whWorker* w, int max_delay);
 WH_API int wh_worker_submit(whWorker* w, const whRowBlock* blk, int mem, size_t nnz, int train,
                             uint64_t* ticket);

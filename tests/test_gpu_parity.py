@@ -420,3 +420,33 @@ def test_hot_key_table_changes_nothing(gpu, monkeypatch):
         for a, b in zip(res[0][1], res[1][1]):
             assert np.array_equal(a, b)
         assert res[0][2] == res[1][2]
+
+
+def test_bounded_staleness_option(gpu):
+    """wh_worker_set_max_delay: d = 0 is the default (sequential numbers); d > 0 lets a pull overtake the worker's
+    own last d pushes, as the reference does with max_concurrency minibatches in flight -- a different but close
+    trajectory; the arguments are validated."""
+    rng = np.random.default_rng(56)
+    blks = [random_block(rng, 3000, 20, 20000, with_value=False, empty_rows=False) for _ in range(8)]
+    objv = {}
+    for d in (0, 2):
+        srv = capi.Server(gpu, capi.ALGO_FTRL, 0.5, 0.1, 0.1, 1.0, 0, 2 ** 20)
+        wk = capi.Worker(gpu, srv, capi.LOSS_LOGIT, 2 ** 20, depth=3)
+        with pytest.raises(capi.WormholeError):
+            wk.set_max_delay(3)                          # needs d < depth
+        wk.set_max_delay(d)
+        pend, out = [], []
+        for b in blks:
+            if len(pend) == 3:
+                out.append(wk.wait(pend.pop(0)))
+            pend.append(wk.submit(b))
+            if len(pend) == 1 and d:
+                with pytest.raises(capi.WormholeError):
+                    wk.set_max_delay(0)                  # not while minibatches are in flight
+        out += [wk.wait(t) for t in pend]
+        objv[d] = np.array(out)[:, 0]
+        wk.close(); srv.close()
+    assert objv[0][0] == objv[2][0]                      # the first minibatch sees the same (empty) model
+    # stale by at most two minibatches: close (and identical whenever the GPU was done before the next submit --
+    # max_delay is a permission, not an obligation)
+    assert np.all(np.abs(objv[2] - objv[0]) <= 0.05 * objv[0])

@@ -197,7 +197,10 @@ int wh_worker_wait(whWorker* w, uint64_t ticket, double* prog);
 int wh_worker_set_max_delay(whWorker* w, int max_delay) {
   WH_REQUIRE(w && max_delay >= 0 && max_delay < w->depth, "wh_worker_set_max_delay: needs 0 <= max_delay < depth");
   WH_REQUIRE(w->next_wait == w->next_ticket, "wh_worker_set_max_delay: minibatches are in flight");
-  WH_REQUIRE(max_delay == 0 || !w->server || w->server->map.world == 1, "wh_worker_set_max_delay: sharded jobs keep max_delay 0 (their barriers assume one order)");
+  // sharded jobs: only with owner-side push (wh_worker_ipc_attach done), whose two barriers sit inside the push
+  // phase and therefore stay in ticket order; every rank must choose the same value
+  WH_REQUIRE(max_delay == 0 || !w->server || w->server->map.world == 1 || w->outbox_cap != 0,
+             "wh_worker_set_max_delay: a sharded job needs wh_worker_ipc_attach first (push in turns keeps max_delay 0)");
   w->max_delay = max_delay;
   return WH_OK;
 }
