@@ -257,7 +257,7 @@ WH_API int wh_worker_wait(whWorker* w, uint64_t ticket, double* prog);
  * (device); the gradient is written to d_grads[num_uniq] (device) for the caller's push. prog[5]
  * (new_w) is 0: the servers own that count (wh_server_nnz_w). */
 /* Sharded jobs, owner-side push. After wh_server_ipc_attach, a worker can publish one outbox per lane ({key
- * list, gradients}; capacity max_uniq keys, 64 bytes of handle per lane written to `handles`) and map its peers'
+ * list, gradients, inbox of pulled weights}; capacity max_uniq keys, 64 bytes of handle per lane written to `handles`) and map its peers'
  * (`handles` = all ranks' exports in rank order, world x depth x 64 bytes; same depth everywhere). A push then
  * needs two barriers instead of `world`: every owner reads, per source rank in ascending order, the slice of that
  * rank's outbox that falls into its key range and applies it as one push message. */

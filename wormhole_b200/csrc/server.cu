@@ -283,12 +283,12 @@ server_push_turn_kernel(HandleParams h, ShardMap m, int target, const uint64_t* 
 
 // All-rank rendezvous. flags[g][r] lives on GPU g and is written by rank r only.
 // the barrier proper, for the first `world` threads of one block (callers fence before and after)
-__device__ __forceinline__ void shard_barrier_wait(const ShardMap& m, unsigned long long epoch, long long* counters, int t) {
+__device__ __forceinline__ void shard_barrier_wait(const ShardMap& m, unsigned long long epoch, long long* counters, int t, int cls = 0) {
   if (t < m.world) {
-    volatile unsigned long long* out = m.flags[t] + m.rank;
+    volatile unsigned long long* out = m.flags[t] + cls * kMaxShards + m.rank;
     *out = epoch;
     __threadfence_system();
-    const volatile unsigned long long* in = m.flags[m.rank] + t;
+    const volatile unsigned long long* in = m.flags[m.rank] + cls * kMaxShards + t;
     const long long t0 = clock64();
     while (*in < epoch) {
       if (clock64() - t0 > 20000000000ll) {   // ~10 s: a peer is gone; report instead of hanging the GPU
@@ -299,22 +299,9 @@ __device__ __forceinline__ void shard_barrier_wait(const ShardMap& m, unsigned l
   }
 }
 
-__global__ void shard_barrier_kernel(ShardMap m, unsigned long long epoch, long long* counters) {
-  const int t = threadIdx.x;
+__global__ void shard_barrier_kernel(ShardMap m, unsigned long long epoch, long long* counters, int cls) {
   __threadfence_system();   // everything this GPU wrote to its peers before the barrier is visible first
-  if (t < m.world) {
-    volatile unsigned long long* out = m.flags[t] + m.rank;
-    *out = epoch;
-    __threadfence_system();
-    const volatile unsigned long long* in = m.flags[m.rank] + t;
-    const long long t0 = clock64();
-    while (*in < epoch) {
-      if (clock64() - t0 > 20000000000ll) {   // ~10 s: a peer is gone; report instead of hanging the GPU
-        atomicAdd(reinterpret_cast<unsigned long long*>(counters + 2), 1ull);
-        break;
-      }
-    }
-  }
+  shard_barrier_wait(m, epoch, counters, threadIdx.x, cls);
   __threadfence_system();
 }
 
@@ -470,10 +457,69 @@ int server_push_turn_launch(whServer* s, cudaStream_t stream, int turn, const ui
   return WH_OK;
 }
 
-int server_barrier_launch(whServer* s, cudaStream_t stream) {
+int server_barrier_launch(whServer* s, cudaStream_t stream, int cls) {
   if (s->map.world <= 1) return WH_OK;
-  s->epoch++;
-  WH_LAUNCH(shard_barrier_kernel, 1, 32, 0, stream, s->map, s->epoch, s->counters.as<long long>());
+  // flags only ever grow, so the barriers of one class must complete in the order they were issued, whichever
+  // streams they sit in: each waits for its predecessor of the same class
+  if (!s->barrier_ev[cls]) WH_CUDA(cudaEventCreateWithFlags(&s->barrier_ev[cls], cudaEventDisableTiming));
+  else WH_CUDA(cudaStreamWaitEvent(stream, s->barrier_ev[cls], 0));
+  s->epoch[cls]++;
+  WH_LAUNCH(shard_barrier_kernel, 1, 32, 0, stream, s->map, s->epoch[cls], s->counters.as<long long>(), cls);
+  WH_CUDA(cudaEventRecord(s->barrier_ev[cls], stream));
+  return WH_OK;
+}
+
+// ---- owner-served pull ---------------------------------------------------------------------------------------
+// 224 k scattered 4-byte reads over NVLink per pull (one per remote key) took 42 us at 8 GPUs: the fabric is bound by
+// the number of requests, not by bytes. Here the OWNER reads each source's slice of keys (contiguous: coalesced
+// 128-byte requests), gathers the weights from its own HBM and writes them into the source's inbox, again coalesced.
+struct ServeArgs {
+  unsigned char* outbox[kMaxShards];
+  int world;
+};
+__global__ void __launch_bounds__(256)
+server_serve_all_kernel(int algo, const void* table, uint64_t key_begin, uint64_t key_end, ServeArgs a, size_t cap, int me,
+                        long long* counters) {
+  __shared__ unsigned s_cut[kMaxShards][2];
+  if (threadIdx.x < 2 * a.world) {   // one thread per cut: the headers sit in the source GPUs' memory
+    const int src = threadIdx.x >> 1;
+    s_cut[src][threadIdx.x & 1] = reinterpret_cast<const volatile unsigned*>(a.outbox[src])[4 + me + (threadIdx.x & 1)];
+  }
+  __syncthreads();
+  const size_t gt = (size_t)blockIdx.x * blockDim.x + threadIdx.x, gsz = (size_t)gridDim.x * blockDim.x;
+  int bad = 0;
+  for (size_t i0 = gt; ; i0 += gsz) {
+    // one position of every source's slice per trip: the remote key reads of a trip are independent
+    uint64_t k[kMaxShards];
+    bool live[kMaxShards], any = false;
+#pragma unroll
+    for (int src = 0; src < kMaxShards; ++src) {
+      live[src] = src < a.world && s_cut[src][0] + i0 < s_cut[src][1];
+      if (live[src]) { k[src] = __ldcg(reinterpret_cast<const uint64_t*>(a.outbox[src] + 256) + s_cut[src][0] + i0); any = true; }
+    }
+    if (!__syncthreads_or(any)) break;
+#pragma unroll
+    for (int src = 0; src < kMaxShards; ++src) {
+      if (!live[src]) continue;
+      float w = 0.f;
+      if (k[src] >= key_begin && k[src] < key_end) {
+        const uint64_t e = k[src] - key_begin;
+        if (algo == WH_ALGO_FTRL) w = __ldcg(reinterpret_cast<const float*>(reinterpret_cast<const float4*>(table) + e));
+        else if (algo == WH_ALGO_ADAGRAD) w = __ldcg(reinterpret_cast<const float*>(reinterpret_cast<const float2*>(table) + e));
+        else w = __ldcg(reinterpret_cast<const float*>(table) + e);
+      } else bad = 1;
+      reinterpret_cast<float*>(a.outbox[src] + 256 + cap * 12)[s_cut[src][0] + i0] = w;
+    }
+  }
+  commit_counters(counters, 0, bad);
+}
+
+int server_serve_all_launch(whServer* s, cudaStream_t stream, unsigned char* const* outboxes, size_t cap) {
+  ServeArgs a;
+  a.world = s->map.world;
+  for (int src = 0; src < a.world; ++src) a.outbox[src] = outboxes[src];
+  WH_LAUNCH(server_serve_all_kernel, (unsigned)s->ctx->num_sms, 256, 0, stream, s->algo, s->table.p, s->key_begin, s->key_end, a, cap,
+            s->map.rank, s->counters.as<long long>());
   return WH_OK;
 }
 
@@ -539,11 +585,11 @@ int wh_server_create(whContext* ctx, const whServerConfig* c, whServer** out) {
   int r = s->table.reserve(s->entries() * esz);
   if (r == WH_OK && s->hslots) r = s->hkeys.reserve(s->hslots * 8);
   if (r == WH_OK) r = s->counters.reserve(64);
-  if (r == WH_OK) r = s->flags.reserve(kMaxShards * 8);
+  if (r == WH_OK) r = s->flags.reserve(kBarrierClasses * kMaxShards * 8);
   if (r != WH_OK) { delete s; return r; }
   WH_CUDA(cudaMemsetAsync(s->table.p, 0, s->table.cap, ctx->stream));  // entries default to 0 (:72,108-109,146-148)
   WH_CUDA(cudaMemsetAsync(s->counters.p, 0, 64, ctx->stream));
-  WH_CUDA(cudaMemsetAsync(s->flags.p, 0, kMaxShards * 8, ctx->stream));
+  WH_CUDA(cudaMemsetAsync(s->flags.p, 0, kBarrierClasses * kMaxShards * 8, ctx->stream));
   if (s->hslots) WH_CUDA(cudaMemsetAsync(s->hkeys.p, 0xff, s->hslots * 8, ctx->stream));
   s->map.world = 1; s->map.rank = 0;
   s->map.bounds[0] = c->key_begin; s->map.bounds[1] = c->key_end;
@@ -558,6 +604,7 @@ int wh_server_destroy(whServer* s) {
   DeviceGuard g(s->ctx->device);
   cudaStreamSynchronize(s->ctx->stream);
   for (void* p : s->peer_base) if (p) cudaIpcCloseMemHandle(p);
+  for (auto e : s->barrier_ev) if (e) cudaEventDestroy(e);
   s->table.release(); s->counters.release(); s->flags.release(); s->hkeys.release();
   delete s;
   return WH_OK;

@@ -5,6 +5,9 @@
 
 namespace wh {
 constexpr int kMaxShards = 8;
+// Barrier classes: each has its own flag row and epoch counter, so that barriers of different classes may complete in
+// any relative order (0: pull/turn barriers and the trailing one, 1: key lists posted, 2: pulls served, 3: gradients posted).
+constexpr int kBarrierClasses = 4;
 // The shards of one box as seen from one GPU: every rank's table / counters / barrier flags are mapped
 // into this process (CUDA IPC over NVLink), so a kernel can address any shard directly.
 struct ShardMap {
@@ -12,15 +15,16 @@ struct ShardMap {
   uint64_t bounds[kMaxShards + 1] = {0};          // shard g owns keys [bounds[g], bounds[g+1])
   void* table[kMaxShards] = {nullptr};
   long long* counters[kMaxShards] = {nullptr};
-  unsigned long long* flags[kMaxShards] = {nullptr};   // flags[g][r]: last barrier epoch rank r announced to rank g
+  unsigned long long* flags[kMaxShards] = {nullptr};   // flags[g][cls * kMaxShards + r]: last epoch of class cls rank r announced to rank g
 };
 }  // namespace wh
 
 struct whServer {
   whContext* ctx = nullptr;
   wh::ShardMap map;                 // world == 1: just this shard
-  wh::DevBuf flags;                 // this rank's barrier flags (kMaxShards x u64)
-  unsigned long long epoch = 0;     // barriers issued so far (all ranks in lock step)
+  wh::DevBuf flags;                 // this rank's barrier flags (kBarrierClasses x kMaxShards x u64)
+  unsigned long long epoch[wh::kBarrierClasses] = {0, 0, 0, 0};   // barriers issued so far, per class (all ranks in lock step)
+  cudaEvent_t barrier_ev[wh::kBarrierClasses] = {nullptr, nullptr, nullptr, nullptr};   // keeps a class's barriers in issue order across streams
   unsigned long long steps = 0;     // training minibatches pushed so far (SGD: t of every shard follows from it)
   void* peer_base[3 * wh::kMaxShards] = {nullptr};   // pointers opened with cudaIpcOpenMemHandle
   int algo = WH_ALGO_FTRL;
@@ -46,7 +50,10 @@ int server_push_launch(whServer* s, cudaStream_t stream, const uint64_t* keys, s
 int server_pull_sharded_launch(whServer* s, cudaStream_t stream, const uint64_t* keys, size_t n, const unsigned* d_n, float* vals);
 int server_push_turn_launch(whServer* s, cudaStream_t stream, int turn, const uint64_t* keys, size_t n, const unsigned* d_n,
                             long long* acc, const FixedScale* fs, float mul, unsigned copies, size_t stride);
-int server_barrier_launch(whServer* s, cudaStream_t stream);
+int server_barrier_launch(whServer* s, cudaStream_t stream, int cls = 0);
+// Owner-served pull: for every source rank, the weights of the slice of its posted key list that this shard owns are
+// gathered locally and written into that rank's inbox (behind keys and gradients in its outbox), coalesced over NVLink.
+int server_serve_all_launch(whServer* s, cudaStream_t stream, unsigned char* const* outboxes, size_t cap);
 // owner-side application of one source rank's outbox slice; cuts of an outbox for all destinations
 // all sources of one step in one cooperative launch (outboxes[src], src = 0..world-1, ascending source order)
 int server_apply_all_launch(whServer* s, cudaStream_t stream, unsigned char* const* outboxes, size_t cap);

@@ -61,6 +61,9 @@ struct whWorker {
   wh::PinnedBuf pinned;
   // ev_pushed[t % ring]: completion of minibatch t's push (or, for evaluation, of its pull)
   cudaEvent_t ev_pushed[wh::kMaxDepth + 1] = {nullptr};
+  // sharded jobs with owner-served pull: ev_served[t % ring] = every owner has served the pull of minibatch t (and
+  // therefore finished applying minibatch t - 1): the lane outbox of minibatch t - 1 may be overwritten after it
+  cudaEvent_t ev_served[wh::kMaxDepth + 1] = {nullptr};
   int max_delay = 0;                 // pull(t) waits for push(t - 1 - max_delay); pushes stay in order
   // sharded jobs: every rank's lane outboxes, [rank][lane] (own ones included); 0 capacity = not attached
   size_t outbox_cap = 0;
@@ -166,7 +169,8 @@ int wh_worker_create_ex(whContext* ctx, whServer* server, int loss, uint64_t max
   int r = w->pinned.reserve(512 * kMaxDepth);
   for (int i = 0; r == WH_OK && i < depth; ++i) r = lane_init(w, i);
   for (int i = 0; r == WH_OK && i <= kMaxDepth; ++i)
-    if (cudaEventCreateWithFlags(&w->ev_pushed[i], cudaEventDisableTiming) != cudaSuccess) r = WH_ERR_CUDA;
+    if (cudaEventCreateWithFlags(&w->ev_pushed[i], cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&w->ev_served[i], cudaEventDisableTiming) != cudaSuccess) r = WH_ERR_CUDA;
   if (r != WH_OK) { for (int i = 0; i < depth; ++i) lane_release(w->lane[i]); w->pinned.release(); delete w; return r; }
   *out = w;
   return WH_OK;
@@ -186,6 +190,7 @@ int wh_worker_destroy(whWorker* w) {
   for (void* p : w->opened) if (p) cudaIpcCloseMemHandle(p);
   for (int i = 0; i < w->depth; ++i) lane_release(w->lane[i]);
   for (auto e : w->ev_pushed) if (e) cudaEventDestroy(e);
+  for (auto e : w->ev_served) if (e) cudaEventDestroy(e);
   w->pinned.release();
   w->hot_tags.release();
   delete w;
@@ -262,6 +267,16 @@ int wh_worker_submit(whWorker* w, const whRowBlock* blk, int mem, size_t nnz, in
   const bool fused = hot && train;    // forward + backward in one launch, which also zeroes the localizer's directory
   const HotView hv = lane_hot_view(w, l);
 
+  const unsigned long long tk = w->next_ticket;       // this minibatch's ticket (1, 2, ...)
+  const int ring = kMaxDepth + 1;
+  static int serve = -1;   // WH_SERVE=0: every worker gathers its weights itself over NVLink (the older pull)
+  if (serve < 0) { const char* e = getenv("WH_SERVE"); serve = e ? atoi(e) : 1; }
+  const bool served = outboxed && serve != 0;
+  // this lane's outbox still holds the keys and gradients of minibatch tk - depth, which the owners read while they
+  // apply it; "every owner has served pull tk - depth + 1" says they are done with it
+  if (served && w->depth > 1 && tk > (unsigned long long)w->depth)
+    WH_CUDA(cudaStreamWaitEvent(cx->stream, w->ev_served[(tk - w->depth + 1) % ring], 0));
+
   WH_TRY(prof_begin(cx));
   // Localize
   if (hot) WH_TRY(localize_direct_hot(cx, in, hv, uniq, l.index.as<uint32_t>(), d_nuniq, !fused));
@@ -269,13 +284,23 @@ int wh_worker_submit(whWorker* w, const whRowBlock* blk, int mem, size_t nnz, in
   else WH_TRY(localize_sort(cx, in, uniq, nullptr, l.index.as<uint32_t>(), d_nuniq));
   if (outboxed) WH_TRY(outbox_cuts_launch(s, cx->stream, l.outbox.as<unsigned char>()));
   // ZPull: one Handle::Pull per unique key, after every earlier push
-  const unsigned long long tk = w->next_ticket;       // this minibatch's ticket (1, 2, ...)
-  const int ring = kMaxDepth + 1;
+  if (served) WH_TRY(server_barrier_launch(s, cx->stream, 1));   // every rank's key list is posted (off the critical cycle)
   // bounded staleness (the reference's max_concurrency > 1 lets a worker pull before its earlier pushes have
   // landed): with max_delay = d the pull of minibatch t waits for the push of minibatch t - 1 - d only
   if (tk > 1ull + (unsigned)w->max_delay) WH_CUDA(cudaStreamWaitEvent(cx->stream, w->ev_pushed[(tk - 1 - w->max_delay) % ring], 0));
   const bool sharded = s->map.world > 1;
-  if (sharded) {
+  float* pulled = l.w.as<float>();
+  if (served) {
+    // owner-served pull: each owner, after its own earlier pushes (the event above), answers the slices of all
+    // ranks' key lists that it owns and writes the weights into their inboxes; "all served" completes the pull
+    const int lane_idx = (int)(&l - w->lane);
+    unsigned char* boxes[kMaxShards];
+    for (int src = 0; src < s->map.world; ++src) boxes[src] = w->peer_outbox[src][lane_idx];
+    WH_TRY(server_serve_all_launch(s, cx->stream, boxes, w->outbox_cap));
+    WH_TRY(server_barrier_launch(s, cx->stream, 2));
+    WH_CUDA(cudaEventRecord(w->ev_served[tk % ring], cx->stream));
+    pulled = reinterpret_cast<float*>(l.outbox.as<unsigned char>() + 256 + w->outbox_cap * 12);
+  } else if (sharded) {
     // gather straight from the GPUs that own the keys; nobody may start pushing before everyone has pulled
     WH_TRY(server_pull_sharded_launch(s, cx->stream, uniq, ucap, d_nuniq, l.w.as<float>()));
     if (!outboxed || !train) WH_TRY(server_barrier_launch(s, cx->stream));
@@ -286,15 +311,15 @@ int wh_worker_submit(whWorker* w, const whRowBlock* blk, int mem, size_t nnz, in
   // Init (Xw), the per-example part of Evaluate, and the dual of CalcGrad: one pass over the rows. With
   // binary features |dual| <= 1 bounds every term of X^T dual, so the fixed-point scale is known up front.
   const bool scale_ready = d_value == nullptr;
-  if (hot && !fused) WH_TRY(hot_w_launch(cx, hv, l.w.as<float>()));   // evaluation: the slot-indexed weights for spmv_loss
+  if (hot && !fused) WH_TRY(hot_w_launch(cx, hv, pulled));   // evaluation: the slot-indexed weights for spmv_loss
   if (fused) {
     // ... and with the hot-key table the transposed product rides in the same launch (spmv.cu)
-    WH_TRY(spmv_fused_hot_launch(cx, w->loss, rows, n, d_offset, l.index.as<uint32_t>(), d_label, l.w.as<float>(), hv,
+    WH_TRY(spmv_fused_hot_launch(cx, w->loss, rows, n, d_offset, l.index.as<uint32_t>(), d_label, pulled, hv,
                                  l.xw.as<float>(), nullptr, d_eval, fs, acc, acc_copies(), ucap,
                                  cx->directory.p, div_up(w->max_key, 32) * sizeof(uint2)));
     WH_PROF(cx, "spmv_fused");
   } else {
-    WH_TRY(spmv_loss_launch(cx, w->loss, rows, n, d_offset, l.index.as<uint32_t>(), d_value, d_label, l.w.as<float>(),
+    WH_TRY(spmv_loss_launch(cx, w->loss, rows, n, d_offset, l.index.as<uint32_t>(), d_value, d_label, pulled,
                             l.xw.as<float>(), train ? l.dual.as<float>() : nullptr, d_eval,
                             (train && scale_ready) ? fs : nullptr, hot ? hv.w : nullptr));
     WH_PROF(cx, "spmv_loss");
@@ -322,7 +347,8 @@ int wh_worker_submit(whWorker* w, const whRowBlock* blk, int mem, size_t nnz, in
       const int lane_idx = (int)(&l - w->lane);
       static int apply_all = -1;   // WH_APPLY_ALL=0: one launch per source (the older path)
       if (apply_all < 0) { const char* e = getenv("WH_APPLY_ALL"); apply_all = e ? atoi(e) : 1; }
-      WH_TRY(server_barrier_launch(s, cx->stream));
+      // every rank's gradients are posted (with the owner-served pull: a barrier class of its own, see server.cuh)
+      WH_TRY(server_barrier_launch(s, cx->stream, served ? 3 : 0));
       if (apply_all) {
         // the `world` messages in ascending source order in one cooperative launch
         unsigned char* boxes[kMaxShards];
@@ -332,7 +358,10 @@ int wh_worker_submit(whWorker* w, const whRowBlock* blk, int mem, size_t nnz, in
         for (int src = 0; src < s->map.world; ++src)
           WH_TRY(server_apply_from_launch(s, cx->stream, w->peer_outbox[src][lane_idx], w->outbox_cap));
       }
-      WH_TRY(server_barrier_launch(s, cx->stream));
+      // Nobody may pull from, or refill an outbox of, a step that some owner is still applying. With the
+      // owner-served pull both follow from stream order -- an owner serves pull t+1 after its own apply t, and the
+      // outbox is refilled only after "all served t+1" -- so no trailing barrier; one lane has no such slack.
+      if (!served || w->depth == 1) WH_TRY(server_barrier_launch(s, cx->stream));
       s->steps++;
     } else if (sharded) {
       for (int turn = 0; turn < s->map.world; ++turn) {   // turn k: this rank is the only writer of shard (rank+k)%world
@@ -454,7 +483,7 @@ int wh_worker_ipc_export(whWorker* w, size_t max_uniq, void* handles) {
   cudaIpcMemHandle_t* h = reinterpret_cast<cudaIpcMemHandle_t*>(handles);
   for (int i = 0; i < w->depth; ++i) {
     Lane& l = w->lane[i];
-    WH_TRY(l.outbox.reserve(256 + max_uniq * 12));
+    WH_TRY(l.outbox.reserve(256 + max_uniq * 16));   // header | keys | gradients | inbox of pulled weights
     WH_CUDA(cudaMemsetAsync(l.outbox.p, 0, 256, w->ctx->stream));
     WH_CUDA(cudaIpcGetMemHandle(&h[i], l.outbox.p));
   }
