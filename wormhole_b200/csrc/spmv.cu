@@ -1,6 +1,9 @@
 // Pieces (2) and (5): SpMV::Times / TransTimes and SpMM::Times / TransTimes. See spmv.cuh.
 #include <stdlib.h>
 
+#include <utility>
+#include <vector>
+
 #include "hot.cuh"
 #include "loss.cuh"
 #include "spmv.cuh"
@@ -393,7 +396,10 @@ spmv_fused_hot_kernel(int loss, size_t rows, unsigned rows_per_block, unsigned s
                       const size_t* __restrict__ offset, const uint32_t* __restrict__ codes,
                       const float* __restrict__ label, const float* __restrict__ w, HotView hot,
                       float* __restrict__ y, float* __restrict__ dual, double* part_objv, unsigned* part_correct,
-                      long long* acc, float scale, unsigned copies, size_t stride, uint4* dirty, size_t dirty16) {
+                      long long* acc, float scale, unsigned copies, size_t stride, uint4* dirty, size_t dirty16,
+                      FixedScale* fs, double fs_inv) {
+  // the push that follows reads the fixed-point scale from device memory: host-known here (|dual| <= 1, binary features)
+  if (blockIdx.x == 0 && threadIdx.x == 0) { fs->scale = scale; fs->inv = fs_inv; }
   // side job: the localizer's directory is no longer needed once the codes exist; every block zeroes a slice
   {
     const size_t per = (dirty16 + gridDim.x - 1) / gridDim.x, lo = (size_t)blockIdx.x * per, hi = min(dirty16, lo + per);
@@ -491,6 +497,16 @@ spmv_fused_hot_kernel(int loss, size_t rows, unsigned rows_per_block, unsigned s
   }
 }
 
+// one event per context for the fork above (contexts live as long as the library; events are never destroyed)
+static cudaEvent_t fused_event(whContext* ctx) {
+  static std::vector<std::pair<whContext*, cudaEvent_t>> evs;
+  for (auto& e : evs) if (e.first == ctx) return e.second;
+  cudaEvent_t ev = nullptr;
+  if (cudaEventCreateWithFlags(&ev, cudaEventDisableTiming) != cudaSuccess) return nullptr;
+  evs.push_back({ctx, ev});
+  return ev;
+}
+
 int hot_w_launch(whContext* ctx, const HotView& hot, const float* w) {
   WH_LAUNCH(hot_w_kernel, kHotSlots / 256, 256, 0, ctx->stream, hot, w);
   return WH_OK;
@@ -500,7 +516,8 @@ int hot_w_launch(whContext* ctx, const HotView& hot, const float* w) {
 // be NULL), the evaluation partials in `out`, X^T dual in acc (fixed point, scale written to fs for the push).
 int spmv_fused_hot_launch(whContext* ctx, int loss, size_t rows, size_t nnz, const size_t* offset, const uint32_t* codes,
                           const float* label, const float* w, const HotView& hot, float* xw, float* dual, EvalOut* out,
-                          FixedScale* fs, long long* acc, unsigned copies, size_t stride, void* dirty, size_t dirty_bytes) {
+                          FixedScale* fs, long long* acc, unsigned copies, size_t stride, void* dirty, size_t dirty_bytes,
+                          whContext* reduce_ctx) {
   // one block per SM if the rows allow it, a thread per row. A block needs a whole SM's shared memory, so a few SMs
   // are left to the kernels of the neighbouring minibatches (the AUC cluster of the previous one holds 8 SMs for
   // ~150 us): with a block for every SM the last blocks had to wait for a free SM and the launch took two waves.
@@ -524,8 +541,17 @@ int spmv_fused_hot_launch(whContext* ctx, int loss, size_t rows, size_t nnz, con
   float sc; double inv;
   unit_terms_scale(nnz, &sc, &inv);
   WH_LAUNCH(spmv_fused_hot_kernel, grid, rpb, budget, ctx->stream, loss, rows, rpb, cap, offset, codes, label, w, hot, xw,
-            dual, po, pc, acc, sc, copies, stride, reinterpret_cast<uint4*>(dirty), dirty_bytes / 16);
-  return loss_reduce_launch(ctx, grid, po, nullptr, pc, out, fs, nnz);
+            dual, po, pc, acc, sc, copies, stride, reinterpret_cast<uint4*>(dirty), dirty_bytes / 16, fs, inv);
+  // The one-block fold of the evaluation partials feeds only the progress numbers and the AUC kernel: with a side
+  // context it leaves the chain (pull -> forward/backward -> push) and runs where the AUC runs, after this kernel.
+  if (reduce_ctx && reduce_ctx != ctx) {
+    cudaEvent_t ev = fused_event(ctx);
+    if (!ev) return WH_ERR_CUDA;
+    WH_CUDA(cudaEventRecord(ev, ctx->stream));
+    WH_CUDA(cudaStreamWaitEvent(reduce_ctx->stream, ev, 0));
+    return loss_reduce_launch(reduce_ctx, grid, po, nullptr, pc, out, nullptr, nnz);
+  }
+  return loss_reduce_launch(ctx, grid, po, nullptr, pc, out, nullptr, nnz);
 }
 
 // --------------------------------------------------------------------------------- SpMM --

@@ -316,7 +316,7 @@ int wh_worker_submit(whWorker* w, const whRowBlock* blk, int mem, size_t nnz, in
     // ... and with the hot-key table the transposed product rides in the same launch (spmv.cu)
     WH_TRY(spmv_fused_hot_launch(cx, w->loss, rows, n, d_offset, l.index.as<uint32_t>(), d_label, pulled, hv,
                                  l.xw.as<float>(), nullptr, d_eval, fs, acc, acc_copies(), ucap,
-                                 cx->directory.p, div_up(w->max_key, 32) * sizeof(uint2)));
+                                 cx->directory.p, div_up(w->max_key, 32) * sizeof(uint2), &l.ax));
     WH_PROF(cx, "spmv_fused");
   } else {
     WH_TRY(spmv_loss_launch(cx, w->loss, rows, n, d_offset, l.index.as<uint32_t>(), d_value, d_label, pulled,
