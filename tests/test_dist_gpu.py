@@ -11,7 +11,7 @@ from tests.util import random_block
 pytestmark = pytest.mark.gpu
 MAX_KEY = 1000003
 L1, L2, ETA, BETA = 0.5, 0.1, 0.1, 1.0
-STEPS = 4
+STEPS = 7
 
 
 def minibatch(rank, step):
@@ -129,7 +129,7 @@ def _p2p_rank_main(rank, world, port_no, out_dir, algo, owner_push):
     dist.all_gather_object(handles, srv.ipc_export())
     srv.ipc_attach(rank, world, MAX_KEY, handles)
     dist.barrier()
-    depth = 2 if algo == capi.ALGO_FTRL else 1       # FTRL case: two minibatches in flight per rank
+    depth = 3 if algo == capi.ALGO_FTRL else 1       # FTRL case: three minibatches in flight per rank
     wk = capi.Worker(ctx, srv, capi.LOSS_LOGIT, MAX_KEY, depth=depth)
     if owner_push:      # outboxes: the owners read each source's slice and apply it (2 barriers per step)
         boxes = [None] * world
