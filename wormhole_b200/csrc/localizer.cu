@@ -250,12 +250,9 @@ int localize_direct(whContext* ctx, const LocInput& in, uint64_t* d_uniq, uint32
   // (an even entry count, or at least one spare id of readable memory behind an odd one)
   const bool tma = n >= 2 && ((uintptr_t)in.index & 15) == 0 && (n & 1) == 0;
   const size_t ring_smem = (size_t)kTmaStages * kTileIds * 8 + kTmaStages * 8;
-  static bool attr = false;
-  if (!attr) {
-    WH_CUDA(cudaFuncSetAttribute(loc_mark_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(ring_smem + kMarkCache * 4)));
-    WH_CUDA(cudaFuncSetAttribute(loc_rank_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ring_smem));
-    attr = true;
-  }
+  // (per device, so not cached in a static: a process may hold contexts on several GPUs)
+  WH_CUDA(cudaFuncSetAttribute(loc_mark_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(ring_smem + kMarkCache * 4)));
+  WH_CUDA(cudaFuncSetAttribute(loc_rank_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ring_smem));
   const unsigned tgrid = (unsigned)std::min<size_t>(div_up(n ? n : 1, kTileIds), (size_t)ctx->num_sms * 2);
   if (n && tma) {
     WH_LAUNCH(loc_mark_tma_kernel, tgrid, kTmaThreads, ring_smem + kMarkCache * 4, ctx->stream, in.index, n, in.xf, dir);

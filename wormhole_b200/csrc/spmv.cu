@@ -170,8 +170,7 @@ int spmv_times_launch(whContext* ctx, size_t rows, const size_t* offset, const u
   const unsigned grid = (unsigned)div_up(rows, kRowsPerBlock);
   if (value) {
     const size_t smem = kTileCap * 8;
-    static bool attr = false;
-    if (!attr) { WH_CUDA(cudaFuncSetAttribute(spmv_times_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); attr = true; }
+    WH_CUDA(cudaFuncSetAttribute(spmv_times_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));   // per device
     WH_LAUNCH(spmv_times_kernel<true>, grid, kRowsPerBlock, smem, ctx->stream, rows, offset, index, value, x, y);
   } else {
     WH_LAUNCH(spmv_times_kernel<false>, grid, kRowsPerBlock, kTileCap * 4, ctx->stream, rows, offset, index, value, x, y);
@@ -327,12 +326,8 @@ int spmv_trans_accumulate_launch(whContext* ctx, size_t rows, size_t nnz, const 
   if (mode < 0) { const char* e = getenv("WH_TRANS_MODE"); mode = e ? atoi(e) : 0; }
   if (value) {
     const size_t smem = kTileCap * 8;
-    static bool attr = false;
-    if (!attr) {
-      WH_CUDA(cudaFuncSetAttribute(spmv_trans_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      WH_CUDA(cudaFuncSetAttribute(spmv_trans_agg_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      attr = true;
-    }
+    WH_CUDA(cudaFuncSetAttribute(spmv_trans_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));   // per device
+    WH_CUDA(cudaFuncSetAttribute(spmv_trans_agg_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     if (mode == 0) WH_LAUNCH(spmv_trans_kernel<true>, grid, kRowsPerBlock, smem, ctx->stream, rows, offset, index, value, x, acc, fs, copies, stride);
     else WH_LAUNCH(spmv_trans_agg_kernel<true>, grid, kRowsPerBlock, smem, ctx->stream, rows, offset, index, value, x, acc, fs, copies, stride);
   } else {
