@@ -97,6 +97,7 @@ struct whContext {
   wh::DevBuf scan_tmp;       // block sums of the directory scan
   wh::DevBuf scan_state;     // tile states of the one-launch scan (scan.cuh); zeroed when (re)allocated
   unsigned scan_epoch = 0;   // call counter of scan_state
+  cudaEvent_t side_ev = nullptr;   // orders work handed to another context's stream after this one's (created on first use)
   wh::DevBuf sort_tmp[6];    // radix sort ping-pong + histograms
   wh::DevBuf acc;            // int64 fixed-point accumulators of the transposed products
   wh::DevBuf small;          // device scalars (counts, plans, metric partials)

@@ -137,6 +137,7 @@ int wh_destroy(whContext* c) {
   if (!c) return WH_OK;
   wh::DeviceGuard g(c->device);
   cudaStreamSynchronize(c->stream);
+  if (c->side_ev) cudaEventDestroy(c->side_ev);
   c->directory.release(); c->scan_tmp.release(); c->scan_state.release(); c->acc.release(); c->small.release();
   for (auto& b : c->sort_tmp) b.release();
   for (auto& b : c->stage) b.release();

@@ -492,16 +492,6 @@ spmv_fused_hot_kernel(int loss, size_t rows, unsigned rows_per_block, unsigned s
   }
 }
 
-// one event per context for the fork above (contexts live as long as the library; events are never destroyed)
-static cudaEvent_t fused_event(whContext* ctx) {
-  static std::vector<std::pair<whContext*, cudaEvent_t>> evs;
-  for (auto& e : evs) if (e.first == ctx) return e.second;
-  cudaEvent_t ev = nullptr;
-  if (cudaEventCreateWithFlags(&ev, cudaEventDisableTiming) != cudaSuccess) return nullptr;
-  evs.push_back({ctx, ev});
-  return ev;
-}
-
 int hot_w_launch(whContext* ctx, const HotView& hot, const float* w) {
   WH_LAUNCH(hot_w_kernel, kHotSlots / 256, 256, 0, ctx->stream, hot, w);
   return WH_OK;
@@ -540,10 +530,9 @@ int spmv_fused_hot_launch(whContext* ctx, int loss, size_t rows, size_t nnz, con
   // The one-block fold of the evaluation partials feeds only the progress numbers and the AUC kernel: with a side
   // context it leaves the chain (pull -> forward/backward -> push) and runs where the AUC runs, after this kernel.
   if (reduce_ctx && reduce_ctx != ctx) {
-    cudaEvent_t ev = fused_event(ctx);
-    if (!ev) return WH_ERR_CUDA;
-    WH_CUDA(cudaEventRecord(ev, ctx->stream));
-    WH_CUDA(cudaStreamWaitEvent(reduce_ctx->stream, ev, 0));
+    if (!ctx->side_ev) WH_CUDA(cudaEventCreateWithFlags(&ctx->side_ev, cudaEventDisableTiming));
+    WH_CUDA(cudaEventRecord(ctx->side_ev, ctx->stream));
+    WH_CUDA(cudaStreamWaitEvent(reduce_ctx->stream, ctx->side_ev, 0));
     return loss_reduce_launch(reduce_ctx, grid, po, nullptr, pc, out, nullptr, nnz);
   }
   return loss_reduce_launch(ctx, grid, po, nullptr, pc, out, nullptr, nnz);

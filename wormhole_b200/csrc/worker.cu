@@ -88,6 +88,7 @@ static void lane_release(Lane& l) {
   for (auto& b : l.cx.stage) b.release();
   for (auto& b : l.ax.stage) b.release();
   for (auto e : l.cx.prof.ev) cudaEventDestroy(e);
+  if (l.cx.side_ev) cudaEventDestroy(l.cx.side_ev);
   if (l.ev_fork) cudaEventDestroy(l.ev_fork);
   if (l.ev_auc) cudaEventDestroy(l.ev_auc);
   if (l.ev_done) cudaEventDestroy(l.ev_done);
