@@ -95,6 +95,12 @@ struct DirEmit {
 
 // The directory scan in one launch (scan.cuh: decoupled look-back). The state buffer belongs to the context.
 static int dir_scan(whContext* ctx, uint2* dir, uint64_t* d_uniq, size_t words, unsigned* d_nuniq) {
+  static int coop = -1;   // WH_SCAN_COOP=0: the look-back scan for every size
+  if (coop < 0) { const char* e = getenv("WH_SCAN_COOP"); coop = e ? atoi(e) : 1; }
+  if (coop && scan_coop_fits(ctx, words)) {
+    WH_TRY(ctx->scan_tmp.reserve(div_up(words, kScanThreads * kOnepassItems) * sizeof(unsigned) + 256));
+    return scan_coop(ctx, DirPopc{dir}, DirEmit{dir, d_uniq}, words, ctx->scan_tmp.as<unsigned>(), d_nuniq);
+  }
   const size_t need = scan_onepass_bytes(words);
   if (ctx->scan_state.cap < need) {
     WH_TRY(ctx->scan_state.reserve(need));
