@@ -38,9 +38,10 @@ bool direct_supported(uint64_t max_key);
 struct HotView;
 // Direct localizer with the worker's hot-key table (hot.cuh): d_codes[i] = kHotFlag | slot for table keys, the rank
 // otherwise; also fills hot.rank for this minibatch.
-// clear_dir = false leaves the directory dirty: the caller must zero ctx->directory (max_key/32 uint2 words) before
-// the next localize on this context -- the fused forward/backward kernel does it on the side.
+// resolve = false stops after the scan: d_codes[i] of an entry that is not a table key is its transformed key (< 2^28),
+// to be turned into prefix + popc by the reader of the codes from ctx->directory, which the caller must zero
+// (max_key/32 uint2 words) before the next localize on this context.
 int localize_direct_hot(whContext* ctx, const LocInput& in, const HotView& hot, uint64_t* d_uniq, uint32_t* d_codes,
-                        unsigned* d_nuniq, bool clear_dir = true);
+                        unsigned* d_nuniq, bool resolve = true);
 
 }  // namespace wh

@@ -403,15 +403,36 @@ __device__ __forceinline__ void hot_rank_slot(const HotView& hot, const uint2* _
   hot.rank[p] = r;
 }
 
-// rank pass: entries that are not table keys hold their key; the directory turns it into the rank
-__global__ void __launch_bounds__(256) loc_rank_cold_kernel(size_t n, const uint2* __restrict__ dir, uint32_t* __restrict__ codes,
-                                                            HotView hot) {
-  // (the blocks also rank the table keys, a slice each: nothing in this launch reads hot.rank)
-  {
+// the table keys' ranks as the scan's epilogue (a slice per block), or as a launch of their own after the look-back scan
+struct HotRankEpilogue {
+  HotView hot;
+  const uint2* dir;
+  static constexpr bool kPresent = true;
+  __device__ void operator()() const {
     const int per = (kHotSlots + (int)gridDim.x - 1) / (int)gridDim.x;
     const int lo = (int)blockIdx.x * per, hi = min(kHotSlots, lo + per);
     for (int p = lo + (int)threadIdx.x; p < hi; p += (int)blockDim.x) hot_rank_slot(hot, dir, p);
   }
+};
+__global__ void hot_rank_kernel(HotView hot, const uint2* __restrict__ dir) {
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p < kHotSlots) hot_rank_slot(hot, dir, p);
+}
+// directory scan that also leaves hot.rank filled (and hot.present reset)
+static int dir_scan_hot(whContext* ctx, uint2* dir, uint64_t* d_uniq, size_t words, unsigned* d_nuniq, const HotView& hot) {
+  static int coop = -1;
+  if (coop < 0) { const char* e = getenv("WH_SCAN_COOP"); coop = e ? atoi(e) : 1; }
+  if (coop && scan_coop_fits(ctx, words)) {
+    WH_TRY(ctx->scan_tmp.reserve(div_up(words, kScanThreads * kOnepassItems) * sizeof(unsigned) + 256));
+    return scan_coop(ctx, DirPopc{dir}, DirEmit{dir, d_uniq}, words, ctx->scan_tmp.as<unsigned>(), d_nuniq, HotRankEpilogue{hot, dir});
+  }
+  WH_TRY(dir_scan(ctx, dir, d_uniq, words, d_nuniq));
+  WH_LAUNCH(hot_rank_kernel, kHotSlots / 256, 256, 0, ctx->stream, hot, dir);
+  return WH_OK;
+}
+
+// rank pass: entries that are not table keys hold their key; the directory turns it into the rank
+__global__ void __launch_bounds__(256) loc_rank_cold_kernel(size_t n, const uint2* __restrict__ dir, uint32_t* __restrict__ codes) {
   constexpr int kIlp = 8;
   const size_t stride = (size_t)gridDim.x * blockDim.x;
   for (size_t i0 = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i0 < n; i0 += stride * kIlp) {
@@ -428,7 +449,7 @@ __global__ void __launch_bounds__(256) loc_rank_cold_kernel(size_t n, const uint
 }
 
 int localize_direct_hot(whContext* ctx, const LocInput& in, const HotView& hot, uint64_t* d_uniq, uint32_t* d_codes,
-                        unsigned* d_nuniq, bool clear_dir) {
+                        unsigned* d_nuniq, bool resolve) {
   const size_t words = div_up(in.xf.max_key, 32);
   if (ctx->directory.cap < words * sizeof(uint2) || ctx->directory_words < words) {
     WH_TRY(ctx->directory.reserve(words * sizeof(uint2)));
@@ -457,15 +478,17 @@ int localize_direct_hot(whContext* ctx, const LocInput& in, const HotView& hot, 
   }
   WH_LAUNCH(hot_present_kernel, kHotSlots / 256, 256, 0, ctx->stream, hot, dir);
   WH_PROF(ctx, "loc_mark");
-  WH_TRY(dir_scan(ctx, dir, d_uniq, words, d_nuniq));
+  WH_TRY(dir_scan_hot(ctx, dir, d_uniq, words, d_nuniq, hot));
   WH_PROF(ctx, "loc_dir_scan");
-  const unsigned rgrid = (unsigned)std::min<size_t>(div_up(n, 256 * 8), (size_t)ctx->num_sms * 8);
-  WH_LAUNCH(loc_rank_cold_kernel, rgrid, 256, 0, ctx->stream, n, dir, d_codes, hot);
-  WH_PROF(ctx, "loc_rank");
-  if (clear_dir) {   // (otherwise the caller's next kernel clears it as a side job: spmv_fused_hot_launch)
+  if (resolve) {
+    const unsigned rgrid = (unsigned)std::min<size_t>(div_up(n, 256 * 8), (size_t)ctx->num_sms * 8);
+    WH_LAUNCH(loc_rank_cold_kernel, rgrid, 256, 0, ctx->stream, n, dir, d_codes);
+    WH_PROF(ctx, "loc_rank");
     WH_CUDA(cudaMemsetAsync(dir, 0, words * sizeof(uint2), ctx->stream));
     WH_PROF(ctx, "loc_dir_clear");
   }
+  // (!resolve: entries that are not table keys still hold their key, and the directory stays as the scan left it --
+  //  the caller turns keys into ranks where it reads the codes, and zeroes the directory afterwards)
   return WH_OK;
 }
 

@@ -191,8 +191,10 @@ int scan_onepass(whContext* ctx, F f, G g, size_t n, void* state, unsigned* epoc
 // walk far back, one L2 round trip per 32 predecessors (14 us for the 4 MB directory). With every tile resident a grid
 // barrier replaces the chain: tile sums, barrier, each block adds up its predecessors' sums in one strided read,
 // apply -- the elements stay in registers across the barrier.
-template <int ITEMS, typename F, typename G>
-__global__ void __launch_bounds__(kScanThreads) scan_coop_kernel(F f, G g, size_t n, unsigned* sums, unsigned* total) {
+// H: an optional epilogue, run by every block after one more grid barrier (i.e. when every g(...) has been applied).
+struct NoEpilogue { __device__ void operator()() const {} static constexpr bool kPresent = false; };
+template <int ITEMS, typename F, typename G, typename H>
+__global__ void __launch_bounds__(kScanThreads) scan_coop_kernel(F f, G g, H h, size_t n, unsigned* sums, unsigned* total) {
   namespace cg = cooperative_groups;
   cg::grid_group grid = cg::this_grid();
   const unsigned tile = blockIdx.x;
@@ -216,16 +218,21 @@ __global__ void __launch_bounds__(kScanThreads) scan_coop_kernel(F f, G g, size_
     if (base + k < n) g(base + k, v[k], run);
     run += v[k];
   }
+  if (H::kPresent) {
+    __threadfence();
+    grid.sync();
+    h();
+  }
 }
 // true if the cooperative variant can take an input of n elements on this device (all tiles resident)
 static inline bool scan_coop_fits(const whContext* ctx, size_t n) {
   return div_up(n ? n : 1, kScanThreads * kOnepassItems) <= (size_t)ctx->num_sms * 4;
 }
-template <typename F, typename G>
-int scan_coop(whContext* ctx, F f, G g, size_t n, unsigned* sums, unsigned* total) {
+template <typename F, typename G, typename H = NoEpilogue>
+int scan_coop(whContext* ctx, F f, G g, size_t n, unsigned* sums, unsigned* total, H h = H()) {
   const unsigned nt = (unsigned)div_up(n ? n : 1, kScanThreads * kOnepassItems);
-  void* args[] = {&f, &g, &n, &sums, &total};
-  WH_CUDA(cudaLaunchCooperativeKernel((const void*)scan_coop_kernel<kOnepassItems, F, G>, dim3(nt), dim3(kScanThreads), args, 0,
+  void* args[] = {&f, &g, &h, &n, &sums, &total};
+  WH_CUDA(cudaLaunchCooperativeKernel((const void*)scan_coop_kernel<kOnepassItems, F, G, H>, dim3(nt), dim3(kScanThreads), args, 0,
                                       ctx->stream));
   wh::g_launches.fetch_add(1, std::memory_order_relaxed);
   return WH_OK;

@@ -374,6 +374,16 @@ __device__ __forceinline__ float gather_sw(const float* __restrict__ w, const fl
   const float* p = (code & kHotFlag) ? s_w + (code & (kHotSlots - 1)) : w + code;
   return *p;
 }
+// the code of an entry: staged codes are final; a band too long for the staging buffer is walked in global memory,
+// where entries that are not table keys still hold their key
+__device__ __forceinline__ uint32_t code_at(const uint32_t* idx, bool staged, const uint2* __restrict__ dir, unsigned pos) {
+  uint32_t c = idx[pos];
+  if (!staged && !(c & kHotFlag)) {
+    const uint2 e = __ldg(dir + (c >> 5));
+    c = e.y + __popc(e.x & ((1u << (c & 31)) - 1u));
+  }
+  return c;
+}
 // 64-bit add in shared memory out of two native 32-bit atomics. (atomicAdd on a 64-bit shared word compiles to a
 // compare-and-swap spin loop, ATOMS.CAST.SPIN, which collapsed under the table's contention: 600 instructions
 // per warp step.) The low word's returned old value tells this add whether IT wrapped; the carry rides on the
@@ -391,15 +401,10 @@ spmv_fused_hot_kernel(int loss, size_t rows, unsigned rows_per_block, unsigned s
                       const size_t* __restrict__ offset, const uint32_t* __restrict__ codes,
                       const float* __restrict__ label, const float* __restrict__ w, HotView hot,
                       float* __restrict__ y, float* __restrict__ dual, double* part_objv, unsigned* part_correct,
-                      long long* acc, float scale, unsigned copies, size_t stride, uint4* dirty, size_t dirty16,
+                      long long* acc, float scale, unsigned copies, size_t stride, const uint2* __restrict__ dir,
                       FixedScale* fs, double fs_inv) {
   // the push that follows reads the fixed-point scale from device memory: host-known here (|dual| <= 1, binary features)
   if (blockIdx.x == 0 && threadIdx.x == 0) { fs->scale = scale; fs->inv = fs_inv; }
-  // side job: the localizer's directory is no longer needed once the codes exist; every block zeroes a slice
-  {
-    const size_t per = (dirty16 + gridDim.x - 1) / gridDim.x, lo = (size_t)blockIdx.x * per, hi = min(dirty16, lo + per);
-    for (size_t i = lo + threadIdx.x; i < hi; i += blockDim.x) dirty[i] = make_uint4(0u, 0u, 0u, 0u);
-  }
   extern __shared__ __align__(16) unsigned char smem[];
   long long* s_acc = reinterpret_cast<long long*>(smem);                       // kHotSlots
   float* s_w = reinterpret_cast<float*>(s_acc + kHotSlots);                    // kHotSlots: the table keys' weights
@@ -424,7 +429,24 @@ spmv_fused_hot_kernel(int loss, size_t rows, unsigned rows_per_block, unsigned s
   const size_t begin = s_off[0];
   const size_t cnt = s_off[rows_per_block] - begin;
   const bool staged = cnt <= (size_t)stage_cap;
-  if (staged) stage_run(s_idx, codes + begin, (unsigned)cnt);
+  // Staging is also the rank pass: an entry that is not a table key still holds its transformed key (the mark pass
+  // left it there) and becomes prefix + popc from the localizer's directory on its way into shared memory -- no
+  // separate launch that reads and rewrites the codes.
+  if (staged) {
+    for (unsigned i0 = threadIdx.x; i0 < (unsigned)cnt; i0 += blockDim.x * kStageIlp) {
+      uint32_t c[kStageIlp];
+      uint2 e[kStageIlp];
+#pragma unroll
+      for (int u = 0; u < kStageIlp; ++u) { const unsigned i = i0 + u * blockDim.x; c[u] = i < (unsigned)cnt ? __ldcs(codes + begin + i) : kHotFlag; }
+#pragma unroll
+      for (int u = 0; u < kStageIlp; ++u) if (!(c[u] & kHotFlag)) e[u] = __ldg(dir + (c[u] >> 5));
+#pragma unroll
+      for (int u = 0; u < kStageIlp; ++u) {
+        const unsigned i = i0 + u * blockDim.x;
+        if (i < (unsigned)cnt) s_idx[i] = (c[u] & kHotFlag) ? c[u] : e[u].y + __popc(e[u].x & ((1u << (c[u] & 31)) - 1u));
+      }
+    }
+  }
   __syncthreads();
   const uint32_t* idx = staged ? s_idx : codes + begin;   // generic pointer: shared or global
   const size_t r = r0 + threadIdx.x;
@@ -441,11 +463,11 @@ spmv_fused_hot_kernel(int loss, size_t rows, unsigned rows_per_block, unsigned s
     for (; j + 8 <= len; j += 8) {   // eight gathers in flight, the adds stay in CSR order
       float g[8];
 #pragma unroll
-      for (int u = 0; u < 8; ++u) g[u] = gather_sw(w, s_w, idx[lb + j + u]);
+      for (int u = 0; u < 8; ++u) g[u] = gather_sw(w, s_w, code_at(idx, staged, dir, lb + j + u));
 #pragma unroll
       for (int u = 0; u < 8; ++u) sum += g[u];
     }
-    for (; j < len; ++j) sum += gather_sw(w, s_w, idx[lb + j]);
+    for (; j < len; ++j) sum += gather_sw(w, s_w, code_at(idx, staged, dir, lb + j));
     y[r] = sum;
     loss_row(loss, label[r], sum, &dl, &objv, &correct);
     if (dual) dual[r] = dl;
@@ -463,7 +485,7 @@ spmv_fused_hot_kernel(int loss, size_t rows, unsigned rows_per_block, unsigned s
   unsigned pos = len ? (2u * lane) % len : 0u;
   for (unsigned j = 0; j < maxlen; ++j) {
     const bool valid = j < len;
-    const uint32_t c = valid ? idx[lb + pos] : 0u;
+    const uint32_t c = valid ? code_at(idx, staged, dir, lb + pos) : 0u;
     if (++pos >= len) pos = 0u;
     const bool is_hot = valid && (c & kHotFlag);
     if (valid && !is_hot) atomicAdd(reinterpret_cast<unsigned long long*>(gacc + c), (unsigned long long)q);
@@ -497,11 +519,11 @@ int hot_w_launch(whContext* ctx, const HotView& hot, const float* w) {
   return WH_OK;
 }
 
-// Binary features, codes from localize_direct_hot, acc all zero on entry. Leaves Xw in xw, the dual in dual (may
+// Binary features, codes from localize_direct_hot(..., resolve = false) and its directory, acc all zero on entry. Leaves Xw in xw, the dual in dual (may
 // be NULL), the evaluation partials in `out`, X^T dual in acc (fixed point, scale written to fs for the push).
 int spmv_fused_hot_launch(whContext* ctx, int loss, size_t rows, size_t nnz, const size_t* offset, const uint32_t* codes,
                           const float* label, const float* w, const HotView& hot, float* xw, float* dual, EvalOut* out,
-                          FixedScale* fs, long long* acc, unsigned copies, size_t stride, void* dirty, size_t dirty_bytes,
+                          FixedScale* fs, long long* acc, unsigned copies, size_t stride, const void* directory,
                           whContext* reduce_ctx) {
   // one block per SM if the rows allow it, a thread per row. A block needs a whole SM's shared memory, so a few SMs
   // are left to the kernels of the neighbouring minibatches (the AUC cluster of the previous one holds 8 SMs for
@@ -526,7 +548,7 @@ int spmv_fused_hot_launch(whContext* ctx, int loss, size_t rows, size_t nnz, con
   float sc; double inv;
   unit_terms_scale(nnz, &sc, &inv);
   WH_LAUNCH(spmv_fused_hot_kernel, grid, rpb, budget, ctx->stream, loss, rows, rpb, cap, offset, codes, label, w, hot, xw,
-            dual, po, pc, acc, sc, copies, stride, reinterpret_cast<uint4*>(dirty), dirty_bytes / 16, fs, inv);
+            dual, po, pc, acc, sc, copies, stride, reinterpret_cast<const uint2*>(directory), fs, inv);
   // The one-block fold of the evaluation partials feeds only the progress numbers and the AUC kernel: with a side
   // context it leaves the chain (pull -> forward/backward -> push) and runs where the AUC runs, after this kernel.
   if (reduce_ctx && reduce_ctx != ctx) {

@@ -61,7 +61,7 @@ int hot_w_launch(whContext* ctx, const HotView& hot, const float* w);
 int spmv_fused_hot_launch(whContext* ctx, int loss, size_t rows, size_t nnz, const size_t* offset, const uint32_t* codes,
                           const float* label, const float* w, const HotView& hot, float* xw, float* dual, EvalOut* out,
                           FixedScale* fs, long long* acc, unsigned copies, size_t stride,
-                          void* dirty = nullptr, size_t dirty_bytes = 0,   // dirty: memory to zero on the side (16-byte multiple)
+                          const void* directory,   // the localizer's directory of this minibatch (uint2 words), left untouched
                           whContext* reduce_ctx = nullptr);                  // where the evaluation partials are folded (default: ctx)
 
 int spmv_times_launch(whContext* ctx, size_t rows, const size_t* offset, const uint32_t* index,

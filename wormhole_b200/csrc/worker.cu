@@ -265,7 +265,7 @@ int wh_worker_submit(whWorker* w, const whRowBlock* blk, int mem, size_t nnz, in
   const bool hot_ok = w->hot_enabled && direct && d_value == nullptr;
   if (hot_ok && !w->hot_tried) WH_TRY(hot_census(w, l, in, ucap));
   const bool hot = hot_ok && w->hot_ready;
-  const bool fused = hot && train;    // forward + backward in one launch, which also zeroes the localizer's directory
+  const bool fused = hot && train;    // forward + backward in one launch, which is also the rank pass of the localizer
   const HotView hv = lane_hot_view(w, l);
 
   const unsigned long long tk = w->next_ticket;       // this minibatch's ticket (1, 2, ...)
@@ -317,7 +317,7 @@ int wh_worker_submit(whWorker* w, const whRowBlock* blk, int mem, size_t nnz, in
     // ... and with the hot-key table the transposed product rides in the same launch (spmv.cu)
     WH_TRY(spmv_fused_hot_launch(cx, w->loss, rows, n, d_offset, l.index.as<uint32_t>(), d_label, pulled, hv,
                                  l.xw.as<float>(), nullptr, d_eval, fs, acc, acc_copies(), ucap,
-                                 cx->directory.p, div_up(w->max_key, 32) * sizeof(uint2), &l.ax));
+                                 cx->directory.p, &l.ax));
     WH_PROF(cx, "spmv_fused");
   } else {
     WH_TRY(spmv_loss_launch(cx, w->loss, rows, n, d_offset, l.index.as<uint32_t>(), d_value, d_label, pulled,
@@ -329,6 +329,8 @@ int wh_worker_submit(whWorker* w, const whRowBlock* blk, int mem, size_t nnz, in
   WH_CUDA(cudaEventRecord(l.ev_fork, cx->stream));
   WH_CUDA(cudaStreamWaitEvent(l.ax.stream, l.ev_fork, 0));
   WH_TRY(auc_launch(&l.ax, rows, d_label, l.xw.as<float>(), d_eval));
+  // the fused kernel was the last reader of the localizer's directory: zero it for the lane's next minibatch, off the chain
+  if (fused) WH_CUDA(cudaMemsetAsync(cx->directory.p, 0, div_up(w->max_key, 32) * sizeof(uint2), l.ax.stream));
   WH_CUDA(cudaEventRecord(l.ev_auc, l.ax.stream));
   if (train) {
     // CalcGrad: X^T dual into the fixed-point accumulator; ZPush: convert + update in one pass
