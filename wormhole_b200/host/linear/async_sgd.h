@@ -3,7 +3,9 @@
 // conf keys. The scheduler / ps::App plumbing of the reference (roles, dispatch, ZeroMQ) is not
 // reproduced: construct a server, hand it to a worker, feed RowBlock<FeaID> minibatches.
 #pragma once
+#include <functional>
 #include <memory>
+#include <string>
 #include <vector>
 
 #include "base/localizer.h"
@@ -39,6 +41,9 @@ class AsgdServer {
   }
   ~AsgdServer() { wh_server_destroy(server_); }
   whServer* server() const { return server_; }
+  /// IterServer::SaveModel / LoadModel (learn/solver/iter_solver.h:99-119): the records of w != 0
+  void SaveModel(const std::string& path) const { WH_CHECK(wh_server_save(server_, path.c_str())); }
+  void LoadModel(const std::string& path) { WH_CHECK(wh_server_load(server_, path.c_str())); }
   /// ISGDHandle::new_w summed so far = |w|_0 (learn/linear/async_sgd.h:35-41)
   int64_t nnz_w() const { int64_t n = 0; WH_CHECK(wh_server_nnz_w(server_, &n)); return n; }
   /// Entry fields of the given keys
@@ -84,6 +89,24 @@ class AsgdWorker {
     WH_CHECK(wh_worker_wait(worker_, ticket, prog.data.data()));
     if (reporter) reporter(prog);
   }
+  /// The two halves of the above, for max_concurrency minibatches in flight (learn/solver/minibatch_solver.h:307-311):
+  /// Submit enqueues, Wait collects in submission order and calls `reporter`.
+  uint64_t Submit(const data::DeviceMinibatch& mb, bool train = true) {
+    uint64_t ticket = 0;
+    WH_CHECK(wh_worker_submit(worker_, &mb.blk, WH_DEVICE, mb.nnz, train ? 1 : 0, &ticket));
+    return ticket;
+  }
+  void Wait(uint64_t ticket) {
+    Progress prog;
+    WH_CHECK(wh_worker_wait(worker_, ticket, prog.data.data()));
+    if (reporter) reporter(prog);
+  }
+  /// ScalarLoss::Predict (learn/linear/loss.h:55-63): one value per row, sigmoid(Xw) if prob_predict else Xw
+  void Predict(const data::DeviceMinibatch& mb, bool prob_predict, std::vector<float>* out) {
+    out->resize(mb.blk.size);
+    WH_CHECK(wh_worker_predict(worker_, &mb.blk, WH_DEVICE, prob_predict ? 1 : 0, out->data()));
+  }
+  int depth() const { const int c = conf_.max_concurrency(); return c < 1 ? 1 : (c > 8 ? 8 : c); }
  private:
   Config conf_;
   whWorker* worker_ = nullptr;
