@@ -137,3 +137,53 @@ def test_cpp_minibatch_iter_and_device_minibatches(tmp_path, checker, fmt, shuf,
     assert np.array_equal(progs[:, 1], pcs[:, 1]) and np.array_equal(progs[:, 4], pcs[:, 4])
     assert np.all(np.abs(progs[:, 0] - pcs[:, 0]) <= 1e-4 * np.abs(pcs[:, 0]))
     assert bytes_read == len(text)
+
+
+def build_difacto_binary(tmp):
+    from wormhole_b200 import build
+    build.build()
+    exe = os.path.join(str(tmp), "difacto_facade_test")
+    cmd = ["/usr/bin/g++", "-std=c++14", "-O1", "-Wall", "-I" + os.path.join(ROOT, "include"),
+           "-I" + os.path.join(ROOT, "wormhole_b200", "host"), os.path.join(ROOT, "tests", "cpp", "difacto_facade_test.cc"),
+           "-o", exe, "-L" + os.path.join(ROOT, "wormhole_b200"), "-lwormhole_b200",
+           "-Wl,-rpath," + os.path.join(ROOT, "wormhole_b200"), "-L/usr/local/cuda/lib64", "-lcudart"]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    return exe
+
+
+def test_difacto_facade_compiles_and_links(tmp_path):
+    assert os.path.exists(build_difacto_binary(tmp_path))
+
+
+@pytest.mark.gpu
+def test_difacto_facade_equals_the_ctypes_path(tmp_path):
+    """difacto::AsyncSGD (C++) and capi.Difacto (ctypes) are two bindings of one C ABI: same conf, same minibatches,
+    same hash-seeded embedding init -> identical progress vectors; the table rows follow learn/difacto/progress.h."""
+    from wormhole_b200 import capi
+    from wormhole_b200.solver import DifactoProgress
+    exe = build_difacto_binary(tmp_path)
+    rng = np.random.default_rng(79)
+    blks = [random_block(rng, 2000, 14, 3000, with_value=(m % 2 == 1), empty_rows=False) for m in range(3)]
+    fin, fout = str(tmp_path / "in.bin"), str(tmp_path / "out.bin")
+    with open(fin, "wb") as f:
+        put(f, np.array([MAX_KEY, len(blks)], np.uint64))
+        for b in blks:
+            put(f, b.offset); put(f, b.index)
+            put(f, b.value if b.value is not None else np.zeros(0, np.float32)); put(f, b.label)
+    r = subprocess.run([exe, fin, fout], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout + r.stderr
+    with open(fout, "rb") as f:
+        progs = get(f, np.float64).reshape(-1, 8)
+        rows = get(f, np.uint8).tobytes().decode().splitlines()
+    ctx = capi.Context(0)
+    d = capi.Difacto(ctx, l1=1.0, l2=0.0, eta=.01, beta=1.0, l1_shrk=True, dim=5, threshold=5, v_l2=0.0, init_scale=.01,
+                     max_key=MAX_KEY, seed=7)
+    want = np.array([d.process_minibatch(b, True, dp) for dp in range(2) for b in blks])
+    d.close(); ctx.close()
+    assert np.array_equal(progs, want)
+    assert progs[:, 7].sum() > 0                      # embeddings were created
+    table = DifactoProgress()
+    for p, row in zip(want, rows):
+        table.data = list(p)
+        assert table.PrintStr() == row
