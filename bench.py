@@ -332,9 +332,9 @@ def run_ours(args):
         traffic = None
         try:
             tr = json.load(open(os.path.join(ROOT, "profiles", "r1_d_traffic.json")))
-            kname = {"spmv_fused": "spmv_fused_hot_kernel", "push": "server_push_kernel<1>", "loc_mark": "loc_mark_hot_plain_kernel",
-                     "loc_rank": "loc_rank_cold_kernel", "pull": "server_pull_kernel",
-                     "loc_dir_scan": "scan_onepass_kernel<DirPopc, DirEmit>"}.get(top[0])
+            kname = {"spmv_fused": "spmv_fused_hot_kernel", "push": "server_push_kernel<1>", "loc_mark": "loc_mark_hot_plain_kernel<1>",
+                     "pull": "server_pull_kernel",
+                     "loc_dir_scan": "scan_coop_kernel<4, DirPopc, DirEmit, HotRankEpilogue>"}.get(top[0])
             default_cfg = rows == ROWS and world == 1 and (args.algo, args.loss, args.shape) == ("ftrl", "logit", "criteo")
             traffic = tr.get(kname) if default_cfg else None
         except Exception:
