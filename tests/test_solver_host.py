@@ -57,3 +57,20 @@ def test_difacto_stop_rule():
     assert not s(600.0, 1000, False)                                   # 100 -> 0.6
     assert not s(590.0, 1000, False)                                   # improved by 0.01
     assert s(589.9, 1000, False) and "minimal requirement" in out.getvalue()
+
+
+def test_cpp_progress_rows_equal_the_reference(tmp_path):
+    """the C++ facade's Progress structs (wormhole_b200/host/{linear,difacto}/progress.h) against the same golden rows"""
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe = str(tmp_path / "progress_test")
+    r = subprocess.run(["/usr/bin/g++", "-std=c++14", "-I" + os.path.join(root, "wormhole_b200", "host"),
+                        os.path.join(root, "tests", "cpp", "progress_test.cc"), "-o", exe], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    inp = "".join("L " + " ".join(repr(float(x)) for x in v) + "\n" for v in G["linear"]["in"])
+    inp += "".join("D " + " ".join(repr(float(x)) for x in v) + "\n" for v in G["difacto"]["in"])
+    out = subprocess.run([exe], input=inp, capture_output=True, text=True).stdout.split("\n")
+    assert out[0] == G["linear"]["head"] and out[1] == G["difacto"]["head"]
+    n = len(G["linear"]["rows"])
+    assert out[2:2 + n] == G["linear"]["rows"]
+    assert out[2 + n:2 + n + len(G["difacto"]["rows"])] == G["difacto"]["rows"]
