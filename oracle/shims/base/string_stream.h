@@ -1,25 +1,40 @@
-// Shadows /root/reference/learn/base/string_stream.h so that oracle/_ref does not
-// depend on which dmlc::Stream::Write signature is in scope. Same behaviour:
-// an in-memory Stream. Test infrastructure only.
+// Stand-in for learn/base/string_stream.h inside oracle/_ref: an in-memory dmlc::Stream (append-only writes,
+// sequential reads, str() returns everything written). It replaces the reference's header because the stand-in
+// dmlc::Stream (shims/dmlc/io.h) also declares string overloads of Read / Write, which a derived class must
+// re-export with using-declarations. Test infrastructure only.
 #pragma once
-#include <cstring>
+#include <algorithm>
 #include <string>
+#include <vector>
+
 #include "dmlc/io.h"
+
 namespace dmlc {
+
 class StringStream : public Stream {
  public:
-  StringStream() : pos_(0) {}
-  explicit StringStream(const std::string& s) : buf_(s), pos_(0) {}
   using Stream::Read;
   using Stream::Write;
-  virtual size_t Read(void* ptr, size_t size) {
-    CHECK_LE(size + pos_, buf_.size());
-    memcpy(ptr, buf_.data() + pos_, size); pos_ += size; return size;
+
+  StringStream() {}
+  explicit StringStream(const std::string& initial) : bytes_(initial.begin(), initial.end()) {}
+
+  // reading past the end is a programming error in the callers (serialised Workload messages): abort like CHECK_LE
+  size_t Read(void* dst, size_t n) override {
+    CHECK(cursor_ + n <= bytes_.size()) << "StringStream: read of " << n << " bytes at " << cursor_ << " of " << bytes_.size();
+    std::copy(bytes_.begin() + cursor_, bytes_.begin() + cursor_ + n, static_cast<char*>(dst));
+    cursor_ += n;
+    return n;
   }
-  virtual void Write(const void* ptr, size_t size) { buf_.append((const char*)ptr, size); }
-  std::string str() { return buf_; }
+  void Write(const void* src, size_t n) override {
+    const char* p = static_cast<const char*>(src);
+    bytes_.insert(bytes_.end(), p, p + n);
+  }
+  std::string str() const { return std::string(bytes_.begin(), bytes_.end()); }
+
  private:
-  std::string buf_;
-  size_t pos_;
+  std::vector<char> bytes_;
+  size_t cursor_ = 0;
 };
+
 }  // namespace dmlc
