@@ -406,8 +406,19 @@ __device__ __forceinline__ void hot_rank_slot(const HotView& hot, const uint2* _
 // the table keys' ranks as the scan's epilogue (a slice per block), or as a launch of their own after the look-back scan
 struct HotRankEpilogue {
   HotView hot;
-  const uint2* dir;
+  uint2* dir;
   static constexpr bool kPresent = true;
+  // before the scan: table keys that occur in this minibatch enter the directory like any other key
+  __device__ void before() const {
+    const int per = (kHotSlots + (int)gridDim.x - 1) / (int)gridDim.x;
+    const int lo = (int)blockIdx.x * per, hi = min(kHotSlots, lo + per);
+    for (int p = lo + (int)threadIdx.x; p < hi; p += (int)blockDim.x) {
+      if (__ldcg(hot.present + p)) {
+        const unsigned k = reinterpret_cast<const unsigned*>(hot.tags)[p];
+        atomicOr(&dir[k >> 5].x, 1u << (k & 31));
+      }
+    }
+  }
   __device__ void operator()() const {
     const int per = (kHotSlots + (int)gridDim.x - 1) / (int)gridDim.x;
     const int lo = (int)blockIdx.x * per, hi = min(kHotSlots, lo + per);
@@ -419,6 +430,8 @@ __global__ void hot_rank_kernel(HotView hot, const uint2* __restrict__ dir) {
   if (p < kHotSlots) hot_rank_slot(hot, dir, p);
 }
 // directory scan that also leaves hot.rank filled (and hot.present reset)
+// (also enters the present table keys into the directory first: as the cooperative scan's first phase, or as a launch of
+//  its own in front of the look-back scan)
 static int dir_scan_hot(whContext* ctx, uint2* dir, uint64_t* d_uniq, size_t words, unsigned* d_nuniq, const HotView& hot) {
   static int coop = -1;
   if (coop < 0) { const char* e = getenv("WH_SCAN_COOP"); coop = e ? atoi(e) : 1; }
@@ -426,6 +439,7 @@ static int dir_scan_hot(whContext* ctx, uint2* dir, uint64_t* d_uniq, size_t wor
     WH_TRY(ctx->scan_tmp.reserve(div_up(words, kScanThreads * kOnepassItems) * sizeof(unsigned) + 256));
     return scan_coop(ctx, DirPopc{dir}, DirEmit{dir, d_uniq}, words, ctx->scan_tmp.as<unsigned>(), d_nuniq, HotRankEpilogue{hot, dir});
   }
+  WH_LAUNCH(hot_present_kernel, kHotSlots / 256, 256, 0, ctx->stream, hot, dir);
   WH_TRY(dir_scan(ctx, dir, d_uniq, words, d_nuniq));
   WH_LAUNCH(hot_rank_kernel, kHotSlots / 256, 256, 0, ctx->stream, hot, dir);
   return WH_OK;
@@ -476,7 +490,6 @@ int localize_direct_hot(whContext* ctx, const LocInput& in, const HotView& hot, 
   } else {
     WH_LAUNCH(loc_mark_hot_kernel, tgrid, kTmaThreads, mark_smem, ctx->stream, in.index, n, in.xf, dir, hot, d_codes);
   }
-  WH_LAUNCH(hot_present_kernel, kHotSlots / 256, 256, 0, ctx->stream, hot, dir);
   WH_PROF(ctx, "loc_mark");
   WH_TRY(dir_scan_hot(ctx, dir, d_uniq, words, d_nuniq, hot));
   WH_PROF(ctx, "loc_dir_scan");

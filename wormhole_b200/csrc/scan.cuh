@@ -191,12 +191,22 @@ int scan_onepass(whContext* ctx, F f, G g, size_t n, void* state, unsigned* epoc
 // walk far back, one L2 round trip per 32 predecessors (14 us for the 4 MB directory). With every tile resident a grid
 // barrier replaces the chain: tile sums, barrier, each block adds up its predecessors' sums in one strided read,
 // apply -- the elements stay in registers across the barrier.
-// H: an optional epilogue, run by every block after one more grid barrier (i.e. when every g(...) has been applied).
-struct NoEpilogue { __device__ void operator()() const {} static constexpr bool kPresent = false; };
+// H: optional extra phases, each separated from the scan by a grid barrier: h.before() runs in every block before any
+// element is read, h() after every g(...) has been applied.
+struct NoEpilogue {
+  __device__ void before() const {}
+  __device__ void operator()() const {}
+  static constexpr bool kPresent = false;
+};
 template <int ITEMS, typename F, typename G, typename H>
 __global__ void __launch_bounds__(kScanThreads) scan_coop_kernel(F f, G g, H h, size_t n, unsigned* sums, unsigned* total) {
   namespace cg = cooperative_groups;
   cg::grid_group grid = cg::this_grid();
+  if (H::kPresent) {
+    h.before();
+    __threadfence();
+    grid.sync();
+  }
   const unsigned tile = blockIdx.x;
   const size_t base = (size_t)tile * (kScanThreads * ITEMS) + (size_t)threadIdx.x * ITEMS;
   unsigned v[ITEMS], s = 0;
