@@ -92,6 +92,49 @@ struct DirEmit {
     }
   }
 };
+// the same, and Handle::Pull for every key it emits (batch.cuh: PullAtEmit)
+struct DirEmitPull {
+  uint2* dir;
+  uint64_t* uniq;
+  PullAtEmit p;
+  __device__ void operator()(size_t i, unsigned v, unsigned prefix) const {
+    dir[i].y = prefix;
+    if (!v) return;
+    unsigned bits = dir[i].x;
+    const uint64_t base = (uint64_t)i << 5;
+    // first the loads of all keys of the word (independent), then the stores
+    float wv[4];
+    unsigned done = 0;
+    while (bits) {
+      unsigned chunk = 0, bb = bits;
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        if (!bb) break;
+        const uint64_t k = base + (__ffs(bb) - 1);
+        bb &= bb - 1;
+        float w = 0.f;
+        if (k >= p.key_begin && k < p.key_end) {
+          const uint64_t e = k - p.key_begin;
+          if (p.algo == WH_ALGO_FTRL) w = __ldg(reinterpret_cast<const float*>(reinterpret_cast<const float4*>(p.table) + e));
+          else if (p.algo == WH_ALGO_ADAGRAD) w = __ldg(reinterpret_cast<const float*>(reinterpret_cast<const float2*>(p.table) + e));
+          else w = __ldg(reinterpret_cast<const float*>(p.table) + e);
+        } else {
+          atomicAdd(reinterpret_cast<unsigned long long*>(p.counters + 1), 1ull);
+        }
+        wv[u] = w;
+        ++chunk;
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        if (u >= (int)chunk) break;
+        uniq[prefix + done + u] = base + (__ffs(bits) - 1);
+        p.w[prefix + done + u] = wv[u];
+        bits &= bits - 1;
+      }
+      done += chunk;
+    }
+  }
+};
 
 // The directory scan in one launch (scan.cuh: decoupled look-back). The state buffer belongs to the context.
 static int dir_scan(whContext* ctx, uint2* dir, uint64_t* d_uniq, size_t words, unsigned* d_nuniq) {
@@ -432,11 +475,19 @@ __global__ void hot_rank_kernel(HotView hot, const uint2* __restrict__ dir) {
 // directory scan that also leaves hot.rank filled (and hot.present reset)
 // (also enters the present table keys into the directory first: as the cooperative scan's first phase, or as a launch of
 //  its own in front of the look-back scan)
-static int dir_scan_hot(whContext* ctx, uint2* dir, uint64_t* d_uniq, size_t words, unsigned* d_nuniq, const HotView& hot) {
+static int dir_scan_hot(whContext* ctx, uint2* dir, uint64_t* d_uniq, size_t words, unsigned* d_nuniq, const HotView& hot,
+                        const PullAtEmit* pull, bool* pulled) {
   static int coop = -1;
   if (coop < 0) { const char* e = getenv("WH_SCAN_COOP"); coop = e ? atoi(e) : 1; }
+  *pulled = false;
   if (coop && scan_coop_fits(ctx, words)) {
     WH_TRY(ctx->scan_tmp.reserve(div_up(words, kScanThreads * kOnepassItems) * sizeof(unsigned) + 256));
+    if (pull && pull->table) {
+      if (pull->after) WH_CUDA(cudaStreamWaitEvent(ctx->stream, pull->after, 0));
+      *pulled = true;
+      return scan_coop(ctx, DirPopc{dir}, DirEmitPull{dir, d_uniq, *pull}, words, ctx->scan_tmp.as<unsigned>(), d_nuniq,
+                       HotRankEpilogue{hot, dir});
+    }
     return scan_coop(ctx, DirPopc{dir}, DirEmit{dir, d_uniq}, words, ctx->scan_tmp.as<unsigned>(), d_nuniq, HotRankEpilogue{hot, dir});
   }
   WH_LAUNCH(hot_present_kernel, kHotSlots / 256, 256, 0, ctx->stream, hot, dir);
@@ -462,8 +513,15 @@ __global__ void __launch_bounds__(256) loc_rank_cold_kernel(size_t n, const uint
   }
 }
 
+bool pull_at_emit_supported(const whContext* ctx, uint64_t max_key) {
+  static int coop = -1;
+  if (coop < 0) { const char* e = getenv("WH_SCAN_COOP"); coop = e ? atoi(e) : 1; }
+  const char* off = getenv("WH_PULL_AT_EMIT");
+  return coop && !(off && atoi(off) == 0) && direct_supported(max_key) && scan_coop_fits(ctx, div_up(max_key, 32));
+}
+
 int localize_direct_hot(whContext* ctx, const LocInput& in, const HotView& hot, uint64_t* d_uniq, uint32_t* d_codes,
-                        unsigned* d_nuniq, bool resolve) {
+                        unsigned* d_nuniq, bool resolve, const PullAtEmit* pull) {
   const size_t words = div_up(in.xf.max_key, 32);
   if (ctx->directory.cap < words * sizeof(uint2) || ctx->directory_words < words) {
     WH_TRY(ctx->directory.reserve(words * sizeof(uint2)));
@@ -491,7 +549,9 @@ int localize_direct_hot(whContext* ctx, const LocInput& in, const HotView& hot, 
     WH_LAUNCH(loc_mark_hot_kernel, tgrid, kTmaThreads, mark_smem, ctx->stream, in.index, n, in.xf, dir, hot, d_codes);
   }
   WH_PROF(ctx, "loc_mark");
-  WH_TRY(dir_scan_hot(ctx, dir, d_uniq, words, d_nuniq, hot));
+  bool pulled = false;
+  WH_TRY(dir_scan_hot(ctx, dir, d_uniq, words, d_nuniq, hot, pull, &pulled));
+  WH_REQUIRE(!(pull && pull->table) || pulled, "localize_direct_hot: the pull could not ride in the scan (directory too large for the cooperative scan)");
   WH_PROF(ctx, "loc_dir_scan");
   if (resolve) {
     const unsigned rgrid = (unsigned)std::min<size_t>(div_up(n, 256 * 8), (size_t)ctx->num_sms * 8);

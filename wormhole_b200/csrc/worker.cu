@@ -278,9 +278,18 @@ int wh_worker_submit(whWorker* w, const whRowBlock* blk, int mem, size_t nnz, in
   if (served && w->depth > 1 && tk > (unsigned long long)w->depth)
     WH_CUDA(cudaStreamWaitEvent(cx->stream, w->ev_served[(tk - w->depth + 1) % ring], 0));
 
+  // local dense shard: Handle::Pull rides in the scan that emits the unique keys (after the push it has to see)
+  const bool emit_pull = fused && s->map.world == 1 && s->hslots == 0 && pull_at_emit_supported(cx, w->max_key);
+  PullAtEmit pe;
+  if (emit_pull) {
+    pe.table = s->table.p; pe.algo = s->algo; pe.key_begin = s->key_begin; pe.key_end = s->key_end;
+    pe.w = l.w.as<float>(); pe.counters = s->counters.as<long long>();
+    if (tk > 1ull + (unsigned)w->max_delay) pe.after = w->ev_pushed[(tk - 1 - w->max_delay) % ring];
+  }
+
   WH_TRY(prof_begin(cx));
   // Localize
-  if (hot) WH_TRY(localize_direct_hot(cx, in, hv, uniq, l.index.as<uint32_t>(), d_nuniq, !fused));
+  if (hot) WH_TRY(localize_direct_hot(cx, in, hv, uniq, l.index.as<uint32_t>(), d_nuniq, !fused, emit_pull ? &pe : nullptr));
   else if (direct) WH_TRY(localize_direct(cx, in, uniq, nullptr, l.index.as<uint32_t>(), d_nuniq));
   else WH_TRY(localize_sort(cx, in, uniq, nullptr, l.index.as<uint32_t>(), d_nuniq));
   if (outboxed) WH_TRY(outbox_cuts_launch(s, cx->stream, l.outbox.as<unsigned char>()));
@@ -288,7 +297,7 @@ int wh_worker_submit(whWorker* w, const whRowBlock* blk, int mem, size_t nnz, in
   if (served) WH_TRY(server_barrier_launch(s, cx->stream, 1));   // every rank's key list is posted (off the critical cycle)
   // bounded staleness (the reference's max_concurrency > 1 lets a worker pull before its earlier pushes have
   // landed): with max_delay = d the pull of minibatch t waits for the push of minibatch t - 1 - d only
-  if (tk > 1ull + (unsigned)w->max_delay) WH_CUDA(cudaStreamWaitEvent(cx->stream, w->ev_pushed[(tk - 1 - w->max_delay) % ring], 0));
+  if (!emit_pull && tk > 1ull + (unsigned)w->max_delay) WH_CUDA(cudaStreamWaitEvent(cx->stream, w->ev_pushed[(tk - 1 - w->max_delay) % ring], 0));
   const bool sharded = s->map.world > 1;
   float* pulled = l.w.as<float>();
   if (served) {
@@ -305,7 +314,7 @@ int wh_worker_submit(whWorker* w, const whRowBlock* blk, int mem, size_t nnz, in
     // gather straight from the GPUs that own the keys; nobody may start pushing before everyone has pulled
     WH_TRY(server_pull_sharded_launch(s, cx->stream, uniq, ucap, d_nuniq, l.w.as<float>()));
     if (!outboxed || !train) WH_TRY(server_barrier_launch(s, cx->stream));
-  } else {
+  } else if (!emit_pull) {
     WH_TRY(server_pull_launch(s, cx->stream, uniq, ucap, d_nuniq, l.w.as<float>()));
   }
   WH_PROF(cx, "pull");
