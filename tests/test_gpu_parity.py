@@ -403,8 +403,9 @@ def test_hot_key_table_changes_nothing(gpu, monkeypatch):
         blks.append(RowBlock(off, ids, None, (rng.random(rows) < 0.3).astype(np.float32)))
     for algo, loss in [(capi.ALGO_FTRL, capi.LOSS_LOGIT), (capi.ALGO_ADAGRAD, capi.LOSS_SQUARE_HINGE), (capi.ALGO_SGD, capi.LOSS_LOGIT)]:
         res = []
-        for hot in ("1", "0"):
+        for hot, emit in (("1", "0"), ("0", "0"), ("1", "1")):     # last: Handle::Pull folded into the scan's emit
             monkeypatch.setenv("WH_HOT", hot)
+            monkeypatch.setenv("WH_PULL_AT_EMIT", emit)
             srv = capi.Server(gpu, algo, 0.5, 0.1, 0.1, 1.0, 0, 2 ** 22)
             wk = capi.Worker(gpu, srv, loss, 2 ** 22, depth=2)
             pend, out = [], []
@@ -416,10 +417,11 @@ def test_hot_key_table_changes_nothing(gpu, monkeypatch):
             keys = np.unique(np.concatenate([b.index % np.uint64(2 ** 22) for b in blks]))
             res.append((np.array(out), srv.get_state(keys), srv.nnz_w()))
             wk.close(); srv.close()
-        assert np.array_equal(res[0][0], res[1][0])
-        for a, b in zip(res[0][1], res[1][1]):
-            assert np.array_equal(a, b)
-        assert res[0][2] == res[1][2]
+        for other in res[1:]:
+            assert np.array_equal(res[0][0], other[0])
+            for a, b in zip(res[0][1], other[1]):
+                assert np.array_equal(a, b)
+            assert res[0][2] == other[2]
 
 
 def test_bounded_staleness_option(gpu):
