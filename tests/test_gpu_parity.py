@@ -401,20 +401,22 @@ def test_hot_key_table_changes_nothing(gpu, monkeypatch):
         off = np.zeros(rows + 1, np.uint64); off[1:] = np.cumsum(nnz)
         ids = (rng.zipf(1.3, int(off[-1])) % 50000).astype(np.uint64) * np.uint64(2654435761)   # power law, hashed
         blks.append(RowBlock(off, ids, None, (rng.random(rows) < 0.3).astype(np.float32)))
-    for algo, loss in [(capi.ALGO_FTRL, capi.LOSS_LOGIT), (capi.ALGO_ADAGRAD, capi.LOSS_SQUARE_HINGE), (capi.ALGO_SGD, capi.LOSS_LOGIT)]:
+    # (the last case has a directory too large for the cooperative scan: look-back scan + separate table-key launches)
+    for algo, loss, mk in [(capi.ALGO_FTRL, capi.LOSS_LOGIT, 2 ** 22), (capi.ALGO_ADAGRAD, capi.LOSS_SQUARE_HINGE, 2 ** 22),
+                           (capi.ALGO_SGD, capi.LOSS_LOGIT, 2 ** 22), (capi.ALGO_SGD, capi.LOSS_LOGIT, 2 ** 28)]:
         res = []
         for hot, emit in (("1", "0"), ("0", "0"), ("1", "1")):     # last: Handle::Pull folded into the scan's emit
             monkeypatch.setenv("WH_HOT", hot)
             monkeypatch.setenv("WH_PULL_AT_EMIT", emit)
-            srv = capi.Server(gpu, algo, 0.5, 0.1, 0.1, 1.0, 0, 2 ** 22)
-            wk = capi.Worker(gpu, srv, loss, 2 ** 22, depth=2)
+            srv = capi.Server(gpu, algo, 0.5, 0.1, 0.1, 1.0, 0, mk)
+            wk = capi.Worker(gpu, srv, loss, mk, depth=2)
             pend, out = [], []
             for m, b in enumerate(blks):
                 if len(pend) == 2:
                     out.append(wk.wait(pend.pop(0)))
                 pend.append(wk.submit(b, train=(m != 3)))
             out += [wk.wait(t) for t in pend]
-            keys = np.unique(np.concatenate([b.index % np.uint64(2 ** 22) for b in blks]))
+            keys = np.unique(np.concatenate([b.index % np.uint64(mk) for b in blks]))
             res.append((np.array(out), srv.get_state(keys), srv.nnz_w()))
             wk.close(); srv.close()
         for other in res[1:]:
