@@ -405,9 +405,11 @@ def test_hot_key_table_changes_nothing(gpu, monkeypatch):
     for algo, loss, mk in [(capi.ALGO_FTRL, capi.LOSS_LOGIT, 2 ** 22), (capi.ALGO_ADAGRAD, capi.LOSS_SQUARE_HINGE, 2 ** 22),
                            (capi.ALGO_SGD, capi.LOSS_LOGIT, 2 ** 22), (capi.ALGO_SGD, capi.LOSS_LOGIT, 2 ** 28)]:
         res = []
-        for hot, emit in (("1", "0"), ("0", "0"), ("1", "1")):     # last: Handle::Pull folded into the scan's emit
+        # third: Handle::Pull folded into the scan's emit; fourth: the table rebuilt every 3 minibatches
+        for hot, emit, refresh in (("1", "0", "0"), ("0", "0", "0"), ("1", "1", "0"), ("1", "0", "3")):
             monkeypatch.setenv("WH_HOT", hot)
             monkeypatch.setenv("WH_PULL_AT_EMIT", emit)
+            monkeypatch.setenv("WH_HOT_REFRESH", refresh)
             srv = capi.Server(gpu, algo, 0.5, 0.1, 0.1, 1.0, 0, mk)
             wk = capi.Worker(gpu, srv, loss, mk, depth=2)
             pend, out = [], []

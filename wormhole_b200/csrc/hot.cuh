@@ -5,8 +5,9 @@
 // each of mark, rank, forward gather and backward atomic, and it is the number of those accesses (not their bytes)
 // that bounds the step. So the worker keeps a small table of the stream's most frequent keys and serves them from
 // shared memory / L1 instead:
-//   * the table is a 4-way bucketed hash of the transformed keys (2 048 buckets x 4 tags, 32 KB), built once on
-//     the host from a census of the worker's first minibatch and copied into shared memory by the kernels;
+//   * the table is a 4-way bucketed hash of the transformed keys (2 048 buckets x 4 tags, 32 KB), built on the host from a
+//     census of one of the worker's minibatches (the first, then every WH_HOT_REFRESH-th) and copied into shared
+//     memory by the kernels;
 //   * an entry whose key is in the table gets the CODE  kHotFlag | slot  instead of its rank as local index; the
 //     forward product reads its weight from a 32 KB slot-indexed array, the backward product adds it up in a
 //     shared-memory accumulator and flushes the block's sums once (spmv.cu, spmv_fused_hot_kernel);

@@ -16,6 +16,8 @@
 // a side stream of the lane.
 #include <stdlib.h>
 
+#include <algorithm>
+
 #include <vector>
 
 #include "batch.cuh"
@@ -72,9 +74,13 @@ struct whWorker {
   unsigned long long next_ticket = 1, next_wait = 1;
   long long seen_new_w = 0;
   // hot keys (hot.cuh): the table image shared by the lanes; built from a census of the first eligible minibatch
-  wh::DevBuf hot_tags;
+  // ... and rebuilt every hot_refresh eligible minibatches (WH_HOT_REFRESH, default 2048, 0 = never), for streams whose
+  // popular keys drift. Two image buffers alternate: kernels already enqueued keep the pointer they were launched with.
+  wh::DevBuf hot_tags[2];
+  int hot_cur = 0;                       // the buffer new minibatches use
   bool hot_enabled = true, hot_tried = false, hot_ready = false;
   int hot_keys = 0;
+  long long hot_refresh = 2048, hot_since = 0;
 };
 
 using namespace wh;
@@ -120,7 +126,7 @@ static int lane_init(whWorker* w, int i) {
 
 static HotView lane_hot_view(const whWorker* w, Lane& l) {
   HotView v;
-  v.tags = w->hot_tags.as<uint4>();
+  v.tags = w->hot_tags[w->hot_cur].as<uint4>();
   v.present = l.hot.as<unsigned>();
   v.rank = v.present + kHotSlots;
   v.w = reinterpret_cast<float*>(v.rank + kHotSlots);
@@ -146,10 +152,14 @@ static int hot_census(whWorker* w, Lane& l, const LocInput& in, size_t ucap) {
     WH_CUDA(cudaMemcpy(hk.data(), keys.p, (size_t)U * 8, cudaMemcpyDeviceToHost));
     WH_CUDA(cudaMemcpy(hc.data(), cnt.p, (size_t)U * 4, cudaMemcpyDeviceToHost));
   }
-  w->hot_keys = hot_build_image(hk.data(), hc.data(), U, image.data());
-  if (w->hot_keys < 64) return WH_OK;            // nothing repeats enough to be worth a table
-  WH_TRY(w->hot_tags.reserve((size_t)kHotSlots * 4));
-  WH_CUDA(cudaMemcpy(w->hot_tags.p, image.data(), (size_t)kHotSlots * 4, cudaMemcpyHostToDevice));
+  w->hot_since = 0;
+  const int placed = hot_build_image(hk.data(), hc.data(), U, image.data());
+  if (placed < 64) return WH_OK;                 // nothing repeats enough to be worth a (new) table
+  const int next = w->hot_ready ? 1 - w->hot_cur : w->hot_cur;   // a refresh fills the buffer that is not in use
+  WH_TRY(w->hot_tags[next].reserve((size_t)kHotSlots * 4));
+  WH_CUDA(cudaMemcpy(w->hot_tags[next].p, image.data(), (size_t)kHotSlots * 4, cudaMemcpyHostToDevice));
+  w->hot_cur = next;
+  w->hot_keys = placed;
   w->hot_ready = true;
   return WH_OK;
 }
@@ -167,6 +177,7 @@ int wh_worker_create_ex(whContext* ctx, whServer* server, int loss, uint64_t max
   whWorker* w = new whWorker();
   w->ctx = ctx; w->server = server; w->loss = loss; w->max_key = max_key; w->depth = depth;
   { const char* e = getenv("WH_HOT"); w->hot_enabled = !(e && atoi(e) == 0); }   // WH_HOT=0: plain kernels only
+  { const char* e = getenv("WH_HOT_REFRESH"); if (e) w->hot_refresh = atoll(e); }
   int r = w->pinned.reserve(512 * kMaxDepth);
   for (int i = 0; r == WH_OK && i < depth; ++i) r = lane_init(w, i);
   for (int i = 0; r == WH_OK && i <= kMaxDepth; ++i)
@@ -193,7 +204,7 @@ int wh_worker_destroy(whWorker* w) {
   for (auto e : w->ev_pushed) if (e) cudaEventDestroy(e);
   for (auto e : w->ev_served) if (e) cudaEventDestroy(e);
   w->pinned.release();
-  w->hot_tags.release();
+  w->hot_tags[0].release(); w->hot_tags[1].release();
   delete w;
   return WH_OK;
 }
@@ -263,7 +274,9 @@ int wh_worker_submit(whWorker* w, const whRowBlock* blk, int mem, size_t nnz, in
   LocInput in{d_index, n, make_xform(w->max_key)};
   // hot keys (hot.cuh): binary features in a direct-addressed key space
   const bool hot_ok = w->hot_enabled && direct && d_value == nullptr;
-  if (hot_ok && !w->hot_tried) WH_TRY(hot_census(w, l, in, ucap));
+  // (a refresh overwrites the image that was current two refreshes ago: the interval must exceed the minibatches in flight)
+  const long long refresh = w->hot_refresh > 0 ? std::max<long long>(w->hot_refresh, w->depth + 1) : 0;
+  if (hot_ok && (!w->hot_tried || (refresh > 0 && ++w->hot_since >= refresh))) WH_TRY(hot_census(w, l, in, ucap));
   const bool hot = hot_ok && w->hot_ready;
   const bool fused = hot && train;    // forward + backward in one launch, which is also the rank pass of the localizer
   const HotView hv = lane_hot_view(w, l);
