@@ -280,6 +280,9 @@ int wh_worker_submit(whWorker* w, const whRowBlock* blk, int mem, size_t nnz, in
   const bool hot = hot_ok && w->hot_ready;
   const bool fused = hot && train;    // forward + backward in one launch, which is also the rank pass of the localizer
   const HotView hv = lane_hot_view(w, l);
+  // Accumulator replicas exist to spread the atomics on popular keys; the fused kernel adds those up in shared memory,
+  // so one replica is enough there (measured: push 20.6 -> 16 us, step 121 -> 112 us with three minibatches in flight)
+  const unsigned copies = fused ? 1u : acc_copies();
 
   const unsigned long long tk = w->next_ticket;       // this minibatch's ticket (1, 2, ...)
   const int ring = kMaxDepth + 1;
@@ -338,7 +341,7 @@ int wh_worker_submit(whWorker* w, const whRowBlock* blk, int mem, size_t nnz, in
   if (fused) {
     // ... and with the hot-key table the transposed product rides in the same launch (spmv.cu)
     WH_TRY(spmv_fused_hot_launch(cx, w->loss, rows, n, d_offset, l.index.as<uint32_t>(), d_label, pulled, hv,
-                                 l.xw.as<float>(), nullptr, d_eval, fs, acc, acc_copies(), ucap,
+                                 l.xw.as<float>(), nullptr, d_eval, fs, acc, copies, ucap,
                                  cx->directory.p, &l.ax));
     WH_PROF(cx, "spmv_fused");
   } else {
@@ -357,7 +360,7 @@ int wh_worker_submit(whWorker* w, const whRowBlock* blk, int mem, size_t nnz, in
   if (train) {
     // CalcGrad: X^T dual into the fixed-point accumulator; ZPush: convert + update in one pass
     if (!fused) {
-      WH_TRY(spmv_trans_accumulate_launch(cx, rows, n, d_offset, l.index.as<uint32_t>(), d_value, l.dual.as<float>(), acc, fs, acc_copies(), ucap, scale_ready));
+      WH_TRY(spmv_trans_accumulate_launch(cx, rows, n, d_offset, l.index.as<uint32_t>(), d_value, l.dual.as<float>(), acc, fs, copies, ucap, scale_ready));
       WH_PROF(cx, "spmv_trans");
     }
     const float mul = w->loss == WH_LOSS_SQUARE_HINGE ? -2.f : 1.f;
@@ -368,7 +371,7 @@ int wh_worker_submit(whWorker* w, const whRowBlock* blk, int mem, size_t nnz, in
       // (barrier), each owner walks the source ranks in ascending order -- one push message each -- reading its
       // slice straight from the source GPU; a second barrier keeps outboxes and tables stable until all are done
       float* ob_grads = reinterpret_cast<float*>(l.outbox.as<unsigned char>() + 256 + w->outbox_cap * 8);
-      WH_TRY(fixed_finish_launch(cx, acc, ucap, fs, ob_grads, mul, acc_copies(), ucap, d_nuniq));
+      WH_TRY(fixed_finish_launch(cx, acc, ucap, fs, ob_grads, mul, copies, ucap, d_nuniq));
       const int lane_idx = (int)(&l - w->lane);
       static int apply_all = -1;   // WH_APPLY_ALL=0: one launch per source (the older path)
       if (apply_all < 0) { const char* e = getenv("WH_APPLY_ALL"); apply_all = e ? atoi(e) : 1; }
@@ -390,12 +393,12 @@ int wh_worker_submit(whWorker* w, const whRowBlock* blk, int mem, size_t nnz, in
       s->steps++;
     } else if (sharded) {
       for (int turn = 0; turn < s->map.world; ++turn) {   // turn k: this rank is the only writer of shard (rank+k)%world
-        WH_TRY(server_push_turn_launch(s, cx->stream, turn, uniq, ucap, d_nuniq, acc, fs, mul, acc_copies(), ucap));
+        WH_TRY(server_push_turn_launch(s, cx->stream, turn, uniq, ucap, d_nuniq, acc, fs, mul, copies, ucap));
         WH_TRY(server_barrier_launch(s, cx->stream));
       }
       s->steps++;
     } else {
-      WH_TRY(server_push_acc_launch(s, cx->stream, uniq, ucap, d_nuniq, acc, fs, mul, acc_copies(), ucap));
+      WH_TRY(server_push_acc_launch(s, cx->stream, uniq, ucap, d_nuniq, acc, fs, mul, copies, ucap));
     }
     WH_PROF(cx, "push");
   }
