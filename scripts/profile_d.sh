@@ -7,6 +7,6 @@ python bench.py $ARGS > gpurun_out/d_plain.log 2>&1
 ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum --clock-control none -c 400 --csv \
     --log-file gpurun_out/d_launches.csv python bench.py $ARGS > gpurun_out/d_ncu1.log 2>&1
 ncu --set full --clock-control none --import-source on \
-    -k regex:"loc_mark_hot|hot_present|scan_coop|server_pull|spmv_fused|loss_reduce|server_push|auc_cluster" \
-    --launch-skip 40 -c 8 -o gpurun_out/d_full -f python bench.py $ARGS > gpurun_out/d_ncu2.log 2>&1
+    -k regex:"loc_mark_hot|scan_coop|server_pull|spmv_fused|loss_reduce|server_push|auc_cluster" \
+    --launch-skip 35 -c 7 -o gpurun_out/d_full -f python bench.py $ARGS > gpurun_out/d_ncu2.log 2>&1
 tail -2 gpurun_out/d_ncu2.log
