@@ -239,7 +239,8 @@ WH_API int wh_worker_destroy(whWorker* w);
  * stay valid and unchanged until the matching wait. wait blocks until that minibatch is done and
  * fills prog[6]. Tickets are collected in submission order. Every pull sees all earlier pushes, so
  * the numbers equal strictly sequential processing; staging, localize and AUC of neighbouring
- * minibatches overlap. */
+ * minibatches overlap. (Binary features in a hashed key space take the worker's hot-key path -- a cache of the
+ * stream's most frequent keys, rebuilt from time to time; it changes the speed, never the numbers.) */
 /* Bounded staleness. 0 (default): every pull sees all earlier pushes -- the numbers of sequential processing,
  * the configuration parity is judged in ("max_delay = 0"). d > 0: the pull of minibatch t only waits for the push
  * of minibatch t-1-d, as in the reference when max_concurrency minibatches are in flight and a pull overtakes the
@@ -258,9 +259,11 @@ WH_API int wh_worker_wait(whWorker* w, uint64_t ticket, double* prog);
  * (new_w) is 0: the servers own that count (wh_server_nnz_w). */
 /* Sharded jobs, owner-side push. After wh_server_ipc_attach, a worker can publish one outbox per lane ({key
  * list, gradients, inbox of pulled weights}; capacity max_uniq keys, 64 bytes of handle per lane written to `handles`) and map its peers'
- * (`handles` = all ranks' exports in rank order, world x depth x 64 bytes; same depth everywhere). A push then
- * needs two barriers instead of `world`: every owner reads, per source rank in ascending order, the slice of that
- * rank's outbox that falls into its key range and applies it as one push message. */
+ * (`handles` = all ranks' exports in rank order, world x depth x 64 bytes; same depth everywhere). Pull and push are
+ * then served by the OWNERS: once every rank has posted its key list, each owner writes the weights of the slices it
+ * owns into the requesters' inboxes; once every rank has posted its gradients, each owner applies, per source rank in
+ * ascending order, the slice of that rank's outbox that falls into its key range as one push message. Every rank must
+ * submit the same sequence of minibatches (train / evaluate alike): the barriers in between are collective. */
 WH_API int wh_worker_ipc_export(whWorker* w, size_t max_uniq, void* handles);
 WH_API int wh_worker_ipc_attach(whWorker* w, const void* handles);
 /* The PRED workload (learn/linear/async_sgd.h:263-265 -> ScalarLoss::Predict, learn/linear/loss.h:55-63): Localize,
