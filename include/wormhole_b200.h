@@ -279,13 +279,15 @@ WH_API int wh_worker_process_minibatch(whWorker* w, const whRowBlock* blk, int m
                                        double* prog);
 
 /* ---- (4b) the reader in front of the path ------------------------------- */
-/* Text formats of MinibatchIter (learn/base/minibatch_iter.h:44-59). "crb" (lz4 + recordio) and "adfea" are not built. */
-enum { WH_FMT_LIBSVM = 0, WH_FMT_CRITEO = 1, WH_FMT_CRITEO_TEST = 2 };
+/* Text formats of MinibatchIter (learn/base/minibatch_iter.h:44-59). "crb" (lz4 + recordio) is not built. */
+enum { WH_FMT_LIBSVM = 0, WH_FMT_CRITEO = 1, WH_FMT_CRITEO_TEST = 2, WH_FMT_ADFEA = 3 };
 typedef struct whRows whRows; /* a device-resident dmlc::data::RowBlockContainer<uint64_t> */
 /* ParseNext of one chunk of text (whole lines; host or device memory, < 4 GiB) on the GPU:
  *   criteo / criteo_test  CriteoParser::ParseNext, learn/base/criteo_parser.h:38-89: label, 13 integer fields and 26
  *                         8-byte categorical fields, tab separated; index = CityHash64(field) >> 10 | field_no << 54.
  *   libsvm                dmlc-core's LibSVMParser (un-vendored): `label index[:value] ...`, numbers as atof / strtoull.
+ *   adfea                 AdfeaParser::ParseNext, learn/base/adfea_parser.h:38-82, one row per line: `lineid count label
+ *                         idx:gid ...`; index = idx >> 10 | gid << 54, label = (first character of the label token == '1').
  * Where the reference would read past the end of a line or CHECK-fail (short lines, categorical fields that are not
  * 8 bytes) the call fails with WH_ERR_INVALID and names the line; numeric literals that cannot be converted exactly
  * with one double operation (> 15 digits or |exponent| > 22) are refused rather than rounded differently.

@@ -47,6 +47,15 @@ class PortIO:
             raise ValueError(rc, rows.value)
         return RowBlock(off[:rows.value + 1], idx[:nnz.value], None, lab[:rows.value])
 
+    def parse_adfea(self, text):
+        t = len(text.split()) + 1
+        off, lab, idx = np.zeros(t + 1, np.uint64), np.zeros(t, np.float32), np.zeros(t, np.uint64)
+        rows, nnz = C.c_size_t(0), C.c_size_t(0)
+        rc = self.L.wh_o_parse_adfea(text, C.c_size_t(len(text)), C.byref(rows), C.byref(nnz), O._p(off), O._p(lab), O._p(idx))
+        if rc:
+            raise ValueError(rc, rows.value)
+        return RowBlock(off[:rows.value + 1], idx[:nnz.value], None, lab[:rows.value])
+
     def parse_libsvm(self, text):
         m = self._lines(text)
         t = len(text.split()) + 1

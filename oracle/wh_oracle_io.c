@@ -162,3 +162,49 @@ WH_O_API int wh_o_parse_libsvm(const char* text, size_t len, size_t* rows, size_
   *nvalue = nv;
   return (nv == 0 || nv == n) ? 0 : 8;
 }
+
+/* learn/base/adfea_parser.h:38-82: a token stream; "idx:gid" tokens are features (index = idx >> 10 | gid << 54 for
+ * 64-bit indices), every third other token opens a row whose label is (first character == '1'). Outputs sized by the
+ * caller: offset[tokens+1], label[tokens], index[tokens]. Returns 0, or 10 where the reference's CHECK_NE(head, p)
+ * fails (a token that does not start with a digit). */
+static int is_sp(char c) { return c == ' ' || c == '\t' || c == '\n' || c == '\v' || c == '\f' || c == '\r'; }
+WH_O_API int wh_o_parse_adfea(const char* text, size_t len, size_t* rows, size_t* nnz, uint64_t* offset, float* label,
+                              uint64_t* index) {
+  const char *p = text, *end = text + len;
+  size_t r = 0, n = 0;
+  int i = 0;
+  offset[0] = 0;
+  while (p != end && is_sp(*p)) ++p;                                   /* :48 */
+  while (p != end) {
+    const char* head = p;
+    while (p != end && *p >= '0' && *p <= '9') ++p;
+    if (head == p) return 10;                                          /* :53 CHECK_NE */
+    if (p != end && *p == ':') {                                       /* :55-65 */
+      char buf[32];
+      size_t m = (size_t)(p - head) < 31 ? (size_t)(p - head) : 31;
+      uint64_t idx, gid;
+      const char* g;
+      memcpy(buf, head, m); buf[m] = 0;
+      idx = strtoull(buf, NULL, 10);
+      g = ++p;
+      while (p != end && *p >= '0' && *p <= '9') ++p;
+      m = (size_t)(p - g) < 31 ? (size_t)(p - g) : 31;
+      memcpy(buf, g, m); buf[m] = 0;
+      gid = strtoull(buf, NULL, 10);
+      index[n++] = (idx >> 10) | (gid << 54);
+    } else {                                                           /* :67-77 */
+      if (i == 2) {
+        i = 0;
+        if (r != 0) offset[r] = n;
+        label[r++] = *head == '1' ? 1.f : 0.f;
+      } else {
+        ++i;
+      }
+    }
+    while (p != end && is_sp(*p)) ++p;
+  }
+  if (r != 0) offset[r] = n;                                           /* :79-81 */
+  *rows = r;
+  *nnz = n;
+  return 0;
+}

@@ -9,7 +9,7 @@ import pytest
 
 from oracle import oracle as O
 from oracle.oracle_io import PortIO, RefIter, minibatches
-from tests.util import agaricus_text, criteo_text, libsvm_text
+from tests.util import adfea_text, agaricus_text, criteo_text, libsvm_text
 from wormhole_b200 import capi
 from wormhole_b200.reader import MinibatchIter, part_range
 
@@ -72,6 +72,21 @@ def test_empty_and_blank_text(gpu):
 def test_libsvm_parse_bit_exact(gpu, mode):
     text = libsvm_text(np.random.default_rng(22), 4000, with_value=mode, key_space=2 ** 63)
     same(capi.parse_text(gpu, "libsvm", text).to_host(), PortIO().parse_libsvm(text))
+
+
+def test_adfea_parse_bit_exact(gpu, tmp_path):
+    text = adfea_text(np.random.default_rng(26), 4000)
+    same(capi.parse_text(gpu, "adfea", text).to_host(), PortIO().parse_adfea(text))
+    for bad, msg in ((b"7 2 1 5:3 9:1\n8 1 x 4:2\n", "line 2"), (b"7 2 1 5:3\n8 1\n", "fewer than three"), (b"7 2 1 5:3 9\n", "out of order")):
+        with pytest.raises(capi.WormholeError, match=msg):
+            capi.parse_text(gpu, "adfea", bad)
+    f = tmp_path / "a.adfea"
+    f.write_bytes(text)
+    got = [b.to_host() for b in MinibatchIter(gpu, str(f), 0, 1, "adfea", 700, chunk_bytes=40000)]
+    want = list(minibatches([PortIO().parse_adfea(text)], 700))
+    assert len(got) == len(want) == 6
+    for a, b in zip(got, want):
+        same(a, b)
 
 
 def test_agaricus_text(gpu):

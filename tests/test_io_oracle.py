@@ -8,7 +8,7 @@ import numpy as np
 import pytest
 
 from oracle.oracle_io import PortIO, RefIter, minibatches
-from tests.util import agaricus_text, criteo_text, libsvm_text
+from tests.util import adfea_text, agaricus_text, criteo_text, libsvm_text
 
 libc = ctypes.CDLL("libc.so.6")
 needs_ref = pytest.mark.skipif(not RefIter.available(), reason="oracle/_ref/libwh_ref_io.so not built")
@@ -116,3 +116,20 @@ def test_parts_cover_the_file_once(tmp_path):
             rows += b.rows
             idx.append(b.index)
     assert rows == whole.rows and np.array_equal(np.concatenate(idx), whole.index)
+
+
+@needs_ref
+def test_adfea_port_vs_reference_reader(tmp_path, monkeypatch):
+    text = adfea_text(np.random.default_rng(9), 2000)
+    f = tmp_path / "a.adfea"
+    f.write_bytes(text)
+    port = PortIO().parse_adfea(text)
+    assert port.rows == 2000 and port.value is None
+    monkeypatch.setenv("WH_ORACLE_CHUNK", "30000")
+    got = list(RefIter(str(f), "adfea", 600))
+    want = list(minibatches([port], 600))
+    assert [b.rows for b in got] == [600, 600, 600, 200]
+    for a, b in zip(got, want):
+        same(a, b)
+    with pytest.raises(ValueError):
+        PortIO().parse_adfea(b"1 2 x 5:3\n")

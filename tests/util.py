@@ -81,3 +81,17 @@ def agaricus_text():
     for r in range(len(lab)):
         lines.append(" ".join([str(int(lab[r]))] + ["%d:1" % int(i) for i in idx[off[r]:off[r + 1]]]))
     return ("\n".join(lines) + "\n").encode()
+
+
+def adfea_text(rng, rows):
+    """Synthetic text in the adfea layout (learn/base/adfea_parser.h): `lineid count label idx:gid ...`, one row per
+    line, some blank lines and rows without features."""
+    out = []
+    for r in range(rows):
+        n = int(rng.integers(0, 15))
+        toks = [str(r + 1), str(n), str(int(rng.integers(0, 2)))]
+        toks += ["%d:%d" % (int(rng.integers(0, 2 ** 62)), int(rng.integers(0, 1000))) for _ in range(n)]
+        out.append((" " if rng.random() < .8 else "\t").join(toks))
+        if rng.random() < 0.03:
+            out.append("")
+    return ("\n".join(out) + "\n").encode()

@@ -422,7 +422,7 @@ class Worker:
             self.h = None
 
 
-FMT = {"libsvm": 0, "criteo": 1, "criteo_test": 2}
+FMT = {"libsvm": 0, "criteo": 1, "criteo_test": 2, "adfea": 3}
 
 
 class Rows:

@@ -291,6 +291,65 @@ struct LibsvmEmit {
   }
 };
 
+// ---- adfea (learn/base/adfea_parser.h:38-82), one thread per line ------------------------------------------
+// The reference walks a token stream: a token "idx:gid" is a feature, index = idx >> 10 | gid << 54; every third
+// token without a colon opens a row, its first character == '1' being the label (the two before it are the line id
+// and a count). With one row per line that is: three plain tokens, then features. Lines of any other shape, and
+// tokens that do not start with a digit (CHECK_NE(head, p)), fail the call.
+__device__ __forceinline__ bool is_space_adfea(char c) { return c == ' ' || c == '\t' || c == '\v' || c == '\f'; }
+struct AdfeaCount {
+  const char* text;
+  size_t len;
+  const uint32_t* starts;
+  __device__ unsigned long long operator()(size_t r) const {
+    const char *p = text + starts[r], *end = text + len;
+    const char* lend = line_end(p, end);
+    unsigned tok = 0;
+    bool in = false;
+    for (; p != lend; ++p) { const bool b = is_space_adfea(*p); if (!b && !in) ++tok; in = !b; }
+    if (tok == 0) return 0ULL;                          // blank line
+    return (1ULL << 32) | (tok > 3 ? tok - 3 : 0u);
+  }
+};
+struct AdfeaEmit {
+  const char* text;
+  size_t len;
+  const uint32_t* starts;
+  float* label;
+  size_t* offset;
+  uint64_t* index;
+  unsigned long long* err;
+  __device__ void operator()(size_t line, unsigned long long v, unsigned long long prefix) const {
+    if (!v) return;
+    const size_t r = (size_t)(prefix >> 32);
+    size_t o = (size_t)(prefix & 0xffffffffULL);
+    offset[r + 1] = o + (size_t)(v & 0xffffffffULL);
+    const char *p = text + starts[line], *end = text + len;
+    const char* lend = line_end(p, end);
+    unsigned t = 0;
+    bool bad = false;
+    label[r] = 0.f;
+    for (;;) {
+      while (p != lend && is_space_adfea(*p)) ++p;
+      if (p == lend) break;
+      const char* head = p;
+      while (p != lend && is_digit(*p)) ++p;
+      if (p == head) { bad = true; break; }                                   // CHECK_NE(head, p)
+      if (p != lend && *p == ':') {
+        const char* g = ++p;
+        while (p != lend && is_digit(*p)) ++p;
+        if (t < 3 || (p != lend && !is_space_adfea(*p))) { bad = true; break; }
+        index[o++] = (parse_u64(head, g - 1) >> 10) | (parse_u64(g, p) << 54);  // :52-56
+      } else {
+        if (t >= 3 || (p != lend && !is_space_adfea(*p))) { bad = true; break; }
+        if (t == 2) label[r] = *head == '1' ? 1.f : 0.f;                        // :65
+      }
+      ++t;
+    }
+    if (bad || t < 3) report(err, t < 3 && !bad ? 11 : 10, line);
+  }
+};
+
 // ---- container kernels -------------------------------------------------------------------------------------
 __global__ void rebase_offsets_kernel(const size_t* src, size_t n, size_t src_base, size_t dst_base, size_t* dst) {
   const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -369,6 +428,8 @@ const char* parse_error_text(int code) {
     case 7: return "bytes after the 26th categorical field";
     case 8: return "some features carry a value and some do not";
     case 9: return "numeric literal outside the exactly convertible range (or inf / nan / hex)";
+    case 10: return "adfea: a token is neither digits nor digits:digits, or features and plain tokens are out of order";
+    case 11: return "adfea: fewer than three leading tokens (line id, count, label)";
   }
   return "malformed input";
 }
@@ -436,8 +497,8 @@ int wh_rows_copy(whContext* ctx, const whRows* r, size_t* offset, float* label, 
 
 int wh_parse_text(whContext* ctx, int format, const char* text, size_t len, int mem, whRows** out) {
   WH_REQUIRE(ctx && out && (text || len == 0), "wh_parse_text: null argument");
-  WH_REQUIRE(format == WH_FMT_LIBSVM || format == WH_FMT_CRITEO || format == WH_FMT_CRITEO_TEST,
-             "wh_parse_text: unknown format %d (crb and adfea are not built)", format);
+  WH_REQUIRE(format == WH_FMT_LIBSVM || format == WH_FMT_CRITEO || format == WH_FMT_CRITEO_TEST || format == WH_FMT_ADFEA,
+             "wh_parse_text: unknown format %d (crb is not built)", format);
   WH_REQUIRE(mem == WH_HOST || mem == WH_DEVICE, "wh_parse_text: bad mem %d", mem);
   WH_REQUIRE(len < (1ULL << 32), "wh_parse_text: a chunk is at most 4 GiB - 1 bytes (got %zu)", len);
   DeviceGuard g(ctx->device);
@@ -476,7 +537,27 @@ int wh_parse_text(whContext* ctx, int format, const char* text, size_t len, int 
             EmitLineStart{starts}, len, sums);
 
   unsigned long long* hp = ctx->pinned.as<unsigned long long>();
-  if (format == WH_FMT_LIBSVM) {
+  if (format == WH_FMT_ADFEA) {
+    // as libsvm below, with the adfea functors and no values
+    const unsigned nbl = (unsigned)div_up(lines, kScanTile);
+    WH_TRY(ctx->stage[2].reserve((size_t)nbl * sizeof(unsigned long long)));
+    unsigned long long* sums2 = ctx->stage[2].as<unsigned long long>();
+    AdfeaCount cf{d_text, len, starts};
+    WH_LAUNCH((scan_tile_sums_kernel<unsigned long long, AdfeaCount>), nbl, kScanThreads, 0, st, cf, lines, sums2);
+    WH_LAUNCH((scan_sums_kernel<unsigned long long>), 1, 1024, 0, st, sums2, (size_t)nbl, d_u64 + 1);
+    WH_CUDA(cudaMemcpyAsync(hp, d_u64 + 1, 8, cudaMemcpyDeviceToHost, st));
+    WH_CUDA(cudaStreamSynchronize(st));
+    const size_t rows = (size_t)(hp[0] >> 32), nnz = (size_t)(hp[0] & 0xffffffffULL);
+    WH_TRY(rows_reserve(r, rows, nnz, false, false));
+    WH_CUDA(cudaMemsetAsync(r->offset.p, 0, sizeof(size_t), st));
+    AdfeaEmit em{d_text, len, starts, r->label.as<float>(), r->offset.as<size_t>(), r->index.as<uint64_t>(), d_u64 + 3};
+    WH_LAUNCH((scan_apply_kernel<unsigned long long, AdfeaCount, AdfeaEmit>), nbl, kScanThreads, 0, st, cf, em, lines, sums2);
+    WH_CUDA(cudaMemcpyAsync(hp + 1, d_u64 + 3, 8, cudaMemcpyDeviceToHost, st));
+    WH_CUDA(cudaStreamSynchronize(st));
+    r->rows = rows;
+    r->nnz = nnz;
+    r->has_value = false;
+  } else if (format == WH_FMT_LIBSVM) {
     // 2. tokens per line -> row number and offset of every line; 3. parse into place
     const unsigned nbl = (unsigned)div_up(lines, kScanTile);
     WH_TRY(ctx->stage[2].reserve((size_t)nbl * sizeof(unsigned long long)));

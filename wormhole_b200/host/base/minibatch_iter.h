@@ -8,7 +8,7 @@
 //   DeviceValue()  the same minibatch as DEVICE pointers + its entry count, for
 //                  AsgdWorker::ProcessMinibatch(const DeviceMinibatch&) / wh_worker_submit(..., WH_DEVICE, ...)
 //
-// Formats: libsvm, criteo, criteo_test (crb needs lz4 + recordio and adfea is not built: LOG(FATAL) equivalent).
+// Formats: libsvm, criteo, criteo_test, adfea (crb needs lz4 + recordio: LOG(FATAL) equivalent).
 #pragma once
 #include <algorithm>
 #include <cstdio>
@@ -93,7 +93,8 @@ class MinibatchIter {
     if (!strcmp(type, "libsvm")) fmt_ = WH_FMT_LIBSVM;
     else if (!strcmp(type, "criteo")) fmt_ = WH_FMT_CRITEO;
     else if (!strcmp(type, "criteo_test")) fmt_ = WH_FMT_CRITEO_TEST;
-    else { fprintf(stderr, "[FATAL] unknown datatype %s (libsvm, criteo, criteo_test are built)\n", type); abort(); }
+    else if (!strcmp(type, "adfea")) fmt_ = WH_FMT_ADFEA;
+    else { fprintf(stderr, "[FATAL] unknown datatype %s (libsvm, criteo, criteo_test, adfea are built)\n", type); abort(); }
     if (shuf_buf) {
       if (!(shuf_buf > minibatch_size)) { fprintf(stderr, "[FATAL] Check failed: shuf_buf > minibatch_size\n"); abort(); }
       buf_reader_ = new MinibatchIter(uri, part_index, num_parts, type, shuf_buf, 0, 1.0f, chunk_bytes, 2);

@@ -119,7 +119,7 @@ class MinibatchIter:
         self.ctx, self.mb_size, self.shuf_buf, self.neg = ctx, int(minibatch_size), int(shuf_buf), negative_sampling
         self.rand = rand
         if type not in capi.FMT:
-            raise capi.WormholeError("unknown datatype %s (libsvm, criteo, criteo_test are built)" % type)  # :58
+            raise capi.WormholeError("unknown datatype %s (libsvm, criteo, criteo_test, adfea are built)" % type)  # :58
         if shuf_buf:
             if not shuf_buf > minibatch_size:                                                      # :37
                 raise capi.WormholeError("shuf_buf must exceed minibatch_size")
