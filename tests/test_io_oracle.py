@@ -133,3 +133,27 @@ def test_adfea_port_vs_reference_reader(tmp_path, monkeypatch):
         same(a, b)
     with pytest.raises(ValueError):
         PortIO().parse_adfea(b"1 2 x 5:3\n")
+
+
+@needs_ref
+@pytest.mark.parametrize("crlf", [False, True])
+def test_part_ranges_of_the_gpu_reader_equal_the_reference_split(tmp_path, crlf):
+    """wormhole_b200.reader.part_range (host logic of the GPU reader: which bytes part k of n owns) against the rows the
+    reference's MinibatchIter reads for the same part: every part holds exactly the same rows."""
+    from wormhole_b200.reader import part_range
+    text = criteo_text(np.random.default_rng(10), 700, crlf=crlf, short_lines=False)
+    f = tmp_path / "c.txt"
+    f.write_bytes(text)
+    covered = 0
+    for nparts in (1, 3, 7):
+        for k in range(nparts):
+            b, e = part_range(str(f), k, nparts)
+            mine = PortIO().parse_criteo(text[b:e]) if e > b else None
+            ref = list(RefIter(str(f), "criteo", 10 ** 6, part=k, nparts=nparts))
+            if mine is None or mine.rows == 0:
+                assert not ref
+            else:
+                assert len(ref) == 1
+                same(ref[0], mine)
+            covered += (e - b) if nparts == 7 else 0
+    assert covered == len(text)
