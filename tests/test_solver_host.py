@@ -74,3 +74,39 @@ def test_cpp_progress_rows_equal_the_reference(tmp_path):
     n = len(G["linear"]["rows"])
     assert out[2:2 + n] == G["linear"]["rows"]
     assert out[2 + n:2 + n + len(G["difacto"]["rows"])] == G["difacto"]["rows"]
+
+
+def test_cpp_text_split_tiles_the_file_at_line_starts(tmp_path):
+    """TextSplit of the C++ reader (host/base/minibatch_iter.h): the chunks of all parts, in order, are the file, and
+    every chunk starts at a line start and ends with a line break -- the same tiling as reader.part_range."""
+    import subprocess
+    import numpy as np
+    from tests.util import criteo_text
+    from wormhole_b200.reader import part_range
+    from wormhole_b200 import build
+    build.build()
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe = str(tmp_path / "textsplit_test")
+    r = subprocess.run(["/usr/bin/g++", "-std=c++14", "-I" + os.path.join(root, "include"),
+                        "-I" + os.path.join(root, "wormhole_b200", "host"), os.path.join(root, "tests", "cpp", "textsplit_test.cc"),
+                        "-o", exe, "-L" + os.path.join(root, "wormhole_b200"), "-lwormhole_b200",
+                        "-Wl,-rpath," + os.path.join(root, "wormhole_b200"), "-L/usr/local/cuda/lib64", "-lcudart"],
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    text = criteo_text(np.random.default_rng(12), 400, crlf=True)
+    f = tmp_path / "c.txt"
+    f.write_bytes(text)
+    for nparts in (1, 4):
+        out = subprocess.run([exe, str(f), str(nparts), "5000"], capture_output=True, text=True).stdout.splitlines()
+        pos = 0
+        for line in out:
+            t = line.split()
+            if t[1] == "read":
+                b, e = part_range(str(f), int(t[0]), nparts)
+                assert int(t[2]) == e - b and pos == e
+                continue
+            size, first, last = int(t[1]), int(t[2]), int(t[3])
+            assert text[pos] == first and text[pos + size - 1] == last and last in (10, 13)
+            assert pos == 0 or text[pos - 1] in (10, 13)                 # a chunk starts at a line start
+            pos += size
+        assert pos == len(text)
