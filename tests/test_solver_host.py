@@ -110,3 +110,17 @@ def test_cpp_text_split_tiles_the_file_at_line_starts(tmp_path):
             assert pos == 0 or text[pos - 1] in (10, 13)                 # a chunk starts at a line start
             pos += size
         assert pos == len(text)
+
+
+def test_cpp_config_parses_demo_conf_and_overrides(tmp_path):
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe = str(tmp_path / "config_test")
+    r = subprocess.run(["/usr/bin/g++", "-std=c++14", "-I" + os.path.join(root, "wormhole_b200", "host"),
+                        os.path.join(root, "tests", "cpp", "config_test.cc"), "-o", exe], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    out = subprocess.run([exe], capture_output=True, text=True).stdout.splitlines()
+    assert out == ["parse 1", "train learn/data/agaricus.txt.train",
+                   "pass 3 minibatch 1000 shuffle 10 conc 2 algo 3 loss 2",      # defaults of config.proto
+                   "has_eta 0 eta 0.01", "override 1", "has_eta 1 eta 0.1 algo 2 minibatch 500",
+                   "unknown 0", "badenum 0"]
