@@ -140,6 +140,9 @@ WH_API int wh_spmv_trans_times(whContext* ctx, const whLocalBlock* D, int mem, c
  *     because reading it back would need a synchronising copy.
  *   - ysize must not exceed WH_STATIC_SCRATCH_MAX_OUTPUTS; larger requests fail with
  *     WH_ERR_INVALID and a message naming the limit.
+ *   - every D->index[j] must be < ysize (true of any block localized against ysize keys). The call
+ *     cannot check this without reading the indices back; an index beyond ysize would add into the
+ *     library's static array past the cleared range, or past the array itself.
  *   - the first call on each device looks up the array's device address; make that first call
  *     before any stream capture begins.
  *   - the array is shared by every call on that GPU and keeps the last call's contents (each call

@@ -9,7 +9,7 @@ import subprocess
 import numpy as np
 import pytest
 
-from tests.util import random_block
+from tests.util import FLIP_ABS, STRAGGLERS, assert_state_close, random_block
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 MAX_KEY = 2 ** 20
@@ -97,7 +97,7 @@ def test_facade_matches_the_checker(tmp_path, checker):
     assert np.array_equal(progs[:, 1], pcs[:, 1]) and np.array_equal(progs[:, 4], pcs[:, 4])
     assert np.all(np.abs(progs[:, 0] - pcs[:, 0]) <= 1e-4 * np.abs(pcs[:, 0]))
     for a, b in ((w, cw), (z, cz), (cg, ccg)):
-        assert np.all(np.abs(a - b) <= 1e-5 * np.maximum(np.abs(b), 1.0))
+        assert_state_close(a, b, what="facade", stragglers=STRAGGLERS, flip_abs=FLIP_ABS)
     assert abs(int(nnz[0]) - int((cw != 0).sum())) <= 2 and progs[:, 5].sum() == nnz[0]
 
 

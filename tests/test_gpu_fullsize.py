@@ -7,6 +7,7 @@ import ctypes
 import numpy as np
 import pytest
 
+from tests.util import FLIP_ABS, STRAGGLERS, assert_state_close
 from wormhole_b200 import capi, synth
 
 pytestmark = pytest.mark.gpu
@@ -25,9 +26,8 @@ def criteo():
 
 
 def state_close(got, want, rtol=1e-5):
-    for a, b in zip(got, want):
-        err = np.abs(a.astype(np.float64) - b)
-        assert np.all(err <= rtol * np.maximum(np.abs(b), 1.0)), float((err / np.maximum(np.abs(b), 1.0)).max())
+    for name, a, b in zip(("w", "z", "cg"), got, want):
+        assert_state_close(a, b, rtol=rtol, what="fullsize " + name, stragglers=STRAGGLERS, flip_abs=FLIP_ABS)
 
 
 @pytest.mark.parametrize("algo,loss", [(capi.ALGO_FTRL, capi.LOSS_LOGIT), (capi.ALGO_ADAGRAD, capi.LOSS_SQUARE_HINGE),

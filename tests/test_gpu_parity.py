@@ -8,7 +8,7 @@ error is of that order and depends on its summation order); AUC within 1e-4."""
 import numpy as np
 import pytest
 
-from tests.util import random_block, wide_ids
+from tests.util import FLIP_ABS, STRAGGLERS, assert_state_close, random_block, wide_ids
 from wormhole_b200 import capi
 from wormhole_b200.rowblock import RowBlock
 
@@ -290,12 +290,10 @@ def test_server_rejects_foreign_keys(gpu):
 
 # ---------------------------------------------------------------- the whole path ------------
 
-def weights_close(gpu_state, ref_state, rtol=1e-5):
+def weights_close(gpu_state, ref_state, rtol=1e-5, what=""):
     """Per-entry fields within rtol of the field's magnitude scale; reports the worst offender."""
     for name, a, b in zip(("w", "z", "cg"), gpu_state, ref_state):
-        err = np.abs(a.astype(np.float64) - b)
-        tol = rtol * np.maximum(np.abs(b), 1.0)
-        assert (err <= tol).all(), "%s: worst %g at %d" % (name, (err / tol).max(), int(np.argmax(err / tol)))
+        assert_state_close(a, b, rtol=rtol, what=what + name, stragglers=STRAGGLERS, flip_abs=FLIP_ABS)
 
 
 @pytest.mark.parametrize("algo", [capi.ALGO_SGD, capi.ALGO_ADAGRAD, capi.ALGO_FTRL])

@@ -1,5 +1,5 @@
 """The allocation-free transposed product (wh_spmv_trans_times_static) against the regular entry
-point (wh_spmv_trans_times), through the C-ABI.
+point (wh_spmv_trans_times) and against the CPU checker, through the C-ABI.
 
 Why the variant exists: some callers cannot allocate device memory -- a worker that shares its GPU
 with other minibatch streams (an allocation synchronises the whole device and would stall them),
@@ -29,7 +29,7 @@ def _abs_terms(D, x, U):
     return out
 
 
-def test_static_scratch_variant_matches_allocating_entry_point():
+def test_static_scratch_variant_matches_allocating_entry_point(checker):
     import torch
     L = capi.lib()
     ctx = capi.Context(0)
@@ -65,6 +65,10 @@ def test_static_scratch_variant_matches_allocating_entry_point():
         err = np.abs(got.astype(np.float64) - want.astype(np.float64))
         assert np.all(err <= 1e-5 * _abs_terms(D, x, U) + 1e-30), float(err.max())
         assert not np.isnan(got).any()
+        # the two entry points share their kernels, so also hold the result against the CPU checker's
+        # SpMV::TransTimes (learn/base/spmv.h:95-119), with the bound the parity tests use for that product
+        ref = checker.spmv_trans_times(D, x, U).astype(np.float64)
+        assert np.all(np.abs(got.astype(np.float64) - ref) <= 1e-5 * _abs_terms(D, x, U) + 1e-30)
 
     # sizes beyond the fixed scratch are refused with a message that names the limit
     rc = L.wh_spmv_trans_times_static(C.c_void_p(stream), C.byref(lb), C.c_size_t(len(D.index)),
