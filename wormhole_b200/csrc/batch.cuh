@@ -42,7 +42,7 @@ bool pull_at_emit_supported(const whContext* ctx, uint64_t max_key);
 // reads its weight, so the separate pull launch disappears from the chain. `after` (may be NULL) is waited for on the
 // stream before the scan: the event of the push that this pull has to see.
 struct PullAtEmit {
-  const void* table = nullptr;   // NULL = no pull here
+  const void* table = nullptr;   // the shard's ShardEntry array; NULL = no pull here
   int algo = 0;
   uint64_t key_begin = 0, key_end = 0;
   float* w = nullptr;            // out: weight per unique key

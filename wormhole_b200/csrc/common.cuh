@@ -99,6 +99,7 @@ struct whContext {
   unsigned scan_epoch = 0;   // call counter of scan_state
   cudaEvent_t side_ev = nullptr;   // orders work handed to another context's stream after this one's (created on first use)
   wh::DevBuf sort_tmp[6];    // radix sort ping-pong + histograms
+  wh::DevBuf auc;            // histogram block of the counting AUC (loss.cu); zeroed when allocated
   wh::DevBuf acc;            // int64 fixed-point accumulators of the transposed products
   wh::DevBuf small;          // device scalars (counts, plans, metric partials)
   wh::DevBuf stage[8];       // staging of host arguments
@@ -262,6 +263,13 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, unsigned parity) {
 __device__ __forceinline__ uint64_t ld_stream_u64(const uint64_t* p) {
   uint64_t v;
   asm volatile("ld.global.nc.L1::no_allocate.u64 %0, [%1];" : "=l"(v) : "l"(p));
+  return v;
+}
+// ... and that are the first to leave L2 as well (a stream of ids must not push the table entries out of L2)
+__device__ __forceinline__ uint64_t ld_stream_evict_first_u64(const uint64_t* p) {
+  uint64_t v, pol;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+  asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.u64 %0, [%1], %2;" : "=l"(v) : "l"(p), "l"(pol));
   return v;
 }
 __device__ __forceinline__ uint32_t ld_stream_u32(const uint32_t* p) {

@@ -1,6 +1,8 @@
 // Context life cycle, error strings, scratch buffers.
 #include <stdarg.h>
 
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace wh {
@@ -120,6 +122,9 @@ int wh_create(int device, whContext** out) {
                   prop.major, prop.minor);
     return WH_ERR_UNSUPPORTED;
   }
+  // WH_L2_FETCH=32|64|128: the L2's DRAM fetch granularity (a device-wide hint; the path's table accesses are random
+  // 4- to 16-byte reads, of which a wider fetch only keeps one sector)
+  if (const char* e = getenv("WH_L2_FETCH")) { const int g = atoi(e); if (g == 32 || g == 64 || g == 128) cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)g); }
   whContext* c = new whContext();
   c->device = device;
   c->num_sms = prop.multiProcessorCount;
@@ -138,7 +143,7 @@ int wh_destroy(whContext* c) {
   wh::DeviceGuard g(c->device);
   cudaStreamSynchronize(c->stream);
   if (c->side_ev) cudaEventDestroy(c->side_ev);
-  c->directory.release(); c->scan_tmp.release(); c->scan_state.release(); c->acc.release(); c->small.release();
+  c->directory.release(); c->scan_tmp.release(); c->scan_state.release(); c->acc.release(); c->auc.release(); c->small.release();
   for (auto& b : c->sort_tmp) b.release();
   for (auto& b : c->stage) b.release();
   c->pinned.release();

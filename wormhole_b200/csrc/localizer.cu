@@ -20,6 +20,7 @@
 #include "batch.cuh"
 #include "hot.cuh"
 #include "scan.cuh"
+#include "server.cuh"
 
 namespace wh {
 
@@ -114,10 +115,7 @@ struct DirEmitPull {
         bb &= bb - 1;
         float w = 0.f;
         if (k >= p.key_begin && k < p.key_end) {
-          const uint64_t e = k - p.key_begin;
-          if (p.algo == WH_ALGO_FTRL) w = __ldg(reinterpret_cast<const float*>(reinterpret_cast<const float4*>(p.table) + e));
-          else if (p.algo == WH_ALGO_ADAGRAD) w = __ldg(reinterpret_cast<const float*>(reinterpret_cast<const float2*>(p.table) + e));
-          else w = __ldg(reinterpret_cast<const float*>(p.table) + e);
+          w = __ldg(&static_cast<const ShardEntry*>(p.table)[k - p.key_begin].w);
         } else {
           atomicAdd(reinterpret_cast<unsigned long long*>(p.counters + 1), 1ull);
         }

@@ -12,6 +12,7 @@
 //    order unspecified (binary_class_evaluation.h:25-26); here tied (pos,neg) pairs count 1/2,
 //    and the two extremes are reported as auc_lo / auc_hi.
 #include <cooperative_groups.h>
+#include <stdlib.h>
 
 #include "loss.cuh"
 #include "scan.cuh"
@@ -109,12 +110,6 @@ int loss_forward_launch(whContext* ctx, int loss, size_t rows, const float* labe
 
 // ---------------------------------------------------------------------------------- AUC --
 
-// Order-preserving map float -> uint32 (-0 and +0 compare equal, as in the reference's "<").
-__device__ __forceinline__ unsigned ordered_bits(float f) {
-  if (f == 0.f) f = 0.f;
-  unsigned b = __float_as_uint(f);
-  return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
-}
 
 // key = ordered(score) << 1 | (label > 0): ascending by score, negatives first among equals.
 __global__ void __launch_bounds__(256)
@@ -198,6 +193,239 @@ int auc_launch_multiblock(whContext* ctx, size_t n, const float* label, const fl
   return WH_OK;
 }
 
+
+// ---- AUC without a sort: two-level counting on the ordered score bits ---------------------------------------
+// AUC needs, for every negative example, the number of positives with a smaller score (and with an equal one).
+// A sort delivers that, but a sort of 100 000 keys is a chain of passes with barriers in between (the one-cluster
+// kernel below: 165 us on 8 SMs). Counting does not need the order:
+//   hist     bin = top 16 bits of the order-preserving score key (sign, exponent, 7 mantissa bits); one 64-bit RED per
+//            example into {positives << 32 | negatives} of its bin. (The worker's fused kernel does this in its
+//            epilogue, where the score is in a register.)
+//   scan     one block walks the 65 536 bins: positives below each bin (which settles every pair whose members fall
+//            into different bins: sum over bins of negatives x positives below), and the slice of `pos_low` that
+//            will hold the bin's positives; the histogram is zeroed on the way for the next minibatch.
+//   scatter  every positive drops the low 16 bits of its key into its bin's slice (order within the bin does not
+//            matter), and the bin remembers the smallest and largest of them.
+//   count    every negative compares its low 16 bits with the positives of its own bin -- 60 on average at the
+//            Criteo shape, because the binning is logarithmic like the floats themselves; a bin whose positives
+//            are all equal (the all-zero scores of an untrained model) is answered from min == max.
+// All integer: bit-reproducible, tie bounds kept. Used up to 2^20 examples; the multi-launch sort serves beyond.
+constexpr unsigned kAucBins = 1u << 16;
+constexpr unsigned kAucHeavy = 64;          // bins with more positives than this are sorted, and searched instead of scanned
+constexpr unsigned kAucSortMax = 1u << 16;  // ... if they fit one block's shared memory
+constexpr int kAucScanThreads = 1024, kAucScanBlocks = kAucBins / kAucScanThreads;
+struct AucScratch {            // one per context, zeroed when allocated
+  unsigned long long* hist;    // [kAucBins]  positives << 32 | negatives; all zero between minibatches
+  unsigned* begin;             // [kAucBins]  first slot of the bin's positives in pos_low
+  unsigned* cursor;            // [kAucBins]  next free slot while scattering; end of the slice afterwards
+  unsigned* lo_min;            // [kAucBins]  smallest / largest low half among the bin's positives
+  unsigned* lo_max;
+  unsigned* heavy;             // [kAucBins]  bins with more than kAucHeavy positives
+  unsigned long long* cross;   // [kAucScanBlocks]  pairs settled by the bins alone, per scan block
+  unsigned* nheavy;            // zero between minibatches
+};
+constexpr size_t kAucScratchBytes = (size_t)kAucBins * (8 + 5 * 4) + kAucScanBlocks * 8 + 64;
+static AucScratch auc_scratch(void* base) {
+  AucScratch a;
+  a.hist = static_cast<unsigned long long*>(base);
+  a.begin = reinterpret_cast<unsigned*>(a.hist + kAucBins);
+  a.cursor = a.begin + kAucBins; a.lo_min = a.cursor + kAucBins; a.lo_max = a.lo_min + kAucBins; a.heavy = a.lo_max + kAucBins;
+  a.cross = reinterpret_cast<unsigned long long*>(a.heavy + kAucBins);
+  a.nheavy = reinterpret_cast<unsigned*>(a.cross + kAucScanBlocks);
+  return a;
+}
+
+__global__ void __launch_bounds__(256)
+auc_hist_kernel(size_t n, const float* __restrict__ label, const float* __restrict__ xw, unsigned long long* hist) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) auc_hist_add(hist, label[i], xw[i]);
+}
+
+// One bin per thread. A block first adds up the positives of all bins below its own 1 024 (a strided, coalesced read
+// of at most 512 KB out of L2 -- cheaper than a second launch or a grid barrier), then scans its own.
+__global__ void __launch_bounds__(kAucScanThreads)
+auc_scan_kernel(AucScratch a, unsigned nparts, const double* part_objv, const unsigned* part_correct, EvalOut* out) {
+  const unsigned t = threadIdx.x, b = blockIdx.x * kAucScanThreads + t;
+  const unsigned long long v = a.hist[b];
+  unsigned below = 0;
+  for (unsigned i = t; i < blockIdx.x * kAucScanThreads; i += kAucScanThreads) below += (unsigned)(__ldcg(a.hist + i) >> 32);
+  unsigned base;
+  block_exclusive_scan<unsigned>(below, &base);
+  const unsigned p = (unsigned)(v >> 32), ng = (unsigned)v;
+  unsigned tot;
+  const unsigned pos_below = base + block_exclusive_scan<unsigned>(p, &tot);
+  a.begin[b] = pos_below; a.cursor[b] = pos_below;
+  if (p) { a.lo_min[b] = 0xffffffffu; a.lo_max[b] = 0u; }
+  if (p > kAucHeavy) a.heavy[atomicAdd(a.nheavy, 1u)] = b;
+  unsigned long long cross = (unsigned long long)ng * pos_below;
+  __shared__ unsigned long long s_x[kAucScanThreads / 32];
+#pragma unroll
+  for (int s = 16; s > 0; s >>= 1) cross += __shfl_down_sync(0xffffffffu, cross, s);
+  if ((t & 31) == 0) s_x[t >> 5] = cross;
+  __syncthreads();
+  if (t == 0) {
+    unsigned long long x = 0;
+    for (int w = 0; w < kAucScanThreads / 32; ++w) x += s_x[w];
+    a.cross[blockIdx.x] = x;
+    if (blockIdx.x == kAucScanBlocks - 1) out->npos = base + tot;
+  }
+  if (blockIdx.x == 0) {
+    // (fused worker path) the evaluation partial sums of the step's blocks, in a fixed order
+    __shared__ double s_o[kAucScanThreads / 32];
+    __shared__ unsigned long long s_c[kAucScanThreads / 32];
+    double o = 0; unsigned long long c = 0;
+    for (unsigned i = t; i < nparts; i += kAucScanThreads) { o += part_objv[i]; c += part_correct[i]; }
+#pragma unroll
+    for (int s = 16; s > 0; s >>= 1) { o += __shfl_down_sync(0xffffffffu, o, s); c += __shfl_down_sync(0xffffffffu, c, s); }
+    if ((t & 31) == 0) { s_o[t >> 5] = o; s_c[t >> 5] = c; }
+    __syncthreads();
+    if (t == 0) {
+      double oo = 0; unsigned long long cc = 0;
+      for (int w = 0; w < kAucScanThreads / 32; ++w) { oo += s_o[w]; cc += s_c[w]; }
+      out->area_lo = 0; out->ties = 0; out->ngroups = 0;   // the count kernel adds into these
+      if (nparts) { out->objv = oo; out->logloss = 0; out->correct = cc; }
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256)
+auc_scatter_kernel(size_t n, const float* __restrict__ label, const float* __restrict__ xw, AucScratch a,
+                   unsigned short* __restrict__ pos_low) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  // the scan has read the histogram: leave it zero for the next minibatch
+  for (size_t h = i; h < kAucBins; h += (size_t)gridDim.x * blockDim.x) a.hist[h] = 0ull;
+  const bool pos = i < n && label[i] > 0;
+  const unsigned ob = pos ? ordered_bits(xw[i]) : 0u;
+  const unsigned b = ob >> 16, lo = ob & 0xffffu;
+  const unsigned peers = __ballot_sync(0xffffffffu, pos);
+  if (!pos) return;
+  // an untrained or very sparse model gives every example the same score: one slot counter would take a ticket
+  // from every positive in turn. Lanes that all sit in one bin take their tickets with one atomic.
+  int same;
+  __match_all_sync(peers, b, &same);
+  unsigned slot;
+  if (same) {
+    const int leader = __ffs(peers) - 1;
+    const unsigned lane = threadIdx.x & 31;
+    unsigned base = 0;
+    const unsigned mn = __reduce_min_sync(peers, lo), mx = __reduce_max_sync(peers, lo);
+    if ((int)lane == leader) {
+      base = atomicAdd(a.cursor + b, (unsigned)__popc(peers));
+      atomicMin(a.lo_min + b, mn); atomicMax(a.lo_max + b, mx);
+    }
+    base = __shfl_sync(peers, base, leader);
+    slot = base + __popc(peers & lanemask_lt());
+  } else {
+    slot = atomicAdd(a.cursor + b, 1u);
+    atomicMin(a.lo_min + b, lo); atomicMax(a.lo_max + b, lo);
+  }
+  pos_low[slot] = (unsigned short)lo;
+}
+
+// Heavy bins: a block sorts the bin's positives in shared memory (bitonic, 16-bit keys), in place.
+__device__ __forceinline__ bool auc_bin_sorted(unsigned n, unsigned mn, unsigned mx) {
+  return n > kAucHeavy && n <= kAucSortMax && mn != mx;
+}
+__global__ void __launch_bounds__(1024)
+auc_sort_heavy_kernel(AucScratch a, unsigned short* __restrict__ pos_low) {
+  extern __shared__ unsigned short s_k[];
+  const unsigned nheavy = *a.nheavy;
+  for (unsigned h = blockIdx.x; h < nheavy; h += gridDim.x) {
+    const unsigned b = a.heavy[h], beg = a.begin[b], n = a.cursor[b] - beg;
+    if (!auc_bin_sorted(n, a.lo_min[b], a.lo_max[b])) continue;   // (uniform per block)
+    unsigned N = 128;
+    while (N < n) N <<= 1;
+    for (unsigned i = threadIdx.x; i < N; i += blockDim.x) s_k[i] = i < n ? pos_low[beg + i] : (unsigned short)0xffffu;
+    __syncthreads();
+    for (unsigned k = 2; k <= N; k <<= 1)
+      for (unsigned j = k >> 1; j > 0; j >>= 1) {
+        for (unsigned i = threadIdx.x; i < N; i += blockDim.x) {
+          const unsigned p = i ^ j;
+          if (p > i) {
+            const unsigned short x = s_k[i], y = s_k[p];
+            if (((i & k) == 0) == (x > y)) { s_k[i] = y; s_k[p] = x; }
+          }
+        }
+        __syncthreads();
+      }
+    for (unsigned i = threadIdx.x; i < n; i += blockDim.x) pos_low[beg + i] = s_k[i];
+    __syncthreads();
+  }
+}
+
+__global__ void __launch_bounds__(256)
+auc_count_kernel(size_t n, const float* __restrict__ label, const float* __restrict__ xw, AucScratch a,
+                 const unsigned short* __restrict__ pos_low, EvalOut* out) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  unsigned long long lt = 0, eq = 0;
+  if (blockIdx.x == 0 && threadIdx.x < kAucScanBlocks) lt = a.cross[threadIdx.x];   // the pairs the bins alone settle
+  if (blockIdx.x == 0 && threadIdx.x == 0) *a.nheavy = 0u;                          // (the sort kernel has finished)
+  if (i < n && !(label[i] > 0)) {
+    const unsigned ob = ordered_bits(xw[i]);
+    const unsigned b = ob >> 16, lo = ob & 0xffffu;
+    const unsigned beg = a.begin[b], end = a.cursor[b];
+    if (end > beg) {
+      const unsigned mn = a.lo_min[b], mx = a.lo_max[b], cnt = end - beg;
+      if (mn == mx) {            // all positives of the bin share one score
+        if (mn < lo) lt += cnt; else if (mn == lo) eq = cnt;
+      } else if (mx < lo) {
+        lt += cnt;
+      } else if (mn <= lo) {
+        if (auc_bin_sorted(cnt, mn, mx)) {
+          unsigned l0 = beg, h0 = end;          // first position with a key >= lo
+          while (l0 < h0) { const unsigned m = (l0 + h0) >> 1; if (pos_low[m] < lo) l0 = m + 1; else h0 = m; }
+          unsigned l1 = l0, h1 = end;           // first position with a key > lo
+          while (l1 < h1) { const unsigned m = (l1 + h1) >> 1; if (pos_low[m] <= lo) l1 = m + 1; else h1 = m; }
+          lt += l0 - beg; eq = l1 - l0;
+        } else {
+          unsigned l = 0, e = 0;
+          for (unsigned j = beg; j < end; ++j) { const unsigned p = pos_low[j]; l += p < lo; e += p == lo; }
+          lt += l; eq = e;
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int s = 16; s > 0; s >>= 1) { lt += __shfl_xor_sync(0xffffffffu, lt, s); eq += __shfl_xor_sync(0xffffffffu, eq, s); }
+  __shared__ unsigned long long s_l[8], s_e[8];
+  if ((threadIdx.x & 31) == 0) { s_l[threadIdx.x >> 5] = lt; s_e[threadIdx.x >> 5] = eq; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    unsigned long long l = 0, e = 0;
+    for (int w = 0; w < 8; ++w) { l += s_l[w]; e += s_e[w]; }
+    if (l) atomicAdd(&out->area_lo, l);
+    if (e) atomicAdd(&out->ties, e);
+  }
+}
+
+constexpr size_t kAucCountMax = 1u << 20;
+int auc_scratch_get(whContext* ctx, void** base) {
+  if (ctx->auc.cap < kAucScratchBytes) {
+    WH_TRY(ctx->auc.reserve(kAucScratchBytes));
+    WH_CUDA(cudaMemsetAsync(ctx->auc.p, 0, kAucScratchBytes, ctx->stream));
+  }
+  *base = ctx->auc.p;
+  return WH_OK;
+}
+unsigned long long* auc_hist_ptr(void* scratch_base) { return static_cast<unsigned long long*>(scratch_base); }
+
+// hist_filled: the caller's kernel has already added every example to the histogram of this context's scratch.
+int auc_count_launch(whContext* ctx, size_t n, const float* label, const float* xw, EvalOut* out, bool hist_filled,
+                     unsigned nparts, const double* part_objv, const unsigned* part_correct) {
+  void* base;
+  WH_TRY(auc_scratch_get(ctx, &base));
+  AucScratch a = auc_scratch(base);
+  WH_TRY(ctx->sort_tmp[0].reserve(n * 2 + 64));
+  unsigned short* pos_low = ctx->sort_tmp[0].as<unsigned short>();
+  const unsigned nb = (unsigned)div_up(n, 256);
+  if (!hist_filled) WH_LAUNCH(auc_hist_kernel, nb, 256, 0, ctx->stream, n, label, xw, a.hist);
+  WH_LAUNCH(auc_scan_kernel, kAucScanBlocks, kAucScanThreads, 0, ctx->stream, a, nparts, part_objv, part_correct, out);
+  WH_LAUNCH(auc_scatter_kernel, nb, 256, 0, ctx->stream, n, label, xw, a, pos_low);
+  WH_CUDA(cudaFuncSetAttribute(auc_sort_heavy_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(kAucSortMax * 2)));
+  WH_LAUNCH(auc_sort_heavy_kernel, 16, 1024, kAucSortMax * 2, ctx->stream, a, pos_low);
+  WH_LAUNCH(auc_count_kernel, nb, 256, 0, ctx->stream, n, label, xw, a, pos_low, out);
+  return WH_OK;
+}
 
 // ---- AUC in ONE launch: a thread-block cluster sorts and counts -------------------------------
 // 8 CTAs x 1024 threads (one cluster: hardware barrier + distributed shared memory) run the
@@ -579,6 +807,9 @@ auc_cluster_reg_kernel(size_t n, const float* __restrict__ label, const float* _
 int auc_launch(whContext* ctx, size_t n, const float* label, const float* xw, EvalOut* out) {
   if (n == 0) return WH_OK;
   WH_REQUIRE(n < (size_t)INT32_MAX, "AUC: %zu examples exceed 32-bit counters", n);
+  static int mode = -1;   // WH_AUC=cluster: the one-cluster sort of round 1 (kept for comparison)
+  if (mode < 0) { const char* e = getenv("WH_AUC"); mode = (e && e[0] == 'c') ? 1 : 0; }
+  if (mode == 0 && n <= kAucCountMax) return auc_count_launch(ctx, n, label, xw, out, false, 0, nullptr, nullptr);
   if (n <= kAucClusterMax) {
     WH_TRY(ctx->sort_tmp[0].reserve(n * 8)); WH_TRY(ctx->sort_tmp[1].reserve(n * 8));
     WH_TRY(ctx->sort_tmp[5].reserve((n + 1) * 8));

@@ -24,7 +24,26 @@ int auc_launch(whContext* ctx, size_t rows, const float* label, const float* xw,
 // the multi-launch radix-sort variant (any size); auc_launch uses it beyond 2^20 examples
 int auc_launch_multiblock(whContext* ctx, size_t rows, const float* label, const float* xw, EvalOut* out);
 
+// The counting AUC (loss.cu). auc_scratch_get: the context's histogram block (zeroed at allocation, left all zero by
+// every auc_count_launch); auc_hist_ptr: its 65 536 x u64 histogram, for kernels that add their examples themselves
+// (auc_hist_add) and then call auc_count_launch(..., hist_filled = true). nparts > 0 also folds the caller's
+// per-block objective / accuracy partial sums into `out` (fixed order), which saves the one-block reduce launch.
+int auc_scratch_get(whContext* ctx, void** base);
+unsigned long long* auc_hist_ptr(void* scratch_base);
+int auc_count_launch(whContext* ctx, size_t n, const float* label, const float* xw, EvalOut* out, bool hist_filled,
+                     unsigned nparts, const double* part_objv, const unsigned* part_correct);
+
 #ifdef __CUDACC__
+// Order-preserving map float -> uint32 (-0 and +0 compare equal, as in the reference's "<").
+__device__ __forceinline__ unsigned ordered_bits(float f) {
+  if (f == 0.f) f = 0.f;
+  unsigned b = __float_as_uint(f);
+  return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+// one example into the AUC histogram: bin = top 16 bits of the ordered score, positives in the high word
+__device__ __forceinline__ void auc_hist_add(unsigned long long* hist, float label, float score) {
+  atomicAdd(hist + (ordered_bits(score) >> 16), label > 0 ? (1ull << 32) : 1ull);
+}
 // exp / log in fp64 rounded to fp32: the correctly rounded fp32 result in all but ~1e-9 of cases (what glibc's
 // expf / logf deliver on the reference's side)
 __device__ __forceinline__ float exp_rn(float a) { return (float)exp((double)a); }

@@ -11,114 +11,28 @@
 #include <algorithm>
 #include <vector>
 
+#include "handle.cuh"
 #include "scan.cuh"
 #include "server.cuh"
 
 namespace wh {
 
-// learn/linear/penalty.h:36-41
-__device__ __forceinline__ float l1l2_solve(float z, float eta, float l1, float l2) {
-  if (z <= l1 && z >= -l1) return 0.f;
-  return (z > 0.f ? z - l1 : z + l1) / (eta + l2);
-}
-
-struct HandleParams {
-  int algo;
-  float l1, l2, alpha, beta;
-  float eta_sgd;            // SGDHandle::eta for this push message
-  uint64_t key_begin, key_end;
-  // un-hashed 64-bit keys (ps::FLAGS_max_key at its default): open addressing instead of direct addressing
-  unsigned long long* hkeys;   // NULL = dense shard; else one key per slot, kEmptyKey = free
-  uint64_t hmask;              // slots - 1 (a power of two)
-};
-constexpr unsigned long long kEmptyKey = ~0ull;
-
-__device__ __forceinline__ uint64_t hash_mix(uint64_t x) {
-  x ^= x >> 33; x *= 0xff51afd7ed558ccdULL; x ^= x >> 33; x *= 0xc4ceb9fe1a85ec53ULL; x ^= x >> 33; return x;
-}
-// Where does key k live? insert = true claims a free slot for a key not seen before (entries are zero by
-// default, as ps-lite's store default-constructs on first touch); insert = false leaves absent keys absent.
-// Returns false if the key is outside the shard / the table is full (counted as a bad key by the caller).
-__device__ __forceinline__ bool find_slot(const HandleParams& h, uint64_t k, bool insert, uint64_t* slot, bool* present) {
-  *present = true;
-  if (h.hkeys == nullptr) {
-    if (k < h.key_begin || k >= h.key_end) return false;
-    *slot = k - h.key_begin;
-    return true;
-  }
-  if (k == kEmptyKey) return false;
-  uint64_t i = hash_mix(k) & h.hmask;
-  for (uint64_t probes = 0; probes <= h.hmask; ++probes, i = (i + 1) & h.hmask) {
-    unsigned long long cur = h.hkeys[i];
-    if (cur == k) { *slot = i; return true; }
-    if (cur == kEmptyKey) {
-      if (!insert) { *present = false; *slot = i; return true; }
-      cur = atomicCAS(h.hkeys + i, kEmptyKey, (unsigned long long)k);
-      if (cur == kEmptyKey || cur == k) { *slot = i; return true; }
-    }
-  }
-  return false;
-}
-
-// One key of one push message. Returns the change of |w|_0 (learn/linear/async_sgd.h:35-41).
-__device__ __forceinline__ int handle_push(const HandleParams& h, void* table, uint64_t slot, float g) {
-  float old_w, new_w;
-  if (h.algo == WH_ALGO_FTRL) {        // async_sgd.h:160-175
-    float4* e = reinterpret_cast<float4*>(table) + slot;
-    float4 v = *e;
-    old_w = v.x;
-    float sqrt_n = v.z;
-    float n2 = sqrtf(sqrt_n * sqrt_n + g * g);
-    float sigma = (n2 - sqrt_n) / h.alpha;
-    float z = v.y + (g - sigma * old_w);
-    new_w = l1l2_solve(-z, (h.beta + n2) / h.alpha, h.l1, h.l2);
-    *e = make_float4(new_w, z, n2, 0.f);
-  } else if (h.algo == WH_ALGO_ADAGRAD) {  // async_sgd.h:123-135
-    float2* e = reinterpret_cast<float2*>(table) + slot;
-    float2 v = *e;
-    old_w = v.x;
-    float n2 = sqrtf(v.y * v.y + g * g);
-    float eta = (n2 + h.beta) / h.alpha;
-    new_w = l1l2_solve(eta * old_w - g, eta, h.l1, h.l2);
-    *e = make_float2(new_w, n2);
-  } else {                              // async_sgd.h:91-95
-    float* e = reinterpret_cast<float*>(table) + slot;
-    old_w = *e;
-    new_w = l1l2_solve(h.eta_sgd * old_w - g, h.eta_sgd, h.l1, h.l2);
-    *e = new_w;
-  }
-  return (old_w == 0.f && new_w != 0.f) ? 1 : ((old_w != 0.f && new_w == 0.f) ? -1 : 0);
-}
-
-__device__ __forceinline__ void commit_counters(long long* counters, int delta, int bad) {
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) {
-    delta += __shfl_xor_sync(0xffffffffu, delta, o);
-    bad += __shfl_xor_sync(0xffffffffu, bad, o);
-  }
-  if ((threadIdx.x & 31) == 0) {
-    if (delta) atomicAdd(reinterpret_cast<unsigned long long*>(counters), (unsigned long long)(long long)delta);
-    if (bad) atomicAdd(reinterpret_cast<unsigned long long*>(counters + 1), (unsigned long long)bad);
-  }
-}
-
 template <bool FROM_ACC>
 __global__ void __launch_bounds__(256)
-server_push_kernel(HandleParams h, void* table, const uint64_t* __restrict__ keys, size_t n,
+server_push_kernel(HandleParams h, ShardView table, const uint64_t* __restrict__ keys, size_t n,
                    const unsigned* d_n, const float* __restrict__ grads, long long* acc,
                    const FixedScale* fs, float mul, long long* counters, unsigned copies, size_t stride) {
   if (d_n) n = *d_n;
   int delta = 0, bad = 0;
   // grid-stride: the launch is sized for the number of SMs, not for the upper bound of n (which is only known
   // on the device and is ~15x smaller than the bound at Criteo shape)
-  const size_t entry_bytes = h.algo == WH_ALGO_FTRL ? 16 : (h.algo == WH_ALGO_ADAGRAD ? 8 : 4);
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
     const uint64_t k = keys[i];
     uint64_t slot;
     bool present;
     const bool ok = find_slot(h, k, true, &slot, &present);
     // start the entry's trip from DRAM now, so that it overlaps the accumulator loads instead of following them
-    if (ok) asm volatile("prefetch.global.L2 [%0];" ::"l"(reinterpret_cast<const char*>(table) + slot * entry_bytes));
+    if (ok) asm volatile("prefetch.global.L2 [%0];" ::"l"(table.e + slot));
     float g;
     if (FROM_ACC) {
       const long long a = sum_and_clear_replicas(acc, copies, stride, i);
@@ -134,7 +48,7 @@ server_push_kernel(HandleParams h, void* table, const uint64_t* __restrict__ key
 
 // learn/linear/async_sgd.h:97-99,137-139,177-179: send[0] = w
 __global__ void __launch_bounds__(256)
-server_pull_kernel(HandleParams h, const void* table,
+server_pull_kernel(HandleParams h, const ShardEntry* __restrict__ tab,
                    const uint64_t* __restrict__ keys, size_t n, const unsigned* d_n,
                    float* __restrict__ vals, long long* counters) {
   if (d_n) n = *d_n;
@@ -142,20 +56,13 @@ server_pull_kernel(HandleParams h, const void* table,
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
     uint64_t k = keys[i], s;
     bool present;
-    const int algo = h.algo;
-    if (find_slot(h, k, false, &s, &present)) {
-      float w;
-      if (!present) w = 0.f;
-      else if (algo == WH_ALGO_FTRL) w = __ldg(reinterpret_cast<const float*>(reinterpret_cast<const float4*>(table) + s));
-      else if (algo == WH_ALGO_ADAGRAD) w = __ldg(reinterpret_cast<const float*>(reinterpret_cast<const float2*>(table) + s));
-      else w = __ldg(reinterpret_cast<const float*>(table) + s);
-      vals[i] = w;
-    } else { vals[i] = 0.f; bad = 1; }
+    if (find_slot(h, k, false, &s, &present)) vals[i] = present ? __ldg(&tab[s].w) : 0.f;
+    else { vals[i] = 0.f; bad = 1; }
   }
   commit_counters(counters, 0, bad);
 }
 
-__global__ void server_state_kernel(HandleParams h, void* table,
+__global__ void server_state_kernel(HandleParams h, ShardView table,
                                     const uint64_t* __restrict__ keys, size_t n, float* w, float* z,
                                     float* cg, const float* sw, const float* sz, const float* scg,
                                     int set, long long* counters) {
@@ -166,25 +73,25 @@ __global__ void server_state_kernel(HandleParams h, void* table,
   const int algo = h.algo;
   if (!find_slot(h, k, set != 0, &s, &present)) { atomicAdd(reinterpret_cast<unsigned long long*>(counters + 1), 1ull); return; }
   if (!present) { if (w) w[i] = 0.f; if (z) z[i] = 0.f; if (cg) cg[i] = 0.f; return; }
-  float vw, vz = 0.f, vc = 0.f;
-  if (algo == WH_ALGO_FTRL) { float4 v = reinterpret_cast<float4*>(table)[s]; vw = v.x; vz = v.y; vc = v.z; }
-  else if (algo == WH_ALGO_ADAGRAD) { float2 v = reinterpret_cast<float2*>(table)[s]; vw = v.x; vc = v.y; }
-  else vw = reinterpret_cast<float*>(table)[s];
+  float vw = table.e[s].w, vz = 0.f, vc = 0.f;
+  if (algo == WH_ALGO_FTRL) { vz = table.e[s].z; vc = table.e[s].n; }
+  else if (algo == WH_ALGO_ADAGRAD) vc = table.e[s].n;
   if (!set) { if (w) w[i] = vw; if (z) z[i] = vz; if (cg) cg[i] = vc; return; }
   float nw = sw ? sw[i] : vw, nz = sz ? sz[i] : vz, nc = scg ? scg[i] : vc;
-  if (algo == WH_ALGO_FTRL) reinterpret_cast<float4*>(table)[s] = make_float4(nw, nz, nc, 0.f);
-  else if (algo == WH_ALGO_ADAGRAD) reinterpret_cast<float2*>(table)[s] = make_float2(nw, nc);
-  else reinterpret_cast<float*>(table)[s] = nw;
+  table.e[s].w = nw;
+  if (algo == WH_ALGO_FTRL) { table.e[s].z = nz; table.e[s].n = nc; }
+  else if (algo == WH_ALGO_ADAGRAD) table.e[s].n = nc;
   int delta = (vw == 0.f && nw != 0.f) ? 1 : ((vw != 0.f && nw == 0.f) ? -1 : 0);  // TLoad: Update(w, 0), :59-62
   if (delta) atomicAdd(reinterpret_cast<unsigned long long*>(counters), (unsigned long long)(long long)delta);
 }
 
-static HandleParams make_params(whServer* s, bool start_push) {
+HandleParams make_params(whServer* s, bool start_push) {
   HandleParams h;
   h.algo = s->algo; h.l1 = s->l1; h.l2 = s->l2; h.alpha = s->alpha; h.beta = s->beta;
   h.key_begin = s->key_begin; h.key_end = s->key_end;
   h.hkeys = s->hkeys.as<unsigned long long>(); h.hmask = s->hslots ? s->hslots - 1 : 0;
   h.eta_sgd = 0.f;
+  if (start_push) s->version++;
   if (start_push && s->algo == WH_ALGO_SGD) {  // SGDHandle::Start, async_sgd.h:85-90
     h.eta_sgd = (s->beta + sqrtf((float)s->t)) / s->alpha;
     s->t += 1;
@@ -194,14 +101,14 @@ static HandleParams make_params(whServer* s, bool start_push) {
 
 int server_pull_launch(whServer* s, cudaStream_t stream, const uint64_t* keys, size_t n, const unsigned* d_n, float* vals) {
   if (n == 0) return WH_OK;
-  WH_LAUNCH(server_pull_kernel, (unsigned)std::min<size_t>(div_up(n, 256), (size_t)s->ctx->num_sms * 8), 256, 0, stream, make_params(s, false), s->table.p,
+  WH_LAUNCH(server_pull_kernel, (unsigned)std::min<size_t>(div_up(n, 256), (size_t)s->ctx->num_sms * 8), 256, 0, stream, make_params(s, false), s->view().e,
             keys, n, d_n, vals, s->counters.as<long long>());
   return WH_OK;
 }
 int server_push_launch(whServer* s, cudaStream_t stream, const uint64_t* keys, size_t n, const unsigned* d_n, const float* grads) {
   HandleParams h = make_params(s, true);  // Start() runs even for an empty message
   if (n == 0) return WH_OK;
-  WH_LAUNCH(server_push_kernel<false>, (unsigned)std::min<size_t>(div_up(n, 256), (size_t)s->ctx->num_sms * 8), 256, 0, stream, h, s->table.p, keys, n,
+  WH_LAUNCH(server_push_kernel<false>, (unsigned)std::min<size_t>(div_up(n, 256), (size_t)s->ctx->num_sms * 8), 256, 0, stream, h, s->view(), keys, n,
             d_n, grads, (long long*)nullptr, (const FixedScale*)nullptr, 1.f, s->counters.as<long long>(), 1u, (size_t)0);
   return WH_OK;
 }
@@ -209,7 +116,7 @@ int server_push_acc_launch(whServer* s, cudaStream_t stream, const uint64_t* key
                            const FixedScale* fs, float mul, unsigned copies, size_t stride) {
   HandleParams h = make_params(s, true);
   if (n == 0) return WH_OK;
-  WH_LAUNCH(server_push_kernel<true>, (unsigned)std::min<size_t>(div_up(n, 256), (size_t)s->ctx->num_sms * 8), 256, 0, stream, h, s->table.p, keys, n,
+  WH_LAUNCH(server_push_kernel<true>, (unsigned)std::min<size_t>(div_up(n, 256), (size_t)s->ctx->num_sms * 8), 256, 0, stream, h, s->view(), keys, n,
             d_n, (const float*)nullptr, acc, fs, mul, s->counters.as<long long>(), copies, stride);
   return WH_OK;
 }
@@ -246,13 +153,8 @@ server_pull_sharded_kernel(int algo, ShardMap m, uint64_t max_key, const uint64_
     if (k < max_key) {
       const int g = shard_of(m, k);
       const uint64_t s = k - m.bounds[g];
-      const void* table = m.table[g];
-      float w;
       // ld.cg: the owner's L2 is the point of coherence for its table; a volatile load compiles to LDG.STRONG.SYS
-      if (algo == WH_ALGO_FTRL) w = __ldcg(reinterpret_cast<const float*>(reinterpret_cast<const float4*>(table) + s));
-      else if (algo == WH_ALGO_ADAGRAD) w = __ldcg(reinterpret_cast<const float*>(reinterpret_cast<const float2*>(table) + s));
-      else w = __ldcg(reinterpret_cast<const float*>(table) + s);
-      vals[i] = w;
+      vals[i] = __ldcg(&static_cast<const ShardEntry*>(m.table[g])[s].w);
     } else { vals[i] = 0.f; bad = 1; }
   }
   commit_counters(counters, 0, bad);
@@ -272,7 +174,7 @@ server_push_turn_kernel(HandleParams h, ShardMap m, int target, const uint64_t* 
       // stores may alias), and a thread pays `copies` memory latencies in a row
       long long a = sum_and_clear_replicas(acc, copies, stride, i);
       const float g = (float)((double)a * fs->inv) * mul;
-      delta = handle_push(h, m.table[target], k - m.bounds[target], g);
+      delta = handle_push(h, shard_view(m.table[target]), k - m.bounds[target], g);
     }
   }
 #pragma unroll
@@ -305,14 +207,13 @@ __global__ void shard_barrier_kernel(ShardMap m, unsigned long long epoch, long 
   __threadfence_system();
 }
 
-static HandleParams make_params(whServer* s, bool start_push);
 
 // A worker's outbox: {header: U at word 0, slice cuts at words 4..4+world} | keys[cap] | grads[cap].
 // The owner of a key range applies, for one source rank, the slice of that rank's (key, gradient) list that
 // falls into its range -- read directly from the source GPU's memory. One launch per source, in ascending
 // source order: each is one push message for this shard's handle.
 __global__ void __launch_bounds__(256)
-server_apply_from_kernel(HandleParams h, void* table, const unsigned char* outbox, size_t cap, int me, long long* counters) {
+server_apply_from_kernel(HandleParams h, ShardView table, const unsigned char* outbox, size_t cap, int me, long long* counters) {
   // one thread per block fetches the two cut positions: they sit in the SOURCE GPU's memory, and tens of
   // thousands of threads loading the same remote word serialise on NVLink (measured: 8x slower push)
   __shared__ unsigned s_cut[2];
@@ -341,7 +242,7 @@ struct ApplyAllArgs {
   int world;
 };
 __global__ void __launch_bounds__(256)
-server_apply_all_kernel(HandleParams h, void* table, ApplyAllArgs a, size_t cap, int me, long long* counters) {
+server_apply_all_kernel(HandleParams h, ShardView table, ApplyAllArgs a, size_t cap, int me, long long* counters) {
   // (the barriers before and after stay separate one-block launches: folded into this kernel they kept a block on
   //  every SM spinning while the peers caught up -- 4.36 -> 3.92 G examples/s at 8 GPUs)
   namespace cg = cooperative_groups;
@@ -404,7 +305,7 @@ __global__ void outbox_cuts_kernel(unsigned char* outbox, ShardMap m) {
 
 int server_apply_from_launch(whServer* s, cudaStream_t stream, const unsigned char* outbox, size_t cap) {
   HandleParams h = make_params(s, true);   // one push message: SGD's t advances even for an empty slice
-  WH_LAUNCH(server_apply_from_kernel, (unsigned)s->ctx->num_sms, 256, 0, stream, h, s->table.p, outbox, cap,
+  WH_LAUNCH(server_apply_from_kernel, (unsigned)s->ctx->num_sms, 256, 0, stream, h, s->view(), outbox, cap,
             s->map.rank, s->counters.as<long long>());
   return WH_OK;
 }
@@ -417,7 +318,7 @@ int server_apply_all_launch(whServer* s, cudaStream_t stream, unsigned char* con
     a.eta_sgd[src] = make_params(s, true).eta_sgd;   // one push message per source: SGDHandle::Start each
   }
   int me = s->map.rank;
-  void* table = s->table.p;
+  ShardView table = s->view();
   long long* counters = s->counters.as<long long>();
   void* args[] = {&h, &table, &a, &cap, &me, &counters};
   const unsigned grid = (unsigned)s->ctx->num_sms;   // one light block per SM: co-resident with anything
@@ -478,7 +379,7 @@ struct ServeArgs {
   int world;
 };
 __global__ void __launch_bounds__(256)
-server_serve_all_kernel(int algo, const void* table, uint64_t key_begin, uint64_t key_end, ServeArgs a, size_t cap, int me,
+server_serve_all_kernel(const ShardEntry* tab, uint64_t key_begin, uint64_t key_end, ServeArgs a, size_t cap, int me,
                         long long* counters) {
   __shared__ unsigned s_cut[kMaxShards][2];
   if (threadIdx.x < 2 * a.world) {   // one thread per cut: the headers sit in the source GPUs' memory
@@ -502,12 +403,8 @@ server_serve_all_kernel(int algo, const void* table, uint64_t key_begin, uint64_
     for (int src = 0; src < kMaxShards; ++src) {
       if (!live[src]) continue;
       float w = 0.f;
-      if (k[src] >= key_begin && k[src] < key_end) {
-        const uint64_t e = k[src] - key_begin;
-        if (algo == WH_ALGO_FTRL) w = __ldcg(reinterpret_cast<const float*>(reinterpret_cast<const float4*>(table) + e));
-        else if (algo == WH_ALGO_ADAGRAD) w = __ldcg(reinterpret_cast<const float*>(reinterpret_cast<const float2*>(table) + e));
-        else w = __ldcg(reinterpret_cast<const float*>(table) + e);
-      } else bad = 1;
+      if (k[src] >= key_begin && k[src] < key_end) w = __ldcg(&tab[k[src] - key_begin].w);
+      else bad = 1;
       reinterpret_cast<float*>(a.outbox[src] + 256 + cap * 12)[s_cut[src][0] + i0] = w;
     }
   }
@@ -518,7 +415,7 @@ int server_serve_all_launch(whServer* s, cudaStream_t stream, unsigned char* con
   ServeArgs a;
   a.world = s->map.world;
   for (int src = 0; src < a.world; ++src) a.outbox[src] = outboxes[src];
-  WH_LAUNCH(server_serve_all_kernel, (unsigned)s->ctx->num_sms, 256, 0, stream, s->algo, s->table.p, s->key_begin, s->key_end, a, cap,
+  WH_LAUNCH(server_serve_all_kernel, (unsigned)s->ctx->num_sms, 256, 0, stream, s->view().e, s->key_begin, s->key_end, a, cap,
             s->map.rank, s->counters.as<long long>());
   return WH_OK;
 }
@@ -529,12 +426,8 @@ int server_serve_all_launch(whServer* s, cudaStream_t stream, unsigned char* con
 // learn/linear/async_sgd.h:59-66,73-75,111-113,150-152). The record framing of ps-lite's KVStore::Save is
 // not in the reference tree; this library writes {uint64 key, float w} records in ascending key order.
 struct NonZero {
-  const void* table; int algo;
-  __device__ float w(size_t i) const {
-    if (algo == WH_ALGO_FTRL) return reinterpret_cast<const float4*>(table)[i].x;
-    if (algo == WH_ALGO_ADAGRAD) return reinterpret_cast<const float2*>(table)[i].x;
-    return reinterpret_cast<const float*>(table)[i];
-  }
+  const ShardEntry* tab;
+  __device__ float w(size_t i) const { return tab[i].w; }
   __device__ unsigned operator()(size_t i) const { return w(i) != 0.f ? 1u : 0u; }
 };
 struct DumpOut {
@@ -580,9 +473,8 @@ int wh_server_create(whContext* ctx, const whServerConfig* c, whServer** out) {
   if (c->has_lr_eta) s->alpha = c->lr_eta;
   if (c->has_lr_beta) s->beta = c->lr_beta;
   s->key_begin = c->key_begin; s->key_end = c->key_end;
-  const size_t esz = c->algo == WH_ALGO_FTRL ? 16 : (c->algo == WH_ALGO_ADAGRAD ? 8 : 4);
   s->hslots = c->hash_slots;
-  int r = s->table.reserve(s->entries() * esz);
+  int r = s->table.reserve(shard_bytes(s->entries()));
   if (r == WH_OK && s->hslots) r = s->hkeys.reserve(s->hslots * 8);
   if (r == WH_OK) r = s->counters.reserve(64);
   if (r == WH_OK) r = s->flags.reserve(kBarrierClasses * kMaxShards * 8);
@@ -658,7 +550,8 @@ static int state_io(whServer* s, const uint64_t* keys, size_t n, int mem, float*
   WH_TRY(to_device(ctx, ctx->stage[4], sw, n, mem, &dsw));
   WH_TRY(to_device(ctx, ctx->stage[5], sz, n, mem, &dsz));
   WH_TRY(to_device(ctx, ctx->stage[6], scg, n, mem, &dsc));
-  WH_LAUNCH(server_state_kernel, (unsigned)div_up(n, 256), 256, 0, ctx->stream, make_params(s, false), s->table.p, dk, n, dw, dz, dc, dsw, dsz, dsc, set, s->counters.as<long long>());
+  if (set) s->version++;
+  WH_LAUNCH(server_state_kernel, (unsigned)div_up(n, 256), 256, 0, ctx->stream, make_params(s, false), s->view(), dk, n, dw, dz, dc, dsw, dsz, dsc, set, s->counters.as<long long>());
   WH_TRY(out_commit(ctx, w, dw, n, mem));
   WH_TRY(out_commit(ctx, z, dz, n, mem));
   WH_TRY(out_commit(ctx, cg, dc, n, mem));
@@ -692,7 +585,7 @@ int wh_server_save(whServer* s, const char* path) {
   WH_TRY(ctx->stage[0].reserve(cap * 8)); WH_TRY(ctx->stage[1].reserve(cap * 4));
   WH_TRY(ctx->scan_tmp.reserve(div_up(n, kScanTile) * sizeof(unsigned) + 256));
   unsigned* total = ctx->small.as<unsigned>() + 64;
-  NonZero nz{s->table.p, s->algo};
+  NonZero nz{s->view().e};
   WH_TRY(scan_and_apply<unsigned>(ctx, nz, DumpOut{nz, s->key_begin, s->hkeys.as<unsigned long long>(), ctx->stage[0].as<uint64_t>(), ctx->stage[1].as<float>()},
                                   n, ctx->scan_tmp.as<unsigned>(), total));
   std::vector<uint64_t> keys(cap);

@@ -10,10 +10,32 @@ constexpr int kMaxShards = 8;
 constexpr int kBarrierClasses = 4;
 // The shards of one box as seen from one GPU: every rank's table / counters / barrier flags are mapped
 // into this process (CUDA IPC over NVLink), so a kernel can address any shard directly.
+// One shard's table: an array of 32-byte entries, one DRAM sector each. What bounds every kernel that touches the
+// table is the NUMBER of random lines it touches, not their bytes (B200 serves ~20-35 G random lines/s; measured:
+// with w in an array of its own and the optimizer state in another, the push went from 14.5 to 20 us and the
+// shared-GPU step paid two lines per key), so everything one key ever needs sits in one sector: the weight, the
+// optimizer state -- FTRL {z, sq_cum_grad}, AdaGrad {-, sq_cum_grad}, SGD nothing -- and the key's fixed-point
+// gradient accumulator of the shared-GPU training step (direct.cu; zero between minibatches). There the forward
+// gather brings the sector into L2, the accumulating RED and the push then find it there.
+struct alignas(32) ShardEntry {
+  float w;           // SGDEntry / AdaGradEntry / FTRLEntry::w (learn/linear/async_sgd.h:72,108,146)
+  float z, n;        // FTRLEntry::z / sq_cum_grad (:147-148), AdaGradEntry::sq_cum_grad (:109)
+  unsigned pad0;
+  long long acc;     // X^T dual of the minibatch in flight, fixed point
+  long long pad1;
+};
+struct ShardView {
+  ShardEntry* e = nullptr;     // [entries]
+};
+#if defined(__CUDACC__)
+__host__ __device__
+#endif
+static inline ShardView shard_view(void* base) { ShardView v; v.e = static_cast<ShardEntry*>(base); return v; }
+static inline size_t shard_bytes(size_t entries) { return entries * sizeof(ShardEntry); }
 struct ShardMap {
   int world = 1, rank = 0;
   uint64_t bounds[kMaxShards + 1] = {0};          // shard g owns keys [bounds[g], bounds[g+1])
-  void* table[kMaxShards] = {nullptr};
+  void* table[kMaxShards] = {nullptr};              // shard g's ShardEntry array
   long long* counters[kMaxShards] = {nullptr};
   unsigned long long* flags[kMaxShards] = {nullptr};   // flags[g][cls * kMaxShards + r]: last epoch of class cls rank r announced to rank g
 };
@@ -32,7 +54,9 @@ struct whServer {
   float alpha = 0.1f, beta = 1.f;   // ISGDHandle defaults, learn/linear/async_sgd.h:49
   uint64_t key_begin = 0, key_end = 0;
   int t = 1;                        // SGDHandle::t, learn/linear/async_sgd.h:100
-  wh::DevBuf table;                 // FTRL: float4 {w, z, sq_cum_grad, 0}; AdaGrad: float2 {w, sq_cum_grad}; SGD: float w
+  unsigned long long version = 0;   // counts everything that changed the shard (push messages, set_state, load)
+  wh::DevBuf table;                 // ShardEntry[entries]
+  wh::ShardView view() const { return wh::shard_view(table.p); }
   wh::DevBuf counters;              // [0] new_w (long long), [1] out-of-range keys seen
   wh::DevBuf hkeys;                 // hash shard: the key held by each slot (all ones = free)
   uint64_t hslots = 0;              // 0 = dense shard

@@ -315,6 +315,16 @@ int fixed_prepare(whContext* ctx, FixedScale* fs, const float* x, size_t nx, con
   return WH_OK;
 }
 
+__global__ void fixed_unit_x_kernel(FixedScale* fs) { fs->maxx_bits = __float_as_uint(1.f); fs->maxv_bits = 0; }
+// The same choice for terms dual * value with |dual| <= 1 known up front: only max|value| has to be found.
+int fixed_prepare_unit_x(whContext* ctx, FixedScale* fs, const float* value, size_t nnz) {
+  const unsigned cap = (unsigned)ctx->num_sms * 8;
+  WH_LAUNCH(fixed_unit_x_kernel, 1, 1, 0, ctx->stream, fs);
+  WH_LAUNCH(absmax_kernel, (unsigned)std::min<size_t>(div_up(nnz ? nnz : 1, 256), cap), 256, 0, ctx->stream, value, nnz, &fs->maxv_bits);
+  WH_LAUNCH(fixed_scale_kernel, 1, 1, 0, ctx->stream, fs, nnz, 1);
+  return WH_OK;
+}
+
 // Scale selection + accumulation only; the caller converts (fixed_finish or the fused push).
 int spmv_trans_accumulate_launch(whContext* ctx, size_t rows, size_t nnz, const size_t* offset,
                                  const uint32_t* index, const float* value, const float* x,

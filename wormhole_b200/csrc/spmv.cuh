@@ -79,6 +79,7 @@ int spmm_trans_times_launch(whContext* ctx, size_t rows, size_t nnz, const size_
                             FixedScale* fs);
 // Chooses the fixed-point scale for terms x * value^vpow (max|x|, max|value| reductions + one tiny kernel).
 int fixed_prepare(whContext* ctx, FixedScale* fs, const float* x, size_t nx, const float* value, size_t nnz, int vpow);
+int fixed_prepare_unit_x(whContext* ctx, FixedScale* fs, const float* value, size_t nnz);   // ... with |x| <= 1 known
 // A whLocalBlock resolved to device pointers.
 struct DevLocal {
   size_t rows = 0, nnz = 0;

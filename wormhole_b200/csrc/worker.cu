@@ -21,6 +21,7 @@
 #include <vector>
 
 #include "batch.cuh"
+#include "direct.cuh"
 #include "hot.cuh"
 #include "loss.cuh"
 #include "server.cuh"
@@ -43,6 +44,7 @@ struct Lane {
   char* pinned = nullptr;    // 512 B of the worker's pinned block
   DevBuf outbox;             // sharded jobs: {U, cuts | keys | grads}, mapped by every peer
   DevBuf hot;                // hot-key state of the lane (hot.cuh): present | rank | w, kHotSlots each
+  DirectLane dx;             // accumulators of the shared-GPU path (direct.cuh)
   bool busy = false, train = false;
   size_t rows = 0;
   // state between wh_worker_begin and wh_worker_finish
@@ -81,13 +83,18 @@ struct whWorker {
   bool hot_enabled = true, hot_tried = false, hot_ready = false;
   int hot_keys = 0;
   long long hot_refresh = 2048, hot_since = 0;
+  // worker and server on one GPU, hashed keys: keys address the shard directly (direct.cuh). WH_DIRECT=0 keeps the
+  // localize -> pull -> forward/backward -> push chain of launches.
+  bool dx_enabled = true, dx_tried = false;
+  wh::DirectTable dx;
+  long long dx_since = 0;
 };
 
 using namespace wh;
 
 static void lane_release(Lane& l) {
   for (DevBuf* b : {&l.in_index, &l.in_offset, &l.in_value, &l.in_label, &l.uniq, &l.index, &l.w, &l.xw, &l.dual,
-                    &l.scal, &l.outbox, &l.hot, &l.cx.directory, &l.cx.scan_tmp, &l.cx.scan_state, &l.cx.acc, &l.cx.small, &l.ax.scan_tmp, &l.ax.small})
+                    &l.scal, &l.outbox, &l.hot, &l.dx.bitmap, &l.dx.part, &l.dx.part_touched, &l.cx.directory, &l.cx.scan_tmp, &l.cx.scan_state, &l.cx.acc, &l.cx.auc, &l.ax.auc, &l.cx.small, &l.ax.scan_tmp, &l.ax.small})
     b->release();
   for (auto& b : l.cx.sort_tmp) b.release();
   for (auto& b : l.ax.sort_tmp) b.release();
@@ -121,6 +128,11 @@ static int lane_init(whWorker* w, int i) {
   WH_TRY(l.cx.small.reserve(1 << 14));
   WH_TRY(l.ax.small.reserve(1 << 14));
   l.pinned = w->pinned.as<char>() + 512 * i;
+  // the AUC histogram of the lane's side context: allocated and zeroed here, so that the first fused kernel (which
+  // adds to it from the main stream) finds it ready
+  void* hist;
+  WH_TRY(auc_scratch_get(&l.ax, &hist));
+  WH_CUDA(cudaStreamSynchronize(l.ax.stream));
   return WH_OK;
 }
 
@@ -135,9 +147,9 @@ static HotView lane_hot_view(const whWorker* w, Lane& l) {
 
 // Census of one minibatch: localize it with counts, bring (key, count) to the host, pick the table. Runs once per
 // worker, synchronously; its only product is the table image (a cache hint -- results never depend on it).
-static int hot_census(whWorker* w, Lane& l, const LocInput& in, size_t ucap) {
+static int hot_census(whWorker* w, Lane& l, const LocInput& in, size_t ucap, bool for_direct) {
   whContext* cx = &l.cx;
-  w->hot_tried = true;
+  if (for_direct) w->dx_tried = true; else w->hot_tried = true;
   DevBuf keys, cnt, idx;
   struct Free { DevBuf *a, *b, *c; ~Free() { a->release(); b->release(); c->release(); } } guard{&keys, &cnt, &idx};
   WH_TRY(keys.reserve(ucap * 8)); WH_TRY(cnt.reserve(ucap * 4)); WH_TRY(idx.reserve(in.nnz * 4));
@@ -151,6 +163,14 @@ static int hot_census(whWorker* w, Lane& l, const LocInput& in, size_t ucap) {
   if (U) {
     WH_CUDA(cudaMemcpy(hk.data(), keys.p, (size_t)U * 8, cudaMemcpyDeviceToHost));
     WH_CUDA(cudaMemcpy(hc.data(), cnt.p, (size_t)U * 4, cudaMemcpyDeviceToHost));
+  }
+  if (for_direct) {
+    // the table is shared by the lanes and single-buffered: let the minibatches in flight finish first
+    for (int i = 0; i < w->depth; ++i) WH_CUDA(cudaStreamSynchronize(w->lane[i].cx.stream));
+    w->dx_since = 0;
+    WH_TRY(direct_table_build(cx, &w->dx, hk.data(), hc.data(), U));
+    w->dx.seen_version = ~0ull;   // the weight mirror has to be filled
+    return WH_OK;
   }
   w->hot_since = 0;
   const int placed = hot_build_image(hk.data(), hc.data(), U, image.data());
@@ -178,6 +198,7 @@ int wh_worker_create_ex(whContext* ctx, whServer* server, int loss, uint64_t max
   w->ctx = ctx; w->server = server; w->loss = loss; w->max_key = max_key; w->depth = depth;
   { const char* e = getenv("WH_HOT"); w->hot_enabled = !(e && atoi(e) == 0); }   // WH_HOT=0: plain kernels only
   { const char* e = getenv("WH_HOT_REFRESH"); if (e) w->hot_refresh = atoll(e); }
+  { const char* e = getenv("WH_DIRECT"); w->dx_enabled = !(e && atoi(e) == 0); }
   int r = w->pinned.reserve(512 * kMaxDepth);
   for (int i = 0; r == WH_OK && i < depth; ++i) r = lane_init(w, i);
   for (int i = 0; r == WH_OK && i <= kMaxDepth; ++i)
@@ -205,6 +226,7 @@ int wh_worker_destroy(whWorker* w) {
   for (auto e : w->ev_served) if (e) cudaEventDestroy(e);
   w->pinned.release();
   w->hot_tags[0].release(); w->hot_tags[1].release();
+  w->dx.release();
   delete w;
   return WH_OK;
 }
@@ -272,11 +294,69 @@ int wh_worker_submit(whWorker* w, const whRowBlock* blk, int mem, size_t nnz, in
   if (train) WH_TRY(ensure_acc(cx, ucap, &acc));
 
   LocInput in{d_index, n, make_xform(w->max_key)};
+  // Worker and server on one GPU, hashed key space, the shard covering all of it: keys address the shard directly,
+  // two launches per minibatch (direct.cu)
+  const bool dx_ok = w->dx_enabled && direct && s->map.world == 1 && s->hslots == 0 && s->key_begin == 0 &&
+                     s->key_end >= w->max_key && n < (1ull << 31) && rows < (1ull << 31) &&
+                     w->max_delay == 0;   // (the accumulators live in the shard: one minibatch adds at a time)
+  if (dx_ok) {
+    const long long dx_refresh = w->hot_refresh > 0 ? std::max<long long>(w->hot_refresh, w->depth + 1) : 0;
+    if (!w->dx_tried || (dx_refresh > 0 && ++w->dx_since >= dx_refresh)) WH_TRY(hot_census(w, l, in, ucap, true));
+  }
+  if (dx_ok && w->dx.ready) {
+    const unsigned long long tk = w->next_ticket;
+    const int ring = kMaxDepth + 1;
+    WH_TRY(direct_lane_prepare(cx, &l.dx, w->max_key));
+    if (tk > 1ull + (unsigned)w->max_delay) WH_CUDA(cudaStreamWaitEvent(cx->stream, w->ev_pushed[(tk - 1 - w->max_delay) % ring], 0));
+    if (w->dx.seen_version != s->version) {
+      // the shard was changed by someone else (wh_server_push / set_state / load, another worker): refill the mirror
+      WH_CUDA(cudaStreamSynchronize(ctx->stream));
+      for (int i = 0; i < w->depth; ++i) WH_CUDA(cudaStreamSynchronize(w->lane[i].cx.stream));
+      WH_TRY(direct_table_refresh_w(cx, &w->dx, s->view().e));
+      w->dx.seen_version = s->version;
+    }
+    WH_TRY(prof_begin(cx));
+    if (d_value && train) { WH_TRY(fixed_prepare_unit_x(cx, fs, d_value, n)); WH_PROF(cx, "value_scale"); }
+    void* hist;
+    WH_TRY(auc_scratch_get(&l.ax, &hist));
+    unsigned nparts = 0;
+    WH_TRY(cx->stage[7].reserve((size_t)ctx->num_sms * 16 + 64));
+    double* po = cx->stage[7].as<double>();
+    unsigned* pc = reinterpret_cast<unsigned*>(po + ctx->num_sms);
+    DirectStep st;
+    st.loss = w->loss; st.train = train != 0; st.rows = rows; st.nnz = n;
+    st.offset = d_offset; st.index = d_index; st.value = d_value; st.label = d_label; st.xf = in.xf;
+    st.shard = s->view().e; st.xw = l.xw.as<float>(); st.part_objv = po; st.part_correct = pc;
+    st.auc_hist = auc_hist_ptr(hist); st.fs = fs; st.counters = s->counters.as<long long>();
+    WH_TRY(direct_fused_launch(cx, st, w->dx, l.dx, &nparts));
+    WH_PROF(cx, "fused_direct");
+    // evaluation partials + AUC on the side stream (nothing downstream of them but the progress numbers)
+    WH_CUDA(cudaEventRecord(l.ev_fork, cx->stream));
+    WH_CUDA(cudaStreamWaitEvent(l.ax.stream, l.ev_fork, 0));
+    WH_TRY(auc_count_launch(&l.ax, rows, d_label, l.xw.as<float>(), d_eval, true, nparts, po, pc));
+    WH_CUDA(cudaEventRecord(l.ev_auc, l.ax.stream));
+    if (train) {
+      if (w->max_delay > 0 && tk > 1) WH_CUDA(cudaStreamWaitEvent(cx->stream, w->ev_pushed[(tk - 1) % ring], 0));
+      WH_TRY(direct_push_launch(s, cx->stream, w->dx, l.dx, fs, w->loss == WH_LOSS_SQUARE_HINGE ? -2.f : 1.f, ctx->num_sms));
+      w->dx.seen_version = s->version;
+      WH_PROF(cx, "push");
+    }
+    WH_CUDA(cudaMemcpyAsync(l.pinned + 256, s->counters.p, 24, cudaMemcpyDeviceToHost, cx->stream));
+    WH_CUDA(cudaEventRecord(w->ev_pushed[tk % ring], cx->stream));
+    WH_CUDA(cudaStreamWaitEvent(cx->stream, l.ev_auc, 0));
+    if (cx->prof.on) WH_TRY(prof_mark(cx, "auc_tail"));
+    WH_CUDA(cudaMemcpyAsync(l.pinned, d_eval, sizeof(EvalOut), cudaMemcpyDeviceToHost, cx->stream));
+    WH_CUDA(cudaEventRecord(l.ev_done, cx->stream));
+    l.busy = true; l.train = train != 0; l.rows = rows;
+    l.ticket = w->next_ticket++;
+    *ticket = l.ticket;
+    return WH_OK;
+  }
   // hot keys (hot.cuh): binary features in a direct-addressed key space
   const bool hot_ok = w->hot_enabled && direct && d_value == nullptr;
   // (a refresh overwrites the image that was current two refreshes ago: the interval must exceed the minibatches in flight)
   const long long refresh = w->hot_refresh > 0 ? std::max<long long>(w->hot_refresh, w->depth + 1) : 0;
-  if (hot_ok && (!w->hot_tried || (refresh > 0 && ++w->hot_since >= refresh))) WH_TRY(hot_census(w, l, in, ucap));
+  if (hot_ok && (!w->hot_tried || (refresh > 0 && ++w->hot_since >= refresh))) WH_TRY(hot_census(w, l, in, ucap, false));
   const bool hot = hot_ok && w->hot_ready;
   const bool fused = hot && train;    // forward + backward in one launch, which is also the rank pass of the localizer
   const HotView hv = lane_hot_view(w, l);
@@ -298,7 +378,7 @@ int wh_worker_submit(whWorker* w, const whRowBlock* blk, int mem, size_t nnz, in
   const bool emit_pull = fused && s->map.world == 1 && s->hslots == 0 && pull_at_emit_supported(cx, w->max_key);
   PullAtEmit pe;
   if (emit_pull) {
-    pe.table = s->table.p; pe.algo = s->algo; pe.key_begin = s->key_begin; pe.key_end = s->key_end;
+    pe.table = s->view().e; pe.algo = s->algo; pe.key_begin = s->key_begin; pe.key_end = s->key_end;
     pe.w = l.w.as<float>(); pe.counters = s->counters.as<long long>();
     if (tk > 1ull + (unsigned)w->max_delay) pe.after = w->ev_pushed[(tk - 1 - w->max_delay) % ring];
   }
