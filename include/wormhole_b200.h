@@ -168,7 +168,9 @@ WH_API int wh_bin_eval(whContext* ctx, const float* label, const float* predict,
  * (learn/linear/loss.h:32-49,81-115,128-156,172-182).
  * prog[6] = {objv, acc, auc, count, new_ex, new_w} (learn/linear/progress.h:28-34), host memory.
  * grad[U] (NULL: skip CalcGrad), xw[rows] and dual[rows] (NULL: not returned) follow `mem`.
- * WH_LOSS_SQUARE is unimplemented in the reference (loss.h:163-166,178-180) and fails here too. */
+ * WH_LOSS_SQUARE: declared by the reference (learn/linear/config.proto:30-34, "1/2 (p - y)^2") but never implemented
+ * there (loss.h:163-166 is an empty TODO, CreateLoss :178-180 aborts). Implemented here as the declaration reads, with
+ * y = +-1 as in the other losses: dual = p - y, objective = sum 1/2 (p - y)^2. It has no reference to be checked against. */
 WH_API int wh_linear_loss(whContext* ctx, int loss, const whLocalBlock* D, int mem, const float* w,
                           size_t U, double* prog, float* grad, float* xw, float* dual);
 
@@ -250,6 +252,11 @@ WH_API int wh_worker_destroy(whWorker* w);
  * worker's own earlier pushes (learn/solver/minibatch_solver.h:307-311); pushes are still applied in order.
  * Needs d < depth. Sharded jobs: after wh_worker_ipc_attach only, and the same d on every rank. */
 WH_API int wh_worker_set_max_delay(whWorker* w, int max_delay);
+/* The worker's table of frequent keys (a cache of the stream's most popular transformed keys, built from a census of one
+ * of its minibatches; it changes the speed, never the numbers): the keys it holds (up to cap; *n = how many there are),
+ * the wall-clock cost of the last census and how many were taken. No counterpart in the reference; bench.py reports the
+ * hit rate with it. */
+WH_API int wh_worker_table_keys(whWorker* w, uint32_t* keys, size_t cap, size_t* n, double* census_ms, int* censuses);
 WH_API int wh_worker_submit(whWorker* w, const whRowBlock* blk, int mem, size_t nnz, int train,
                             uint64_t* ticket);
 WH_API int wh_worker_wait(whWorker* w, uint64_t ticket, double* prog);

@@ -73,15 +73,15 @@ def _rank_main(rank, world, port_no, out_dir):
     dist.destroy_process_group()
 
 
-def test_two_gpus_match_the_cpu_simulation(tmp_path):
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_gpus_match_the_cpu_simulation(tmp_path, world):
     import torch
-    if torch.cuda.device_count() < 2:
-        pytest.skip("needs two GPUs (gpurun --gpus 2)")
+    if torch.cuda.device_count() < world:
+        pytest.skip("needs %d GPUs (gpurun --gpus %d)" % (world, world))
     import torch.multiprocessing as mp
     from oracle import oracle as O
     from wormhole_b200.dist import key_range
     s = socket.socket(); s.bind(("127.0.0.1", 0)); port_no = s.getsockname()[1]; s.close()
-    world = 2
     mp.spawn(_rank_main, args=(world, port_no, str(tmp_path)), nprocs=world, join=True)
     # the same message order on the CPU checker: pulls see the model as of the previous step, pushes
     # are applied per (owner, source) in ascending source order, SGD's t advances per push message
@@ -150,19 +150,19 @@ def _p2p_rank_main(rank, world, port_no, out_dir, algo, owner_push):
     dist.destroy_process_group()
 
 
+@pytest.mark.parametrize("world", [2, 4, 8])
 @pytest.mark.parametrize("owner_push", [False, True])
 @pytest.mark.parametrize("algo_name", ["FTRL", "SGD"])
-def test_two_gpus_peer_mapped_shards(tmp_path, algo_name, owner_push):
+def test_gpus_peer_mapped_shards(tmp_path, algo_name, owner_push, world):
     import torch
-    if torch.cuda.device_count() < 2:
-        pytest.skip("needs two GPUs (gpurun --gpus 2)")
+    if torch.cuda.device_count() < world:
+        pytest.skip("needs %d GPUs (gpurun --gpus %d)" % (world, world))
     import torch.multiprocessing as mp
     from oracle import oracle as O
     from wormhole_b200 import capi
     from wormhole_b200.dist import key_range
     algo = {"FTRL": capi.ALGO_FTRL, "SGD": capi.ALGO_SGD}[algo_name]
     s = socket.socket(); s.bind(("127.0.0.1", 0)); port_no = s.getsockname()[1]; s.close()
-    world = 2
     mp.spawn(_p2p_rank_main, args=(world, port_no, str(tmp_path), algo, owner_push), nprocs=world, join=True)
     # CPU checker, same order: all pulls of a step see the model as of the previous step; shard s then takes
     # the pushes one handle update each -- of sources s, s-1, ... (mod world) when the workers push in turns, of
@@ -195,3 +195,27 @@ def test_two_gpus_peer_mapped_shards(tmp_path, algo_name, owner_push):
                 continue
             assert_state_close(got[name], ref[b:e], what="p2p " + name, stragglers=STRAGGLERS, flip_abs=FLIP_ABS)
         assert abs(int(got["nnz"]) - int((W[b:e] != 0).sum())) <= 2
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+@pytest.mark.parametrize("algo,loss", [("ftrl", "logit"), ("sgd", "sqhinge")])
+def test_bench_configuration_parity_leg(world, algo, loss):
+    """The path bench.py times at N > 1 -- 2^24 hashed keys, Criteo-shape minibatches, table-key codes, owner-served
+    pull, cooperative apply, four minibatches in flight -- against the CPU simulation, through bench.py's own parity_check
+    leg (20 000-row minibatches keep the checker's share short; the SCALE run repeats it at 100 000)."""
+    import json
+    import subprocess
+    import sys
+    import torch
+    if torch.cuda.device_count() < world:
+        pytest.skip("needs %d GPUs (gpurun --gpus %d)" % (world, world))
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port_no = s.getsockname()[1]; s.close()
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(world), "--master-addr", "127.0.0.1",
+           "--master-port", str(port_no), os.path.join(root, "bench.py"), "--gpus", str(world), "--steps", "4", "--warmup", "3",
+           "--rows", "20000", "--pool", "4", "--algo", algo, "--loss", loss, "--no-others", "--no-cpu"]
+    out = subprocess.run(cmd, capture_output=True, text=True, timeout=900, cwd=root)
+    assert out.returncode == 0, out.stderr[-2000:]
+    line = json.loads([l for l in out.stdout.splitlines() if l.startswith("{")][-1])
+    pc = line["parity_check"]
+    assert pc["ok"] and pc["ranks"] == world and pc["values_compared"] > 10000, pc

@@ -194,3 +194,16 @@ def test_direct_criteo_shape_vs_checker(gpu, checker):
     for name, x, y in zip(("w", "z", "cg"), srv.get_state(keys), (w, z, cg)):
         assert_state_close(x, y, what="direct criteo " + name, stragglers=STRAGGLERS, flip_abs=FLIP_ABS)
     wk.close(); srv.close(); checker.linear_destroy(job)
+
+
+def test_bench_line_parity_leg_one_gpu():
+    """bench.py's own parity_check leg at N = 1 (the shared-GPU step against the checker, outside the timed regions)."""
+    import json
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--steps", "4", "--warmup", "3", "--rows", "20000",
+                          "--pool", "4", "--no-others", "--no-cpu"], capture_output=True, text=True, timeout=600, cwd=root)
+    assert out.returncode == 0, out.stderr[-2000:]
+    line = json.loads([l for l in out.stdout.splitlines() if l.startswith("{")][-1])
+    assert line["parity_check"]["ok"] and line["gpu_launches"] > 0 and line["hot"]["keys_placed"] > 0, line

@@ -138,7 +138,43 @@ def test_errors_are_reported(gpu):
     with pytest.raises(capi.WormholeError):
         gpu.localize(blk, 2 ** 40, method=capi.LOC_DIRECT)   # direct addressing needs a hashed space
     with pytest.raises(capi.WormholeError):
-        gpu.linear_loss(capi.LOSS_SQUARE, gpu.localize(blk), np.zeros(1, np.float32))  # loss.h:178-180
+        gpu.linear_loss(3, gpu.localize(blk), np.zeros(1, np.float32))  # not a Config::Loss value (loss.h:178-180)
+
+
+def test_square_loss_closed_form(gpu, checker):
+    """Config::SQUARE = 1/2 (p - y)^2 (learn/linear/config.proto:30-34). The reference declares it and never implemented
+    it (learn/linear/loss.h:163-166), so there is NO ORACLE: the device is held to the closed form in fp64 -- dual = Xw - y,
+    grad = X^T dual, objv = sum 1/2 dual^2 -- standalone and through the worker (AdaGrad update via the checker's handle)."""
+    from oracle import oracle as O
+    rng = np.random.default_rng(77)
+    max_key = 2 ** 20
+    srv = capi.Server(gpu, capi.ALGO_ADAGRAD, 0.01, 0.1, 0.1, 1.0, 0, max_key)
+    wk = capi.Worker(gpu, srv, capi.LOSS_SQUARE, max_key)
+    W, CG = np.zeros(max_key, np.float32), np.zeros(max_key, np.float32)
+    for m in range(4):
+        blk = random_block(rng, 3000, 12, 20000, with_value=(m % 2 == 1), empty_rows=False)
+        D = checker.localize(blk, max_key)
+        keys = D.uniq.astype(np.int64)
+        w = W[keys].copy()
+        prog, grad = gpu.linear_loss(capi.LOSS_SQUARE, D, w)[:2]
+        rows = np.repeat(np.arange(D.rows), np.diff(D.offset.astype(np.int64)))
+        val = np.ones(len(D.index)) if D.value is None else D.value.astype(np.float64)
+        xw = np.zeros(D.rows); np.add.at(xw, rows, w[D.index].astype(np.float64) * val)
+        y = np.where(D.label > 0, 1.0, -1.0)
+        dual = xw - y
+        g = np.zeros(len(keys)); np.add.at(g, D.index, dual[rows] * val)
+        absg = np.zeros(len(keys)); np.add.at(absg, D.index, np.abs(dual[rows] * val))
+        assert np.all(np.abs(grad - g) <= 1e-5 * absg + 1e-6)
+        assert abs(prog[0] - 0.5 * (dual ** 2).sum()) <= 1e-5 * 0.5 * (dual ** 2).sum()
+        pg = wk.process_minibatch(blk)
+        assert abs(pg[0] - prog[0]) <= 1e-9 * abs(prog[0]) and pg[4] == D.rows
+        cg = CG[keys].copy()
+        checker.handle_push(O.ALGO_ADAGRAD, 0.01, 0.1, 0.1, 1.0, grad.astype(np.float32), w, None, cg, 1)
+        W[keys], CG[keys] = w, cg
+        gw, _, gcg = srv.get_state(D.uniq)
+        assert_state_close(gw, w, what="square w", stragglers=STRAGGLERS, flip_abs=FLIP_ABS)
+        assert_state_close(gcg, cg, what="square cg", stragglers=STRAGGLERS, flip_abs=FLIP_ABS)
+    wk.close(); srv.close()
 
 
 # ---------------------------------------------------------------- (2)/(5) SpMV, SpMM -------

@@ -366,6 +366,13 @@ class Worker:
     def set_max_delay(self, d):
         _check(lib().wh_worker_set_max_delay(self.h, C.c_int(d)))
 
+    def table_keys(self):
+        """-> (keys held by the worker's table of frequent keys, ms the last census took, censuses taken)."""
+        keys = np.zeros(16384, np.uint32)
+        n, ms, cnt = C.c_size_t(), C.c_double(), C.c_int()
+        _check(lib().wh_worker_table_keys(self.h, _ptr(keys), C.c_size_t(len(keys)), C.byref(n), C.byref(ms), C.byref(cnt)))
+        return keys[:min(n.value, len(keys))], ms.value, cnt.value
+
     def submit(self, blk, train=True, mem=WH_HOST, nnz=0):
         """Enqueue one minibatch (up to `depth` in flight); returns a ticket for wait()."""
         t = C.c_uint64()

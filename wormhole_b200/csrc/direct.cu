@@ -452,7 +452,8 @@ int direct_table_build(whContext* ctx, DirectTable* t, const uint64_t* keys, con
     return counts[x] != counts[y] ? counts[x] > counts[y] : keys[x] < keys[y];
   });
   int placed = 0;
-  for (size_t i = 0; i < want; ++i) {
+  const char* off = getenv("WH_DX_TABLE");   // WH_DX_TABLE=0: an empty table, every key takes the general route (bench.py's comparison)
+  for (size_t i = 0; i < want && !(off && atoi(off) == 0); ++i) {
     const uint64_t k = keys[order[i]];
     if (counts[order[i]] < 2 || k >= (1ull << 28)) continue;
     const unsigned k32 = (unsigned)k, b = (k32 * 0x9E3779B1u) >> (32 - 10);
@@ -530,7 +531,6 @@ int direct_fused_launch(whContext* ctx, const DirectStep& st, const DirectTable&
   ecap = std::max<size_t>(64, ecap & ~(size_t)3);
   WH_REQUIRE(fixed + ecap * per_entry * ng <= budget, "direct_fused_launch: %zu bytes of shared memory", fixed + ecap * per_entry * ng);
   const size_t smem = fixed + ecap * per_entry * ng;
-  WH_TRY(ctx->stage[7].reserve((size_t)grid * 16 + 64));
   DxArgs a;
   a.loss = st.loss; a.rows = (unsigned)st.rows; a.rows_per_block = rpb; a.ecap = (unsigned)ecap;
   a.offset = st.offset; a.index = st.index; a.value = st.value; a.label = st.label; a.xf = st.xf; a.shard = st.shard;

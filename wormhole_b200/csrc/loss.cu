@@ -875,8 +875,7 @@ int wh_bin_eval(whContext* ctx, const float* label, const float* predict, size_t
 int wh_linear_loss(whContext* ctx, int loss, const whLocalBlock* D, int mem, const float* w, size_t U,
                    double* prog, float* grad, float* xw, float* dual) {
   WH_REQUIRE(ctx && D && prog, "wh_linear_loss: NULL argument");
-  WH_REQUIRE(loss == WH_LOSS_LOGIT || loss == WH_LOSS_SQUARE_HINGE,
-             "wh_linear_loss: unknown loss type %d (SQUARE is unimplemented in the reference, learn/linear/loss.h:163-180)", loss);
+  WH_REQUIRE(loss == WH_LOSS_LOGIT || loss == WH_LOSS_SQUARE_HINGE || loss == WH_LOSS_SQUARE, "wh_linear_loss: unknown loss type %d", loss);
   DeviceGuard g(ctx->device);
   DevLocal d;
   WH_TRY(stage_local(ctx, D, mem, &d));

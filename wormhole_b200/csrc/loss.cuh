@@ -55,6 +55,13 @@ __device__ __forceinline__ void loss_row(int loss, float lab, float p, float* du
   if (loss == WH_LOSS_LOGIT) {
     *dual = -y / (1.f + exp_rn(y * p));
     *objv = (double)log_rn(1.f + exp_rn(-y * p));
+  } else if (loss == WH_LOSS_SQUARE) {
+    // learn/linear/config.proto:30-34 declares SQUARE = 1 as 1/2 (p - y)^2; the reference never implemented it
+    // (learn/linear/loss.h:163-166 is an empty TODO, CreateLoss :178-180 aborts). Here: y = +-1 like the other losses,
+    // dual = d/dp = p - y, objective = 1/2 (p - y)^2. No reference to compare with; tests hold it to the closed form.
+    const float d = p - y;
+    *dual = d;
+    *objv = 0.5 * (double)(d * d);
   } else {
     *dual = y * ((y * p > 1.0f) ? 1.f : 0.f);
     const float t = fmaxf(1.f - y * p, 0.f);

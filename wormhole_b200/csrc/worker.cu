@@ -17,6 +17,7 @@
 #include <stdlib.h>
 
 #include <algorithm>
+#include <chrono>
 
 #include <vector>
 
@@ -88,6 +89,8 @@ struct whWorker {
   bool dx_enabled = true, dx_tried = false;
   wh::DirectTable dx;
   long long dx_since = 0;
+  double census_ms = 0;      // wall time of the last census (either table), for wh_worker_table_keys
+  int census_count = 0;
 };
 
 using namespace wh;
@@ -150,6 +153,9 @@ static HotView lane_hot_view(const whWorker* w, Lane& l) {
 static int hot_census(whWorker* w, Lane& l, const LocInput& in, size_t ucap, bool for_direct) {
   whContext* cx = &l.cx;
   if (for_direct) w->dx_tried = true; else w->hot_tried = true;
+  const auto t_begin = std::chrono::steady_clock::now();
+  struct Timer { whWorker* w; std::chrono::steady_clock::time_point t0;
+                 ~Timer() { w->census_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count(); w->census_count++; } } timer{w, t_begin};
   DevBuf keys, cnt, idx;
   struct Free { DevBuf *a, *b, *c; ~Free() { a->release(); b->release(); c->release(); } } guard{&keys, &cnt, &idx};
   WH_TRY(keys.reserve(ucap * 8)); WH_TRY(cnt.reserve(ucap * 4)); WH_TRY(idx.reserve(in.nnz * 4));
@@ -189,8 +195,7 @@ extern "C" {
 int wh_worker_create_ex(whContext* ctx, whServer* server, int loss, uint64_t max_key, int depth, whWorker** out) {
   WH_REQUIRE(ctx && out, "wh_worker_create: NULL argument");
   WH_REQUIRE(server == nullptr || server->ctx == ctx, "wh_worker_create: server lives on another context");
-  WH_REQUIRE(loss == WH_LOSS_LOGIT || loss == WH_LOSS_SQUARE_HINGE,
-             "wh_worker_create: unknown loss type %d (SQUARE is unimplemented in the reference, learn/linear/loss.h:163-180)", loss);
+  WH_REQUIRE(loss == WH_LOSS_LOGIT || loss == WH_LOSS_SQUARE_HINGE || loss == WH_LOSS_SQUARE, "wh_worker_create: unknown loss type %d", loss);
   WH_REQUIRE(max_key != 0, "wh_worker_create: max_key must be positive");
   WH_REQUIRE(depth >= 1 && depth <= kMaxDepth, "wh_worker_create: depth %d outside [1, %d]", depth, kMaxDepth);
   DeviceGuard g(ctx->device);
@@ -232,6 +237,22 @@ int wh_worker_destroy(whWorker* w) {
 }
 
 int wh_worker_wait(whWorker* w, uint64_t ticket, double* prog);
+
+int wh_worker_table_keys(whWorker* w, uint32_t* keys, size_t cap, size_t* n, double* census_ms, int* censuses) {
+  WH_REQUIRE(w && n, "wh_worker_table_keys: NULL argument");
+  DeviceGuard g(w->ctx->device);
+  *n = 0;
+  if (census_ms) *census_ms = w->census_ms;
+  if (censuses) *censuses = w->census_count;
+  const void* src = nullptr; size_t slots = 0;
+  if (w->dx.ready) { src = w->dx.tags.p; slots = kDxSlots; }
+  else if (w->hot_ready) { src = w->hot_tags[w->hot_cur].p; slots = kHotSlots; }
+  if (!src) return WH_OK;
+  std::vector<uint32_t> img(slots);
+  WH_CUDA(cudaMemcpy(img.data(), src, slots * 4, cudaMemcpyDeviceToHost));
+  for (uint32_t k : img) if (k != 0xffffffffu) { if (keys && *n < cap) keys[*n] = k; ++*n; }
+  return WH_OK;
+}
 
 int wh_worker_set_max_delay(whWorker* w, int max_delay) {
   WH_REQUIRE(w && max_delay >= 0 && max_delay < w->depth, "wh_worker_set_max_delay: needs 0 <= max_delay < depth");
@@ -298,7 +319,8 @@ int wh_worker_submit(whWorker* w, const whRowBlock* blk, int mem, size_t nnz, in
   // two launches per minibatch (direct.cu)
   const bool dx_ok = w->dx_enabled && direct && s->map.world == 1 && s->hslots == 0 && s->key_begin == 0 &&
                      s->key_end >= w->max_key && n < (1ull << 31) && rows < (1ull << 31) &&
-                     w->max_delay == 0;   // (the accumulators live in the shard: one minibatch adds at a time)
+                     w->max_delay == 0 &&   // (the accumulators live in the shard: one minibatch adds at a time)
+                     w->loss != WH_LOSS_SQUARE;   // (|dual| <= 1 sizes the fixed point up front; the square loss has no such bound)
   if (dx_ok) {
     const long long dx_refresh = w->hot_refresh > 0 ? std::max<long long>(w->hot_refresh, w->depth + 1) : 0;
     if (!w->dx_tried || (dx_refresh > 0 && ++w->dx_since >= dx_refresh)) WH_TRY(hot_census(w, l, in, ucap, true));
@@ -320,9 +342,9 @@ int wh_worker_submit(whWorker* w, const whRowBlock* blk, int mem, size_t nnz, in
     void* hist;
     WH_TRY(auc_scratch_get(&l.ax, &hist));
     unsigned nparts = 0;
-    WH_TRY(cx->stage[7].reserve((size_t)ctx->num_sms * 16 + 64));
+    WH_TRY(cx->stage[7].reserve((size_t)kDxMaxBlocks * 16 + 64));   // (a block per SM and wave, direct.cu)
     double* po = cx->stage[7].as<double>();
-    unsigned* pc = reinterpret_cast<unsigned*>(po + ctx->num_sms);
+    unsigned* pc = reinterpret_cast<unsigned*>(po + kDxMaxBlocks);
     DirectStep st;
     st.loss = w->loss; st.train = train != 0; st.rows = rows; st.nnz = n;
     st.offset = d_offset; st.index = d_index; st.value = d_value; st.label = d_label; st.xf = in.xf;
@@ -353,7 +375,7 @@ int wh_worker_submit(whWorker* w, const whRowBlock* blk, int mem, size_t nnz, in
     return WH_OK;
   }
   // hot keys (hot.cuh): binary features in a direct-addressed key space
-  const bool hot_ok = w->hot_enabled && direct && d_value == nullptr;
+  const bool hot_ok = w->hot_enabled && direct && d_value == nullptr && w->loss != WH_LOSS_SQUARE;
   // (a refresh overwrites the image that was current two refreshes ago: the interval must exceed the minibatches in flight)
   const long long refresh = w->hot_refresh > 0 ? std::max<long long>(w->hot_refresh, w->depth + 1) : 0;
   if (hot_ok && (!w->hot_tried || (refresh > 0 && ++w->hot_since >= refresh))) WH_TRY(hot_census(w, l, in, ucap, false));
@@ -416,7 +438,7 @@ int wh_worker_submit(whWorker* w, const whRowBlock* blk, int mem, size_t nnz, in
   WH_PROF(cx, "pull");
   // Init (Xw), the per-example part of Evaluate, and the dual of CalcGrad: one pass over the rows. With
   // binary features |dual| <= 1 bounds every term of X^T dual, so the fixed-point scale is known up front.
-  const bool scale_ready = d_value == nullptr;
+  const bool scale_ready = d_value == nullptr && w->loss != WH_LOSS_SQUARE;
   if (hot && !fused) WH_TRY(hot_w_launch(cx, hv, pulled));   // evaluation: the slot-indexed weights for spmv_loss
   if (fused) {
     // ... and with the hot-key table the transposed product rides in the same launch (spmv.cu)

@@ -79,11 +79,20 @@ class SquareHingeLoss : public BinClassLoss<V> {
   int Type() const override { return WH_LOSS_SQUARE_HINGE; }
 };
 
-/// learn/linear/loss.h:172-182. SQUARE is an empty TODO in the reference (:163-166) and fatal here too.
+/// square loss 1/2 (p - y)^2 as learn/linear/config.proto:30-34 declares it. The reference's class is an empty TODO
+/// (learn/linear/loss.h:163-166) and its CreateLoss aborts on it (:178-180); this one computes it (no reference to compare).
+template <typename V>
+class SquareLoss : public ScalarLoss<V> {
+ protected:
+  int Type() const override { return WH_LOSS_SQUARE; }
+};
+
+/// learn/linear/loss.h:172-182
 template <typename V>
 static ScalarLoss<V>* CreateLoss(Config::Loss loss) {
   switch (loss) {
     case Config::LOGIT: return new LogitLoss<V>();
+    case Config::SQUARE: return new SquareLoss<V>();
     case Config::SQUARE_HINGE: return new SquareHingeLoss<V>();
     default: fprintf(stderr, "[FATAL] unknown type: %d\n", (int)loss); abort();
   }
