@@ -78,7 +78,9 @@ WH_API const char* wh_version(void);
 WH_API uint64_t wh_kernel_launches(void);
 WH_API int wh_create(int device, whContext** out);
 WH_API int wh_destroy(whContext* ctx);
-/* Use an existing CUDA stream (cudaStream_t as void*) instead of the context's own. */
+/* Use an existing CUDA stream (cudaStream_t as void*) instead of the context's own. Synchronises the old stream first.
+ * Workers created on the context follow: their first lane rides the context's stream, whichever it is at each call.
+ * Callers that mix their own device work with WH_DEVICE calls (which only enqueue) must use this stream for it. */
 WH_API int wh_set_stream(whContext* ctx, void* cuda_stream);
 WH_API int wh_sync(whContext* ctx);
 /* Opt-in timing of the library's own kernels with CUDA events on the context's stream (what
@@ -289,7 +291,8 @@ WH_API int wh_worker_process_minibatch(whWorker* w, const whRowBlock* blk, int m
                                        double* prog);
 
 /* ---- (4b) the reader in front of the path ------------------------------- */
-/* Text formats of MinibatchIter (learn/base/minibatch_iter.h:44-59). "crb" (lz4 + recordio) is not built. */
+/* Formats of MinibatchIter (learn/base/minibatch_iter.h:44-59): the text formats below through wh_parse_text, "crb"
+ * (CompressedRowBlock records in RecordIO framing) through wh_parse_crb. */
 enum { WH_FMT_LIBSVM = 0, WH_FMT_CRITEO = 1, WH_FMT_CRITEO_TEST = 2, WH_FMT_ADFEA = 3 };
 typedef struct whRows whRows; /* a device-resident dmlc::data::RowBlockContainer<uint64_t> */
 /* ParseNext of one chunk of text (whole lines; host or device memory, < 4 GiB) on the GPU:
@@ -299,11 +302,23 @@ typedef struct whRows whRows; /* a device-resident dmlc::data::RowBlockContainer
  *   adfea                 AdfeaParser::ParseNext, learn/base/adfea_parser.h:38-82, one row per line: `lineid count label
  *                         idx:gid ...`; index = idx >> 10 | gid << 54, label = (first character of the label token == '1').
  * Where the reference would read past the end of a line or CHECK-fail (short lines, categorical fields that are not
- * 8 bytes) the call fails with WH_ERR_INVALID and names the line; numeric literals that cannot be converted exactly
- * with one double operation (> 15 digits or |exponent| > 22) are refused rather than rounded differently.
+ * 8 bytes) the call fails with WH_ERR_INVALID and names the line. Numeric literals are converted like strtod / atof
+ * (correctly rounded; literals of 16 and more digits or large exponents through exact big-integer arithmetic); only
+ * inf / nan / hexadecimal literals are refused.
  * *out == NULL on entry: a new container is returned; otherwise that container is cleared and refilled, reusing
  * its device buffers (no allocation in steady state). */
 WH_API int wh_parse_text(whContext* ctx, int format, const char* text, size_t len, int mem, whRows** out);
+/* CRBParser::ParseNext, learn/base/crb_parser.h:27-40, for every record of a chunk: `data` (HOST memory) holds whole
+ * RecordIO records (dmlc/recordio.h framing: magic 0xced7230a, {cflag:3 | length:29}, payload padded to 4 bytes; split
+ * records are re-joined), each a CompressedRowBlock (learn/base/compressed_row_block.h:44-69,116-137: magic, index
+ * size -- 8 here --, row count, then label / offset / index / value / weight as {int size, LZ4 block}). The LZ4 blocks
+ * are decoded on the host (a strictly sequential byte code) and the rows appended to the device container; a value
+ * array of all ones was already dropped by the writer (:27-35). Same *out convention as wh_parse_text. */
+WH_API int wh_parse_crb(whContext* ctx, const char* data, size_t len, whRows** out);
+/* The LZ4 block decoder wh_parse_crb uses in place of lz4's LZ4_decompress_safe (compressed_row_block.h:121-123; lz4 is
+ * not vendored by the reference): decodes one block into dst[0, cap), returns the decoded size or -1 on malformed
+ * input. Host memory, no GPU involved. */
+WH_API long wh_lz4_block_decode(const void* src, size_t n, void* dst, size_t cap);
 /* RowBlockContainer: Clear / Push(RowBlock slice) / Push(Row) / GetBlock, as MinibatchIter::Next uses them
  * (learn/base/minibatch_iter.h:74-147). append takes rows [begin, begin+n) of src, or the n rows listed in the HOST
  * array row_ids (the shuffled order rdp_[i], :102-110). drop_unit_values is the all-ones rule (:116-118).

@@ -178,3 +178,52 @@ def minibatches(chunks, mb_size, shuf_buf=0, neg_sampling=1.0, rand=None):
         if mb.rows == 0:
             return                                                  # :122 out_blk_.size > 0
         yield mb
+
+
+# ---- crb: CompressedRowBlock::Compress (learn/base/compressed_row_block.h:18-49,100-112) + dmlc-core's RecordIOWriter ----
+# Test infrastructure like the rest of oracle/. LZ4 itself is not restated: the blocks are compressed by liblz4 through
+# pyarrow's "lz4_raw" codec (LZ4's block format), which is what pins the library's own decoder.
+CRB_MAGIC, RECORDIO_MAGIC = 1196140743, 0xced7230a
+
+
+def lz4_block(data):
+    import pyarrow as pa
+    return pa.compress(data, codec="lz4_raw", asbytes=True)
+
+
+def crb_record(blk):
+    """One RowBlock -> the bytes CompressedRowBlock::Compress<uint64_t> appends to its string."""
+    import struct
+    nrows = blk.rows
+    off = np.ascontiguousarray(blk.offset, np.uint64)
+    nnz = int(off[-1] - off[0])
+    value = blk.value
+    if value is not None and np.all(value[:nnz] == 1):
+        value = None                                    # :27-35
+    out = [struct.pack("<iii", CRB_MAGIC, 8, nrows)]
+    for arr in (np.ascontiguousarray(blk.label, np.float32), off, np.ascontiguousarray(blk.index, np.uint64),
+                None if value is None else np.ascontiguousarray(value, np.float32), None):   # weight: NULL
+        if arr is None:
+            out.append(struct.pack("<i", 0))
+        else:
+            c = lz4_block(arr.tobytes())
+            out.append(struct.pack("<i", len(c)) + c)
+    return b"".join(out)
+
+
+def recordio_write(records):
+    """dmlc::RecordIOWriter::WriteRecord (dmlc-core, un-vendored; restated from its published format): a payload that holds
+    the magic at a 4-byte boundary is split there into parts flagged 1 / 2 / 3, otherwise one part flagged 0."""
+    import struct
+    magic = struct.pack("<I", RECORDIO_MAGIC)
+    out = []
+    for rec in records:
+        cuts = [i for i in range(0, len(rec) - 3, 4) if rec[i:i + 4] == magic]
+        parts, last = [], 0
+        for c in cuts:
+            parts.append(rec[last:c]); last = c + 4
+        parts.append(rec[last:])
+        for k, part in enumerate(parts):
+            flag = 0 if len(parts) == 1 else (1 if k == 0 else (3 if k == len(parts) - 1 else 2))
+            out.append(magic + struct.pack("<I", (flag << 29) | len(part)) + part + b"\0" * (-len(part) % 4))
+    return b"".join(out)

@@ -33,6 +33,22 @@ def same(a, b):
         assert np.array_equal(a.value.view(np.uint32), b.value.view(np.uint32))
 
 
+def test_long_literals_like_atof(gpu):
+    """Values written with repr(float) / "%.17g" (17 significant digits), with exponents beyond +-22, with 40 digits, and
+    around the float range: bit-identical to the checker's atof (learn/base/criteo_parser.h / dmlc-core's libsvm parser)."""
+    rng = np.random.default_rng(5)
+    vals = [repr(float(x)) for x in rng.standard_normal(400)]
+    vals += ["%.17g" % x for x in rng.standard_normal(400) * 10.0 ** rng.integers(-30, 30, 400)]
+    vals += ["0.30000000000000004", "1e-30", "1E+30", "2.5e-40", "3e38", "4e38", "1e-46", "7e-46", "123456789012345678901234567890.5e-10",
+             "0.00000000000000000000000000000000000012345678901234567", "9007199254740993", "9007199254740992.5", "1.7976931348623157e308",
+             "4.9406564584124654e-324", "1e400", "1e-400", "00012.5000e+01", ".5e1", "5.e-1"]
+    lines = []
+    for i in range(0, len(vals), 4):
+        lines.append("%s " % vals[i] + " ".join("%d:%s" % (7 * i + j, v) for j, v in enumerate(vals[i:i + 4])))
+    text = ("\n".join(lines) + "\n").encode()
+    same(capi.parse_text(gpu, "libsvm", text).to_host(), PortIO().parse_libsvm(text))
+
+
 @pytest.mark.parametrize("crlf,trail", [(False, True), (True, True), (False, False)])
 def test_criteo_parse_bit_exact(gpu, crlf, trail):
     text = criteo_text(np.random.default_rng(21), 5000, crlf=crlf, trailing_newline=trail)
@@ -55,8 +71,10 @@ def test_malformed_criteo_lines_are_named(gpu):
     for bad in (b"1\t5\t5\n", good.replace(b"0a1b2c3d\n", b"0a1b\n"), good[:-1] + b"\textra\n"):
         with pytest.raises(capi.WormholeError, match="line 3"):
             capi.parse_text(gpu, "criteo", good + good + bad + good)
-    with pytest.raises(capi.WormholeError, match="exactly convertible"):
-        capi.parse_text(gpu, "libsvm", b"1 3:0.12345678901234567890\n")
+    with pytest.raises(capi.WormholeError, match="inf / nan / hex"):
+        capi.parse_text(gpu, "libsvm", b"1 3:0x1p3\n")
+    v = capi.parse_text(gpu, "libsvm", b"1 3:0.12345678901234567890\n").to_host().value   # long literals convert like atof
+    assert v[0] == np.float32(0.12345678901234567890)
     with pytest.raises(capi.WormholeError, match="some features"):
         capi.parse_text(gpu, "libsvm", b"1 3:1 4\n")
 

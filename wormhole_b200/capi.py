@@ -515,6 +515,14 @@ class Rows:
     __del__ = close
 
 
+def parse_crb(ctx, data, into=None):
+    """wh_parse_crb: one chunk of whole RecordIO records of CompressedRowBlocks (host bytes) -> Rows."""
+    h = C.c_void_p() if into is None else into.h
+    buf = (C.c_char * len(data)).from_buffer_copy(data)
+    _check(lib().wh_parse_crb(ctx.h, C.cast(buf, C.c_void_p), C.c_size_t(len(data)), C.byref(h)))
+    return Rows(ctx, h) if into is None else into
+
+
 def parse_text(ctx, fmt, text, mem=WH_HOST, length=None, into=None):
     """wh_parse_text: one chunk of whole lines -> Rows. text: bytes / numpy uint8 (host) or a device address with
     `length`. into: a Rows to refill (its buffers are reused) instead of creating one."""

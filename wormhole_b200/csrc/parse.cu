@@ -67,24 +67,97 @@ __device__ uint64_t cityhash64_short(const char* s, int len) {
 
 // ---- numbers ------------------------------------------------------------------------------------------------
 // atof on [p, end): sign, digits, fraction, exponent; anything after the longest valid prefix is ignored and no
-// digits at all give 0, as strtod does. The value is formed as M * 10^e with ONE correctly rounded double
-// operation, which equals strtod whenever M < 2^53 and |e| <= 22; literals outside that range, and inf / nan /
-// hex floats, set *bad (the call then fails instead of returning a differently rounded number).
+// digits at all give 0, as strtod does. Fast path: the value is formed as M * 10^e with ONE correctly rounded double
+// operation, which equals strtod whenever M < 2^53 and |e| <= 22. Everything else -- 16 and more significant digits
+// (repr(float), "%.17g"), exponents beyond +-22 -- takes the exact path below: big-integer arithmetic on up to 36
+// significant digits (further ones only feed the sticky bit), rounded to nearest-even once, like strtod. Every caller
+// stores the result as float, so magnitudes beyond the float range return +-inf and below it 0 without the long
+// arithmetic. Only inf / nan / hex literals set *bad: there the reference's behaviour is genuinely different.
 __constant__ double kP10[23] = {1e0, 1e1, 1e2, 1e3, 1e4, 1e5, 1e6, 1e7, 1e8, 1e9, 1e10, 1e11,
                                 1e12, 1e13, 1e14, 1e15, 1e16, 1e17, 1e18, 1e19, 1e20, 1e21, 1e22};
+constexpr int kBigLimbs = 20;   // 640 bits: 36 digits (120 bits) x 10^40, or shifted past a 10^86 divisor
+struct Big { uint32_t w[kBigLimbs]; };
+__device__ void big_zero(Big& b) { for (int i = 0; i < kBigLimbs; ++i) b.w[i] = 0; }
+__device__ void big_mul_add(Big& b, uint32_t m, uint32_t add) {
+  uint64_t c = add;
+  for (int i = 0; i < kBigLimbs; ++i) { c += (uint64_t)b.w[i] * m; b.w[i] = (uint32_t)c; c >>= 32; }
+}
+__device__ int big_bits(const Big& b) {
+  for (int i = kBigLimbs - 1; i >= 0; --i) if (b.w[i]) return 32 * i + 32 - __clz(b.w[i]);
+  return 0;
+}
+__device__ int big_bit(const Big& b, int i) { return (b.w[i >> 5] >> (i & 31)) & 1; }
+__device__ void big_shl1_or(Big& b, uint32_t bit) {
+  for (int i = kBigLimbs - 1; i > 0; --i) b.w[i] = (b.w[i] << 1) | (b.w[i - 1] >> 31);
+  b.w[0] = (b.w[0] << 1) | bit;
+}
+__device__ bool big_ge(const Big& a, const Big& b) {
+  for (int i = kBigLimbs - 1; i >= 0; --i) if (a.w[i] != b.w[i]) return a.w[i] > b.w[i];
+  return true;
+}
+__device__ void big_sub(Big& a, const Big& b) {
+  uint64_t br = 0;
+  for (int i = 0; i < kBigLimbs; ++i) { const uint64_t d = (uint64_t)a.w[i] - b.w[i] - br; a.w[i] = (uint32_t)d; br = (d >> 32) & 1; }
+}
+// bits [lo, lo + 64) of b
+__device__ uint64_t big_extract64(const Big& b, int lo) {
+  uint64_t v = 0;
+  for (int i = 0; i < 64; ++i) { const int k = lo + i; if (k >= 0 && k < 32 * kBigLimbs) v |= (uint64_t)big_bit(b, k) << i; }
+  return v;
+}
+__device__ bool big_any_below(const Big& b, int hi) {
+  for (int k = 0; k < hi && k < 32 * kBigLimbs; ++k) if (big_bit(b, k)) return true;
+  return false;
+}
+// the double nearest to digits x 10^e10 (ties to even); digits = up to 36 decimal digits in `m`, sticky = a non-zero tail was dropped
+__device__ double exact_decimal(const Big& m, int e10, bool sticky) {
+  Big q;
+  int exp2 = 0;
+  if (e10 >= 0) {
+    q = m;
+    for (int i = 0; i < e10; ++i) big_mul_add(q, 10u, 0u);
+  } else {
+    Big den, rem;
+    big_zero(den); den.w[0] = 1;
+    for (int i = 0; i < -e10; ++i) big_mul_add(den, 10u, 0u);
+    const int s = max(0, big_bits(den) + 66 - big_bits(m));
+    // num = m << s, divided by den bit by bit (restoring division); the quotient has 66 or 67 bits
+    big_zero(q); big_zero(rem);
+    const int nb = big_bits(m) + s;
+    for (int i = nb - 1; i >= 0; --i) {
+      const int src = i - s;
+      big_shl1_or(rem, src >= 0 ? (uint32_t)big_bit(m, src) : 0u);
+      const bool ge = big_ge(rem, den);
+      if (ge) big_sub(rem, den);
+      big_shl1_or(q, ge ? 1u : 0u);
+    }
+    if (big_bits(rem)) sticky = true;
+    exp2 = -s;
+  }
+  const int L = big_bits(q);
+  if (L <= 53) return ldexp((double)big_extract64(q, 0), exp2);   // exact (sticky can only be set with a long quotient)
+  const int drop = L - 53;
+  uint64_t mant = big_extract64(q, drop) & ((1ULL << 53) - 1);
+  const bool guard = big_bit(q, drop - 1) != 0;
+  const bool rest = sticky || big_any_below(q, drop - 1);
+  if (guard && (rest || (mant & 1))) ++mant;     // may reach 2^53: still exactly representable
+  return ldexp((double)mant, exp2 + drop);
+}
+
 __device__ double parse_number(const char* p, const char* end, int* bad) {
   while (p != end && (is_blank(*p) || *p == '\v' || *p == '\f')) ++p;
   bool neg = false;
   if (p != end && (*p == '-' || *p == '+')) { neg = *p == '-'; ++p; }
   if (p != end && (*p == 'i' || *p == 'I' || *p == 'n' || *p == 'N')) { *bad = 1; return 0; }
   if (p + 1 < end && *p == '0' && (p[1] == 'x' || p[1] == 'X')) { *bad = 1; return 0; }
+  const char* digits = p;
   uint64_t m = 0;
   int e = 0, ndig = 0;
   bool any = false, big = false;
   for (; p != end && is_digit(*p); ++p) {
     any = true;
     if (m == 0 && *p == '0') continue;
-    if (++ndig > 18) big = true; else m = m * 10 + (uint64_t)(*p - '0');
+    if (++ndig > 18) { big = true; ++e; } else m = m * 10 + (uint64_t)(*p - '0');
   }
   if (p != end && *p == '.') {
     ++p;
@@ -95,6 +168,8 @@ __device__ double parse_number(const char* p, const char* end, int* bad) {
     }
   }
   if (!any) return 0;
+  const char* digits_end = p;
+  int ex = 0;
   if (p != end && (*p == 'e' || *p == 'E')) {
     const char* q = p + 1;
     bool eneg = false;
@@ -102,13 +177,33 @@ __device__ double parse_number(const char* p, const char* end, int* bad) {
     if (q != end && is_digit(*q)) {
       int x = 0;
       for (; q != end && is_digit(*q); ++q) x = x < 10000 ? x * 10 + (*q - '0') : x;
-      e += eneg ? -x : x;
+      ex = eneg ? -x : x;
     }
   }
   double r;
   if (m == 0) r = 0;
-  else if (big || m >= (1ULL << 53) || e > 22 || e < -22) { *bad = 1; return 0; }
-  else r = e >= 0 ? (double)m * kP10[e] : (double)m / kP10[-e];
+  else if (!big && m < (1ULL << 53) && e + ex <= 22 && e + ex >= -22) {
+    const int ee = e + ex;
+    r = ee >= 0 ? (double)m * kP10[ee] : (double)m / kP10[-ee];
+  } else {
+    // the exact path: walk the digits again, keeping 36 of them
+    Big M;
+    big_zero(M);
+    int kept = 0, e10 = ex;
+    bool sticky = false, frac = false, lead = true;
+    for (const char* d = digits; d != digits_end; ++d) {
+      if (*d == '.') { frac = true; continue; }
+      const uint32_t v = (uint32_t)(*d - '0');
+      if (lead && v == 0) { if (frac) --e10; continue; }
+      lead = false;
+      if (kept < 36) { big_mul_add(M, 10u, v); ++kept; if (frac) --e10; }
+      else { if (v) sticky = true; if (!frac) ++e10; }
+    }
+    const int mag = kept + e10;                 // value in [10^(mag-1), 10^mag)
+    if (mag > 40) r = HUGE_VAL;                 // beyond the float range either way: the stored float is inf
+    else if (mag < -50) r = 0;                  // ... or 0
+    else r = exact_decimal(M, e10, sticky);
+  }
   return neg ? -r : r;
 }
 
@@ -427,7 +522,7 @@ const char* parse_error_text(int code) {
     case 6: return "categorical field is not 8 bytes followed by white space (criteo_parser.h:79 CHECK)";
     case 7: return "bytes after the 26th categorical field";
     case 8: return "some features carry a value and some do not";
-    case 9: return "numeric literal outside the exactly convertible range (or inf / nan / hex)";
+    case 9: return "inf / nan / hexadecimal numeric literal";
     case 10: return "adfea: a token is neither digits nor digits:digits, or features and plain tokens are out of order";
     case 11: return "adfea: fewer than three leading tokens (line id, count, label)";
   }
@@ -435,6 +530,39 @@ const char* parse_error_text(int code) {
 }
 
 }  // namespace
+
+namespace wh {
+// RowBlockContainer::Push(RowBlock) from host arrays: `rows` rows appended to a device container. offset is relative
+// to offset[0]; value may be NULL (a mix of blocks with and without values is completed with ones, as wh_rows_append).
+int rows_append_host(whContext* ctx, whRows* dst, size_t rows, const size_t* offset, const float* label, const uint64_t* index,
+                     const float* value) {
+  cudaStream_t st = ctx->stream;
+  if (rows == 0) return WH_OK;
+  const size_t add = offset[rows] - offset[0];
+  const bool was_empty = dst->rows == 0;
+  const bool want_value = was_empty ? value != nullptr : (dst->has_value || value != nullptr);
+  WH_TRY(rows_reserve(dst, dst->rows + rows, dst->nnz + add, want_value, true));
+  if (want_value && !dst->has_value && dst->nnz)
+    WH_LAUNCH(fill_f32_kernel, (unsigned)div_up(dst->nnz, 256), 256, 0, st, dst->value.as<float>(), dst->nnz, 1.f);
+  dst->has_value = want_value;
+  std::vector<size_t> off(rows + (was_empty ? 1 : 0));
+  size_t* o = off.data();
+  if (was_empty) *o++ = 0;
+  for (size_t i = 0; i < rows; ++i) o[i] = dst->nnz + (offset[i + 1] - offset[0]);
+  WH_CUDA(cudaMemcpyAsync(dst->offset.as<size_t>() + (was_empty ? 0 : dst->rows + 1), off.data(), off.size() * sizeof(size_t),
+                          cudaMemcpyHostToDevice, st));
+  WH_CUDA(cudaMemcpyAsync(dst->label.as<float>() + dst->rows, label, rows * sizeof(float), cudaMemcpyHostToDevice, st));
+  if (add) {
+    WH_CUDA(cudaMemcpyAsync(dst->index.as<uint64_t>() + dst->nnz, index + offset[0], add * sizeof(uint64_t), cudaMemcpyHostToDevice, st));
+    if (want_value && value) WH_CUDA(cudaMemcpyAsync(dst->value.as<float>() + dst->nnz, value + offset[0], add * sizeof(float), cudaMemcpyHostToDevice, st));
+    if (want_value && !value) WH_LAUNCH(fill_f32_kernel, (unsigned)div_up(add, 256), 256, 0, st, dst->value.as<float>() + dst->nnz, add, 1.f);
+  }
+  WH_CUDA(cudaStreamSynchronize(st));   // the host arrays are the caller's temporaries
+  dst->rows += rows; dst->nnz += add;
+  dst->h_valid = false;
+  return WH_OK;
+}
+}  // namespace wh
 
 extern "C" {
 
@@ -498,7 +626,7 @@ int wh_rows_copy(whContext* ctx, const whRows* r, size_t* offset, float* label, 
 int wh_parse_text(whContext* ctx, int format, const char* text, size_t len, int mem, whRows** out) {
   WH_REQUIRE(ctx && out && (text || len == 0), "wh_parse_text: null argument");
   WH_REQUIRE(format == WH_FMT_LIBSVM || format == WH_FMT_CRITEO || format == WH_FMT_CRITEO_TEST || format == WH_FMT_ADFEA,
-             "wh_parse_text: unknown format %d (crb is not built)", format);
+             "wh_parse_text: unknown format %d (crb records go through wh_parse_crb)", format);
   WH_REQUIRE(mem == WH_HOST || mem == WH_DEVICE, "wh_parse_text: bad mem %d", mem);
   WH_REQUIRE(len < (1ULL << 32), "wh_parse_text: a chunk is at most 4 GiB - 1 bytes (got %zu)", len);
   DeviceGuard g(ctx->device);

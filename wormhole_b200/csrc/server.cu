@@ -601,8 +601,10 @@ int wh_server_save(whServer* s, const char* path) {
   if (s->hslots) std::sort(order.begin(), order.end(), [&](unsigned a, unsigned b) { return keys[a] < keys[b]; });  // slot order -> key order
   FILE* f = fopen(path, "wb");
   WH_REQUIRE(f != nullptr, "wh_server_save: cannot open %s", path);
-  for (unsigned i = 0; i < cnt; ++i) { fwrite(&keys[order[i]], 8, 1, f); fwrite(&ws[order[i]], 4, 1, f); }
-  fclose(f);
+  bool ok = true;
+  for (unsigned i = 0; i < cnt && ok; ++i) ok = fwrite(&keys[order[i]], 8, 1, f) == 1 && fwrite(&ws[order[i]], 4, 1, f) == 1;
+  ok = (fclose(f) == 0) && ok;
+  WH_REQUIRE(ok, "wh_server_save: writing %s failed (disk full?)", path);
   return WH_OK;
 }
 

@@ -152,6 +152,7 @@ static HotView lane_hot_view(const whWorker* w, Lane& l) {
 // worker, synchronously; its only product is the table image (a cache hint -- results never depend on it).
 static int hot_census(whWorker* w, Lane& l, const LocInput& in, size_t ucap, bool for_direct) {
   whContext* cx = &l.cx;
+  if (!l.cx.own_stream) l.cx.stream = w->ctx->stream;   // lane 0 rides the context's stream, whichever that is now (wh_set_stream)
   if (for_direct) w->dx_tried = true; else w->hot_tried = true;
   const auto t_begin = std::chrono::steady_clock::now();
   struct Timer { whWorker* w; std::chrono::steady_clock::time_point t0;
@@ -281,6 +282,7 @@ int wh_worker_submit(whWorker* w, const whRowBlock* blk, int mem, size_t nnz, in
     return WH_ERR_INVALID;
   }
   whContext* cx = &l.cx;
+  if (!l.cx.own_stream) l.cx.stream = w->ctx->stream;   // lane 0 rides the context's stream, whichever that is now (wh_set_stream)
   cx->prof.on = ctx->prof.on;
   size_t n = nnz;
   if (mem == WH_HOST) n = blk->offset[rows];
@@ -547,8 +549,13 @@ int wh_worker_wait(whWorker* w, uint64_t ticket, double* prog) {
   }
   if (cnt[1]) {
     WH_CUDA(cudaMemsetAsync(s->counters.as<long long>() + 1, 0, 8, l.cx.stream));
-    set_error("wh_worker: %lld keys fall outside the server's range [%llu, %llu)", cnt[1],
-              (unsigned long long)s->key_begin, (unsigned long long)s->key_end);
+    if (s->hslots)
+      set_error("wh_worker: %lld keys found no slot: the server's open-addressing table of %llu slots is full (give a larger "
+                "hash_slots), or they fall outside its range [%llu, %llu)", cnt[1], (unsigned long long)s->hslots,
+                (unsigned long long)s->key_begin, (unsigned long long)s->key_end);
+    else
+      set_error("wh_worker: %lld keys fall outside the server's range [%llu, %llu)", cnt[1],
+                (unsigned long long)s->key_begin, (unsigned long long)s->key_end);
     return WH_ERR_INVALID;
   }
   EvalHost h = eval_finish(*reinterpret_cast<const EvalOut*>(l.pinned), l.rows);
@@ -575,6 +582,7 @@ int wh_worker_predict(whWorker* w, const whRowBlock* blk, int mem, int prob, flo
   WH_REQUIRE(blk->offset && blk->index, "wh_worker_predict: offset/index is NULL");
   Lane& l = w->lane[0];
   whContext* cx = &l.cx;
+  if (!l.cx.own_stream) l.cx.stream = w->ctx->stream;   // lane 0 rides the context's stream, whichever that is now (wh_set_stream)
   size_t n;
   if (mem == WH_HOST) n = blk->offset[rows];
   else {
@@ -652,6 +660,7 @@ int wh_worker_begin(whWorker* w, const whRowBlock* blk, int mem, size_t nnz, con
   WH_REQUIRE(rows > 0 && blk->offset && blk->index && blk->label, "wh_worker_begin: empty block or NULL offset/index/label");
   Lane& l = w->lane[0];
   whContext* cx = &l.cx;
+  if (!l.cx.own_stream) l.cx.stream = w->ctx->stream;   // lane 0 rides the context's stream, whichever that is now (wh_set_stream)
   cx->prof.on = ctx->prof.on;
   size_t n = nnz;
   if (mem == WH_HOST) n = blk->offset[rows];
@@ -692,6 +701,7 @@ int wh_worker_finish(whWorker* w, const float* d_weights, float* d_grads, int tr
   whContext* ctx = w->ctx;
   DeviceGuard g(ctx->device);
   whContext* cx = &l.cx;
+  if (!l.cx.own_stream) l.cx.stream = w->ctx->stream;   // lane 0 rides the context's stream, whichever that is now (wh_set_stream)
   l.b_open = false;
   const size_t rows = l.rows, n = l.b_nnz, U = l.b_nuniq;
   FixedScale* fs = reinterpret_cast<FixedScale*>(l.scal.as<char>() + 256);

@@ -108,8 +108,19 @@ class ShardedWorker:
 
     def __init__(self, ctx, worker, kv):
         self.ctx, self.worker, self.kv = ctx, worker, kv
+        # The exchange interleaves torch work (searchsorted, all_to_all, empty) with library launches on the context's
+        # stream, and nothing else orders the two: bind the context to the stream torch is using, here and again at
+        # every minibatch (torch's current stream may change under a torch.cuda.stream(...) block).
+        self._bind()
+
+    def _bind(self):
+        s = torch.cuda.current_stream(self.kv.device).cuda_stream
+        if getattr(self, "_bound", None) != s:
+            self.ctx.set_stream(s)
+            self._bound = s
 
     def process_minibatch(self, blk, train=True, mem=0, nnz=0):
+        self._bind()
         ptr, U = self.worker.begin(blk, mem, nnz)
         keys = _wrap_device_i64(ptr, U, self.kv.device)
         w = self.kv.pull(keys)

@@ -66,6 +66,77 @@ def part_range(path, part_index, num_parts):
         return align(f, total * part_index // num_parts), align(f, total * (part_index + 1) // num_parts)
 
 
+RECORDIO_MAGIC = 0xced7230a
+
+
+def _record_head(buf, i):
+    """Does a RecordIO record START at byte i of buf (magic, then a header word whose flag says whole record or first
+    part)? dmlc-core's InputSplit for recordio finds part boundaries the same way."""
+    if i + 8 > len(buf) or int.from_bytes(buf[i:i + 4], "little") != RECORDIO_MAGIC:
+        return False
+    return (int.from_bytes(buf[i + 4:i + 8], "little") >> 29) in (0, 1)
+
+
+def crb_part_range(path, part_index, num_parts):
+    """Byte range of one part of a RecordIO file: the even split, both ends moved forward to the next record head
+    (4-byte aligned: records are padded to words)."""
+    total = os.path.getsize(path)
+
+    def align(f, x):
+        x = min(total, (x + 3) & ~3)
+        while x < total:
+            f.seek(x)
+            buf = f.read(1 << 16)
+            for i in range(0, len(buf) - 7, 4):
+                if _record_head(buf, i):
+                    return x + i
+            x += max(4, (len(buf) - 8) & ~3)
+        return total
+
+    with open(path, "rb") as f:
+        return align(f, total * part_index // num_parts), align(f, total * (part_index + 1) // num_parts)
+
+
+class _CrbParser:
+    """CRBParser (learn/base/crb_parser.h) over one part of one file: next() -> the rows of the next chunk of records."""
+
+    def __init__(self, ctx, uri, part_index, num_parts, chunk_bytes):
+        self.ctx, self.uri, self.chunk_bytes = ctx, uri, chunk_bytes
+        self.begin, self.end = crb_part_range(uri, part_index, num_parts)
+        self.f = open(uri, "rb")
+        self.before_first()
+
+    def before_first(self):
+        self.pos = self.begin
+        self.bytes_read = 0
+
+    def next(self):
+        while self.pos < self.end:
+            # whole records up to chunk_bytes (at least one; a split record's parts stay together)
+            start, p, open_parts = self.pos, self.pos, False
+            while p < self.end:
+                self.f.seek(p)
+                hdr = self.f.read(8)
+                if len(hdr) < 8 or int.from_bytes(hdr[:4], "little") != RECORDIO_MAGIC:
+                    raise capi.WormholeError("crb: no RecordIO magic at byte %d of %s" % (p, self.uri))
+                lrec = int.from_bytes(hdr[4:], "little")
+                flag, n = lrec >> 29, lrec & ((1 << 29) - 1)
+                nxt = p + 8 + ((n + 3) & ~3)
+                if p > start and not open_parts and nxt - start > self.chunk_bytes:
+                    break
+                open_parts = flag in (1, 2)
+                p = nxt
+            self.f.seek(start)
+            buf = self.f.read(p - start)
+            self.pos = p
+            self.bytes_read += len(buf)
+            rows = capi.parse_crb(self.ctx, buf)
+            if rows.rows:
+                return rows
+            rows.close()
+        return None
+
+
 class _ChunkParser:
     """ParserImpl over one part of one text file: Next() -> the next parsed chunk (capi.Rows) or None."""
 
@@ -118,15 +189,16 @@ class MinibatchIter:
                  chunk_bytes=8 << 20, ring=4, rand=_rand):
         self.ctx, self.mb_size, self.shuf_buf, self.neg = ctx, int(minibatch_size), int(shuf_buf), negative_sampling
         self.rand = rand
-        if type not in capi.FMT:
-            raise capi.WormholeError("unknown datatype %s (libsvm, criteo, criteo_test, adfea are built)" % type)  # :58
+        if type not in capi.FMT and type != "crb":
+            raise capi.WormholeError("unknown datatype %s" % type)  # :58
         if shuf_buf:
             if not shuf_buf > minibatch_size:                                                      # :37
                 raise capi.WormholeError("shuf_buf must exceed minibatch_size")
             self.buf_reader = MinibatchIter(ctx, uri, part_index, num_parts, type, shuf_buf, 0, 1.0, chunk_bytes, 2)
             self.parser = None
         else:
-            self.parser = _ChunkParser(ctx, uri, part_index, num_parts, type, chunk_bytes)
+            self.parser = (_CrbParser(ctx, uri, part_index, num_parts, chunk_bytes) if type == "crb" else   # :50-52
+                           _ChunkParser(ctx, uri, part_index, num_parts, type, chunk_bytes))
             self.buf_reader = None
         # the worker reads a submitted minibatch asynchronously: hand out `ring` containers in turn
         self.ring = [capi.Rows(ctx) for _ in range(ring)]
