@@ -108,6 +108,14 @@ def test_direct_lanes_and_evaluation_passes(gpu):
     same_model(a, c)
 
 
+def test_direct_staged_codes_change_nothing(gpu):
+    """WH_DX_STAGED=1: the codes of a minibatch are made by a launch of their own, ahead of the step."""
+    blks = [synth.criteo_minibatch(m, rows=20000) for m in range(6)] + [random_block(np.random.default_rng(3), 4000, 30, 40000)]
+    a = run(gpu, blks, capi.ALGO_FTRL, capi.LOSS_LOGIT, 2 ** 22, depth=3)
+    b = run(gpu, blks, capi.ALGO_FTRL, capi.LOSS_LOGIT, 2 ** 22, depth=3, WH_DX_STAGED=1)
+    same_model(a, b)
+
+
 def test_direct_table_refresh_changes_nothing(gpu):
     blks = [synth.criteo_minibatch(m, rows=20000) for m in range(8)]
     a = run(gpu, blks, capi.ALGO_ADAGRAD, capi.LOSS_LOGIT, 2 ** 22, depth=3)

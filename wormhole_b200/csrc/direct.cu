@@ -28,6 +28,7 @@
 // sums once, without atomics, into its own row of a [blocks x slots] array that the push kernel adds up. Only keys
 // outside the table pay a RED, into the shard entry that the forward gather has just brought into L2.
 #include <stdlib.h>
+#include <string.h>
 
 #include <algorithm>
 #include <numeric>
@@ -93,6 +94,7 @@ struct DxArgs {
   KeyXform xf;
   ShardEntry* shard;        // a key's weight is shard[key].w, its accumulator shard[key].acc
   const uint4* tags; const float* hot_w;
+  const uint32_t* codes;    // non-NULL: one code per entry, staged by dx_stage_kernel
   unsigned* bitmap; long long* part; unsigned* part_touched;
   float* xw; double* part_objv; unsigned* part_correct; unsigned long long* auc_hist;
   FixedScale* fs;
@@ -108,6 +110,16 @@ struct DxArgs {
 template <bool TRAIN, bool POW2, bool HAS_VAL>
 __device__ __forceinline__ void dx_stage(const DxArgs& a, const uint4* s_tags, unsigned char* s_touch, uint32_t* s_code, float* s_val,
                                          size_t base, unsigned E, unsigned tg) {
+  if (a.codes) {
+    // the codes were made ahead of time by dx_stage_kernel (minibatches in flight: that part of the step does not
+    // depend on the model, so it runs while the previous minibatch is still in its forward / backward / push)
+    const uint64_t pol = l2_policy_evict_first();
+    for (unsigned e = tg; e < E; e += kDxGroup) {
+      s_code[e] = ld_stream_evict_first_u32(a.codes + base + e, pol);
+      if (HAS_VAL) s_val[e] = __ldcs(a.value + base + e);
+    }
+    return;
+  }
   const unsigned mask = (unsigned)(a.xf.max_key - 1);
   const uint64_t* ids = a.index + base;
   uint64_t nxt[kDxIlp];
@@ -146,12 +158,14 @@ __device__ __forceinline__ void dx_stage(const DxArgs& a, const uint4* s_tags, u
 // weight of a code: table keys from shared memory, the rest from the shard -- one generic load from a selected address
 // (two predicated loads, one of which issues: a generic load from a selected address cost 51 instructions per entry in
 //  address-space conversion and 64-bit selects, a branch around two loads 21)
-__device__ __forceinline__ float dx_weight(const ShardEntry* __restrict__ shard, unsigned s_hw32, uint32_t c) {
+// The entry of a key outside the table is wanted three times within the minibatch -- this gather, the accumulating RED,
+// the push -- and the ids, codes and partial sums streaming through L2 in between would evict it: evict-last policy.
+__device__ __forceinline__ float dx_weight(const ShardEntry* __restrict__ shard, unsigned s_hw32, uint32_t c, uint64_t keep) {
   float w;
   const unsigned saddr = s_hw32 + ((c & (kDxSlots - 1)) << 2);
   const ShardEntry* g = shard + (c & 0x0fffffffu);
-  asm volatile("{\n\t.reg .pred p;\n\tsetp.lt.s32 p, %3, 0;\n\t@p ld.shared.f32 %0, [%1];\n\t@!p ld.global.nc.L1::no_allocate.f32 %0, [%2];\n\t}"
-               : "=f"(w) : "r"(saddr), "l"(g), "r"(c));
+  asm volatile("{\n\t.reg .pred p;\n\tsetp.lt.s32 p, %3, 0;\n\t@p ld.shared.f32 %0, [%1];\n\t@!p ld.global.nc.L1::no_allocate.L2::cache_hint.f32 %0, [%2], %4;\n\t}"
+               : "=f"(w) : "r"(saddr), "l"(g), "r"(c), "l"(keep));
   return w;
 }
 // one entry's term into the accumulators (P3): the block's shared-memory sums, or the key's entry in the shard
@@ -173,7 +187,7 @@ __device__ void dx_long_row(const DxArgs& a, const uint4* s_tags, unsigned s_hw,
     dx_stage<false, POW2, HAS_VAL>(a, s_tags, s_touch, s_code, s_val, c0, E, tg);
     group_bar(g);
     if (tg == 0)
-      for (unsigned j = 0; j < E; ++j) { float w = dx_weight(a.shard, s_hw, s_code[j]); if (HAS_VAL) w *= s_val[j]; sum += w; }
+      for (unsigned j = 0; j < E; ++j) { float w = dx_weight(a.shard, s_hw, s_code[j], l2_policy_evict_last()); if (HAS_VAL) w *= s_val[j]; sum += w; }
     group_bar(g);
   }
   float dl = 0.f;
@@ -201,14 +215,36 @@ __device__ void dx_long_row(const DxArgs& a, const uint4* s_tags, unsigned s_hw,
   }
 }
 
+// P1 as a launch of its own, for workers that keep several minibatches in flight: ids -> codes in global memory (4 bytes
+// per entry), key bitmap and table-key flags as in the fused kernel. Small blocks with little shared memory, so that
+// they fit beside the step kernel of the minibatch before.
+template <bool TRAIN, bool POW2>
+__global__ void __launch_bounds__(kDxGroup) dx_stage_kernel(const DxArgs a, size_t nnz, uint32_t* codes_out, unsigned* touched) {
+  __shared__ uint4 s_tags[kDxBuckets];
+  __shared__ unsigned char s_touch[kDxSlots];
+  for (int i = threadIdx.x; i < kDxBuckets; i += blockDim.x) s_tags[i] = __ldg(a.tags + i);
+  for (int i = threadIdx.x; i < kDxSlots / 4; i += blockDim.x) reinterpret_cast<unsigned*>(s_touch)[i] = 0u;
+  __syncthreads();
+  const size_t chunk = ((nnz + gridDim.x - 1) / gridDim.x + 3) & ~(size_t)3;
+  const size_t lo = min(nnz, (size_t)blockIdx.x * chunk), hi = min(nnz, lo + chunk);
+  if (hi > lo) dx_stage<TRAIN, POW2, false>(a, s_tags, s_touch, codes_out + lo, nullptr, lo, (unsigned)(hi - lo), threadIdx.x);
+  if (TRAIN) {
+    __syncthreads();
+    for (int i = threadIdx.x; i < kDxSlots; i += blockDim.x) if (s_touch[i]) touched[i] = 1u;
+  }
+}
+
 template <bool TRAIN, bool POW2, bool HAS_VAL, int NG>
-__global__ void __launch_bounds__(NG * kDxGroup, 1) fused_direct_kernel(const DxArgs a) {
+__global__ void __maxnreg__(48) fused_direct_kernel(const DxArgs a) {
   extern __shared__ __align__(16) unsigned char smem[];
-  uint4* s_tags = reinterpret_cast<uint4*>(smem);                          // 16 KB
-  unsigned* s_acc = reinterpret_cast<unsigned*>(s_tags + kDxBuckets);      // 48 KB: the block's sums for the table keys (3 words each)
+  // (with the codes staged ahead of time the table's tags and flags are not needed here, and their 20 KB are left
+  //  to the next minibatch's dx_stage_kernel blocks, which run beside this kernel)
+  const bool staged = a.codes != nullptr;
+  unsigned* s_acc = reinterpret_cast<unsigned*>(smem);                     // 48 KB: the block's sums for the table keys (3 words each)
   float* s_hwp = reinterpret_cast<float*>(s_acc + 3 * kDxSlots);           // 16 KB: the table keys' weights
-  unsigned char* s_touch = reinterpret_cast<unsigned char*>(s_hwp + kDxSlots);   // 4 KB: table keys this block saw
-  unsigned* s_off_all = reinterpret_cast<unsigned*>(s_touch + kDxSlots);
+  uint4* s_tags = reinterpret_cast<uint4*>(s_hwp + kDxSlots);              // 16 KB
+  unsigned char* s_touch = reinterpret_cast<unsigned char*>(s_tags + (staged ? 0 : kDxBuckets));   // 4 KB: table keys this block saw
+  unsigned* s_off_all = reinterpret_cast<unsigned*>(s_touch + (staged ? 0 : kDxSlots));
   const unsigned s_hw = smem_u32(s_hwp);
   float* s_bcast_all = reinterpret_cast<float*>(s_off_all + NG * (kDxGroup + 4));
   uint32_t* s_code_all = reinterpret_cast<uint32_t*>(s_bcast_all + 4);
@@ -229,12 +265,12 @@ __global__ void __launch_bounds__(NG * kDxGroup, 1) fused_direct_kernel(const Dx
   bool first_tile = true;
   DX_MARK(0);
   for (int i = threadIdx.x; i < kDxBuckets; i += blockDim.x) {
-    s_tags[i] = __ldg(a.tags + i);
+    if (!a.codes) s_tags[i] = __ldg(a.tags + i);
     reinterpret_cast<float4*>(s_hwp)[i] = __ldg(reinterpret_cast<const float4*>(a.hot_w) + i);
   }
   if (TRAIN) {
     for (int i = threadIdx.x; i < 3 * kDxSlots / 4; i += blockDim.x) reinterpret_cast<int4*>(s_acc)[i] = make_int4(0, 0, 0, 0);
-    for (int i = threadIdx.x; i < kDxSlots / 4; i += blockDim.x) reinterpret_cast<unsigned*>(s_touch)[i] = 0u;
+    if (!staged) for (int i = threadIdx.x; i < kDxSlots / 4; i += blockDim.x) reinterpret_cast<unsigned*>(s_touch)[i] = 0u;
   }
   __syncthreads();
 
@@ -279,6 +315,7 @@ __global__ void __launch_bounds__(NG * kDxGroup, 1) fused_direct_kernel(const Dx
     const bool live = tg < R;
     const unsigned lb = live ? s_off[tg] : 0u, len = live ? s_off[tg + 1] - s_off[tg] : 0u;
     float dl = 0.f;
+    const uint64_t keep = l2_policy_evict_last();
     unsigned hbin = 0xffffffffu;   // AUC bin << 1 | positive
     if (live) {
       float sum = 0.f;
@@ -289,12 +326,12 @@ __global__ void __launch_bounds__(NG * kDxGroup, 1) fused_direct_kernel(const Dx
 #pragma unroll
         for (int u = 0; u < kDxGather; ++u) c[u] = s_code[lb + j + u];
 #pragma unroll
-        for (int u = 0; u < kDxGather; ++u) wv[u] = dx_weight(a.shard, s_hw, c[u]);
+        for (int u = 0; u < kDxGather; ++u) wv[u] = dx_weight(a.shard, s_hw, c[u], keep);
 #pragma unroll
         for (int u = 0; u < kDxGather; ++u) sum += HAS_VAL ? wv[u] * s_val[lb + j + u] : wv[u];
       }
       for (; j < len; ++j) {
-        float wv = dx_weight(a.shard, s_hw, s_code[lb + j]);
+        float wv = dx_weight(a.shard, s_hw, s_code[lb + j], keep);
         if (HAS_VAL) wv *= s_val[lb + j];
         sum += wv;
       }
@@ -350,7 +387,7 @@ __global__ void __launch_bounds__(NG * kDxGroup, 1) fused_direct_kernel(const Dx
     long long* dst = a.part + (size_t)blockIdx.x * kDxSlots;
     for (int i = threadIdx.x; i < kDxSlots; i += blockDim.x) {
       dst[i] = dx_smem_sum(s_acc, i, D);
-      const unsigned seen = __ballot_sync(0xffffffffu, s_touch[i] != 0);
+      const unsigned seen = __ballot_sync(0xffffffffu, !staged && s_touch[i] != 0);   // (staged: dx_stage_kernel kept the flags)
       if (lane == 0) a.part_touched[(size_t)blockIdx.x * (kDxSlots / 32) + (i >> 5)] = seen;
     }
   }
@@ -376,7 +413,7 @@ __device__ __forceinline__ int push_entry(const HandleParams& h, ShardEntry* e, 
 __global__ void __launch_bounds__(256)
 push_sweep_kernel(HandleParams h, ShardView t, unsigned* __restrict__ bitmap, unsigned words,
                   const unsigned* __restrict__ tags, const long long* __restrict__ part, const unsigned* __restrict__ part_touched,
-                  unsigned nparts, float* __restrict__ hot_w, const FixedScale* __restrict__ fs, float mul,
+                  unsigned* __restrict__ staged_touched, unsigned nparts, float* __restrict__ hot_w, const FixedScale* __restrict__ fs, float mul,
                   long long* counters, unsigned hot_blocks) {
   const double inv = fs->inv;
   int delta = 0;
@@ -398,7 +435,9 @@ push_sweep_kernel(HandleParams h, ShardView t, unsigned* __restrict__ bitmap, un
     if (ch == 0) {
 #pragma unroll
       for (int c = 1; c < 8; ++c) { s += s_sum[c][sl]; seen |= s_seen[c][sl]; }
-      if ((seen >> (slot & 31)) & 1u) {
+      bool touched = (seen >> (slot & 31)) & 1u;
+      if (staged_touched && staged_touched[slot]) { touched = true; staged_touched[slot] = 0u; }   // (flags of dx_stage_kernel)
+      if (touched) {
         const unsigned k = tags[slot];
         float nw;
         delta = handle_push(h, t, k, (float)((double)s * inv) * mul, &nw);
@@ -406,26 +445,18 @@ push_sweep_kernel(HandleParams h, ShardView t, unsigned* __restrict__ bitmap, un
       }
     }
   } else {
-    // four consecutive bitmap words per thread: one 16-byte load, and the entries of up to four keys in flight
-    const unsigned nthreads = (gridDim.x - hot_blocks) * blockDim.x, quads = (words + 3) / 4;
-    for (unsigned i = (blockIdx.x - hot_blocks) * blockDim.x + threadIdx.x; i < quads; i += nthreads) {
-      uint4 q = make_uint4(0, 0, 0, 0);
-      if (i * 4 + 3 < words) q = __ldcs(reinterpret_cast<const uint4*>(bitmap) + i);
-      else { unsigned* qq = &q.x; for (unsigned j = 0; i * 4 + j < words; ++j) qq[j] = bitmap[i * 4 + j]; }
-      if (!(q.x | q.y | q.z | q.w)) continue;
-      if (i * 4 + 3 < words) reinterpret_cast<uint4*>(bitmap)[i] = make_uint4(0, 0, 0, 0);
-      else for (unsigned j = 0; i * 4 + j < words; ++j) bitmap[i * 4 + j] = 0u;
-      const unsigned wd[4] = {q.x, q.y, q.z, q.w};
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        unsigned bits = wd[j];
-        const unsigned kb = (i * 4 + j) << 5;
-        while (bits) {
-          const unsigned k = kb + (__ffs(bits) - 1);
-          bits &= bits - 1;
-          delta += push_entry(h, t.e + k, inv, mul);
-        }
-      }
+    // a bitmap word per thread. First every key of the word sends for its entry (prefetch: nothing waits), then the
+    // keys are updated one after the other -- walking them load by load cost a DRAM latency per key.
+    const unsigned nthreads = (gridDim.x - hot_blocks) * blockDim.x;
+    for (unsigned i = (blockIdx.x - hot_blocks) * blockDim.x + threadIdx.x; i < words; i += nthreads) {
+      const unsigned word = __ldcs(bitmap + i);
+      if (!word) continue;
+      bitmap[i] = 0u;
+      const unsigned kb = i << 5;
+      for (unsigned bits = word; bits; bits &= bits - 1)
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(t.e + kb + (__ffs(bits) - 1)));
+      for (unsigned bits = word; bits; bits &= bits - 1)
+        delta += push_entry(h, t.e + kb + (__ffs(bits) - 1), inv, mul);
     }
   }
   commit_counters(counters, delta, 0);
@@ -521,12 +552,12 @@ int direct_fused_launch(whContext* ctx, const DirectStep& st, const DirectTable&
   const bool has_val = st.value != nullptr;
   // shared memory: table (tags 16 KB, sums 32 KB, weights 16 KB) | offsets | codes (+ values). A group's tile holds up
   // to 256 rows; size the code area for the average row (longer tiles are cut short, see the R search in the kernel).
-  const size_t fixed = (size_t)kDxSlots * (4 + 12 + 4 + 1) + (size_t)ng * (kDxGroup + 4) * 4 + 16;
+  const size_t fixed = (size_t)kDxSlots * (12 + 4 + (st.codes ? 0 : 4 + 1)) + (size_t)ng * (kDxGroup + 4) * 4 + 16;
   const size_t budget = 227 * 1024 - 1024;   // static shared memory of the kernel comes on top
   const size_t per_entry = has_val ? 8 : 4;
   const size_t avg_len = std::max<size_t>(1, div_up(st.nnz, st.rows));
   const size_t tile_rows = std::min<size_t>(kDxGroup, div_up(rpb, ng));
-  size_t ecap = std::min<size_t>((budget - fixed) / ng / per_entry, tile_rows * avg_len * 5 / 4 + 64);
+  size_t ecap = std::min<size_t>((budget - fixed) / ng / per_entry, tile_rows * avg_len * (st.codes ? 9 : 10) / 8 + 64);
   if (ecap_env > 0) ecap = (size_t)ecap_env;
   ecap = std::max<size_t>(64, ecap & ~(size_t)3);
   WH_REQUIRE(fixed + ecap * per_entry * ng <= budget, "direct_fused_launch: %zu bytes of shared memory", fixed + ecap * per_entry * ng);
@@ -534,7 +565,7 @@ int direct_fused_launch(whContext* ctx, const DirectStep& st, const DirectTable&
   DxArgs a;
   a.loss = st.loss; a.rows = (unsigned)st.rows; a.rows_per_block = rpb; a.ecap = (unsigned)ecap;
   a.offset = st.offset; a.index = st.index; a.value = st.value; a.label = st.label; a.xf = st.xf; a.shard = st.shard;
-  a.tags = t.tags.as<uint4>(); a.hot_w = t.hot_w.as<float>();
+  a.tags = t.tags.as<uint4>(); a.hot_w = t.hot_w.as<float>(); a.codes = st.codes;
   a.bitmap = l.bitmap.as<unsigned>(); a.part = l.part.as<long long>(); a.part_touched = l.part_touched.as<unsigned>();
   a.xw = st.xw; a.part_objv = st.part_objv; a.part_correct = st.part_correct; a.auc_hist = st.auc_hist; a.fs = st.fs; a.counters = st.counters;
   unit_terms_scale(st.nnz, &a.scale, &a.inv);
@@ -574,14 +605,39 @@ int direct_fused_launch(whContext* ctx, const DirectStep& st, const DirectTable&
   return WH_OK;
 }
 
+int direct_stage_launch(whContext* ctx, const DirectStep& st, const DirectTable& t, DirectLane& l) {
+  WH_TRY(l.codes.reserve(st.nnz * 4 + 64));
+  if (!l.touched.p) {
+    WH_TRY(l.touched.reserve((size_t)kDxSlots * 4));
+    WH_CUDA(cudaMemsetAsync(l.touched.p, 0, (size_t)kDxSlots * 4, ctx->stream));
+  }
+  DxArgs a;
+  memset(&a, 0, sizeof(a));
+  a.index = st.index; a.xf = st.xf; a.tags = t.tags.as<uint4>(); a.bitmap = l.bitmap.as<unsigned>(); a.codes = nullptr;
+  // two small blocks per SM: they have to fit into what the step kernel of the minibatch before leaves free
+  const unsigned grid = (unsigned)std::min<size_t>((size_t)ctx->num_sms * 2, div_up(st.nnz, 1024));
+  uint32_t* codes = l.codes.as<uint32_t>();
+  unsigned* touched = l.touched.as<unsigned>();
+  const bool pow2 = st.xf.mode == 1;
+  if (st.train) {
+    if (pow2) WH_LAUNCH((dx_stage_kernel<true, true>), grid, kDxGroup, 0, ctx->stream, a, st.nnz, codes, touched);
+    else WH_LAUNCH((dx_stage_kernel<true, false>), grid, kDxGroup, 0, ctx->stream, a, st.nnz, codes, touched);
+  } else {
+    if (pow2) WH_LAUNCH((dx_stage_kernel<false, true>), grid, kDxGroup, 0, ctx->stream, a, st.nnz, codes, touched);
+    else WH_LAUNCH((dx_stage_kernel<false, false>), grid, kDxGroup, 0, ctx->stream, a, st.nnz, codes, touched);
+  }
+  return WH_OK;
+}
+
 int direct_push_launch(whServer* s, cudaStream_t stream, const DirectTable& t, const DirectLane& l, const FixedScale* fs,
                        float mul, int num_sms) {
   HandleParams h = make_params(s, true);   // one push message: SGDHandle::Start
   const unsigned words = (unsigned)div_up(l.keys, 32);
   const unsigned hot_blocks = kDxSlots / 32;
-  const unsigned sweep = (unsigned)std::min<size_t>(div_up(div_up(words, 4), 256), (size_t)num_sms * 8);
+  const unsigned sweep = (unsigned)std::min<size_t>(div_up(words, 256), (size_t)num_sms * 8);
   WH_LAUNCH(push_sweep_kernel, hot_blocks + sweep, 256, 0, stream, h, s->view(), l.bitmap.as<unsigned>(), words,
-            t.tags.as<unsigned>(), l.part.as<long long>(), l.part_touched.as<unsigned>(), l.blocks, t.hot_w.as<float>(), fs, mul,
+            t.tags.as<unsigned>(), l.part.as<long long>(), l.part_touched.as<unsigned>(), l.touched.as<unsigned>(), l.blocks,
+            t.hot_w.as<float>(), fs, mul,
             s->counters.as<long long>(), hot_blocks);
   return WH_OK;
 }

@@ -30,9 +30,11 @@ struct DirectLane {
   DevBuf bitmap;       // u32[max_key / 32]: keys outside the table that occur in the minibatch
   DevBuf part;         // int64[kDxMaxBlocks][kDxSlots]: each block's sums of X^T dual for the table keys
   DevBuf part_touched; // u32[kDxMaxBlocks][kDxSlots / 32]: ... and which table keys the block saw
+  DevBuf codes;        // u32[nnz]: the minibatch's codes when they are made ahead of the step (direct_stage_launch)
+  DevBuf touched;      // u32[kDxSlots]: table keys seen by direct_stage_launch; cleared by the push
   uint64_t keys = 0;
   unsigned blocks = 0; // rows of `part` the last step wrote
-  void release() { bitmap.release(); part.release(); part_touched.release(); }
+  void release() { bitmap.release(); part.release(); part_touched.release(); codes.release(); touched.release(); }
 };
 
 // Builds the table image from one minibatch's (key, count) pairs (host arrays) and uploads it; synchronous.
@@ -48,6 +50,7 @@ struct DirectStep {
   const size_t* offset; const uint64_t* index; const float* value; const float* label;
   KeyXform xf;
   ShardEntry* shard;            // the shard's entries, addressed by key (key_begin == 0); accumulators are added into
+  const uint32_t* codes;        // NULL, or the codes direct_stage_launch made for this minibatch
   float* xw;                    // out: X w per row
   double* part_objv; unsigned* part_correct;   // out: per-block evaluation partial sums (grid entries)
   unsigned long long* auc_hist; // the AUC histogram every row is added to
@@ -57,6 +60,10 @@ struct DirectStep {
 // Localize + Pull + Init + Evaluate + CalcGrad of AsgdWorker::ProcessMinibatch in one launch. Returns the grid size
 // (= number of evaluation partials) in *nparts.
 int direct_fused_launch(whContext* ctx, const DirectStep& st, const DirectTable& t, DirectLane& l, unsigned* nparts);
+// The part of that launch that does not depend on the model -- key transform, table lookup, key bitmap -- as a launch
+// of its own, for workers with several minibatches in flight: it runs beside the step of the minibatch before. The
+// fused launch then takes st.codes = l.codes.
+int direct_stage_launch(whContext* ctx, const DirectStep& st, const DirectTable& t, DirectLane& l);
 // ZPush: one Handle::Push per key that occurred, gradients taken from the lane's accumulators (which it clears).
 int direct_push_launch(whServer* s, cudaStream_t stream, const DirectTable& t, const DirectLane& l, const FixedScale* fs,
                        float mul, int num_sms);
