@@ -333,8 +333,11 @@ def parity_leg(ctx, rank, world, local, args, max_key, rows, shape, algo, loss, 
     then every rank's shard {w, z, sq_cum_grad} against the CPU checker (oracle/: the checker leg, the one place besides
     the CPU arm where bench.py runs it) driven in the same message order -- all pulls of a step see the model as of the
     previous step, each owner applies the pushes of a step one handle update per source rank in ascending rank order
-    (tests/test_dist_gpu.py). Bar as in tests/util.py: 1e-5 relative + 1e-7; what misses it is counted and must lie within
-    1e-5 of the key's accumulated sum of |gradient terms|, the reference's own fp32 summation error."""
+    (tests/test_dist_gpu.py), and against the same simulation with X^T dual summed exactly. The device has to match the
+    second one entry by entry (1e-5 relative + 1e-7; in practice bit for bit). Against the first, per field and shard, the
+    relative L2 distance must stay within 1e-5 or within the distance the exact-sum simulation itself has from it -- a
+    CPU-only number: the reference's own fp32 summation error, 1e-5 .. 3e-5 of a popular key's gradient at 100 000 rows,
+    which compounds when several workers push per step; per-entry misses are counted and reported."""
     import torch.distributed as dist
     from wormhole_b200 import capi, synth
     from wormhole_b200.dist import key_range
@@ -397,6 +400,9 @@ def parity_leg(ctx, rank, world, local, args, max_key, rows, shape, algo, loss, 
                     We[keys[sl]], Ze[keys[sl]], Ce[keys[sl]] = w, z, cg
             for keys, _, _ in msgs:
                 touched.update(keys.tolist())
+            if os.environ.get("WH_BENCH_DEBUG"):
+                dd = np.abs(Wd.astype(np.float64) - We)
+                sys.stderr.write("parity sim step %d: |W_ref - W_exact| max %g, count > 1e-5: %d\n" % (step, dd.max(), int((dd > 1e-5).sum())))
         allk = np.array(sorted(touched), np.uint64)
         cuts = np.searchsorted(allk, np.array(bounds, np.uint64))
         want_keys = [allk[cuts[r]:cuts[r + 1]] for r in range(world)]
@@ -420,6 +426,7 @@ def parity_leg(ctx, rank, world, local, args, max_key, rows, shape, algo, loss, 
     want_keys, Wd, Zd, Cd, kind, seen, We, Ze, Ce = out
     e_out = 0
     e_abs = e_rel = 0.0
+    rel_l2 = []
     n = n_out = n_flip = 0
     max_abs = max_rel = 0.0
     ok = True
@@ -447,11 +454,18 @@ def parity_leg(ctx, rank, world, local, args, max_key, rows, shape, algo, loss, 
                 max_rel = max(max_rel, float((err / np.maximum(np.abs(b), 1e-7)).max()))
             if flip.any() and float(np.maximum(np.abs(a[flip]), np.abs(b[flip])).max()) > 1e-5:
                 ok = False
-            # what misses the bar must be explained by the reference's own rounding: it adds each key's gradient in
-            # fp32 in row order (learn/base/spmv.h:103-117), exact to ~1e-5 of the sum of |terms| only -- a key that
-            # sits in 64 000 of 100 000 rows carries that into z -- while the device adds integers
-            if rest.any() and not (err[rest] <= 1e-5 * np.maximum(np.maximum(np.abs(b[rest]), 1.0), seen[k][rest])).all():
-                ok = False
+            # Against the reference simulation a per-entry bar cannot hold once several workers push per step: the
+            # reference adds each key's gradient in fp32 in row order (learn/base/spmv.h:103-117), exact to ~1e-5 of the
+            # sum of |terms| only; that error enters w of the popular keys, through Xw every dual, and so every key's
+            # next gradient. (The two CPU simulations differ from each other by exactly these amounts, with no GPU
+            # involved.) Held to the bar in norm instead; the per-entry counts are reported.
+            den = float((b ** 2).sum())
+            if den > 0:
+                d_dev = (float(((a - b) ** 2).sum()) / den) ** 0.5       # device vs reference simulation
+                d_sim = (float(((ex - b) ** 2).sum()) / den) ** 0.5      # exact-sum simulation vs reference simulation (CPU only)
+                rel_l2.append([round(d_dev, 9), round(d_sim, 9)])
+                if d_dev > max(1e-5, 1.01 * d_sim):
+                    ok = False
     if e_out > max(3, 1e-5 * n):     # (a handful of keys on the L1 threshold apart, the two must agree)
         ok = False
     nnz_dev = sum(g[1] for g in got)
@@ -461,6 +475,7 @@ def parity_leg(ctx, rank, world, local, args, max_key, rows, shape, algo, loss, 
     return {"ranks": world, "minibatches_per_rank": steps, "rows": rows, "keys": int(sum(len(k) for k in want_keys)),
             "values_compared": n, "outside_1e-5_rel_1e-7_abs": n_out, "l1_flips": n_flip, "max_abs": max_abs,
             "max_rel": max_rel, "vs_exact_sum_simulation": {"outside_1e-5_rel_1e-7_abs": e_out, "max_abs": e_abs, "max_rel": e_rel},
+            "rel_l2_vs_reference_per_field_[device,exact_sum_simulation]": rel_l2,
             "nnz_w": [int(nnz_dev), nnz_ref], "checker": kind, "ok": bool(ok)}
 
 

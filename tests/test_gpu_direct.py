@@ -40,6 +40,7 @@ class env:
 
 
 def run(gpu, blks, algo, loss, max_key, depth=1, train_mask=None, **switches):
+    switches.setdefault("WH_DX_MIN_COVERAGE", 0)      # these tests want the direct step whatever the table covers
     with env(**switches):
         srv = capi.Server(gpu, algo, 0.5, 0.1, 0.1, 1.0, 0, max_key)
         wk = capi.Worker(gpu, srv, loss, max_key, depth=depth)
@@ -129,7 +130,7 @@ def test_direct_sees_changes_made_behind_its_back(gpu):
     blks = [synth.criteo_minibatch(m, rows=10000) for m in range(4)]
     out = []
     for direct in (1, 0):
-        with env(WH_DIRECT=direct):
+        with env(WH_DIRECT=direct, WH_DX_MIN_COVERAGE=0):
             srv = capi.Server(gpu, capi.ALGO_FTRL, 0.5, 0.1, 0.1, 1.0, 0, max_key)
             wk = capi.Worker(gpu, srv, capi.LOSS_LOGIT, max_key)
             progs = [wk.process_minibatch(blks[0]), wk.process_minibatch(blks[1])]
@@ -159,6 +160,7 @@ def test_direct_valued_features_vs_checker(gpu, checker, algo):
     job = checker.linear_create(algo, O.LOSS_LOGIT, 0.5, 0.1, 0.1, 1.0, max_key)
     srv = capi.Server(gpu, algo, 0.5, 0.1, 0.1, 1.0, 0, max_key)
     wk = capi.Worker(gpu, srv, capi.LOSS_LOGIT, max_key)
+    os.environ["WH_DX_MIN_COVERAGE"] = "0"
     W, Z, CG = (np.zeros(max_key, np.float32) for _ in range(3))
     for m in range(6):
         blk = random_block(rng, 4000, 16, 30000, with_value=True, empty_rows=(m % 2 == 0))
@@ -182,6 +184,7 @@ def test_direct_valued_features_vs_checker(gpu, checker, algo):
         for name, x, e, r in zip(("w", "z", "cg"), got, (W[k], Z[k], CG[k]), (w, z, cg)):
             assert_state_close(x, e, rtol=2e-6, what="direct valued vs exact-sum emulation " + name, flip_abs=FLIP_ABS)
             assert_state_close(x, r, what="direct valued " + name, stragglers=STRAGGLERS, flip_abs=FLIP_ABS, loose_factor=2.0)
+    os.environ.pop("WH_DX_MIN_COVERAGE", None)
     wk.close(); srv.close(); checker.linear_destroy(job)
 
 

@@ -483,6 +483,8 @@ int direct_table_build(whContext* ctx, DirectTable* t, const uint64_t* keys, con
     return counts[x] != counts[y] ? counts[x] > counts[y] : keys[x] < keys[y];
   });
   int placed = 0;
+  unsigned long long covered = 0, total = 0;
+  for (size_t i = 0; i < n; ++i) total += counts[i];
   const char* off = getenv("WH_DX_TABLE");   // WH_DX_TABLE=0: an empty table, every key takes the general route (bench.py's comparison)
   for (size_t i = 0; i < want && !(off && atoi(off) == 0); ++i) {
     const uint64_t k = keys[order[i]];
@@ -493,10 +495,12 @@ int direct_table_build(whContext* ctx, DirectTable* t, const uint64_t* keys, con
       if (image[slot] != kDxEmpty) continue;
       image[slot] = k32;
       ++placed;
+      covered += counts[order[i]];
       break;
     }
   }
   t->placed = placed;   // (an empty table is a valid table: every key then takes the general route)
+  t->coverage = total ? (double)covered / (double)total : 0.0;
   WH_TRY(t->tags.reserve((size_t)kDxSlots * 4)); WH_TRY(t->hot_w.reserve((size_t)kDxSlots * 4));
   WH_CUDA(cudaMemcpyAsync(t->tags.p, image.data(), (size_t)kDxSlots * 4, cudaMemcpyHostToDevice, ctx->stream));
   WH_CUDA(cudaStreamSynchronize(ctx->stream));   // the host vector goes out of scope

@@ -19,6 +19,7 @@ struct DirectTable {
   DevBuf tags;        // uint4[kDxBuckets]: 4 transformed keys per bucket (kDxEmpty = free way)
   DevBuf hot_w;       // f32[kDxSlots]: the shard's weight of every slot's key (mirror kept by the push kernel)
   int placed = 0;
+  double coverage = 0;   // share of the census minibatch's entries whose key is in the table
   bool ready = false;
   unsigned long long seen_version = 0;   // whServer::version the mirror is known to match
   void release() { tags.release(); hot_w.release(); }
