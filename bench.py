@@ -506,32 +506,47 @@ def side_config(ctx, rank, world, local, args, stream, name, algo, loss, shape, 
 
 
 def difacto_config(ctx, rank, world, rows, steps, warmup):
-    """BASELINE.json configs[4]: DiFacto, dim 16, on the Criteo shape (learn/difacto guide values). The
-    DiFacto entry points are synchronous and single-GPU (wh_difacto_process_minibatch): measured on rank 0's GPU only."""
+    """BASELINE.json configs[4]: DiFacto, dim 16, on the Criteo shape (learn/difacto guide values). One
+    GPU: wh_difacto_process_minibatch. Several: every rank is a worker and the shard of its key range, the minibatch in
+    phases with the three exchanges over NCCL (dist.ShardedDifacto). The entry points are synchronous."""
     import torch
-    from wormhole_b200 import capi, synth
-    if world > 1:
-        return {"unavailable": "DiFacto's shard and worker run on one GPU (wh_difacto_*); not sharded across ranks"}
+    import torch.distributed as dist
+    from wormhole_b200 import capi
+    from wormhole_b200.dist import ShardedDifacto, key_range
     max_key = MAX_KEY
+    kb, ke = key_range(rank, world, max_key)
     d = capi.Difacto(ctx, l1=4.0, l2=0.0, eta=.01, beta=1.0, l1_shrk=True, dim=16, threshold=16, v_l2=1e-4, max_key=max_key,
-                     key_begin=0, key_end=max_key)
-    _, blks, raw = make_pool("criteo", 9, 3, rows, want_host=False)
+                     key_begin=kb, key_end=ke)
+    _, blks, raw = make_pool("criteo", 9 + rank, 3, rows, want_host=False)
     U = len(np.unique(raw[0].index % np.uint64(max_key)))
+    if world > 1:
+        sd = ShardedDifacto(ctx, d, max_key, device=torch.device("cuda", torch.cuda.current_device()))
+        run = lambda b, dp: sd.process_minibatch(b, True, dp, capi.WH_DEVICE)
+    else:
+        run = lambda b, dp: d.process_minibatch(b, True, dp, capi.WH_DEVICE)
     for i in range(warmup):
-        d.process_minibatch(blks[i % 3], True, 0, capi.WH_DEVICE)
+        run(blks[i % 3], 0)
     torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+        torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record(torch.cuda.current_stream())
     t0 = time.perf_counter()
     for i in range(steps):
-        d.process_minibatch(blks[(warmup + i) % 3], True, 1, capi.WH_DEVICE)
+        run(blks[(warmup + i) % 3], 1)
     e1.record(torch.cuda.current_stream())
     torch.cuda.synchronize()
     ms = max(e0.elapsed_time(e1), 1e3 * (time.perf_counter() - t0))
+    if world > 1:
+        t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
     d.close()
-    v = rows * steps / (ms * 1e-3)
-    return {"workload": "DiFacto dim 16 (threshold 16, lambda_l1 4, lr_eta .01) on the synthetic Criteo shape, minibatches resident in HBM; the entry point is synchronous",
-            "value": v, "unit": "examples/s", "steps": steps, "warmup": warmup, "ms_per_step": ms / steps,
+    v = world * rows * steps / (ms * 1e-3)
+    return {"workload": "DiFacto dim 16 (threshold 16, lambda_l1 4, lr_eta .01) on the synthetic Criteo shape, minibatches resident in HBM; "
+                        "the entry point is synchronous" + ("; %d key-range shards, count push / ZVPull / ZVPush as all-to-all-v over NCCL" % world if world > 1 else ""),
+            "value": v, "unit": "examples/s", "n_gpus": world, "steps": steps, "warmup": warmup, "ms_per_step": ms / steps,
             "rows_per_minibatch": rows, "unique_keys_per_row_r": round(U / rows, 4)}
 
 
@@ -624,11 +639,16 @@ def run_ours(args):
             others[name] = side_config(ctx, rank, world, local, args, stream, name, a2, l2, "criteo", ROWS, MAX_KEY, NNZ_PER_ROW, K, Wm, pool_n)
         others["kdd_ftrl"] = side_config(ctx, rank, world, local, args, stream, "kdd_ftrl", "ftrl", "logit", "kdd", 1000000,
                                          synth.KDD_VOCAB, 11, max(3, K // 4), 3, 3)
-        if rank == 0:
+        # (every rank takes part; a failure on one rank of several would leave the others in a collective, so it is
+        #  only caught where there is a single rank)
+        if world == 1:
             try:
                 others["difacto_dim16"] = difacto_config(ctx, rank, world, ROWS, max(3, K // 4), 3)
             except Exception as e:  # noqa: BLE001
                 others["difacto_dim16"] = {"unavailable": "failed: %r" % (e,)}
+        else:
+            others["difacto_dim16"] = difacto_config(ctx, rank, world, ROWS, max(3, K // 4), 3)
+        ctx.set_stream(stream.cuda_stream)
     no_table = None
     if default_cfg and world == 1 and not args.no_others and len(table_keys):
         # the same device-resident leg with an empty table of frequent keys, in a process of its own (the switch is read

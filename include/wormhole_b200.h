@@ -370,6 +370,24 @@ WH_API int wh_difacto_set_init_stream(whDifacto* d, const int* rand_values, size
  * (learn/difacto/progress.h:28-36). Synchronous. */
 WH_API int wh_difacto_process_minibatch(whDifacto* d, const whRowBlock* blk, int mem, int train, int data_pass,
                                         double* prog);
+/* The same minibatch in phases, for key-range shards on several GPUs (rank g = AsyncWorker g + the AsyncServer shard of
+ * [g*max_key/S, (g+1)*max_key/S)): ProcessMinibatch cut at its three exchanges -- the count push (learn/difacto/
+ * async_sgd.h:374-381), ZVPull (:424), ZVPush (:408-411). All arrays are DEVICE pointers on the context's device.
+ *   begin   Localize with counts (:366-371): the ascending unique keys and their counts (valid until the next begin).
+ *   finish  Loss::Evaluate / CalcGrad (:385-407) with the pulled model in fixed-width rows -- w[U], has[U] (1: the key came
+ *           with its embedding, model_siz = dim + 1; 0: w only), V[U x dim] -- writes gw[U], G[U x dim] for the push.
+ *           prog[8] as wh_difacto_process_minibatch, new_w / new_V left 0 (the shards own them: shard_progress).
+ *   shard_count_push / shard_pull / shard_push   what the server does with ONE message (:216-244): n keys of this shard's
+ *           range, ascending. Messages are applied in the order of the calls. */
+WH_API int wh_difacto_begin(whDifacto* d, const whRowBlock* blk, int mem, const uint64_t** d_uniq, const uint32_t** d_cnt,
+                            size_t* num_uniq);
+WH_API int wh_difacto_finish(whDifacto* d, const float* d_w, const unsigned char* d_has, const float* d_V, int train,
+                             float* d_gw, float* d_G, double* prog);
+WH_API int wh_difacto_shard_count_push(whDifacto* d, const uint64_t* d_keys, const uint32_t* d_cnt, size_t n);
+WH_API int wh_difacto_shard_pull(whDifacto* d, const uint64_t* d_keys, size_t n, float* d_w, unsigned char* d_has, float* d_V);
+WH_API int wh_difacto_shard_push(whDifacto* d, const uint64_t* d_keys, size_t n, const float* d_gw, const float* d_G,
+                                 const unsigned char* d_has);
+WH_API int wh_difacto_shard_progress(whDifacto* d, double* new_w, double* new_V);
 /* Entry fields of the given keys (host arrays): fea_cnt[n], size[n] (1 or dim+1), w[n*(dim+1)] =
  * {w0, V}, cg[n*(dim+2)] = {sqc_grad_0, z_0, sqc_grad_V}; rows are zero beyond the entry's size. */
 WH_API int wh_difacto_get_state(whDifacto* d, const uint64_t* keys, size_t n, uint32_t* fea_cnt, int* size,

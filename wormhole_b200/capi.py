@@ -339,6 +339,34 @@ class Difacto:
         _check(lib().wh_difacto_process_minibatch(self.h, C.byref(rb), C.c_int(mem), C.c_int(train), C.c_int(data_pass), _ptr(prog)))
         return prog
 
+    # ---- the minibatch in phases (key-range shards on several GPUs; device addresses) ----
+    def begin(self, blk, mem=WH_HOST):
+        pu, pc, n = C.c_void_p(), C.c_void_p(), C.c_size_t()
+        rb = _rowblock(blk)
+        self._begun = blk
+        _check(lib().wh_difacto_begin(self.h, C.byref(rb), C.c_int(mem), C.byref(pu), C.byref(pc), C.byref(n)))
+        return (pu.value or 0), (pc.value or 0), n.value
+
+    def finish(self, w_ptr, has_ptr, v_ptr, train, gw_ptr, g_ptr):
+        prog = np.zeros(8, np.float64)
+        _check(lib().wh_difacto_finish(self.h, C.c_void_p(w_ptr), C.c_void_p(has_ptr), C.c_void_p(v_ptr), C.c_int(train),
+                                       C.c_void_p(gw_ptr), C.c_void_p(g_ptr), _ptr(prog)))
+        return prog
+
+    def shard_count_push(self, keys_ptr, cnt_ptr, n):
+        _check(lib().wh_difacto_shard_count_push(self.h, C.c_void_p(keys_ptr), C.c_void_p(cnt_ptr), C.c_size_t(n)))
+
+    def shard_pull(self, keys_ptr, n, w_ptr, has_ptr, v_ptr):
+        _check(lib().wh_difacto_shard_pull(self.h, C.c_void_p(keys_ptr), C.c_size_t(n), C.c_void_p(w_ptr), C.c_void_p(has_ptr), C.c_void_p(v_ptr)))
+
+    def shard_push(self, keys_ptr, n, gw_ptr, g_ptr, has_ptr):
+        _check(lib().wh_difacto_shard_push(self.h, C.c_void_p(keys_ptr), C.c_size_t(n), C.c_void_p(gw_ptr), C.c_void_p(g_ptr), C.c_void_p(has_ptr)))
+
+    def shard_progress(self):
+        a, b = C.c_double(), C.c_double()
+        _check(lib().wh_difacto_shard_progress(self.h, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
     def get_state(self, keys):
         keys = np.ascontiguousarray(keys, np.uint64)
         n, dim = len(keys), self.dim

@@ -196,6 +196,10 @@ struct whDifacto {
       accG, accX, flags, scal;
   wh::PinnedBuf pinned;
   long long seen_new_w = 0, seen_new_V = 0;
+  // between wh_difacto_begin and wh_difacto_finish (sharded jobs: the model lives elsewhere)
+  bool b_open = false;
+  size_t b_rows = 0, b_nnz = 0, b_U = 0;
+  const size_t* b_offset = nullptr; const float* b_value = nullptr; const float* b_label = nullptr;
   size_t entries() const { return (size_t)(c.key_end - c.key_begin); }
 };
 
@@ -573,6 +577,138 @@ int wh_difacto_process_minibatch(whDifacto* d, const whRowBlock* blk, int mem, i
   }
   dfc_prog(reinterpret_cast<const EvalOut*>(pin), reinterpret_cast<const EvalOut*>(pin + 256), rows, prog);
   prog[6] = (double)(cn[0] - d->seen_new_w); prog[7] = (double)(cn[1] - d->seen_new_V);
+  d->seen_new_w = cn[0]; d->seen_new_V = cn[1];
+  return WH_OK;
+}
+
+// ---- the same minibatch in phases, for key-range shards on several GPUs -------------------------------------
+// AsyncWorker::ProcessMinibatch (learn/difacto/async_sgd.h:363-425) cut at its three exchanges: the count push
+// (:374-381), ZVPull (:424) and ZVPush (:408-411). begin / finish are the worker's halves; the shard_* calls are what
+// the server does with one message (:216-244). The variable-length payloads of ZVPull / ZVPush travel as fixed-width
+// rows {w, has, V[dim]} per key -- `has` is the length flag (model_siz = 1 or dim + 1).
+
+static int dfc_count_to_device(whDifacto* d, size_t n, unsigned** d_n) {
+  unsigned* slot = d->scal.as<unsigned>() + 12;
+  const unsigned v = (unsigned)n;
+  WH_CUDA(cudaMemcpyAsync(slot, &v, 4, cudaMemcpyHostToDevice, d->ctx->stream));   // (pageable source: staged before the call returns)
+  *d_n = slot;
+  return WH_OK;
+}
+
+int wh_difacto_begin(whDifacto* d, const whRowBlock* blk, int mem, const uint64_t** d_uniq, const uint32_t** d_cnt, size_t* num_uniq) {
+  WH_REQUIRE(d && blk && d_uniq && d_cnt && num_uniq, "wh_difacto_begin: NULL argument");
+  WH_REQUIRE(mem == WH_HOST || mem == WH_DEVICE, "wh_difacto_begin: bad mem %d", mem);
+  whContext* ctx = d->ctx;
+  DeviceGuard g(ctx->device);
+  const size_t rows = blk->size;
+  WH_REQUIRE(rows > 0 && blk->offset && blk->index && blk->label, "wh_difacto_begin: empty block or NULL offset/index/label");
+  size_t n;
+  if (mem == WH_HOST) n = blk->offset[rows];
+  else {
+    WH_CUDA(cudaMemcpyAsync(d->pinned.p, blk->offset + rows, sizeof(size_t), cudaMemcpyDeviceToHost, ctx->stream));
+    WH_CUDA(cudaStreamSynchronize(ctx->stream));
+    n = d->pinned.as<size_t>()[0];
+  }
+  WH_REQUIRE(n > 0 && n < (size_t)UINT32_MAX, "wh_difacto_begin: %zu entries", n);
+  const uint64_t* d_index;
+  WH_TRY(to_device(ctx, d->in_index, blk->index, n, mem, &d_index));
+  WH_TRY(to_device(ctx, d->in_offset, blk->offset, rows + 1, mem, &d->b_offset));
+  WH_TRY(to_device(ctx, d->in_value, blk->value, n, mem, &d->b_value));
+  WH_TRY(to_device(ctx, d->in_label, blk->label, rows, mem, &d->b_label));
+  const size_t kcap = (size_t)std::min<uint64_t>(n, d->c.max_key);
+  WH_TRY(d->uniq.reserve(kcap * 8)); WH_TRY(d->cnt.reserve(kcap * 4)); WH_TRY(d->index.reserve(n * 4));
+  unsigned* d_nuniq = d->scal.as<unsigned>();
+  LocInput in{d_index, n, make_xform(d->c.max_key)};
+  if (direct_supported(d->c.max_key)) WH_TRY(localize_direct(ctx, in, d->uniq.as<uint64_t>(), d->cnt.as<uint32_t>(), d->index.as<uint32_t>(), d_nuniq));
+  else WH_TRY(localize_sort(ctx, in, d->uniq.as<uint64_t>(), d->cnt.as<uint32_t>(), d->index.as<uint32_t>(), d_nuniq));
+  WH_CUDA(cudaMemcpyAsync(d->pinned.p, d_nuniq, sizeof(unsigned), cudaMemcpyDeviceToHost, ctx->stream));
+  WH_CUDA(cudaStreamSynchronize(ctx->stream));
+  d->b_rows = rows; d->b_nnz = n; d->b_U = d->pinned.as<unsigned>()[0];
+  d->b_open = true;
+  *d_uniq = d->uniq.as<uint64_t>(); *d_cnt = d->cnt.as<uint32_t>(); *num_uniq = d->b_U;
+  return WH_OK;
+}
+
+int wh_difacto_finish(whDifacto* d, const float* d_w, const unsigned char* d_has, const float* d_V, int train, float* d_gw,
+                      float* d_G, double* prog) {
+  WH_REQUIRE(d && prog && d->b_open, "wh_difacto_finish: no minibatch begun");
+  WH_REQUIRE(d->b_U == 0 || (d_w && d_has && (d->c.dim == 0 || d_V)), "wh_difacto_finish: the pulled model is NULL");
+  WH_REQUIRE(!train || d->b_U == 0 || (d_gw && (d->c.dim == 0 || d_G)), "wh_difacto_finish: training needs gradient buffers");
+  whContext* ctx = d->ctx;
+  DeviceGuard g(ctx->device);
+  d->b_open = false;
+  const int dim = d->c.dim, sd = dim > 0 ? dim : 1;
+  const size_t rows = d->b_rows, U = d->b_U;
+  DfcWork k;
+  WH_TRY(dfc_work(d, rows, U, &k));
+  WH_TRY(difacto_loss_launch(ctx, &d->ax, d->ev_fork, d->ev_auc, rows, d->b_nnz, d->b_offset, d->index.as<uint32_t>(), d->b_value,
+                             d->b_label, U, sd, d_w, d_has, d_V, dim > 0, d->c.grad_clipping, d->c.grad_normalization, train != 0, k));
+  if (train && U) {
+    WH_CUDA(cudaMemcpyAsync(d_gw, k.gw, U * 4, cudaMemcpyDeviceToDevice, ctx->stream));
+    if (dim > 0) WH_CUDA(cudaMemcpyAsync(d_G, k.G, U * (size_t)dim * 4, cudaMemcpyDeviceToDevice, ctx->stream));
+  }
+  char* pin = d->pinned.as<char>();
+  WH_CUDA(cudaMemcpyAsync(pin, k.evW, sizeof(EvalOut), cudaMemcpyDeviceToHost, ctx->stream));
+  WH_CUDA(cudaMemcpyAsync(pin + 256, k.ev, sizeof(EvalOut), cudaMemcpyDeviceToHost, ctx->stream));
+  WH_CUDA(cudaStreamSynchronize(ctx->stream));
+  dfc_prog(reinterpret_cast<const EvalOut*>(pin), reinterpret_cast<const EvalOut*>(pin + 256), rows, prog);
+  return WH_OK;
+}
+
+int wh_difacto_shard_count_push(whDifacto* d, const uint64_t* d_keys, const uint32_t* d_cnt, size_t n) {
+  WH_REQUIRE(d && (n == 0 || (d_keys && d_cnt)), "wh_difacto_shard_count_push: NULL argument");
+  if (n == 0 || d->c.dim == 0) return WH_OK;
+  whContext* ctx = d->ctx;
+  DeviceGuard g(ctx->device);
+  WH_TRY(d->flags.reserve(n));
+  unsigned* d_n;
+  WH_TRY(dfc_count_to_device(d, n, &d_n));
+  WH_LAUNCH(dfc_count_push_kernel, (unsigned)div_up(n, 256), 256, 0, ctx->stream, dfc_params(d), d_keys, d_cnt, d_n, d->base.as<float4>(),
+            d->hasv.as<unsigned char>(), d->flags.as<unsigned char>(), d->counters.as<long long>());
+  return dfc_grow(d, d_keys, n, d_n);
+}
+
+int wh_difacto_shard_pull(whDifacto* d, const uint64_t* d_keys, size_t n, float* d_w, unsigned char* d_has, float* d_V) {
+  WH_REQUIRE(d && (n == 0 || (d_keys && d_w && d_has && (d->c.dim == 0 || d_V))), "wh_difacto_shard_pull: NULL argument");
+  if (n == 0) return WH_OK;
+  whContext* ctx = d->ctx;
+  DeviceGuard g(ctx->device);
+  unsigned* d_n;
+  WH_TRY(dfc_count_to_device(d, n, &d_n));
+  WH_LAUNCH(dfc_pull_kernel, (unsigned)div_up(n, 256), 256, 0, ctx->stream, dfc_params(d), d_keys, d_n, d->base.as<float4>(),
+            d->hasv.as<unsigned char>(), d->V.as<float>(), d_w, d_has, d_V, d->counters.as<long long>());
+  return WH_OK;
+}
+
+int wh_difacto_shard_push(whDifacto* d, const uint64_t* d_keys, size_t n, const float* d_gw, const float* d_G, const unsigned char* d_has) {
+  WH_REQUIRE(d && (n == 0 || (d_keys && d_gw && d_has && (d->c.dim == 0 || d_G))), "wh_difacto_shard_push: NULL argument");
+  if (n == 0) return WH_OK;
+  whContext* ctx = d->ctx;
+  DeviceGuard g(ctx->device);
+  WH_TRY(d->flags.reserve(n));
+  unsigned* d_n;
+  WH_TRY(dfc_count_to_device(d, n, &d_n));
+  WH_LAUNCH(dfc_grad_push_kernel, (unsigned)div_up(n, 256), 256, 0, ctx->stream, dfc_params(d), d_keys, d_n, d_gw, d_G, d_has,
+            d->base.as<float4>(), d->hasv.as<unsigned char>(), d->V.as<float>(), d->cgV.as<float>(), d->flags.as<unsigned char>(),
+            d->counters.as<long long>());
+  return dfc_grow(d, d_keys, n, d_n);
+}
+
+// new_w / new_V of this shard since the last call (the progress numbers the servers own); also reports bad keys
+int wh_difacto_shard_progress(whDifacto* d, double* new_w, double* new_V) {
+  WH_REQUIRE(d && new_w && new_V, "wh_difacto_shard_progress: NULL argument");
+  whContext* ctx = d->ctx;
+  DeviceGuard g(ctx->device);
+  char* pin = d->pinned.as<char>();
+  WH_CUDA(cudaMemcpyAsync(pin + 512, d->counters.p, 32, cudaMemcpyDeviceToHost, ctx->stream));
+  WH_CUDA(cudaStreamSynchronize(ctx->stream));
+  const long long* cn = reinterpret_cast<const long long*>(pin + 512);
+  if (cn[2]) {
+    WH_CUDA(cudaMemsetAsync(d->counters.as<long long>() + 2, 0, 8, ctx->stream));
+    set_error("wh_difacto: %lld keys outside the shard's range", cn[2]);
+    return WH_ERR_INVALID;
+  }
+  *new_w = (double)(cn[0] - d->seen_new_w); *new_V = (double)(cn[1] - d->seen_new_V);
   d->seen_new_w = cn[0]; d->seen_new_V = cn[1];
   return WH_OK;
 }

@@ -131,6 +131,95 @@ class ShardedWorker:
         return prog
 
 
+class ShardedDifacto:
+    """AsyncWorker::ProcessMinibatch of learn/difacto/async_sgd.h:363-425 on rank g of a key-range sharded job: rank g
+    is worker g and the AsyncServer shard of [g*max_key/S, (g+1)*max_key/S). The three exchanges of the minibatch --
+    count push (:374-381), ZVPull (:424), ZVPush (:408-411) -- are all-to-all-v's of the sorted key slices; the owners
+    apply one message per source rank in ascending source order (one valid interleaving of the asynchronous server).
+    The variable-length payloads travel as fixed-width rows {w, has, V[dim]} (has = the length flag)."""
+
+    def __init__(self, ctx, difacto, max_key, group=None, device=None):
+        self.ctx, self.d, self.max_key, self.group = ctx, difacto, max_key, group
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.device = device if device is not None else torch.device("cuda", torch.cuda.current_device())
+        self.bounds = range_boundaries(self.world, max_key, self.device)
+        self.dim = difacto.dim
+        self._bound = None
+        self._bind()
+
+    def _bind(self):
+        s = torch.cuda.current_stream(self.device).cuda_stream
+        if self._bound != s:
+            self.ctx.set_stream(s)
+            self._bound = s
+
+    def _a2a(self, out, inp, out_split, in_split):
+        if self.world == 1:
+            out.copy_(inp)
+        else:
+            dist.all_to_all_single(out, inp, out_split, in_split, group=self.group)
+        return out
+
+    def _sizes(self, keys):
+        cut = torch.searchsorted(keys, self.bounds)
+        send = (cut[1:] - cut[:-1]).tolist()
+        if self.world == 1:
+            return send, list(send)
+        s = torch.tensor(send, dtype=torch.int64, device=self.device)
+        r = torch.empty_like(s)
+        dist.all_to_all_single(r, s, group=self.group)
+        return send, r.tolist()
+
+    def process_minibatch(self, blk, train=True, data_pass=0, mem=0):
+        self._bind()
+        dev, dim, sd = self.device, self.dim, max(self.dim, 1)
+        pu, pc, U = self.d.begin(blk, mem)
+        keys = _wrap_device_i64(pu, U, dev)
+        send, recv = self._sizes(keys)
+        R = sum(recv)
+        rkeys = self._a2a(torch.empty(R, dtype=torch.int64, device=dev), keys, recv, send)
+        ptr = lambda t: t.data_ptr() if t.numel() else 0
+        if train and data_pass == 0 and dim > 0:
+            cnt = _wrap_device(pc, U, "<i4", torch.int32, dev)
+            rcnt = self._a2a(torch.empty(R, dtype=torch.int32, device=dev), cnt, recv, send)
+            o = 0
+            for n in recv:
+                self.d.shard_count_push(ptr(rkeys[o:o + n]), ptr(rcnt[o:o + n]), n)
+                o += n
+        # ZVPull: Handle::Pull does not change the shard, so the S messages are served as one batch
+        rw = torch.empty(R, dtype=torch.float32, device=dev)
+        rhas = torch.empty(R, dtype=torch.uint8, device=dev)
+        rV = torch.empty((R, sd), dtype=torch.float32, device=dev)
+        self.d.shard_pull(ptr(rkeys), R, ptr(rw), ptr(rhas), ptr(rV))
+        w = self._a2a(torch.empty(U, dtype=torch.float32, device=dev), rw, send, recv)
+        has = self._a2a(torch.empty(U, dtype=torch.uint8, device=dev), rhas, send, recv)
+        V = self._a2a(torch.empty((U, sd), dtype=torch.float32, device=dev), rV, send, recv) if dim > 0 else rV[:0]
+        gw = torch.empty(U, dtype=torch.float32, device=dev)
+        G = torch.empty((U, sd), dtype=torch.float32, device=dev)
+        prog = self.d.finish(ptr(w), ptr(has), ptr(V), train, ptr(gw), ptr(G))
+        if train:
+            rgw = self._a2a(rw, gw, recv, send)
+            rG = self._a2a(rV, G, recv, send) if dim > 0 else rV
+            # the push carries the lengths the worker pulled (rhas is unchanged since the pull of these very keys)
+            o = 0
+            for n in recv:
+                self.d.shard_push(ptr(rkeys[o:o + n]), n, ptr(rgw[o:o + n]), ptr(rG[o:o + n]), ptr(rhas[o:o + n]))
+                o += n
+        prog[6], prog[7] = self.d.shard_progress()
+        return prog
+
+
+def _wrap_device(ptr, n, typestr, dtype, device):
+    if n == 0:
+        return torch.empty(0, dtype=dtype, device=device)
+
+    class _Arr:
+        __cuda_array_interface__ = {"shape": (n,), "typestr": typestr, "data": (ptr, False), "version": 2}
+
+    return torch.as_tensor(_Arr(), device=device)
+
+
 def _wrap_device_i64(ptr, n, device):
     """A torch int64 view of n uint64 keys at a raw device address (keys < 2^63 by construction)."""
     if n == 0:
