@@ -351,7 +351,7 @@ typedef struct {
   int v_has_lr_beta; float v_lr_beta;
   float init_scale;             /* V starts uniform in [-init_scale, init_scale] */
   float grad_clipping, grad_normalization;
-  float dropout;                /* must be 0: the reference draws it from rand() on the worker */
+  float dropout;                /* embedding-gradient dropout; > 0 needs wh_difacto_set_dropout_stream */
   uint64_t key_begin, key_end;  /* the shard's key range (dense) */
   uint64_t max_key;             /* ps::FLAGS_max_key */
   uint64_t seed;                /* V init without an init stream: hash of (seed, key, j) */
@@ -364,6 +364,13 @@ WH_API int wh_difacto_destroy(whDifacto* d);
  * rand() sequence (host ints, after the same srand): the i-th embedding float created from now on
  * uses the i-th value. Without a stream V is initialised from a hash of (seed, key, j). */
 WH_API int wh_difacto_set_init_stream(whDifacto* d, const int* rand_values, size_t n);
+/* Gradient dropout (learn/difacto/loss.h:150-154) zeroes an embedding-gradient float when `(float)rand() / RAND_MAX >
+ * 1 - dropout`, drawing from the WORKER process's glibc rand() -- one value per float of the keys that were pulled with
+ * an embedding, ascending key order, every training minibatch. Hand over the next n values of that sequence; the i-th
+ * float from now on uses the i-th value. shared_with_init != 0 (rand_values ignored): draw from the init stream and
+ * advance its cursor instead -- worker and server living in ONE process share one rand() sequence (that is how the
+ * checker runs the reference); in a ps-lite deployment they are separate processes with a sequence each. */
+WH_API int wh_difacto_set_dropout_stream(whDifacto* d, const int* rand_values, size_t n, int shared_with_init);
 /* AsyncWorker::ProcessMinibatch, learn/difacto/async_sgd.h:363-425: Localize with counts ->
  * (train, data_pass 0, dim > 0: count push, cmd = kPushFeaCnt) -> ZVPull -> Loss::Evaluate ->
  * Loss::CalcGrad -> ZVPush. prog[8] = {objv, auc, objv_w, copc(0), count, new_ex, new_w, new_V}
@@ -388,6 +395,16 @@ WH_API int wh_difacto_shard_pull(whDifacto* d, const uint64_t* d_keys, size_t n,
 WH_API int wh_difacto_shard_push(whDifacto* d, const uint64_t* d_keys, size_t n, const float* d_gw, const float* d_G,
                                  const unsigned char* d_has);
 WH_API int wh_difacto_shard_progress(whDifacto* d, double* new_w, double* new_V);
+/* ps::KVWorker<float> messages against this shard on HOST arrays -- what learn/difacto's worker sends (the C++ facade
+ * host/ps.h forwards here). keys ascend. Synchronous.
+ *   zpush_count  ZPush(feaid, feacnt, cmd = kPushFeaCnt), learn/difacto/async_sgd.h:374-379: counts are floats, added as
+ *                (unsigned) counts[i] (:218).
+ *   zvpull       ZVPull(feaid, val, val_siz), :424: sizes[i] = 1 ({w0}) or dim + 1 ({w0, V}), AdaGradHandle::Pull
+ *                :234-244; vals has room for n * (dim + 1) floats, *vals_len = floats written.
+ *   zvpush       ZVPush(feaid, val, val_siz), :408-411: the gradients in the layout zvpull returned. */
+WH_API int wh_difacto_zpush_count(whDifacto* d, const uint64_t* keys, const float* counts, size_t n);
+WH_API int wh_difacto_zvpull(whDifacto* d, const uint64_t* keys, size_t n, float* vals, int* sizes, size_t* vals_len);
+WH_API int wh_difacto_zvpush(whDifacto* d, const uint64_t* keys, size_t n, const float* vals, const int* sizes, size_t vals_len);
 /* Entry fields of the given keys (host arrays): fea_cnt[n], size[n] (1 or dim+1), w[n*(dim+1)] =
  * {w0, V}, cg[n*(dim+2)] = {sqc_grad_0, z_0, sqc_grad_V}; rows are zero beyond the entry's size. */
 WH_API int wh_difacto_get_state(whDifacto* d, const uint64_t* keys, size_t n, uint32_t* fea_cnt, int* size,
@@ -398,6 +415,12 @@ WH_API int wh_difacto_get_state(whDifacto* d, const uint64_t* keys, size_t n, ui
 WH_API int wh_difacto_loss(whContext* ctx, const whLocalBlock* D, const float* model, size_t model_len,
                            const int* model_siz, size_t nkeys, int dim, float grad_clipping,
                            float grad_normalization, double* prog, float* grad);
+/* The same with conf.dropout (learn/difacto/loss.h:150-154): rand_values = the caller's next rand() values, one per
+ * float of model that belongs to an embedding (dim per key with model_siz = dim + 1), consumed in that order. */
+WH_API int wh_difacto_loss_dropout(whContext* ctx, const whLocalBlock* D, const float* model, size_t model_len,
+                                   const int* model_siz, size_t nkeys, int dim, float grad_clipping,
+                                   float grad_normalization, float dropout, const int* rand_values, size_t num_rand,
+                                   double* prog, float* grad);
 
 #ifdef __cplusplus
 }

@@ -144,8 +144,9 @@ class _DifactoMixin:
     def _dl(self):
         raise NotImplementedError
 
-    def difacto_loss(self, D, model, model_siz, dim, nt=2, clip=0.0, norm=0.0, want_grad=True):
-        """Loss(data, model, model_siz, conf); Evaluate; CalcGrad -> (prog[8], grad or None)."""
+    def difacto_loss(self, D, model, model_siz, dim, nt=2, clip=0.0, norm=0.0, want_grad=True, dropout=0.0):
+        """Loss(data, model, model_siz, conf); Evaluate; CalcGrad -> (prog[8], grad or None). dropout > 0 draws from
+        this process's glibc rand() (learn/difacto/loss.h:150-154): srand() first."""
         L, pre = self._dl()
         model = _f32(model)
         siz = np.ascontiguousarray(model_siz, np.int32)
@@ -154,19 +155,19 @@ class _DifactoMixin:
         getattr(L, pre + "difacto_loss")(
             C.c_size_t(D.rows), _p(D.offset), _p(D.index), _p(D.value), _p(D.label), _p(model),
             C.c_size_t(len(model)), _p(siz), C.c_size_t(len(siz)), C.c_int(dim), C.c_int(nt), C.c_float(clip),
-            C.c_float(0.0), C.c_float(norm), _p(prog), _p(grad))
+            C.c_float(dropout), C.c_float(norm), _p(prog), _p(grad))
         return prog, grad
 
     def difacto_create(self, l1=1.0, l2=0.0, eta=.01, beta=1.0, l1_shrk=True, dim=0, threshold=0, v_l2=0.0,
                        v_eta=None, v_beta=None, init_scale=.01, clip=0.0, norm=0.0, nt=2, max_key=NO_MAX_KEY,
-                       seed=0):
+                       seed=0, dropout=0.0):
         L, pre = self._dl()
         f = getattr(L, pre + "difacto_create")
         f.restype = C.c_void_p
         return C.c_void_p(f(C.c_float(l1), C.c_float(l2), C.c_float(eta), C.c_float(beta), C.c_int(l1_shrk),
                             C.c_int(dim), C.c_int(threshold), C.c_float(v_l2), C.c_int(v_eta is not None),
                             C.c_float(v_eta or 0), C.c_int(v_beta is not None), C.c_float(v_beta or 0),
-                            C.c_float(init_scale), C.c_float(0.0), C.c_float(clip), C.c_float(norm), C.c_int(nt),
+                            C.c_float(init_scale), C.c_float(dropout), C.c_float(clip), C.c_float(norm), C.c_int(nt),
                             C.c_uint64(max_key), C.c_uint(seed)))
 
     def difacto_minibatch(self, job, blk, train=True, data_pass=0):

@@ -32,12 +32,13 @@ float orc_logit_objv(const float*, const float*, size_t, int);
 /* learn/difacto/loss.h:24-41 (ctor), :185-253 (Data::Load), :53-94 (Evaluate), :102-158 (CalcGrad),
  * :256-264 (Data::Save). model = concatenation over keys of model_siz[k] floats, model_siz in
  * {0, 1, dim+1}. prog = {objv, auc, objv_w, copc, count, new_ex, new_w, new_V} (progress.h:28-36).
- * grad (same layout as model) may be NULL. dropout must be 0 here (it draws from rand()). */
+ * grad (same layout as model) may be NULL. dropout > 0 draws from this process's rand() (loss.h:150-154), one value per
+ * embedding-gradient float in key order: callers srand() first. */
 ORC_API void orc_difacto_loss(size_t rows, const size_t* offset, const uint32_t* index, const float* value,
                               const float* label, const float* model, size_t model_len, const int* model_siz,
                               size_t nkeys, int dim, int nt, float clip, float dropout, float norm, double* prog,
                               float* grad) {
-  (void)dropout; (void)model_len;
+  (void)model_len;
   /* w.Load(0, ...): :191-203 */
   int64_t* posw = (int64_t*)malloc((nkeys ? nkeys : 1) * sizeof(int64_t));
   float* w = (float*)calloc(nkeys ? nkeys : 1, sizeof(float));
@@ -143,6 +144,8 @@ ORC_API void orc_difacto_loss(size_t rows, const size_t* offset, const uint32_t*
           for (int d = 0; d < dim; ++d) yr[d] += value ? XV[i * dim + d] * vval[j] : XV[i * dim + d];
         }
       if (clip > 0) for (size_t i = 0; i < m * dim; ++i) V[i] = V[i] > clip ? clip : (V[i] < -clip ? -clip : V[i]); /* :145-148 */
+      if (dropout > 0) /* :150-154 */
+        for (size_t i = 0; i < m * dim; ++i) if ((float)rand() / RAND_MAX > 1 - dropout) V[i] = 0;
       if (norm) { /* :155,160-166 */
         float nm = 0;
         for (size_t i = 0; i < m * dim; ++i) nm += V[i] * V[i];

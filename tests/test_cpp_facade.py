@@ -174,8 +174,17 @@ def test_difacto_facade_equals_the_ctypes_path(tmp_path):
     r = subprocess.run([exe, fin, fout], capture_output=True, text=True)
     assert r.returncode == 0, r.stdout + r.stderr
     with open(fout, "rb") as f:
+        one_call = [get(f, t) for t in (np.uint32, np.int32, np.float32, np.float32)]
+        by_messages = [get(f, t) for t in (np.uint32, np.int32, np.float32, np.float32)]
+        progs_msg = get(f, np.float64).reshape(-1, 8)
         progs = get(f, np.float64).reshape(-1, 8)
         rows = get(f, np.uint8).tobytes().decode().splitlines()
+    # the worker driven through ps::KVWorker (count push with cmd, ZVPull with deps, difacto::Loss, ZVPush) leaves the
+    # same model as the one-call path, and sees the same objective / AUC / counts on the way
+    assert len(one_call[0]) > 1000 and (one_call[1] > 1).any()
+    for a, b in zip(one_call, by_messages):
+        assert np.array_equal(a, b)
+    assert np.array_equal(progs_msg[:, :6], progs[:, :6])
     ctx = capi.Context(0)
     d = capi.Difacto(ctx, l1=1.0, l2=0.0, eta=.01, beta=1.0, l1_shrk=True, dim=5, threshold=5, v_l2=0.0, init_scale=.01,
                      max_key=MAX_KEY, seed=7)

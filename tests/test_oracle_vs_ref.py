@@ -184,6 +184,40 @@ def test_difacto_loss(port, ref, with_value, dim):
         assert np.array_equal(ga, gb)
 
 
+def test_difacto_loss_dropout(port, ref):
+    """Gradient dropout draws from the process's glibc rand() (learn/difacto/loss.h:150-154): same seed, same drops."""
+    import ctypes
+    libc = ctypes.CDLL("libc.so.6")
+    rng = np.random.default_rng(10)
+    blk = random_block(rng, 700, 20, 2500, True, empty_rows=True)
+    D = ref.localize(blk, 2 ** 24)
+    model, siz = make_model(rng, len(D.uniq), 5)
+    for dropout, clip, norm in [(0.3, 0.0, 0.0), (0.6, 0.05, 1.0)]:
+        out = []
+        for o in (port, ref):
+            libc.srand(ctypes.c_uint(17))
+            out.append(o.difacto_loss(D, model, siz, 5, 2, clip, norm, dropout=dropout)[1])
+        assert np.array_equal(out[0], out[1])
+        assert 0.5 * dropout < float((out[0] == 0).mean()) * len(out[0]) / max(1, int((siz == 6).sum()) * 5) < 1.5 * dropout
+
+
+def test_difacto_full_job_dropout(port, ref):
+    rng = np.random.default_rng(11)
+    kw = dict(l1=0.3, l2=0.01, eta=0.05, beta=1.0, l1_shrk=True, dim=4, threshold=3, v_l2=1e-4, v_eta=0.02,
+              init_scale=0.01, max_key=2 ** 20, seed=321, dropout=0.25)
+    blks = [random_block(rng, 500, 12, 1500, with_value=(m % 2 == 1), empty_rows=False) for m in range(3)]
+    models = []
+    for o in (port, ref):
+        j = o.difacto_create(**kw)
+        for dp in range(2):
+            for blk in blks:
+                o.difacto_minibatch(j, blk, True, dp)
+        models.append(o.difacto_model(j, 4))
+        o.difacto_destroy(j)
+    for a, b in zip(models[0], models[1]):
+        assert np.array_equal(a, b)
+
+
 @pytest.mark.parametrize("dim,l1_shrk", [(0, True), (4, True), (4, False), (16, True)])
 def test_difacto_full_job(port, ref, dim, l1_shrk):
     """AsyncWorker::ProcessMinibatch + AsyncServer (count push on pass 0, ZVPull, ZVPush) vs the port."""

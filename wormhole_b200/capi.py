@@ -305,13 +305,20 @@ class _DifactoConfig(C.Structure):
                 ("seed", C.c_uint64)]
 
 
-def difacto_loss(ctx, D, model, model_siz, dim, clip=0.0, norm=0.0, want_grad=True):
-    """difacto::Loss(data, model, model_siz, conf); Evaluate; CalcGrad -> (prog[8], grad or None)."""
+def difacto_loss(ctx, D, model, model_siz, dim, clip=0.0, norm=0.0, want_grad=True, dropout=0.0, rand_values=None):
+    """difacto::Loss(data, model, model_siz, conf); Evaluate; CalcGrad -> (prog[8], grad or None). dropout > 0 takes the
+    caller's next glibc rand() values (one per embedding-gradient float)."""
     model = _f32(model)
     siz = np.ascontiguousarray(model_siz, np.int32)
     prog = np.zeros(8, np.float64)
     grad = np.zeros(len(model), np.float32) if want_grad else None
     lb = _localblock(D)
+    if dropout > 0:
+        rv = np.ascontiguousarray(rand_values if rand_values is not None else [], np.int32)
+        _check(lib().wh_difacto_loss_dropout(ctx.h, C.byref(lb), _ptr(model), C.c_size_t(len(model)), _ptr(siz), C.c_size_t(len(siz)),
+                                             C.c_int(dim), C.c_float(clip), C.c_float(norm), C.c_float(dropout), _ptr(rv),
+                                             C.c_size_t(len(rv)), _ptr(prog), _ptr(grad)))
+        return prog, grad
     _check(lib().wh_difacto_loss(ctx.h, C.byref(lb), _ptr(model), C.c_size_t(len(model)), _ptr(siz), C.c_size_t(len(siz)),
                                  C.c_int(dim), C.c_float(clip), C.c_float(norm), _ptr(prog), _ptr(grad)))
     return prog, grad
@@ -321,10 +328,11 @@ class Difacto:
     """AsyncServer + AsyncWorker of learn/difacto/async_sgd.h on one GPU."""
 
     def __init__(self, ctx, l1=1.0, l2=0.0, eta=.01, beta=1.0, l1_shrk=True, dim=0, threshold=0, v_l2=0.0, v_eta=None,
-                 v_beta=None, init_scale=.01, clip=0.0, norm=0.0, max_key=2 ** 24, key_begin=0, key_end=None, seed=0):
+                 v_beta=None, init_scale=.01, clip=0.0, norm=0.0, max_key=2 ** 24, key_begin=0, key_end=None, seed=0,
+                 dropout=0.0):
         self.ctx, self.dim = ctx, dim
         cfg = _DifactoConfig(l1, l2, eta, beta, int(l1_shrk), dim, threshold, v_l2, int(v_eta is not None), v_eta or 0.0,
-                             int(v_beta is not None), v_beta or 0.0, init_scale, clip, norm, 0.0, key_begin,
+                             int(v_beta is not None), v_beta or 0.0, init_scale, clip, norm, dropout, key_begin,
                              key_end if key_end is not None else max_key, max_key, seed)
         self.h = C.c_void_p()
         _check(lib().wh_difacto_create(ctx.h, C.byref(cfg), C.byref(self.h)))
@@ -332,6 +340,12 @@ class Difacto:
     def set_init_stream(self, rand_values):
         v = np.ascontiguousarray(rand_values, np.int32)
         _check(lib().wh_difacto_set_init_stream(self.h, _ptr(v), C.c_size_t(len(v))))
+
+    def set_dropout_stream(self, rand_values=None, shared_with_init=False):
+        """The worker's next rand() values for gradient dropout; shared_with_init: draw from the init stream instead
+        (worker and server in one process)."""
+        v = np.ascontiguousarray(rand_values if rand_values is not None else [], np.int32)
+        _check(lib().wh_difacto_set_dropout_stream(self.h, _ptr(v), C.c_size_t(len(v)), C.c_int(shared_with_init)))
 
     def process_minibatch(self, blk, train=True, data_pass=0, mem=WH_HOST):
         prog = np.zeros(8, np.float64)

@@ -86,12 +86,24 @@ dfc_trans_kernel(size_t rows, const size_t* __restrict__ offset, const uint32_t*
   }
 }
 
-// G[u,:] = (-xxp[u] * V[u,:]) + sum (learn/difacto/loss.h:126-131,142), then clip (:145-148).
+// Gradient dropout (learn/difacto/loss.h:150-154): `if ((T)rand() / RAND_MAX > 1 - V.dropout) g = 0` for every float of
+// V.weight in order -- V.weight holds the keys that came with an embedding, ascending, dim floats each. The rand()
+// values are the caller's (wh_difacto_set_dropout_stream): float number pos[u] * dim + d of this minibatch takes value
+// number *cursor + pos[u] * dim + d of the stream, pos[u] = the key's rank among the keys with an embedding.
+struct DfcDropout {
+  float dropout = 0.f;
+  const int* stream = nullptr; size_t len = 0;
+  long long* cursor = nullptr;       // device: values consumed so far
+  unsigned* pos = nullptr;           // device scratch, U entries
+  unsigned* total = nullptr;         // device: keys with an embedding in this minibatch
+};
+
+// G[u,:] = (-xxp[u] * V[u,:]) + sum (learn/difacto/loss.h:126-131,142), then clip (:145-148), then dropout (:150-154).
 // Also the sum of squares for the optional normalisation (:160-166), in fp64 per block.
 __global__ void __launch_bounds__(256)
 dfc_gv_finish_kernel(size_t U, int dim, const unsigned char* __restrict__ has, const float* __restrict__ V,
                      long long* accG, long long* accX, const FixedScale* __restrict__ fsG,
-                     const FixedScale* __restrict__ fsX, float clip, float* __restrict__ G, double* sumsq) {
+                     const FixedScale* __restrict__ fsX, float clip, DfcDropout drop, float* __restrict__ G, double* sumsq) {
   const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   double sq = 0;
   if (t < U * dim) {
@@ -104,6 +116,10 @@ dfc_gv_finish_kernel(size_t U, int dim, const unsigned char* __restrict__ has, c
       const float z = V[t] * -xxp;
       g = z * 1.0f + (float)((double)ag * fsG->inv);
       if (clip > 0.f) g = g > clip ? clip : (g < -clip ? -clip : g);
+      if (drop.stream) {
+        const unsigned long long o = (unsigned long long)*drop.cursor + (unsigned long long)drop.pos[u] * dim + (t - u * dim);
+        if ((float)drop.stream[o % drop.len] / (float)2147483647 > 1 - drop.dropout) g = 0.f;
+      }
       sq = (double)(g * g);
     }
     G[t] = g;
@@ -129,6 +145,10 @@ __global__ void dfc_normalize_kernel(size_t n, float* G, const double* sumsq) {
   if (i < n) G[i] = G[i] / r;
 }
 
+struct HasVal { const unsigned char* has; __device__ unsigned operator()(size_t i) const { return has[i] ? 1u : 0u; } };
+struct RankOut { unsigned* pos; __device__ void operator()(size_t i, unsigned, unsigned prefix) const { pos[i] = prefix; } };
+__global__ void dfc_advance_kernel(long long* cursor, const unsigned* total, int dim) { *cursor += (long long)*total * dim; }
+
 // Scratch of one DiFacto evaluation (all device pointers; sized by the caller).
 struct DfcWork {
   float *py, *dual, *XV, *xxvv, *gw, *G;
@@ -142,7 +162,8 @@ struct DfcWork {
 int difacto_loss_launch(whContext* ctx, whContext* auc_ctx, cudaEvent_t ev_fork, cudaEvent_t ev_auc, size_t rows,
                         size_t nnz, const size_t* offset, const uint32_t* index, const float* value,
                         const float* label, size_t U, int dim, const float* w, const unsigned char* has,
-                        const float* V, bool any_v, float clip, float norm, bool train, const DfcWork& k) {
+                        const float* V, bool any_v, float clip, float norm, bool train, const DfcWork& k,
+                        const DfcDropout* drop = nullptr) {
   cudaStream_t st = ctx->stream;
   WH_CUDA(cudaMemsetAsync(k.py, 0, rows * 4, st));
   WH_TRY(spmv_times_launch(ctx, rows, offset, index, value, w, k.py));                       // py = X w
@@ -168,8 +189,15 @@ int difacto_loss_launch(whContext* ctx, whContext* auc_ctx, cudaEvent_t ev_fork,
       WH_TRY(fixed_prepare(ctx, k.fsG, k.XV, rows * dim, value, nnz, 1));
       WH_TRY(fixed_prepare(ctx, k.fsX, k.dual, rows, value, nnz, 2));
       WH_LAUNCH(dfc_trans_kernel, grd, 256, 0, st, rows, offset, index, value, has, dim, k.XV, k.dual, k.accG, k.accX, k.fsG, k.fsX);
+      DfcDropout dr;
+      if (drop && drop->stream && drop->dropout > 0.f && U) {
+        dr = *drop;
+        WH_TRY(ctx->scan_tmp.reserve(div_up(U, kScanTile) * sizeof(unsigned) + 256));
+        WH_TRY(scan_and_apply<unsigned>(ctx, HasVal{has}, RankOut{dr.pos}, U, ctx->scan_tmp.as<unsigned>(), dr.total));
+      }
       WH_LAUNCH(dfc_gv_finish_kernel, (unsigned)div_up(U * dim, 256), 256, 0, st, U, dim, has, V, k.accG, k.accX, k.fsG,
-                k.fsX, clip, k.G, k.sumsq);
+                k.fsX, clip, dr, k.G, k.sumsq);
+      if (dr.stream) WH_LAUNCH(dfc_advance_kernel, 1, 1, 0, st, dr.cursor, dr.total, dim);
       if (norm != 0.f) WH_LAUNCH(dfc_normalize_kernel, (unsigned)div_up(U * dim, 256), 256, 0, st, U * dim, k.G, k.sumsq);
       WH_LAUNCH(dfc_clear_kernel, (unsigned)div_up(U, 256), 256, 0, st, k.accX, U, k.sumsq);
     }
@@ -187,8 +215,10 @@ struct whDifacto {
   whContext* ctx = nullptr;
   whDifactoConfig c;
   float v_alpha = .01f, v_beta = 1.f;
-  wh::DevBuf base, hasv, V, cgV, counters, init_stream;
+  wh::DevBuf base, hasv, V, cgV, counters, init_stream, drop_stream, drop_pos;
   size_t init_len = 0;
+  size_t drop_len = 0;               // the worker's rand() values for gradient dropout (0: none given)
+  bool drop_shared = false;          // ... or: dropout draws from the init stream (worker and server in one process)
   // worker side (one minibatch at a time)
   whContext ax;                      // AUC side stream
   cudaEvent_t ev_fork = nullptr, ev_auc = nullptr;
@@ -437,8 +467,7 @@ extern "C" {
 int wh_difacto_create(whContext* ctx, const whDifactoConfig* c, whDifacto** out) {
   WH_REQUIRE(ctx && c && out, "wh_difacto_create: NULL argument");
   WH_REQUIRE(c->dim >= 0 && c->dim <= 256, "wh_difacto_create: dim %d outside [0, 256]", c->dim);
-  WH_REQUIRE(c->dropout == 0.f, "wh_difacto_create: gradient dropout draws from the worker's rand() in the reference "
-                                "(learn/difacto/loss.h:150-154) and is not offered here; set dropout = 0");
+  WH_REQUIRE(c->dropout >= 0.f && c->dropout <= 1.f, "wh_difacto_create: dropout %g outside [0, 1]", (double)c->dropout);
   WH_REQUIRE(c->key_end > c->key_begin && c->key_end - c->key_begin <= (1ull << 30), "wh_difacto_create: bad key range");
   WH_REQUIRE(c->max_key != 0 && c->lr_eta > 0, "wh_difacto_create: max_key and lr_eta must be positive");
   DeviceGuard g(ctx->device);
@@ -473,7 +502,7 @@ int wh_difacto_destroy(whDifacto* d) {
   DeviceGuard g(d->ctx->device);
   cudaStreamSynchronize(d->ctx->stream);
   cudaStreamSynchronize(d->ax.stream);
-  for (wh::DevBuf* b : {&d->base, &d->hasv, &d->V, &d->cgV, &d->counters, &d->init_stream, &d->in_index, &d->in_offset,
+  for (wh::DevBuf* b : {&d->base, &d->hasv, &d->V, &d->cgV, &d->counters, &d->init_stream, &d->drop_stream, &d->drop_pos, &d->in_index, &d->in_offset,
                         &d->in_value, &d->in_label, &d->uniq, &d->cnt, &d->index, &d->w, &d->has, &d->Vs, &d->XV,
                         &d->xxvv, &d->py, &d->dual, &d->gw, &d->G, &d->accG, &d->accX, &d->flags, &d->scal,
                         &d->ax.small, &d->ax.scan_tmp})
@@ -498,6 +527,38 @@ int wh_difacto_set_init_stream(whDifacto* d, const int* v, size_t n) {
   }
   WH_CUDA(cudaMemsetAsync(d->counters.as<long long>() + 3, 0, 8, d->ctx->stream));
   WH_CUDA(cudaStreamSynchronize(d->ctx->stream));
+  return WH_OK;
+}
+
+int wh_difacto_set_dropout_stream(whDifacto* d, const int* v, size_t n, int shared_with_init) {
+  WH_REQUIRE(d && (shared_with_init || n == 0 || v), "wh_difacto_set_dropout_stream: NULL argument");
+  DeviceGuard g(d->ctx->device);
+  WH_CUDA(cudaStreamSynchronize(d->ctx->stream));
+  d->drop_shared = shared_with_init != 0;
+  d->drop_len = d->drop_shared ? 0 : n;
+  if (d->drop_len) {
+    WH_TRY(d->drop_stream.reserve(n * 4));
+    WH_CUDA(cudaMemcpyAsync(d->drop_stream.p, v, n * 4, cudaMemcpyHostToDevice, d->ctx->stream));
+  }
+  WH_CUDA(cudaMemsetAsync(d->counters.as<long long>() + 4, 0, 8, d->ctx->stream));
+  WH_CUDA(cudaStreamSynchronize(d->ctx->stream));
+  return WH_OK;
+}
+
+// the dropout arguments of one training minibatch with U keys (none: conf.dropout == 0 or no embeddings)
+static int dfc_dropout(whDifacto* d, size_t U, bool train, DfcDropout* out) {
+  *out = DfcDropout();
+  if (!train || d->c.dropout <= 0.f || d->c.dim == 0) return WH_OK;
+  const bool shared = d->drop_shared && d->init_len;
+  WH_REQUIRE(shared || d->drop_len, "wh_difacto: embedding dropout = %g draws from the worker's rand() (learn/difacto/loss.h:"
+             "150-154): hand over that sequence with wh_difacto_set_dropout_stream before training", (double)d->c.dropout);
+  WH_TRY(d->drop_pos.reserve((U ? U : 1) * 4));
+  out->dropout = d->c.dropout;
+  out->stream = shared ? d->init_stream.as<int>() : d->drop_stream.as<int>();
+  out->len = shared ? d->init_len : d->drop_len;
+  out->cursor = d->counters.as<long long>() + (shared ? 3 : 4);
+  out->pos = d->drop_pos.as<unsigned>();
+  out->total = d->scal.as<unsigned>() + 10;
   return WH_OK;
 }
 
@@ -554,9 +615,11 @@ int wh_difacto_process_minibatch(whDifacto* d, const whRowBlock* blk, int mem, i
             d->hasv.as<unsigned char>(), d->V.as<float>(), d->w.as<float>(), d->has.as<unsigned char>(), d->Vs.as<float>(), counters);
   // Loss::Evaluate / CalcGrad. U is only known on the device: the per-key kernels run over ucap entries; the
   // tail beyond U is never referenced by the CSR, but must read as "no embedding, zero accumulators".
+  DfcDropout drop;
+  WH_TRY(dfc_dropout(d, ucap, train != 0, &drop));
   WH_TRY(difacto_loss_launch(ctx, &d->ax, d->ev_fork, d->ev_auc, rows, n, d_offset, d->index.as<uint32_t>(), d_value, d_label,
                              ucap, sd, d->w.as<float>(), d->has.as<unsigned char>(), d->Vs.as<float>(), dim > 0,
-                             d->c.grad_clipping, d->c.grad_normalization, train != 0, k));
+                             d->c.grad_clipping, d->c.grad_normalization, train != 0, k, &drop));
   if (train) {
     // ZVPush
     WH_LAUNCH(dfc_grad_push_kernel, ugrid, 256, 0, ctx->stream, p, d->uniq.as<uint64_t>(), d_nuniq, k.gw, k.G,
@@ -641,8 +704,11 @@ int wh_difacto_finish(whDifacto* d, const float* d_w, const unsigned char* d_has
   const size_t rows = d->b_rows, U = d->b_U;
   DfcWork k;
   WH_TRY(dfc_work(d, rows, U, &k));
+  DfcDropout drop;
+  WH_TRY(dfc_dropout(d, U, train != 0, &drop));
   WH_TRY(difacto_loss_launch(ctx, &d->ax, d->ev_fork, d->ev_auc, rows, d->b_nnz, d->b_offset, d->index.as<uint32_t>(), d->b_value,
-                             d->b_label, U, sd, d_w, d_has, d_V, dim > 0, d->c.grad_clipping, d->c.grad_normalization, train != 0, k));
+                             d->b_label, U, sd, d_w, d_has, d_V, dim > 0, d->c.grad_clipping, d->c.grad_normalization, train != 0, k,
+                             &drop));
   if (train && U) {
     WH_CUDA(cudaMemcpyAsync(d_gw, k.gw, U * 4, cudaMemcpyDeviceToDevice, ctx->stream));
     if (dim > 0) WH_CUDA(cudaMemcpyAsync(d_G, k.G, U * (size_t)dim * 4, cudaMemcpyDeviceToDevice, ctx->stream));
@@ -713,6 +779,101 @@ int wh_difacto_shard_progress(whDifacto* d, double* new_w, double* new_V) {
   return WH_OK;
 }
 
+// ---- ps::KVWorker<float>::ZPush(cmd = kPushFeaCnt) / ZVPull / ZVPush on HOST arrays (the C++ facade, host/ps.h) ----
+// One message each against this shard: keys ascending, payloads concatenated with a length per key, as ps-lite moves
+// them (call sites learn/difacto/async_sgd.h:374-381,408-411,424). Synchronous.
+
+// keys outside the shard's range seen by the kernels so far (stream already synchronised)
+static int dfc_bad_keys(whDifacto* d) {
+  long long bad = 0;
+  WH_CUDA(cudaMemcpy(&bad, d->counters.as<long long>() + 2, 8, cudaMemcpyDeviceToHost));
+  if (bad) {
+    WH_CUDA(cudaMemset(d->counters.as<long long>() + 2, 0, 8));
+    set_error("wh_difacto: %lld keys outside the shard's range", bad);
+    return WH_ERR_INVALID;
+  }
+  return WH_OK;
+}
+
+static int dfc_host_keys(whDifacto* d, const uint64_t* keys, size_t n, const uint64_t** dk) {
+  for (size_t i = 1; i < n; ++i)
+    if (keys[i] <= keys[i - 1]) { set_error("wh_difacto: the keys of a message must ascend (position %zu)", i); return WH_ERR_INVALID; }
+  return to_device(d->ctx, d->ctx->stage[0], keys, n, WH_HOST, dk);
+}
+
+int wh_difacto_zpush_count(whDifacto* d, const uint64_t* keys, const float* counts, size_t n) {
+  WH_REQUIRE(d && (n == 0 || (keys && counts)), "wh_difacto_zpush_count: NULL argument");
+  if (n == 0) return WH_OK;
+  whContext* ctx = d->ctx;
+  DeviceGuard g(ctx->device);
+  const uint64_t* dk;
+  WH_TRY(dfc_host_keys(d, keys, n, &dk));
+  std::vector<uint32_t> c(n);
+  for (size_t i = 0; i < n; ++i) c[i] = (unsigned)counts[i];      // val.fea_cnt += (unsigned) recv[0], async_sgd.h:218
+  const uint32_t* dc;
+  WH_TRY(to_device(ctx, ctx->stage[1], c.data(), n, WH_HOST, &dc));
+  WH_TRY(wh_difacto_shard_count_push(d, dk, dc, n));
+  WH_CUDA(cudaStreamSynchronize(ctx->stream));
+  return dfc_bad_keys(d);
+}
+
+int wh_difacto_zvpull(whDifacto* d, const uint64_t* keys, size_t n, float* vals, int* sizes, size_t* vals_len) {
+  WH_REQUIRE(d && vals_len && (n == 0 || (keys && vals && sizes)), "wh_difacto_zvpull: NULL argument");
+  *vals_len = 0;
+  if (n == 0) return WH_OK;
+  whContext* ctx = d->ctx;
+  DeviceGuard g(ctx->device);
+  const int dim = d->c.dim, sd = dim > 0 ? dim : 1;
+  const uint64_t* dk;
+  WH_TRY(dfc_host_keys(d, keys, n, &dk));
+  WH_TRY(ctx->stage[1].reserve(n * 4)); WH_TRY(ctx->stage[2].reserve(n)); WH_TRY(ctx->stage[3].reserve(n * sd * 4));
+  WH_TRY(wh_difacto_shard_pull(d, dk, n, ctx->stage[1].as<float>(), ctx->stage[2].as<unsigned char>(), ctx->stage[3].as<float>()));
+  std::vector<float> w(n), V(dim > 0 ? n * (size_t)dim : 0);
+  std::vector<unsigned char> has(n);
+  WH_CUDA(cudaMemcpyAsync(w.data(), ctx->stage[1].p, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  WH_CUDA(cudaMemcpyAsync(has.data(), ctx->stage[2].p, n, cudaMemcpyDeviceToHost, ctx->stream));
+  if (dim > 0) WH_CUDA(cudaMemcpyAsync(V.data(), ctx->stage[3].p, n * (size_t)dim * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  WH_CUDA(cudaStreamSynchronize(ctx->stream));
+  WH_TRY(dfc_bad_keys(d));
+  size_t o = 0;
+  for (size_t i = 0; i < n; ++i) {       // AdaGradHandle::Pull, async_sgd.h:234-244: {w0} or {w0, V[dim]}
+    vals[o++] = w[i];
+    if (has[i]) { memcpy(vals + o, V.data() + i * (size_t)dim, (size_t)dim * 4); o += (size_t)dim; }
+    sizes[i] = has[i] ? dim + 1 : 1;
+  }
+  *vals_len = o;
+  return WH_OK;
+}
+
+int wh_difacto_zvpush(whDifacto* d, const uint64_t* keys, size_t n, const float* vals, const int* sizes, size_t vals_len) {
+  WH_REQUIRE(d && (n == 0 || (keys && vals && sizes)), "wh_difacto_zvpush: NULL argument");
+  if (n == 0) return WH_OK;
+  whContext* ctx = d->ctx;
+  DeviceGuard g(ctx->device);
+  const int dim = d->c.dim;
+  std::vector<float> gw(n), G(dim > 0 ? n * (size_t)dim : 0, 0.f);
+  std::vector<unsigned char> has(n);
+  size_t o = 0;
+  for (size_t i = 0; i < n; ++i) {
+    const int s = sizes[i];
+    WH_REQUIRE(s == 1 || (dim > 0 && s == dim + 1), "wh_difacto_zvpush: key %zu carries %d floats (1 or dim + 1 = %d)", i, s, dim + 1);
+    WH_REQUIRE(o + (size_t)s <= vals_len, "wh_difacto_zvpush: the lengths add up to more than the %zu values given", vals_len);
+    gw[i] = vals[o];
+    has[i] = s > 1;
+    if (s > 1) memcpy(G.data() + i * (size_t)dim, vals + o + 1, (size_t)dim * 4);
+    o += (size_t)s;
+  }
+  WH_REQUIRE(o == vals_len, "wh_difacto_zvpush: the lengths add up to %zu, %zu values given", o, vals_len);
+  const uint64_t* dk; const float* dgw; const float* dG = nullptr; const unsigned char* dhas;
+  WH_TRY(dfc_host_keys(d, keys, n, &dk));
+  WH_TRY(to_device(ctx, ctx->stage[1], gw.data(), n, WH_HOST, &dgw));
+  WH_TRY(to_device(ctx, ctx->stage[2], has.data(), n, WH_HOST, &dhas));
+  if (dim > 0) WH_TRY(to_device(ctx, ctx->stage[3], G.data(), n * (size_t)dim, WH_HOST, &dG));
+  WH_TRY(wh_difacto_shard_push(d, dk, n, dgw, dG, dhas));
+  WH_CUDA(cudaStreamSynchronize(ctx->stream));
+  return dfc_bad_keys(d);
+}
+
 int wh_difacto_get_state(whDifacto* d, const uint64_t* keys, size_t n, uint32_t* fea_cnt, int* size, float* w, float* cg) {
   WH_REQUIRE(d && (n == 0 || (keys && fea_cnt && size && w && cg)), "wh_difacto_get_state: NULL argument");
   whContext* ctx = d->ctx;
@@ -736,7 +897,21 @@ int wh_difacto_get_state(whDifacto* d, const uint64_t* keys, size_t n, uint32_t*
 
 int wh_difacto_loss(whContext* ctx, const whLocalBlock* D, const float* model, size_t model_len, const int* model_siz,
                     size_t nkeys, int dim, float clip, float norm, double* prog, float* grad) {
+  return wh_difacto_loss_dropout(ctx, D, model, model_len, model_siz, nkeys, dim, clip, norm, 0.f, nullptr, 0, prog, grad);
+}
+
+int wh_difacto_loss_dropout(whContext* ctx, const whLocalBlock* D, const float* model, size_t model_len, const int* model_siz,
+                            size_t nkeys, int dim, float clip, float norm, float dropout, const int* rand_values,
+                            size_t num_rand, double* prog, float* grad) {
   WH_REQUIRE(ctx && D && prog && (nkeys == 0 || (model_siz && (model || model_len == 0))), "wh_difacto_loss: NULL argument");
+  WH_REQUIRE(dropout >= 0.f && dropout <= 1.f, "wh_difacto_loss: dropout %g outside [0, 1]", (double)dropout);
+  if (dropout > 0.f && grad && dim > 0) {
+    size_t need = 0;
+    for (size_t i = 0; i < nkeys; ++i) if (model_siz[i] == dim + 1) need += (size_t)dim;
+    WH_REQUIRE(need == 0 || (rand_values && num_rand >= need),
+               "wh_difacto_loss: dropout needs the caller's next %zu rand() values (one per embedding-gradient float), %zu given", need, num_rand);
+    if (need == 0) dropout = 0.f;
+  }
   WH_REQUIRE(dim >= 0 && dim <= 256, "wh_difacto_loss: dim %d outside [0, 256]", dim);
   DeviceGuard g(ctx->device);
   // a throw-away DiFacto object supplies the scratch (no shard tables: dim-sized buffers only)
@@ -770,9 +945,17 @@ int wh_difacto_loss(whContext* ctx, const whLocalBlock* D, const float* model, s
               tmp.w.as<float>(), tmp.has.as<unsigned char>(), tmp.Vs.as<float>());
     DfcWork k;
     WH_TRY(dfc_work(&tmp, dl.rows, U, &k));
+    DfcDropout drop;
+    if (dropout > 0.f && grad && dim > 0 && U) {
+      WH_TRY(tmp.drop_stream.reserve(num_rand * 4)); WH_TRY(tmp.drop_pos.reserve(U * 4)); WH_TRY(tmp.counters.reserve(64));
+      WH_CUDA(cudaMemcpyAsync(tmp.drop_stream.p, rand_values, num_rand * 4, cudaMemcpyHostToDevice, ctx->stream));
+      WH_CUDA(cudaMemsetAsync(tmp.counters.p, 0, 64, ctx->stream));
+      drop.dropout = dropout; drop.stream = tmp.drop_stream.as<int>(); drop.len = num_rand;
+      drop.cursor = tmp.counters.as<long long>() + 4; drop.pos = tmp.drop_pos.as<unsigned>(); drop.total = tmp.scal.as<unsigned>() + 10;
+    }
     WH_TRY(difacto_loss_launch(ctx, &tmp.ax, tmp.ev_fork, tmp.ev_auc, dl.rows, dl.nnz, dl.offset, dl.index, dl.value, dl.label,
                                U, (int)sd, tmp.w.as<float>(), tmp.has.as<unsigned char>(), tmp.Vs.as<float>(), dim > 0, clip,
-                               norm, grad != nullptr, k));
+                               norm, grad != nullptr, k, &drop));
     if (grad && model_len) {
       WH_TRY(ctx->stage[7].reserve(model_len * 4));
       WH_CUDA(cudaMemsetAsync(ctx->stage[7].p, 0, model_len * 4, ctx->stream));
@@ -793,7 +976,7 @@ int wh_difacto_loss(whContext* ctx, const whLocalBlock* D, const float* model, s
   if (tmp.ev_fork) cudaEventDestroy(tmp.ev_fork);
   if (tmp.ev_auc) cudaEventDestroy(tmp.ev_auc);
   for (wh::DevBuf* b : {&tmp.w, &tmp.has, &tmp.Vs, &tmp.XV, &tmp.xxvv, &tmp.py, &tmp.dual, &tmp.gw, &tmp.G, &tmp.accG,
-                        &tmp.accX, &tmp.scal, &tmp.ax.small, &tmp.ax.scan_tmp})
+                        &tmp.accX, &tmp.scal, &tmp.ax.small, &tmp.ax.scan_tmp, &tmp.drop_stream, &tmp.drop_pos, &tmp.counters})
     b->release();
   for (auto& b : tmp.ax.sort_tmp) b.release();
   tmp.pinned.release();

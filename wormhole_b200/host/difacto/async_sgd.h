@@ -51,6 +51,11 @@ class AsyncSGD {
   void SetInitStream(const std::vector<int>& rand_values) {
     WH_CHECK(wh_difacto_set_init_stream(d_, rand_values.data(), rand_values.size()));
   }
+  /// embedding.dropout > 0: the worker's next rand() values (learn/difacto/loss.h:150-154), or shared = true to draw from
+  /// the init stream (worker and server in one process)
+  void SetDropoutStream(const std::vector<int>& rand_values, bool shared_with_init = false) {
+    WH_CHECK(wh_difacto_set_dropout_stream(d_, rand_values.data(), rand_values.size(), shared_with_init ? 1 : 0));
+  }
   /// AsyncWorker::ProcessMinibatch (:363-425)
   void ProcessMinibatch(const RowBlock<ps::Key>& mb, bool train, int data_pass) {
     whRowBlock rb;
