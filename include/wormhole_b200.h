@@ -276,6 +276,15 @@ WH_API int wh_worker_wait(whWorker* w, uint64_t ticket, double* prog);
  * owns into the requesters' inboxes; once every rank has posted its gradients, each owner applies, per source rank in
  * ascending order, the slice of that rank's outbox that falls into its key range as one push message. Every rank must
  * submit the same sequence of minibatches (train / evaluate alike): the barriers in between are collective. */
+/* Ragged streams: the ranks of a sharded job read different file parts and run out of minibatches at different steps,
+ * while the barriers between the GPUs are collective. A rank WITHOUT a minibatch in a step calls submit_idle instead of
+ * submit (same train flag as the others): it posts an empty key list, serves the others' pulls and applies their pushes;
+ * its ticket's progress is all zero. Before each step every rank tells its server which ranks do send a push message
+ * (bit r = rank r has a minibatch), so that SGD's per-message step count t advances for those only
+ * (learn/linear/async_sgd.h:85-90). The host agrees on the mask by its own means (tools/linear_b200.cc: one pipe
+ * round-trip per step). Default: all ranks. */
+WH_API int wh_worker_submit_idle(whWorker* w, int train, uint64_t* ticket);
+WH_API int wh_server_set_active_sources(whServer* s, uint64_t mask);
 WH_API int wh_worker_ipc_export(whWorker* w, size_t max_uniq, void* handles);
 WH_API int wh_worker_ipc_attach(whWorker* w, const void* handles);
 /* The PRED workload (learn/linear/async_sgd.h:263-265 -> ScalarLoss::Predict, learn/linear/loss.h:55-63): Localize,

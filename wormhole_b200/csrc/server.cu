@@ -315,7 +315,8 @@ int server_apply_all_launch(whServer* s, cudaStream_t stream, unsigned char* con
   HandleParams h = make_params(s, false);
   for (int src = 0; src < a.world; ++src) {
     a.outbox[src] = outboxes[src];
-    a.eta_sgd[src] = make_params(s, true).eta_sgd;   // one push message per source: SGDHandle::Start each
+    // one push message per source that has a minibatch in this step: SGDHandle::Start each
+    a.eta_sgd[src] = ((s->active_sources >> src) & 1) ? make_params(s, true).eta_sgd : 0.f;
   }
   int me = s->map.rank;
   ShardView table = s->view();

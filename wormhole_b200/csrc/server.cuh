@@ -48,6 +48,7 @@ struct whServer {
   unsigned long long epoch[wh::kBarrierClasses] = {0, 0, 0, 0};   // barriers issued so far, per class (all ranks in lock step)
   cudaEvent_t barrier_ev[wh::kBarrierClasses] = {nullptr, nullptr, nullptr, nullptr};   // keeps a class's barriers in issue order across streams
   unsigned long long steps = 0;     // training minibatches pushed so far (SGD: t of every shard follows from it)
+  unsigned long long active_sources = ~0ull;   // bit r: rank r sends a push message in the next step (wh_server_set_active_sources)
   void* peer_base[3 * wh::kMaxShards] = {nullptr};   // pointers opened with cudaIpcOpenMemHandle
   int algo = WH_ALGO_FTRL;
   float l1 = 1.f, l2 = 0.f;

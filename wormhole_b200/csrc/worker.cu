@@ -533,6 +533,66 @@ int wh_worker_submit(whWorker* w, const whRowBlock* blk, int mem, size_t nnz, in
   return WH_OK;
 }
 
+// A step of a sharded job in which THIS rank has no minibatch while others still do (the ranks' file parts hold
+// different numbers of minibatches, the barriers between the GPUs are collective): post an empty key list, serve the
+// others' pulls, apply their pushes. No push message of this rank reaches any shard.
+int wh_worker_submit_idle(whWorker* w, int train, uint64_t* ticket) {
+  WH_REQUIRE(w && ticket && w->server, "wh_worker_submit_idle: NULL argument");
+  whContext* ctx = w->ctx;
+  whServer* s = w->server;
+  WH_REQUIRE(s->map.world > 1 && w->outbox_cap != 0, "wh_worker_submit_idle: only for sharded jobs with outboxes (wh_worker_ipc_attach)");
+  DeviceGuard g(ctx->device);
+  Lane& l = w->lane[w->next_ticket % w->depth];
+  if (l.busy) {
+    set_error("wh_worker_submit_idle: %d minibatches already in flight; wh_worker_wait the oldest first", w->depth);
+    return WH_ERR_INVALID;
+  }
+  whContext* cx = &l.cx;
+  if (!l.cx.own_stream) l.cx.stream = w->ctx->stream;
+  const unsigned long long tk = w->next_ticket;
+  const int ring = kMaxDepth + 1;
+  const char* e = getenv("WH_SERVE");
+  const bool served = !e || atoi(e) != 0;
+  const int lane_idx = (int)(&l - w->lane);
+  EvalOut* d_eval = reinterpret_cast<EvalOut*>(l.scal.as<char>() + 512);
+  unsigned char* boxes[kMaxShards];
+  for (int src = 0; src < s->map.world; ++src) boxes[src] = w->peer_outbox[src][lane_idx];
+  if (served && w->depth > 1 && tk > (unsigned long long)w->depth)
+    WH_CUDA(cudaStreamWaitEvent(cx->stream, w->ev_served[(tk - w->depth + 1) % ring], 0));
+  WH_CUDA(cudaMemsetAsync(l.outbox.p, 0, 256, cx->stream));      // U = 0, every cut = 0
+  WH_CUDA(cudaMemsetAsync(d_eval, 0, sizeof(EvalOut), cx->stream));
+  if (served) WH_TRY(server_barrier_launch(s, cx->stream, 1));
+  if (tk > 1ull + (unsigned)w->max_delay) WH_CUDA(cudaStreamWaitEvent(cx->stream, w->ev_pushed[(tk - 1 - w->max_delay) % ring], 0));
+  if (served) {
+    WH_TRY(server_serve_all_launch(s, cx->stream, boxes, w->outbox_cap));
+    WH_TRY(server_barrier_launch(s, cx->stream, 2));
+    WH_CUDA(cudaEventRecord(w->ev_served[tk % ring], cx->stream));
+  } else if (!train) {
+    WH_TRY(server_barrier_launch(s, cx->stream));
+  }
+  if (train) {
+    if (w->max_delay > 0 && tk > 1) WH_CUDA(cudaStreamWaitEvent(cx->stream, w->ev_pushed[(tk - 1) % ring], 0));
+    WH_TRY(server_barrier_launch(s, cx->stream, served ? 3 : 0));
+    WH_TRY(server_apply_all_launch(s, cx->stream, boxes, w->outbox_cap));
+    if (!served || w->depth == 1) WH_TRY(server_barrier_launch(s, cx->stream));
+    s->steps++;
+  }
+  WH_CUDA(cudaMemcpyAsync(l.pinned + 256, s->counters.p, 24, cudaMemcpyDeviceToHost, cx->stream));
+  WH_CUDA(cudaEventRecord(w->ev_pushed[tk % ring], cx->stream));
+  WH_CUDA(cudaMemcpyAsync(l.pinned, d_eval, sizeof(EvalOut), cudaMemcpyDeviceToHost, cx->stream));
+  WH_CUDA(cudaEventRecord(l.ev_done, cx->stream));
+  l.busy = true; l.train = train != 0; l.rows = 0;
+  l.ticket = w->next_ticket++;
+  *ticket = l.ticket;
+  return WH_OK;
+}
+
+int wh_server_set_active_sources(whServer* s, uint64_t mask) {
+  WH_REQUIRE(s, "wh_server_set_active_sources: NULL argument");
+  s->active_sources = mask;
+  return WH_OK;
+}
+
 int wh_worker_wait(whWorker* w, uint64_t ticket, double* prog) {
   WH_REQUIRE(w && prog, "wh_worker_wait: NULL argument");
   WH_REQUIRE(ticket == w->next_wait, "wh_worker_wait: tickets are collected in submission order (expected %llu, got %llu)",
@@ -574,6 +634,7 @@ int wh_worker_wait(whWorker* w, uint64_t ticket, double* prog) {
   }
   EvalHost h = eval_finish(*reinterpret_cast<const EvalOut*>(l.pinned), l.rows);
   prog[0] = h.objv; prog[1] = h.acc; prog[2] = h.auc; prog[3] = 1; prog[4] = (double)l.rows;
+  if (l.rows == 0) prog[0] = prog[1] = prog[2] = prog[3] = 0;   // an idle step (wh_worker_submit_idle): nothing was evaluated
   prog[5] = (double)(cnt[0] - w->seen_new_w);
   w->seen_new_w = cnt[0];
   return WH_OK;

@@ -96,6 +96,13 @@ class AsgdWorker {
     WH_CHECK(wh_worker_submit(worker_, &mb.blk, WH_DEVICE, mb.nnz, train ? 1 : 0, &ticket));
     return ticket;
   }
+  /// a step of a sharded job in which this rank has no minibatch (wh_worker_submit_idle)
+  uint64_t SubmitIdle(bool train = true) {
+    uint64_t ticket = 0;
+    WH_CHECK(wh_worker_submit_idle(worker_, train ? 1 : 0, &ticket));
+    return ticket;
+  }
+  whWorker* handle() const { return worker_; }
   void Wait(uint64_t ticket) {
     Progress prog;
     WH_CHECK(wh_worker_wait(worker_, ticket, prog.data.data()));
