@@ -479,12 +479,13 @@ def parity_leg(ctx, rank, world, local, args, max_key, rows, shape, algo, loss, 
             "nnz_w": [int(nnz_dev), nnz_ref], "checker": kind, "ok": bool(ok)}
 
 
-def side_config(ctx, rank, world, local, args, stream, name, algo, loss, shape, rows, max_key, nnz_row, steps, warmup, pool_n):
+def side_config(ctx, rank, world, local, args, stream, name, algo, loss, shape, rows, max_key, nnz_row, steps, warmup, pool_n,
+                max_delay=0):
     """A short device-resident measurement of one of BASELINE.json's other configurations (configs[2..3]); same timing
     rules as the headline, fewer steps. Returns its sub-record (rank 0) or None."""
     from wormhole_b200 import capi
     max_uniq = min(rows * nnz_row * (2 if shape == "kdd" else 1), max_key)
-    job = Job(ctx, rank, world, local, algo, loss, max_key, args.depth, args.exchange, max_uniq)
+    job = Job(ctx, rank, world, local, algo, loss, max_key, args.depth, args.exchange, max_uniq, max_delay)
     _, dev, raw = make_pool(shape, rank, pool_n, rows, want_host=False)
     N = int(raw[0].offset[-1])
     U = len(np.unique(raw[0].index % np.uint64(max_key)))
@@ -499,8 +500,8 @@ def side_config(ctx, rank, world, local, args, stream, name, algo, loss, shape, 
     r = U / rows
     bpe = N / rows * 8 + 12 + r * (8 + 2 * STATE_BYTES[algo])
     v = world * rows * steps / (ms * 1e-3)
-    return {"workload": workload_name(shape, algo, loss, max_key, rows), "value": v, "unit": "examples/s", "steps": steps,
-            "warmup": warmup, "ms_per_step": ms / steps, "rows_per_minibatch": rows, "nnz_per_minibatch": N,
+    return {"workload": workload_name(shape, algo, loss, max_key, rows) + (", max_delay %d" % max_delay if max_delay else ""),
+            "value": v, "unit": "examples/s", "steps": steps, "warmup": warmup, "ms_per_step": ms / steps, "rows_per_minibatch": rows, "nnz_per_minibatch": N,
             "unique_keys_per_row_r": round(r, 4), "pool_minibatches": pool_n,
             "step_roofline": {"bytes_per_example": bpe, "frac_of_hbm_peak": v * bpe / (world * pk["hbm_gbs"] * 1e9)}}
 
@@ -542,9 +543,34 @@ def difacto_config(ctx, rank, world, rows, steps, warmup):
         t = torch.tensor([ms], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
+    # step roofline, SURVEY.md 8d config 5: 324 B/example of CSR + 416 B per unique key that carries an embedding
+    # ((1+dim) floats pulled and pushed, entry {w, V, sqc_grad...} read and written) + 32 B per key without one
+    keys = np.unique(raw[0].index % np.uint64(max_key))
+    if world > 1:
+        kt = torch.from_numpy(keys.astype(np.int64)).cuda()
+        nk = torch.tensor([kt.numel()], dtype=torch.int64, device="cuda")
+        dist.broadcast(nk, 0)
+        if rank != 0:
+            kt = torch.empty(int(nk.item()), dtype=torch.int64, device="cuda")
+        dist.broadcast(kt, 0)
+        keys = kt.cpu().numpy().astype(np.uint64)
+    mine = keys[(keys >= np.uint64(kb)) & (keys < np.uint64(ke))]
+    _, size, _, _ = d.get_state(mine)
+    with_v = float((size > 1).sum())
+    if world > 1:
+        t = torch.tensor([with_v], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t)
+        with_v = float(t.item())
     d.close()
     v = world * rows * steps / (ms * 1e-3)
-    return {"workload": "DiFacto dim 16 (threshold 16, lambda_l1 4, lr_eta .01) on the synthetic Criteo shape, minibatches resident in HBM; "
+    pk, _ = peaks()
+    r, r_v = len(keys) / rows, with_v / rows
+    bpe = 324 + 416 * r_v + 32 * (r - r_v)
+    roof = {"bytes_per_example": bpe, "unique_keys_with_embedding_per_row": round(r_v, 4),
+            "frac_of_hbm_peak": v * bpe / (world * pk["hbm_gbs"] * 1e9)}
+    if rank != 0:
+        return None
+    return {"step_roofline": roof, "workload": "DiFacto dim 16 (threshold 16, lambda_l1 4, lr_eta .01) on the synthetic Criteo shape, minibatches resident in HBM; "
                         "the entry point is synchronous" + ("; %d key-range shards, count push / ZVPull / ZVPush as all-to-all-v over NCCL" % world if world > 1 else ""),
             "value": v, "unit": "examples/s", "n_gpus": world, "steps": steps, "warmup": warmup, "ms_per_step": ms / steps,
             "rows_per_minibatch": rows, "unique_keys_per_row_r": round(U / rows, 4)}
@@ -637,6 +663,11 @@ def run_ours(args):
         K, Wm = max(5, min(args.steps, 40)), max(3, min(args.warmup, 5))
         for name, a2, l2 in (("adagrad_logit", "adagrad", "logit"), ("sgd_sqhinge", "sgd", "sqhinge")):
             others[name] = side_config(ctx, rank, world, local, args, stream, name, a2, l2, "criteo", ROWS, MAX_KEY, NNZ_PER_ROW, K, Wm, pool_n)
+        if world > 1 and args.exchange == "p2p":
+            # the reference's own default, max_concurrency = 2 (learn/linear/config.proto): a pull may overtake the worker's
+            # previous push. Not the configuration parity is judged in (max_delay = 0, the headline); reported beside it.
+            others["ftrl_logit_max_delay_1"] = side_config(ctx, rank, world, local, args, stream, "ftrl_logit_max_delay_1", "ftrl", "logit",
+                                                           "criteo", ROWS, MAX_KEY, NNZ_PER_ROW, K, Wm, pool_n, max_delay=1)
         others["kdd_ftrl"] = side_config(ctx, rank, world, local, args, stream, "kdd_ftrl", "ftrl", "logit", "kdd", 1000000,
                                          synth.KDD_VOCAB, 11, max(3, K // 4), 3, 3)
         # (every rank takes part; a failure on one rank of several would leave the others in a collective, so it is

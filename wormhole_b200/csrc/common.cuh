@@ -16,6 +16,9 @@ namespace wh {
 
 void set_error(const char* fmt, ...);
 extern std::atomic<uint64_t> g_launches;
+// WH_TIMELINE=<file>: every profiler mark of every lane with its time since the process's first mark (a debugging aid:
+// where a pipelined step spends its time; the marks cost an event record each)
+extern FILE* g_timeline;
 
 #define WH_CUDA(expr)                                                                      \
   do {                                                                                     \

@@ -3,12 +3,16 @@
 
 #include <stdlib.h>
 
+#include <string>
+
 #include "common.cuh"
 
 namespace wh {
 
 static thread_local char g_err[1024] = "";
 std::atomic<uint64_t> g_launches{0};
+FILE* g_timeline = nullptr;
+static cudaEvent_t g_tl_base = nullptr;
 
 void set_error(const char* fmt, ...) {
   va_list ap;
@@ -59,6 +63,7 @@ int prof_mark(whContext* ctx, const char* name) {
     p.ev.push_back(e);
     p.name.push_back(nullptr);
   }
+  if (g_timeline && !g_tl_base) { WH_CUDA(cudaEventCreate(&g_tl_base)); WH_CUDA(cudaEventRecord(g_tl_base, ctx->stream)); }
   WH_CUDA(cudaEventRecord(p.ev[p.used], ctx->stream));
   p.name[p.used] = name;  // name of the segment that ENDS at this event (NULL = start marker)
   p.used++;
@@ -66,6 +71,12 @@ int prof_mark(whContext* ctx, const char* name) {
 }
 int prof_collect(whContext* ctx) {
   Profiler& p = ctx->prof;
+  if (g_timeline)
+    for (size_t i = 0; i < p.used; ++i) {
+      float t = 0;
+      if (cudaEventElapsedTime(&t, g_tl_base, p.ev[i]) == cudaSuccess)
+        fprintf(g_timeline, "%p %-12s %10.1f\n", (void*)ctx, p.name[i] ? p.name[i] : "begin", (double)t * 1e3);
+    }
   for (size_t i = 1; i < p.used; ++i) {
     if (!p.name[i]) continue;
     float ms = 0;
@@ -87,7 +98,7 @@ int wh_profile_enable(whContext* c, int on) {
   WH_REQUIRE(c != nullptr, "wh_profile_enable: ctx is NULL");
   wh::DeviceGuard g(c->device);
   WH_CUDA(cudaStreamSynchronize(c->stream));
-  c->prof.on = on != 0; c->prof.used = 0;
+  c->prof.on = on != 0 || wh::g_timeline != nullptr; c->prof.used = 0;
   if (on) c->prof.acc.clear();
   return WH_OK;
 }
@@ -126,6 +137,13 @@ int wh_create(int device, whContext** out) {
   // 4- to 16-byte reads, of which a wider fetch only keeps one sector)
   if (const char* e = getenv("WH_L2_FETCH")) { const int g = atoi(e); if (g == 32 || g == 64 || g == 128) cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)g); }
   whContext* c = new whContext();
+  if (const char* tl = getenv("WH_TIMELINE")) {
+    if (!wh::g_timeline) {
+      const char* rk = getenv("RANK");
+      wh::g_timeline = fopen((std::string(tl) + "." + (rk ? rk : "0")).c_str(), "w");
+    }
+    c->prof.on = wh::g_timeline != nullptr;
+  }
   c->device = device;
   c->num_sms = prop.multiProcessorCount;
   c->l2_bytes = (size_t)prop.l2CacheSize;

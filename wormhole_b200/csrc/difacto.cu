@@ -22,7 +22,7 @@ int spmv_trans_accumulate_launch(whContext* ctx, size_t rows, size_t nnz, const 
                                  const uint32_t* index, const float* value, const float* x,
                                  long long* acc, FixedScale* fs, unsigned copies, size_t stride, bool scale_ready = false);
 int fixed_finish_launch(whContext* ctx, long long* acc, size_t n, const FixedScale* fs, float* y, float mul,
-                        unsigned copies, size_t stride, const unsigned* d_n = nullptr);
+                        unsigned copies, size_t stride, const unsigned* d_n = nullptr, unsigned ystride = 1);
 
 // ------------------------------------------------------------------------------ the loss --
 

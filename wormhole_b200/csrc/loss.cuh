@@ -20,7 +20,7 @@ struct EvalOut {
 // dual may be NULL (evaluation only). want_logloss also fills EvalOut::logloss.
 int loss_forward_launch(whContext* ctx, int loss, size_t rows, const float* label, const float* xw,
                         float* dual, EvalOut* out, int want_logloss);
-int auc_launch(whContext* ctx, size_t rows, const float* label, const float* xw, EvalOut* out);
+int auc_launch(whContext* ctx, size_t rows, const float* label, const float* xw, EvalOut* out, bool few_sms = false);
 // the multi-launch radix-sort variant (any size); auc_launch uses it beyond 2^20 examples
 int auc_launch_multiblock(whContext* ctx, size_t rows, const float* label, const float* xw, EvalOut* out);
 

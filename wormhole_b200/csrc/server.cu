@@ -212,20 +212,34 @@ __global__ void shard_barrier_kernel(ShardMap m, unsigned long long epoch, long 
 // The owner of a key range applies, for one source rank, the slice of that rank's (key, gradient) list that
 // falls into its range -- read directly from the source GPU's memory. One launch per source, in ascending
 // source order: each is one push message for this shard's handle.
+// the gradient of one outbox entry: fp32 in the low half, or the fixed-point sum converted as fixed_finish_kernel does
+__device__ __forceinline__ OutboxScale outbox_scale(const unsigned char* outbox) {
+  OutboxScale sc;
+  sc.inv = __ldcg(reinterpret_cast<const double*>(outbox + kOutboxScaleAt));
+  sc.mul = __ldcg(reinterpret_cast<const float*>(outbox + kOutboxScaleAt + 8));
+  sc.fixed = __ldcg(reinterpret_cast<const unsigned*>(outbox + kOutboxScaleAt + 12));
+  return sc;
+}
+__device__ __forceinline__ float outbox_grad(long long g, const OutboxScale& sc) {
+  return sc.fixed ? (float)((double)g * sc.inv) * sc.mul : __int_as_float((int)(unsigned)(unsigned long long)g);
+}
+
 __global__ void __launch_bounds__(256)
 server_apply_from_kernel(HandleParams h, ShardView table, const unsigned char* outbox, size_t cap, int me, long long* counters) {
   // one thread per block fetches the two cut positions: they sit in the SOURCE GPU's memory, and tens of
   // thousands of threads loading the same remote word serialise on NVLink (measured: 8x slower push)
   __shared__ unsigned s_cut[2];
+  __shared__ OutboxScale s_sc;
   if (threadIdx.x < 2) s_cut[threadIdx.x] = reinterpret_cast<const volatile unsigned*>(outbox)[4 + me + threadIdx.x];
+  if (threadIdx.x == 2) s_sc = outbox_scale(outbox);
   __syncthreads();
   const unsigned lo = s_cut[0], hi = s_cut[1];
-  const uint64_t* keys = reinterpret_cast<const uint64_t*>(outbox + 256);
-  const float* grads = reinterpret_cast<const float*>(outbox + 256 + cap * 8);
+  const uint64_t* keys = reinterpret_cast<const uint64_t*>(outbox + outbox_keys_at());
+  const long long* grads = reinterpret_cast<const long long*>(outbox + outbox_grads_at(cap));
   int delta = 0, bad = 0;
   for (size_t i = lo + (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += (size_t)gridDim.x * blockDim.x) {
     const uint64_t k = keys[i];
-    if (k >= h.key_begin && k < h.key_end) delta += handle_push(h, table, k - h.key_begin, grads[i]);
+    if (k >= h.key_begin && k < h.key_end) delta += handle_push(h, table, k - h.key_begin, outbox_grad(__ldcg(grads + i), s_sc));
     else bad = 1;
   }
   commit_counters(counters, delta, bad);
@@ -248,21 +262,25 @@ server_apply_all_kernel(HandleParams h, ShardView table, ApplyAllArgs a, size_t 
   namespace cg = cooperative_groups;
   cg::grid_group grid = cg::this_grid();
   __shared__ unsigned s_cut[kMaxShards][2];
+  __shared__ OutboxScale s_sc[kMaxShards];
   if (threadIdx.x < 2 * a.world) {   // one thread per cut: the headers sit in the source GPUs' memory
     const int src = threadIdx.x >> 1;
     s_cut[src][threadIdx.x & 1] = reinterpret_cast<const volatile unsigned*>(a.outbox[src])[4 + me + (threadIdx.x & 1)];
+  } else if (threadIdx.x >= 32 && threadIdx.x < 32 + a.world) {
+    const int src = threadIdx.x - 32;
+    s_sc[src] = outbox_scale(a.outbox[src]);
   }
   __syncthreads();
   const size_t gt = (size_t)blockIdx.x * blockDim.x + threadIdx.x, gsz = (size_t)gridDim.x * blockDim.x;
   uint64_t k0[kMaxShards];
-  float g0[kMaxShards];
+  long long g0[kMaxShards];
 #pragma unroll
   for (int src = 0; src < kMaxShards; ++src) {
     if (src < a.world) {
       const size_t i = s_cut[src][0] + gt;
       if (i < s_cut[src][1]) {
-        k0[src] = __ldcg(reinterpret_cast<const uint64_t*>(a.outbox[src] + 256) + i);
-        g0[src] = __ldcg(reinterpret_cast<const float*>(a.outbox[src] + 256 + cap * 8) + i);
+        k0[src] = __ldcg(reinterpret_cast<const uint64_t*>(a.outbox[src] + outbox_keys_at()) + i);
+        g0[src] = __ldcg(reinterpret_cast<const long long*>(a.outbox[src] + outbox_grads_at(cap)) + i);
       }
     }
   }
@@ -271,16 +289,16 @@ server_apply_all_kernel(HandleParams h, ShardView table, ApplyAllArgs a, size_t 
   for (int src = 0; src < kMaxShards; ++src) {
     if (src < a.world) {
       h.eta_sgd = a.eta_sgd[src];
-      const uint64_t* keys = reinterpret_cast<const uint64_t*>(a.outbox[src] + 256);
-      const float* grads = reinterpret_cast<const float*>(a.outbox[src] + 256 + cap * 8);
+      const uint64_t* keys = reinterpret_cast<const uint64_t*>(a.outbox[src] + outbox_keys_at());
+      const long long* grads = reinterpret_cast<const long long*>(a.outbox[src] + outbox_grads_at(cap));
       const size_t lo = s_cut[src][0], hi = s_cut[src][1];
       size_t i = lo + gt;
       if (i < hi) {
-        if (k0[src] >= h.key_begin && k0[src] < h.key_end) delta += handle_push(h, table, k0[src] - h.key_begin, g0[src]);
+        if (k0[src] >= h.key_begin && k0[src] < h.key_end) delta += handle_push(h, table, k0[src] - h.key_begin, outbox_grad(g0[src], s_sc[src]));
         else bad = 1;
         for (i += gsz; i < hi; i += gsz) {   // slices longer than the grid
           const uint64_t k = __ldcg(keys + i);
-          if (k >= h.key_begin && k < h.key_end) delta += handle_push(h, table, k - h.key_begin, __ldcg(grads + i));
+          if (k >= h.key_begin && k < h.key_end) delta += handle_push(h, table, k - h.key_begin, outbox_grad(__ldcg(grads + i), s_sc[src]));
           else bad = 1;
         }
       }
@@ -288,6 +306,28 @@ server_apply_all_kernel(HandleParams h, ShardView table, ApplyAllArgs a, size_t 
     }
   }
   commit_counters(counters, delta, bad);
+}
+
+// Blocks per SM of the two exchange kernels (256 threads each). More threads = fewer trips per thread, and every trip is
+// a chain of a remote read and a local access; but the apply kernel is cooperative -- all its blocks must be resident
+// at once, beside whatever the other minibatches in flight are running -- and stalls when it asks for too much
+// (measured on 2 GPUs, ms per step: apply 1 / 2 / 4 blocks per SM = 0.150 / 0.143 / 0.302).
+// Start of a lane's next minibatch: the gradient words of the previous one (U is still in the header) back to zero --
+// the step's kernel adds its fixed-point sums into them
+__global__ void outbox_clear_kernel(unsigned char* outbox, size_t cap) {
+  const unsigned U = reinterpret_cast<const unsigned*>(outbox)[0];
+  long long* g = reinterpret_cast<long long*>(outbox + outbox_grads_at(cap));
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < U && i < cap; i += (size_t)gridDim.x * blockDim.x) g[i] = 0;
+}
+int outbox_clear_launch(whServer* s, cudaStream_t stream, unsigned char* outbox, size_t cap) {
+  WH_LAUNCH(outbox_clear_kernel, (unsigned)s->ctx->num_sms * 2, 256, 0, stream, outbox, cap);
+  return WH_OK;
+}
+
+static unsigned exchange_blocks_per_sm(bool cooperative) {
+  const char* e = getenv(cooperative ? "WH_APPLY_BLOCKS" : "WH_SERVE_BLOCKS");
+  const int b = e ? atoi(e) : (cooperative ? 2 : 4);
+  return (unsigned)(b < 1 ? 1 : (b > 8 ? 8 : b));
 }
 
 // cuts[g] = first position in the ascending key list whose key is >= bounds[g]
@@ -322,7 +362,7 @@ int server_apply_all_launch(whServer* s, cudaStream_t stream, unsigned char* con
   ShardView table = s->view();
   long long* counters = s->counters.as<long long>();
   void* args[] = {&h, &table, &a, &cap, &me, &counters};
-  const unsigned grid = (unsigned)s->ctx->num_sms;   // one light block per SM: co-resident with anything
+  const unsigned grid = (unsigned)s->ctx->num_sms * exchange_blocks_per_sm(true);
   WH_CUDA(cudaLaunchCooperativeKernel((const void*)server_apply_all_kernel, dim3(grid), dim3(256), args, 0, stream));
   wh::g_launches.fetch_add(1, std::memory_order_relaxed);
   return WH_OK;
@@ -406,7 +446,7 @@ server_serve_all_kernel(const ShardEntry* tab, uint64_t key_begin, uint64_t key_
       float w = 0.f;
       if (k[src] >= key_begin && k[src] < key_end) w = __ldcg(&tab[k[src] - key_begin].w);
       else bad = 1;
-      reinterpret_cast<float*>(a.outbox[src] + 256 + cap * 12)[s_cut[src][0] + i0] = w;
+      reinterpret_cast<float*>(a.outbox[src] + outbox_inbox_at(cap))[s_cut[src][0] + i0] = w;
     }
   }
   commit_counters(counters, 0, bad);
@@ -416,7 +456,7 @@ int server_serve_all_launch(whServer* s, cudaStream_t stream, unsigned char* con
   ServeArgs a;
   a.world = s->map.world;
   for (int src = 0; src < a.world; ++src) a.outbox[src] = outboxes[src];
-  WH_LAUNCH(server_serve_all_kernel, (unsigned)s->ctx->num_sms, 256, 0, stream, s->view().e, s->key_begin, s->key_end, a, cap,
+  WH_LAUNCH(server_serve_all_kernel, (unsigned)s->ctx->num_sms * exchange_blocks_per_sm(false), 256, 0, stream, s->view().e, s->key_begin, s->key_end, a, cap,
             s->map.rank, s->counters.as<long long>());
   return WH_OK;
 }

@@ -24,6 +24,20 @@ struct alignas(32) ShardEntry {
   long long acc;     // X^T dual of the minibatch in flight, fixed point
   long long pad1;
 };
+// A worker's outbox (one per lane; CUDA IPC, read and written by the owners of the keys):
+//   header 256 bytes: word 0 = U (unique keys), words 4 .. 4+world = slice cuts, byte 128 = OutboxScale
+//   keys   u64[cap]   ascending unique transformed keys
+//   grads  8 bytes per key: the fp32 gradient in the low half, or (OutboxScale::fixed) the int64 fixed-point sum of
+//          X^T dual exactly as the step's kernel left it -- the owner converts while it applies, which takes a launch
+//          out of the push -> pull cycle
+//   inbox  f32[cap]   the pulled weights, written by the owners
+struct OutboxScale { double inv; float mul; unsigned fixed; };
+__host__ __device__ static inline size_t outbox_keys_at() { return 256; }
+__host__ __device__ static inline size_t outbox_grads_at(size_t cap) { return 256 + cap * 8; }
+__host__ __device__ static inline size_t outbox_inbox_at(size_t cap) { return 256 + cap * 16; }
+static inline size_t outbox_bytes(size_t cap) { return 256 + cap * 20; }
+constexpr size_t kOutboxScaleAt = 128;
+
 struct ShardView {
   ShardEntry* e = nullptr;     // [entries]
 };
@@ -84,6 +98,7 @@ int server_serve_all_launch(whServer* s, cudaStream_t stream, unsigned char* con
 int server_apply_all_launch(whServer* s, cudaStream_t stream, unsigned char* const* outboxes, size_t cap);
 int server_apply_from_launch(whServer* s, cudaStream_t stream, const unsigned char* outbox, size_t cap);
 int outbox_cuts_launch(whServer* s, cudaStream_t stream, unsigned char* outbox);
+int outbox_clear_launch(whServer* s, cudaStream_t stream, unsigned char* outbox, size_t cap);
 int server_push_acc_launch(whServer* s, cudaStream_t stream, const uint64_t* keys, size_t n, const unsigned* d_n, long long* acc,
                            const FixedScale* fs, float mul, unsigned copies, size_t stride);
 }  // namespace wh

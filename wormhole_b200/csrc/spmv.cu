@@ -279,13 +279,13 @@ spmv_trans_agg_kernel(size_t rows, const size_t* __restrict__ offset, const uint
 // y = fixed-point sum back to fp32 (+ p*z for SpMM); clears the accumulator for the next call.
 __global__ void fixed_finish_kernel(long long* acc, size_t n, const FixedScale* __restrict__ fs,
                                     float p, const float* __restrict__ z, float* __restrict__ y,
-                                    float mul, unsigned copies, size_t stride, const unsigned* d_n) {
+                                    float mul, unsigned copies, size_t stride, const unsigned* d_n, unsigned ystride) {
   if (d_n) n = *d_n;   // the count may live on the device (number of unique keys of a minibatch)
   const double inv = fs->inv;
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
     const long long a = sum_and_clear_replicas(acc, copies, stride, i);
     float s = (float)((double)a * inv) * mul;
-    y[i] = z ? z[i] * p + s : s;
+    y[i * ystride] = z ? z[i] * p + s : s;
   }
 }
 
@@ -349,10 +349,10 @@ int spmv_trans_accumulate_launch(whContext* ctx, size_t rows, size_t nnz, const 
 
 // Accumulator -> fp32 (and clear), for callers that ran spmv_trans_accumulate_launch themselves.
 int fixed_finish_launch(whContext* ctx, long long* acc, size_t n, const FixedScale* fs, float* y, float mul,
-                        unsigned copies, size_t stride, const unsigned* d_n) {
+                        unsigned copies, size_t stride, const unsigned* d_n, unsigned ystride) {
   if (n == 0) return WH_OK;
   const unsigned g2 = (unsigned)std::min<size_t>(div_up(n, 256), (size_t)ctx->num_sms * 8);
-  WH_LAUNCH(fixed_finish_kernel, g2, 256, 0, ctx->stream, acc, n, fs, 0.f, (const float*)nullptr, y, mul, copies, stride, d_n);
+  WH_LAUNCH(fixed_finish_kernel, g2, 256, 0, ctx->stream, acc, n, fs, 0.f, (const float*)nullptr, y, mul, copies, stride, d_n, ystride);
   return WH_OK;
 }
 
@@ -362,7 +362,7 @@ int spmv_trans_times_launch(whContext* ctx, size_t rows, size_t nnz, const size_
   if (ysize == 0) return WH_OK;
   WH_TRY(spmv_trans_accumulate_launch(ctx, rows, nnz, offset, index, value, x, acc, fs, copies, ysize, false));
   const unsigned g2 = (unsigned)std::min<size_t>(div_up(ysize, 256), (size_t)ctx->num_sms * 8);
-  WH_LAUNCH(fixed_finish_kernel, g2, 256, 0, ctx->stream, acc, ysize, fs, 0.f, (const float*)nullptr, y, mul, copies, ysize, (const unsigned*)nullptr);
+  WH_LAUNCH(fixed_finish_kernel, g2, 256, 0, ctx->stream, acc, ysize, fs, 0.f, (const float*)nullptr, y, mul, copies, ysize, (const unsigned*)nullptr, 1u);
   return WH_OK;
 }
 
@@ -623,7 +623,7 @@ int spmm_trans_times_launch(whContext* ctx, size_t rows, size_t nnz, const size_
   WH_TRY(fixed_prepare(ctx, fs, x, rows * dim, value, nnz, 1));
   if (rows) WH_LAUNCH(spmm_trans_kernel, (unsigned)div_up(rows * dim, 256), 256, 0, ctx->stream, rows, offset, index, value, x, dim, acc, fs);
   const unsigned g2 = (unsigned)std::min<size_t>(div_up(ysize, 256), (size_t)ctx->num_sms * 8);
-  WH_LAUNCH(fixed_finish_kernel, g2, 256, 0, ctx->stream, acc, ysize, fs, p, (z && p != 0.f) ? z : (const float*)nullptr, y, 1.f, 1u, ysize, (const unsigned*)nullptr);
+  WH_LAUNCH(fixed_finish_kernel, g2, 256, 0, ctx->stream, acc, ysize, fs, p, (z && p != 0.f) ? z : (const float*)nullptr, y, 1.f, 1u, ysize, (const unsigned*)nullptr, 1u);
   return WH_OK;
 }
 

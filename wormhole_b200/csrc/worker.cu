@@ -33,7 +33,7 @@ int spmv_trans_accumulate_launch(whContext* ctx, size_t rows, size_t nnz, const 
                                  const uint32_t* index, const float* value, const float* x,
                                  long long* acc, FixedScale* fs, unsigned copies, size_t stride, bool scale_ready = false);
 int fixed_finish_launch(whContext* ctx, long long* acc, size_t n, const FixedScale* fs, float* y, float mul,
-                        unsigned copies, size_t stride, const unsigned* d_n = nullptr);
+                        unsigned copies, size_t stride, const unsigned* d_n = nullptr, unsigned ystride = 1);
 constexpr int kMaxDepth = 8;
 
 struct Lane {
@@ -119,7 +119,15 @@ static int lane_init(whWorker* w, int i) {
   l.cx.num_sms = l.ax.num_sms = ctx->num_sms;
   l.cx.l2_bytes = l.ax.l2_bytes = ctx->l2_bytes;
   if (i == 0) { l.cx.stream = ctx->stream; l.cx.own_stream = false; }   // lane 0 rides the context's stream
-  else { WH_CUDA(cudaStreamCreateWithFlags(&l.cx.stream, cudaStreamNonBlocking)); l.cx.own_stream = true; }
+  else {
+    // the lanes' own streams carry the model-dependent chain: above the evaluation side streams (WH_PRIO=0: all alike)
+    int least = 0, greatest = 0;
+    WH_CUDA(cudaDeviceGetStreamPriorityRange(&least, &greatest));
+    const char* e = getenv("WH_PRIO");
+    const int prio = (e && atoi(e) == 0) ? least : greatest;
+    WH_CUDA(cudaStreamCreateWithPriority(&l.cx.stream, cudaStreamNonBlocking, prio));
+    l.cx.own_stream = true;
+  }
   WH_CUDA(cudaStreamCreateWithFlags(&l.ax.stream, cudaStreamNonBlocking));
   l.ax.own_stream = true;
   WH_CUDA(cudaEventCreateWithFlags(&l.ev_fork, cudaEventDisableTiming));
@@ -411,6 +419,19 @@ int wh_worker_submit(whWorker* w, const whRowBlock* blk, int mem, size_t nnz, in
   // apply it; "every owner has served pull tk - depth + 1" says they are done with it
   if (served && w->depth > 1 && tk > (unsigned long long)w->depth)
     WH_CUDA(cudaStreamWaitEvent(cx->stream, w->ev_served[(tk - w->depth + 1) % ring], 0));
+  // With the table of frequent keys the step's kernel leaves its fixed-point sums in the outbox itself and the owners
+  // convert while they apply (one launch less between push and pull): zero the words of the lane's previous minibatch,
+  // and tell the owners how to read this one's
+  const bool ob_fixed = outboxed && fused;
+  if (outboxed) {
+    WH_TRY(outbox_clear_launch(s, cx->stream, l.outbox.as<unsigned char>(), w->outbox_cap));
+    OutboxScale* hs = reinterpret_cast<OutboxScale*>(l.pinned + 448);
+    float sc_unused;
+    hs->inv = 0; hs->mul = w->loss == WH_LOSS_SQUARE_HINGE ? -2.f : 1.f; hs->fixed = ob_fixed ? 1u : 0u;
+    if (ob_fixed) unit_terms_scale(n, &sc_unused, &hs->inv);
+    WH_CUDA(cudaMemcpyAsync(l.outbox.as<unsigned char>() + kOutboxScaleAt, hs, sizeof(OutboxScale), cudaMemcpyHostToDevice, cx->stream));
+    if (ob_fixed) acc = reinterpret_cast<long long*>(l.outbox.as<unsigned char>() + outbox_grads_at(w->outbox_cap));
+  }
 
   // local dense shard: Handle::Pull rides in the scan that emits the unique keys (after the push it has to see)
   const bool emit_pull = fused && s->map.world == 1 && s->hslots == 0 && pull_at_emit_supported(cx, w->max_key);
@@ -429,6 +450,7 @@ int wh_worker_submit(whWorker* w, const whRowBlock* blk, int mem, size_t nnz, in
   if (outboxed) WH_TRY(outbox_cuts_launch(s, cx->stream, l.outbox.as<unsigned char>()));
   // ZPull: one Handle::Pull per unique key, after every earlier push
   if (served) WH_TRY(server_barrier_launch(s, cx->stream, 1));   // every rank's key list is posted (off the critical cycle)
+  if (g_timeline) WH_PROF(cx, "cuts+b1");
   // bounded staleness (the reference's max_concurrency > 1 lets a worker pull before its earlier pushes have
   // landed): with max_delay = d the pull of minibatch t waits for the push of minibatch t - 1 - d only
   if (!emit_pull && tk > 1ull + (unsigned)w->max_delay) WH_CUDA(cudaStreamWaitEvent(cx->stream, w->ev_pushed[(tk - 1 - w->max_delay) % ring], 0));
@@ -440,10 +462,12 @@ int wh_worker_submit(whWorker* w, const whRowBlock* blk, int mem, size_t nnz, in
     const int lane_idx = (int)(&l - w->lane);
     unsigned char* boxes[kMaxShards];
     for (int src = 0; src < s->map.world; ++src) boxes[src] = w->peer_outbox[src][lane_idx];
+    if (g_timeline) WH_PROF(cx, "wait_push");
     WH_TRY(server_serve_all_launch(s, cx->stream, boxes, w->outbox_cap));
+    if (g_timeline) WH_PROF(cx, "serve");
     WH_TRY(server_barrier_launch(s, cx->stream, 2));
     WH_CUDA(cudaEventRecord(w->ev_served[tk % ring], cx->stream));
-    pulled = reinterpret_cast<float*>(l.outbox.as<unsigned char>() + 256 + w->outbox_cap * 12);
+    pulled = reinterpret_cast<float*>(l.outbox.as<unsigned char>() + outbox_inbox_at(w->outbox_cap));
   } else if (sharded) {
     // gather straight from the GPUs that own the keys; nobody may start pushing before everyone has pulled
     WH_TRY(server_pull_sharded_launch(s, cx->stream, uniq, ucap, d_nuniq, l.w.as<float>()));
@@ -471,7 +495,7 @@ int wh_worker_submit(whWorker* w, const whRowBlock* blk, int mem, size_t nnz, in
   // AUC on the side stream (nothing downstream of it but the progress numbers)
   WH_CUDA(cudaEventRecord(l.ev_fork, cx->stream));
   WH_CUDA(cudaStreamWaitEvent(l.ax.stream, l.ev_fork, 0));
-  WH_TRY(auc_launch(&l.ax, rows, d_label, l.xw.as<float>(), d_eval));
+  WH_TRY(auc_launch(&l.ax, rows, d_label, l.xw.as<float>(), d_eval, sharded && w->depth > 1));
   // the fused kernel was the last reader of the localizer's directory: zero it for the lane's next minibatch, off the chain
   if (fused) WH_CUDA(cudaMemsetAsync(cx->directory.p, 0, div_up(w->max_key, 32) * sizeof(uint2), l.ax.stream));
   WH_CUDA(cudaEventRecord(l.ev_auc, l.ax.stream));
@@ -488,13 +512,17 @@ int wh_worker_submit(whWorker* w, const whRowBlock* blk, int mem, size_t nnz, in
       // owners apply: gradients go to the outbox as fp32; once every rank has pulled and filled its outbox
       // (barrier), each owner walks the source ranks in ascending order -- one push message each -- reading its
       // slice straight from the source GPU; a second barrier keeps outboxes and tables stable until all are done
-      float* ob_grads = reinterpret_cast<float*>(l.outbox.as<unsigned char>() + 256 + w->outbox_cap * 8);
-      WH_TRY(fixed_finish_launch(cx, acc, ucap, fs, ob_grads, mul, copies, ucap, d_nuniq));
+      if (!ob_fixed) {
+        float* ob_grads = reinterpret_cast<float*>(l.outbox.as<unsigned char>() + outbox_grads_at(w->outbox_cap));
+        WH_TRY(fixed_finish_launch(cx, acc, ucap, fs, ob_grads, mul, copies, ucap, d_nuniq, 2));   // fp32 in the low half of each word
+        if (g_timeline) WH_PROF(cx, "fixed_finish");
+      }
       const int lane_idx = (int)(&l - w->lane);
       static int apply_all = -1;   // WH_APPLY_ALL=0: one launch per source (the older path)
       if (apply_all < 0) { const char* e = getenv("WH_APPLY_ALL"); apply_all = e ? atoi(e) : 1; }
       // every rank's gradients are posted (with the owner-served pull: a barrier class of its own, see server.cuh)
       WH_TRY(server_barrier_launch(s, cx->stream, served ? 3 : 0));
+      if (g_timeline) WH_PROF(cx, "b3");
       if (apply_all) {
         // the `world` messages in ascending source order in one cooperative launch
         unsigned char* boxes[kMaxShards];
@@ -520,8 +548,9 @@ int wh_worker_submit(whWorker* w, const whRowBlock* blk, int mem, size_t nnz, in
     }
     WH_PROF(cx, "push");
   }
-  WH_CUDA(cudaMemcpyAsync(l.pinned + 256, s->counters.p, 24, cudaMemcpyDeviceToHost, cx->stream));
+  // (the next minibatch's pull waits for this event: nothing but the push itself may sit in front of it)
   WH_CUDA(cudaEventRecord(w->ev_pushed[tk % ring], cx->stream));
+  WH_CUDA(cudaMemcpyAsync(l.pinned + 256, s->counters.p, 24, cudaMemcpyDeviceToHost, cx->stream));
   // join the AUC branch, then the progress read-back
   WH_CUDA(cudaStreamWaitEvent(cx->stream, l.ev_auc, 0));
   if (cx->prof.on) WH_TRY(prof_mark(cx, "auc_tail"));
@@ -559,6 +588,7 @@ int wh_worker_submit_idle(whWorker* w, int train, uint64_t* ticket) {
   for (int src = 0; src < s->map.world; ++src) boxes[src] = w->peer_outbox[src][lane_idx];
   if (served && w->depth > 1 && tk > (unsigned long long)w->depth)
     WH_CUDA(cudaStreamWaitEvent(cx->stream, w->ev_served[(tk - w->depth + 1) % ring], 0));
+  WH_TRY(outbox_clear_launch(s, cx->stream, l.outbox.as<unsigned char>(), w->outbox_cap));
   WH_CUDA(cudaMemsetAsync(l.outbox.p, 0, 256, cx->stream));      // U = 0, every cut = 0
   WH_CUDA(cudaMemsetAsync(d_eval, 0, sizeof(EvalOut), cx->stream));
   if (served) WH_TRY(server_barrier_launch(s, cx->stream, 1));
@@ -577,8 +607,8 @@ int wh_worker_submit_idle(whWorker* w, int train, uint64_t* ticket) {
     if (!served || w->depth == 1) WH_TRY(server_barrier_launch(s, cx->stream));
     s->steps++;
   }
-  WH_CUDA(cudaMemcpyAsync(l.pinned + 256, s->counters.p, 24, cudaMemcpyDeviceToHost, cx->stream));
   WH_CUDA(cudaEventRecord(w->ev_pushed[tk % ring], cx->stream));
+  WH_CUDA(cudaMemcpyAsync(l.pinned + 256, s->counters.p, 24, cudaMemcpyDeviceToHost, cx->stream));
   WH_CUDA(cudaMemcpyAsync(l.pinned, d_eval, sizeof(EvalOut), cudaMemcpyDeviceToHost, cx->stream));
   WH_CUDA(cudaEventRecord(l.ev_done, cx->stream));
   l.busy = true; l.train = train != 0; l.rows = 0;
@@ -696,7 +726,7 @@ int wh_worker_ipc_export(whWorker* w, size_t max_uniq, void* handles) {
   cudaIpcMemHandle_t* h = reinterpret_cast<cudaIpcMemHandle_t*>(handles);
   for (int i = 0; i < w->depth; ++i) {
     Lane& l = w->lane[i];
-    WH_TRY(l.outbox.reserve(256 + max_uniq * 16));   // header | keys | gradients | inbox of pulled weights
+    WH_TRY(l.outbox.reserve(outbox_bytes(max_uniq)));   // header | keys | gradients | inbox of pulled weights (server.cuh)
     WH_CUDA(cudaMemsetAsync(l.outbox.p, 0, 256, w->ctx->stream));
     WH_CUDA(cudaIpcGetMemHandle(&h[i], l.outbox.p));
   }
