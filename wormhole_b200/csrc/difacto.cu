@@ -26,23 +26,55 @@ int fixed_finish_launch(whContext* ctx, long long* acc, size_t n, const FixedSca
 
 // ------------------------------------------------------------------------------ the loss --
 
+// The column subset of the minibatch for V (Data::Load, learn/difacto/loss.h:204-253: V.X holds only the entries whose
+// key came with an embedding): per row the run {vstart, vcnt} of its entries with has[key], in CSR order, as (key rank,
+// value) pairs. One thread per row; a row reserves its run with one atomic (where the runs lie does not matter, their
+// inner order does). Keys with an embedding are few (fea_cnt > threshold and w != 0), so everything downstream walks a
+// few entries per row instead of testing all of them once per embedding dimension.
+__global__ void __launch_bounds__(256)
+dfc_subset_kernel(size_t rows, const size_t* __restrict__ offset, const uint32_t* __restrict__ index,
+                  const float* __restrict__ value, const unsigned char* __restrict__ has, unsigned* cursor,
+                  unsigned* __restrict__ vstart, unsigned* __restrict__ vcnt, uint32_t* __restrict__ vidx,
+                  float* __restrict__ vval) {
+  const size_t r = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= rows) return;
+  const size_t b = offset[r], e = offset[r + 1];
+  unsigned n = 0;
+  for (size_t j = b; j < e; ++j) n += has[index[j]] ? 1u : 0u;
+  unsigned at = 0;
+  if (n) at = atomicAdd(cursor, n);
+  vstart[r] = at; vcnt[r] = n;
+  if (!n) return;
+  for (size_t j = b; j < e; ++j) {
+    const uint32_t c = index[j];
+    if (!has[c]) continue;
+    vidx[at] = c;
+    if (value) vval[at] = value[j];
+    ++at;
+  }
+}
+// the keys that came with an embedding, in any order (the per-key passes below only visit these)
+__global__ void dfc_keylist_kernel(size_t U, const unsigned char* __restrict__ has, unsigned* count, uint32_t* __restrict__ list) {
+  const size_t u = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (u < U && has[u]) list[atomicAdd(count, 1u)] = (uint32_t)u;
+}
+
 // learn/difacto/loss.h:66-75: XV[i,:] = sum_j V[idx_j,:] val_j and xxvv[i,:] = sum_j V[idx_j,:]^2 val_j^2
 // over the entries whose key carries an embedding, in CSR order. One thread per (row, d).
 __global__ void __launch_bounds__(256)
-dfc_xv_kernel(size_t rows, const size_t* __restrict__ offset, const uint32_t* __restrict__ index,
-              const float* __restrict__ value, const unsigned char* __restrict__ has, const float* __restrict__ V,
+dfc_xv_kernel(size_t rows, const unsigned* __restrict__ vstart, const unsigned* __restrict__ vcnt,
+              const uint32_t* __restrict__ vidx, const float* __restrict__ vval, bool valued, const float* __restrict__ V,
               int dim, float* __restrict__ XV, float* __restrict__ xxvv) {
   const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   const size_t r = t / dim;
   const int d = (int)(t % dim);
   if (r >= rows) return;
   float a = 0.f, b = 0.f;
-  for (size_t j = offset[r]; j < offset[r + 1]; ++j) {
-    const uint32_t c = index[j];
-    if (!has[c]) continue;
-    const float v = __ldg(V + (size_t)c * dim + d);
+  const unsigned j0 = vstart[r], j1 = j0 + vcnt[r];
+  for (unsigned j = j0; j < j1; ++j) {
+    const float v = __ldg(V + (size_t)vidx[j] * dim + d);
     const float vv = v * v;
-    if (value) { const float x = value[j]; a += v * x; b += vv * (x * x); }
+    if (valued) { const float x = vval[j]; a += v * x; b += vv * (x * x); }
     else { a += v; b += vv; }
   }
   XV[t] = a; xxvv[t] = b;
@@ -67,22 +99,23 @@ __global__ void dfc_scale_rows_kernel(size_t rows, int dim, const float* __restr
 // learn/difacto/loss.h:142 accumulation part: G[idx_j, d] += XVp[i, d] * val_j, and
 // :121-123: xxp[idx_j] += p_i * val_j^2, for entries whose key carries an embedding. Fixed point.
 __global__ void __launch_bounds__(256)
-dfc_trans_kernel(size_t rows, const size_t* __restrict__ offset, const uint32_t* __restrict__ index,
-                 const float* __restrict__ value, const unsigned char* __restrict__ has, int dim,
+dfc_trans_kernel(size_t rows, const unsigned* __restrict__ vstart, const unsigned* __restrict__ vcnt,
+                 const uint32_t* __restrict__ vidx, const float* __restrict__ vval, bool valued, int dim,
                  const float* __restrict__ XVp, const float* __restrict__ p, long long* accG, long long* accX,
                  const FixedScale* __restrict__ fsG, const FixedScale* __restrict__ fsX) {
   const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   const size_t r = t / dim;
   const int d = (int)(t % dim);
   if (r >= rows) return;
+  const unsigned j0 = vstart[r], j1 = j0 + vcnt[r];
+  if (j0 == j1) return;
   const float x = XVp[t], pi = p[r];
   const float sg = fsG->scale, sx = fsX->scale;
-  for (size_t j = offset[r]; j < offset[r + 1]; ++j) {
-    const uint32_t c = index[j];
-    if (!has[c]) continue;
-    const float v = value ? value[j] : 1.f;
-    fixed_add(accG + (size_t)c * dim + d, value ? x * v : x, sg);
-    if (d == 0) fixed_add(accX + c, value ? pi * (v * v) : pi, sx);
+  for (unsigned j = j0; j < j1; ++j) {
+    const uint32_t c = vidx[j];
+    const float v = valued ? vval[j] : 1.f;
+    fixed_add(accG + (size_t)c * dim + d, valued ? x * v : x, sg);
+    if (d == 0) fixed_add(accX + c, valued ? pi * (v * v) : pi, sx);
   }
 }
 
@@ -101,27 +134,26 @@ struct DfcDropout {
 // G[u,:] = (-xxp[u] * V[u,:]) + sum (learn/difacto/loss.h:126-131,142), then clip (:145-148), then dropout (:150-154).
 // Also the sum of squares for the optional normalisation (:160-166), in fp64 per block.
 __global__ void __launch_bounds__(256)
-dfc_gv_finish_kernel(size_t U, int dim, const unsigned char* __restrict__ has, const float* __restrict__ V,
-                     long long* accG, long long* accX, const FixedScale* __restrict__ fsG,
+dfc_gv_finish_kernel(const unsigned* __restrict__ nkeys, const uint32_t* __restrict__ klist, int dim,
+                     const float* __restrict__ V, long long* accG, long long* accX, const FixedScale* __restrict__ fsG,
                      const FixedScale* __restrict__ fsX, float clip, DfcDropout drop, float* __restrict__ G, double* sumsq) {
-  const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const size_t n = (size_t)*nkeys * dim;
   double sq = 0;
-  if (t < U * dim) {
-    const size_t u = t / dim;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const size_t u = klist[i / dim];
+    const int d = (int)(i % dim);
+    const size_t t = u * dim + d;
     const long long ag = accG[t];
     accG[t] = 0;
-    float g = 0.f;
-    if (has[u]) {
-      const float xxp = (float)((double)accX[u] * fsX->inv);
-      const float z = V[t] * -xxp;
-      g = z * 1.0f + (float)((double)ag * fsG->inv);
-      if (clip > 0.f) g = g > clip ? clip : (g < -clip ? -clip : g);
-      if (drop.stream) {
-        const unsigned long long o = (unsigned long long)*drop.cursor + (unsigned long long)drop.pos[u] * dim + (t - u * dim);
-        if ((float)drop.stream[o % drop.len] / (float)2147483647 > 1 - drop.dropout) g = 0.f;
-      }
-      sq = (double)(g * g);
+    const float xxp = (float)((double)accX[u] * fsX->inv);
+    const float z = V[t] * -xxp;
+    float g = z * 1.0f + (float)((double)ag * fsG->inv);
+    if (clip > 0.f) g = g > clip ? clip : (g < -clip ? -clip : g);
+    if (drop.stream) {
+      const unsigned long long o = (unsigned long long)*drop.cursor + (unsigned long long)drop.pos[u] * dim + d;
+      if ((float)drop.stream[o % drop.len] / (float)2147483647 > 1 - drop.dropout) g = 0.f;
     }
+    sq += (double)(g * g);
     G[t] = g;
   }
   __shared__ double s[8];
@@ -131,18 +163,24 @@ dfc_gv_finish_kernel(size_t U, int dim, const unsigned char* __restrict__ has, c
   __syncthreads();
   if (threadIdx.x == 0) { double a = 0; for (int w = 0; w < 8; ++w) a += s[w]; if (a != 0) atomicAdd(sumsq, a); }
 }
-__global__ void dfc_clear_kernel(long long* acc, size_t n, double* sumsq) {
-  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n) acc[i] = 0;
-  if (i == 0 && sumsq) *sumsq = 0;
+// after the pass above: the (X o X)^T p sums of the visited keys back to zero
+__global__ void dfc_clear_keys_kernel(const unsigned* __restrict__ nkeys, const uint32_t* __restrict__ klist, long long* accX,
+                                      double* sumsq) {
+  const size_t n = *nkeys;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) accX[klist[i]] = 0;
+  if (blockIdx.x == 0 && threadIdx.x == 0 && sumsq) *sumsq = 0;
 }
 // learn/difacto/loss.h:160-166
-__global__ void dfc_normalize_kernel(size_t n, float* G, const double* sumsq) {
+__global__ void dfc_normalize_kernel(const unsigned* __restrict__ nkeys, const uint32_t* __restrict__ klist, int dim, float* G,
+                                     const double* sumsq) {
   const float nm = (float)*sumsq;
   if (nm < 1e-10f) return;
   const float r = sqrtf(nm);
-  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n) G[i] = G[i] / r;
+  const size_t n = (size_t)*nkeys * dim;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const size_t t = (size_t)klist[i / dim] * dim + i % dim;
+    G[t] = G[t] / r;
+  }
 }
 
 struct HasVal { const unsigned char* has; __device__ unsigned operator()(size_t i) const { return has[i] ? 1u : 0u; } };
@@ -156,6 +194,10 @@ struct DfcWork {
   FixedScale *fsW, *fsG, *fsX;
   double* sumsq;
   EvalOut *evW, *ev;             // objective before / after the embedding term
+  // the column subset for V (dfc_subset_kernel) and the keys that came with an embedding
+  unsigned *vstart, *vcnt, *vcursor, *kcount;
+  uint32_t *vidx, *klist;
+  float* vval;
 };
 
 // Loss::Evaluate then (if train) Loss::CalcGrad on the strided model {w, has, V}.
@@ -169,8 +211,12 @@ int difacto_loss_launch(whContext* ctx, whContext* auc_ctx, cudaEvent_t ev_fork,
   WH_TRY(spmv_times_launch(ctx, rows, offset, index, value, w, k.py));                       // py = X w
   WH_TRY(loss_forward_launch(ctx, WH_LOSS_LOGIT, rows, label, k.py, nullptr, k.evW, 0));     // objv_w
   const unsigned grd = (unsigned)div_up(rows * (size_t)(dim > 0 ? dim : 1), 256);
+  const unsigned kgrid = (unsigned)ctx->num_sms * 8;
   if (any_v) {
-    WH_LAUNCH(dfc_xv_kernel, grd, 256, 0, st, rows, offset, index, value, has, V, dim, k.XV, k.xxvv);
+    WH_CUDA(cudaMemsetAsync(k.vcursor, 0, 8, st));       // vcursor, kcount
+    WH_LAUNCH(dfc_subset_kernel, (unsigned)div_up(rows, 256), 256, 0, st, rows, offset, index, value, has, k.vcursor, k.vstart,
+              k.vcnt, k.vidx, k.vval);
+    WH_LAUNCH(dfc_xv_kernel, grd, 256, 0, st, rows, k.vstart, k.vcnt, k.vidx, k.vval, value != nullptr, V, dim, k.XV, k.xxvv);
     WH_LAUNCH(dfc_combine_kernel, (unsigned)div_up(rows, 256), 256, 0, st, rows, dim, k.XV, k.xxvv, k.py);
   }
   WH_TRY(loss_forward_launch(ctx, WH_LOSS_LOGIT, rows, label, k.py, train ? k.dual : nullptr, k.ev, 0));
@@ -188,18 +234,20 @@ int difacto_loss_launch(whContext* ctx, whContext* auc_ctx, cudaEvent_t ev_fork,
       // scales: max|XVp| * max|val| for G, max|p| * max|val|^2 for xxp
       WH_TRY(fixed_prepare(ctx, k.fsG, k.XV, rows * dim, value, nnz, 1));
       WH_TRY(fixed_prepare(ctx, k.fsX, k.dual, rows, value, nnz, 2));
-      WH_LAUNCH(dfc_trans_kernel, grd, 256, 0, st, rows, offset, index, value, has, dim, k.XV, k.dual, k.accG, k.accX, k.fsG, k.fsX);
+      WH_LAUNCH(dfc_trans_kernel, grd, 256, 0, st, rows, k.vstart, k.vcnt, k.vidx, k.vval, value != nullptr, dim, k.XV, k.dual,
+                k.accG, k.accX, k.fsG, k.fsX);
+      WH_LAUNCH(dfc_keylist_kernel, (unsigned)div_up(U ? U : 1, 256), 256, 0, st, U, has, k.kcount, k.klist);
       DfcDropout dr;
       if (drop && drop->stream && drop->dropout > 0.f && U) {
         dr = *drop;
         WH_TRY(ctx->scan_tmp.reserve(div_up(U, kScanTile) * sizeof(unsigned) + 256));
         WH_TRY(scan_and_apply<unsigned>(ctx, HasVal{has}, RankOut{dr.pos}, U, ctx->scan_tmp.as<unsigned>(), dr.total));
       }
-      WH_LAUNCH(dfc_gv_finish_kernel, (unsigned)div_up(U * dim, 256), 256, 0, st, U, dim, has, V, k.accG, k.accX, k.fsG,
-                k.fsX, clip, dr, k.G, k.sumsq);
+      WH_LAUNCH(dfc_gv_finish_kernel, kgrid, 256, 0, st, k.kcount, k.klist, dim, V, k.accG, k.accX, k.fsG, k.fsX, clip, dr, k.G,
+                k.sumsq);
       if (dr.stream) WH_LAUNCH(dfc_advance_kernel, 1, 1, 0, st, dr.cursor, dr.total, dim);
-      if (norm != 0.f) WH_LAUNCH(dfc_normalize_kernel, (unsigned)div_up(U * dim, 256), 256, 0, st, U * dim, k.G, k.sumsq);
-      WH_LAUNCH(dfc_clear_kernel, (unsigned)div_up(U, 256), 256, 0, st, k.accX, U, k.sumsq);
+      if (norm != 0.f) WH_LAUNCH(dfc_normalize_kernel, kgrid, 256, 0, st, k.kcount, k.klist, dim, k.G, k.sumsq);
+      WH_LAUNCH(dfc_clear_keys_kernel, kgrid, 256, 0, st, k.kcount, k.klist, k.accX, k.sumsq);
     }
   }
   WH_CUDA(cudaStreamWaitEvent(st, ev_auc, 0));
@@ -223,7 +271,7 @@ struct whDifacto {
   whContext ax;                      // AUC side stream
   cudaEvent_t ev_fork = nullptr, ev_auc = nullptr;
   wh::DevBuf in_index, in_offset, in_value, in_label, uniq, cnt, index, w, has, Vs, XV, xxvv, py, dual, gw, G,
-      accG, accX, flags, scal;
+      accG, accX, flags, scal, vrows, vidx, vval, klist;
   wh::PinnedBuf pinned;
   long long seen_new_w = 0, seen_new_V = 0;
   // between wh_difacto_begin and wh_difacto_finish (sharded jobs: the model lives elsewhere)
@@ -431,8 +479,14 @@ __global__ void dfc_state_kernel(DfcParams p, const uint64_t* __restrict__ keys,
   }
 }
 
-int dfc_work(whDifacto* d, size_t rows, size_t U, DfcWork* k) {
+int dfc_work(whDifacto* d, size_t rows, size_t U, size_t nnz, DfcWork* k) {
   const int dim = d->c.dim > 0 ? d->c.dim : 1;
+  if (d->c.dim > 0) {
+    WH_TRY(d->vrows.reserve(rows * 8)); WH_TRY(d->vidx.reserve((nnz ? nnz : 1) * 4)); WH_TRY(d->vval.reserve((nnz ? nnz : 1) * 4));
+    WH_TRY(d->klist.reserve((U ? U : 1) * 4));
+  }
+  k->vstart = d->vrows.as<unsigned>(); k->vcnt = k->vstart + rows;
+  k->vidx = d->vidx.as<uint32_t>(); k->vval = d->vval.as<float>(); k->klist = d->klist.as<uint32_t>();
   WH_TRY(d->py.reserve(rows * 4)); WH_TRY(d->dual.reserve(rows * 4));
   WH_TRY(d->XV.reserve(rows * dim * 4)); WH_TRY(d->xxvv.reserve(rows * dim * 4));
   WH_TRY(d->gw.reserve((U ? U : 1) * 4)); WH_TRY(d->G.reserve((U ? U : 1) * dim * 4));
@@ -451,6 +505,7 @@ int dfc_work(whDifacto* d, size_t rows, size_t U, DfcWork* k) {
   k->fsW = reinterpret_cast<FixedScale*>(sc + 256); k->fsG = reinterpret_cast<FixedScale*>(sc + 320);
   k->fsX = reinterpret_cast<FixedScale*>(sc + 384); k->sumsq = reinterpret_cast<double*>(sc + 448);
   k->evW = reinterpret_cast<EvalOut*>(sc + 512); k->ev = reinterpret_cast<EvalOut*>(sc + 768);
+  k->vcursor = reinterpret_cast<unsigned*>(sc + 64); k->kcount = k->vcursor + 1;
   return WH_OK;
 }
 
@@ -504,7 +559,7 @@ int wh_difacto_destroy(whDifacto* d) {
   cudaStreamSynchronize(d->ax.stream);
   for (wh::DevBuf* b : {&d->base, &d->hasv, &d->V, &d->cgV, &d->counters, &d->init_stream, &d->drop_stream, &d->drop_pos, &d->in_index, &d->in_offset,
                         &d->in_value, &d->in_label, &d->uniq, &d->cnt, &d->index, &d->w, &d->has, &d->Vs, &d->XV,
-                        &d->xxvv, &d->py, &d->dual, &d->gw, &d->G, &d->accG, &d->accX, &d->flags, &d->scal,
+                        &d->xxvv, &d->py, &d->dual, &d->gw, &d->G, &d->accG, &d->accX, &d->flags, &d->scal, &d->vrows, &d->vidx, &d->vval, &d->klist,
                         &d->ax.small, &d->ax.scan_tmp})
     b->release();
   for (auto& b : d->ax.sort_tmp) b.release();
@@ -600,7 +655,7 @@ int wh_difacto_process_minibatch(whDifacto* d, const whRowBlock* blk, int mem, i
   WH_TRY(d->w.reserve((ucap ? ucap : 1) * 4)); WH_TRY(d->has.reserve(ucap ? ucap : 1));
   WH_TRY(d->Vs.reserve((ucap ? ucap : 1) * sd * 4)); WH_TRY(d->flags.reserve(ucap ? ucap : 1));
   DfcWork k;
-  WH_TRY(dfc_work(d, rows, ucap, &k));
+  WH_TRY(dfc_work(d, rows, ucap, n, &k));
   const DfcParams p = dfc_params(d);
   long long* counters = d->counters.as<long long>();
   const unsigned ugrid = (unsigned)div_up(ucap, 256);
@@ -703,7 +758,7 @@ int wh_difacto_finish(whDifacto* d, const float* d_w, const unsigned char* d_has
   const int dim = d->c.dim, sd = dim > 0 ? dim : 1;
   const size_t rows = d->b_rows, U = d->b_U;
   DfcWork k;
-  WH_TRY(dfc_work(d, rows, U, &k));
+  WH_TRY(dfc_work(d, rows, U, d->b_nnz, &k));
   DfcDropout drop;
   WH_TRY(dfc_dropout(d, U, train != 0, &drop));
   WH_TRY(difacto_loss_launch(ctx, &d->ax, d->ev_fork, d->ev_auc, rows, d->b_nnz, d->b_offset, d->index.as<uint32_t>(), d->b_value,
@@ -944,7 +999,7 @@ int wh_difacto_loss_dropout(whContext* ctx, const whLocalBlock* D, const float* 
     WH_LAUNCH(dfc_unpack_kernel, (unsigned)div_up(U, 256), 256, 0, ctx->stream, U, dim, d_model, d_siz, pos,
               tmp.w.as<float>(), tmp.has.as<unsigned char>(), tmp.Vs.as<float>());
     DfcWork k;
-    WH_TRY(dfc_work(&tmp, dl.rows, U, &k));
+    WH_TRY(dfc_work(&tmp, dl.rows, U, dl.nnz, &k));
     DfcDropout drop;
     if (dropout > 0.f && grad && dim > 0 && U) {
       WH_TRY(tmp.drop_stream.reserve(num_rand * 4)); WH_TRY(tmp.drop_pos.reserve(U * 4)); WH_TRY(tmp.counters.reserve(64));
@@ -976,7 +1031,7 @@ int wh_difacto_loss_dropout(whContext* ctx, const whLocalBlock* D, const float* 
   if (tmp.ev_fork) cudaEventDestroy(tmp.ev_fork);
   if (tmp.ev_auc) cudaEventDestroy(tmp.ev_auc);
   for (wh::DevBuf* b : {&tmp.w, &tmp.has, &tmp.Vs, &tmp.XV, &tmp.xxvv, &tmp.py, &tmp.dual, &tmp.gw, &tmp.G, &tmp.accG,
-                        &tmp.accX, &tmp.scal, &tmp.ax.small, &tmp.ax.scan_tmp, &tmp.drop_stream, &tmp.drop_pos, &tmp.counters})
+                        &tmp.accX, &tmp.scal, &tmp.vrows, &tmp.vidx, &tmp.vval, &tmp.klist, &tmp.ax.small, &tmp.ax.scan_tmp, &tmp.drop_stream, &tmp.drop_pos, &tmp.counters})
     b->release();
   for (auto& b : tmp.ax.sort_tmp) b.release();
   tmp.pinned.release();
