@@ -627,15 +627,16 @@ def run_ours(args):
     sampler.stop()
 
     # the raw host-to-device ceiling of this rank's pinned pool (one cudaMemcpyAsync per minibatch array, no kernels)
-    h2d_bytes = N * 8 + (rows + 1) * 8 + rows * 4
-    scratch = [torch.empty_like(dev[0].index), torch.empty_like(dev[0].offset), torch.empty_like(dev[0].label)]
+    n_min = min(int(h.index.numel()) for h in host)     # (minibatches of the KDD shape differ in their entry counts)
+    h2d_bytes = n_min * 8 + (rows + 1) * 8 + rows * 4
+    scratch = [torch.empty(n_min, dtype=dev[0].index.dtype, device="cuda"), torch.empty_like(dev[0].offset), torch.empty_like(dev[0].label)]
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
     t0 = time.perf_counter()
     for i in range(20):
         h = host[i % pool_n]
-        scratch[0].copy_(h.index, non_blocking=True); scratch[1].copy_(h.offset, non_blocking=True); scratch[2].copy_(h.label, non_blocking=True)
+        scratch[0].copy_(h.index[:n_min], non_blocking=True); scratch[1].copy_(h.offset, non_blocking=True); scratch[2].copy_(h.label, non_blocking=True)
     torch.cuda.synchronize()
     h2d_gbs = 20 * h2d_bytes / (time.perf_counter() - t0) / 1e9
     if world > 1:
@@ -669,7 +670,7 @@ def run_ours(args):
             others["ftrl_logit_max_delay_1"] = side_config(ctx, rank, world, local, args, stream, "ftrl_logit_max_delay_1", "ftrl", "logit",
                                                            "criteo", ROWS, MAX_KEY, NNZ_PER_ROW, K, Wm, pool_n, max_delay=1)
         others["kdd_ftrl"] = side_config(ctx, rank, world, local, args, stream, "kdd_ftrl", "ftrl", "logit", "kdd", 1000000,
-                                         synth.KDD_VOCAB, 11, max(3, K // 4), 3, 3)
+                                         synth.KDD_VOCAB, 11, max(8, K // 2), max(5, args.depth + 1), 3)   # (every lane warm)
         # (every rank takes part; a failure on one rank of several would leave the others in a collective, so it is
         #  only caught where there is a single rank)
         if world == 1:

@@ -335,10 +335,11 @@ int wh_worker_submit(whWorker* w, const whRowBlock* blk, int mem, size_t nnz, in
     const long long dx_refresh = w->hot_refresh > 0 ? std::max<long long>(w->hot_refresh, w->depth + 1) : 0;
     if (!w->dx_tried || (dx_refresh > 0 && ++w->dx_since >= dx_refresh)) WH_TRY(hot_census(w, l, in, ucap, true));
   }
-  // The step pays a RED, a DRAM line and a bitmap bit for every entry whose key is NOT in the table: with a flat key
-  // distribution (KDD2012 shape: 47 % of the entries covered) the chain of launches below, whose localizer turns every
-  // key into a rank first, is the faster one (measured 1.65 against 0.62 G examples/s). WH_DX_MIN_COVERAGE overrides.
-  double min_cov = 0.6;
+  // The step pays a RED, a DRAM line and a bitmap bit for every entry whose key is NOT in the table; the chain of
+  // launches below turns every key into a rank first and pays per unique key instead. KDD2012 shape (47 % of the
+  // entries covered): 1.52 against 1.19 G examples/s in favour of the step; below 40 % (flat key distributions,
+  // unmeasured) the chain is kept. WH_DX_MIN_COVERAGE overrides.
+  double min_cov = 0.4;
   { const char* e = getenv("WH_DX_MIN_COVERAGE"); if (e) min_cov = atof(e); }
   if (dx_ok && w->dx.ready && (w->dx.coverage >= min_cov || getenv("WH_DX_TABLE"))) {
     const unsigned long long tk = w->next_ticket;
