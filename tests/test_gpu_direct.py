@@ -207,6 +207,16 @@ def test_direct_criteo_shape_vs_checker(gpu, checker):
     wk.close(); srv.close(); checker.linear_destroy(job)
 
 
+def test_direct_kdd_shape_equals_chain(gpu):
+    """The KDD2012 shape (ids over 54.7 M values, flat: the table covers under half of the entries, key space 2^26) takes the
+    shared-GPU step by default; three minibatches in flight, bit for bit the chain of launches."""
+    blks = [synth.kdd_minibatch(m, rows=150000) for m in range(4)]
+    a = run(gpu, blks, capi.ALGO_FTRL, capi.LOSS_LOGIT, synth.KDD_VOCAB, depth=3)
+    b = run(gpu, blks, capi.ALGO_FTRL, capi.LOSS_LOGIT, synth.KDD_VOCAB, depth=3, WH_DIRECT=0)
+    same_model(a, b)
+    assert a[3] > 1000
+
+
 def test_bench_line_parity_leg_one_gpu():
     """bench.py's own parity_check leg at N = 1 (the shared-GPU step against the checker, outside the timed regions)."""
     import json
