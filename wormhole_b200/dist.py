@@ -131,34 +131,83 @@ class ShardedWorker:
         return prog
 
 
+class DeviceDifacto:
+    """Adapter: a capi.Difacto (CUDA worker half + shard) behind the tensor-level interface ShardedDifacto drives. A CPU
+    stand-in with the same methods runs the exchange in the world_size-2 gloo tests."""
+
+    def __init__(self, difacto, device):
+        self.d, self.device, self.dim = difacto, device, difacto.dim
+
+    @staticmethod
+    def _p(t):
+        return t.data_ptr() if t.numel() else 0
+
+    def begin(self, blk, mem=0):
+        """Localize with counts -> (ascending unique keys int64[U], counts int32[U]), valid until the next begin."""
+        pu, pc, U = self.d.begin(blk, mem)
+        return _wrap_device_i64(pu, U, self.device), _wrap_device(pc, U, "<i4", torch.int32, self.device)
+
+    def count_push(self, keys, cnt):
+        self.d.shard_count_push(self._p(keys), self._p(cnt), keys.numel())
+
+    def pull(self, keys):
+        n, sd = keys.numel(), max(self.dim, 1)
+        w = torch.empty(n, dtype=torch.float32, device=self.device)
+        has = torch.empty(n, dtype=torch.uint8, device=self.device)
+        V = torch.empty((n, sd), dtype=torch.float32, device=self.device)
+        self.d.shard_pull(self._p(keys), n, self._p(w), self._p(has), self._p(V))
+        return w, has, V
+
+    def finish(self, w, has, V, train):
+        U, sd = w.numel(), max(self.dim, 1)
+        gw = torch.empty(U, dtype=torch.float32, device=self.device)
+        G = torch.empty((U, sd), dtype=torch.float32, device=self.device)
+        prog = self.d.finish(self._p(w), self._p(has), self._p(V), train, self._p(gw), self._p(G))
+        return prog, gw, G
+
+    def push(self, keys, gw, G, has):
+        self.d.shard_push(self._p(keys), keys.numel(), self._p(gw), self._p(G), self._p(has))
+
+    def progress(self):
+        return self.d.shard_progress()
+
+
 class ShardedDifacto:
     """AsyncWorker::ProcessMinibatch of learn/difacto/async_sgd.h:363-425 on rank g of a key-range sharded job: rank g
     is worker g and the AsyncServer shard of [g*max_key/S, (g+1)*max_key/S). The three exchanges of the minibatch --
     count push (:374-381), ZVPull (:424), ZVPush (:408-411) -- are all-to-all-v's of the sorted key slices; the owners
     apply one message per source rank in ascending source order (one valid interleaving of the asynchronous server).
-    The variable-length payloads travel as fixed-width rows {w, has, V[dim]} (has = the length flag)."""
+    The variable-length payloads travel as fixed-width rows {w, has, V[dim]} (has = the length flag).
+
+    `difacto` is a capi.Difacto (wrapped in DeviceDifacto) or anything with DeviceDifacto's methods."""
 
     def __init__(self, ctx, difacto, max_key, group=None, device=None):
-        self.ctx, self.d, self.max_key, self.group = ctx, difacto, max_key, group
+        self.ctx, self.max_key, self.group = ctx, max_key, group
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
-        self.device = device if device is not None else torch.device("cuda", torch.cuda.current_device())
+        if device is None:
+            device = torch.device("cuda", torch.cuda.current_device()) if ctx is not None else torch.device("cpu")
+        self.device = device
+        self.d = difacto if hasattr(difacto, "count_push") else DeviceDifacto(difacto, device)
+        self.dim = self.d.dim
         self.bounds = range_boundaries(self.world, max_key, self.device)
-        self.dim = difacto.dim
         self._bound = None
         self._bind()
 
     def _bind(self):
+        if self.ctx is None:
+            return
         s = torch.cuda.current_stream(self.device).cuda_stream
         if self._bound != s:
             self.ctx.set_stream(s)
             self._bound = s
 
-    def _a2a(self, out, inp, out_split, in_split):
+    def _a2a(self, inp, out_split, in_split):
+        out = torch.empty((sum(out_split),) + tuple(inp.shape[1:]), dtype=inp.dtype, device=self.device)
         if self.world == 1:
             out.copy_(inp)
         else:
-            dist.all_to_all_single(out, inp, out_split, in_split, group=self.group)
+            dist.all_to_all_single(out, inp.contiguous(), out_split, in_split, group=self.group)
         return out
 
     def _sizes(self, keys):
@@ -173,40 +222,31 @@ class ShardedDifacto:
 
     def process_minibatch(self, blk, train=True, data_pass=0, mem=0):
         self._bind()
-        dev, dim, sd = self.device, self.dim, max(self.dim, 1)
-        pu, pc, U = self.d.begin(blk, mem)
-        keys = _wrap_device_i64(pu, U, dev)
+        dim = self.dim
+        keys, cnt = self.d.begin(blk, mem)
         send, recv = self._sizes(keys)
-        R = sum(recv)
-        rkeys = self._a2a(torch.empty(R, dtype=torch.int64, device=dev), keys, recv, send)
-        ptr = lambda t: t.data_ptr() if t.numel() else 0
+        rkeys = self._a2a(keys, recv, send)
         if train and data_pass == 0 and dim > 0:
-            cnt = _wrap_device(pc, U, "<i4", torch.int32, dev)
-            rcnt = self._a2a(torch.empty(R, dtype=torch.int32, device=dev), cnt, recv, send)
+            rcnt = self._a2a(cnt, recv, send)
             o = 0
-            for n in recv:
-                self.d.shard_count_push(ptr(rkeys[o:o + n]), ptr(rcnt[o:o + n]), n)
+            for n in recv:                       # one count-push message per source, ascending
+                self.d.count_push(rkeys[o:o + n], rcnt[o:o + n])
                 o += n
         # ZVPull: Handle::Pull does not change the shard, so the S messages are served as one batch
-        rw = torch.empty(R, dtype=torch.float32, device=dev)
-        rhas = torch.empty(R, dtype=torch.uint8, device=dev)
-        rV = torch.empty((R, sd), dtype=torch.float32, device=dev)
-        self.d.shard_pull(ptr(rkeys), R, ptr(rw), ptr(rhas), ptr(rV))
-        w = self._a2a(torch.empty(U, dtype=torch.float32, device=dev), rw, send, recv)
-        has = self._a2a(torch.empty(U, dtype=torch.uint8, device=dev), rhas, send, recv)
-        V = self._a2a(torch.empty((U, sd), dtype=torch.float32, device=dev), rV, send, recv) if dim > 0 else rV[:0]
-        gw = torch.empty(U, dtype=torch.float32, device=dev)
-        G = torch.empty((U, sd), dtype=torch.float32, device=dev)
-        prog = self.d.finish(ptr(w), ptr(has), ptr(V), train, ptr(gw), ptr(G))
+        rw, rhas, rV = self.d.pull(rkeys)
+        w = self._a2a(rw, send, recv)
+        has = self._a2a(rhas, send, recv)
+        V = self._a2a(rV, send, recv) if dim > 0 else rV[:0]
+        prog, gw, G = self.d.finish(w, has, V, train)
         if train:
-            rgw = self._a2a(rw, gw, recv, send)
-            rG = self._a2a(rV, G, recv, send) if dim > 0 else rV
+            rgw = self._a2a(gw, recv, send)
+            rG = self._a2a(G, recv, send) if dim > 0 else rV
             # the push carries the lengths the worker pulled (rhas is unchanged since the pull of these very keys)
             o = 0
-            for n in recv:
-                self.d.shard_push(ptr(rkeys[o:o + n]), n, ptr(rgw[o:o + n]), ptr(rG[o:o + n]), ptr(rhas[o:o + n]))
+            for n in recv:                       # one gradient-push message per source, ascending
+                self.d.push(rkeys[o:o + n], rgw[o:o + n], rG[o:o + n], rhas[o:o + n])
                 o += n
-        prog[6], prog[7] = self.d.shard_progress()
+        prog[6], prog[7] = self.d.progress()
         return prog
 
 
