@@ -13,7 +13,8 @@ import numpy as np
 from .rowblock import LocalBlock, RowBlock
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libwormhole_b200.so")
+# (WH_LIB: another build of the same library -- kernel variants compiled with different constants, timing experiments)
+LIB_PATH = os.environ.get("WH_LIB") or os.path.join(HERE, "libwormhole_b200.so")
 
 WH_HOST, WH_DEVICE = 0, 1
 LOSS_SQUARE, LOSS_LOGIT, LOSS_SQUARE_HINGE = 1, 2, 4

@@ -275,6 +275,11 @@ __device__ __forceinline__ uint64_t ld_stream_evict_first_u64(const uint64_t* p)
   asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.u64 %0, [%1], %2;" : "=l"(v) : "l"(p), "l"(pol));
   return v;
 }
+__device__ __forceinline__ uint64_t ld_stream_evict_first_u64(const uint64_t* p, uint64_t pol) {
+  uint64_t v;
+  asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.u64 %0, [%1], %2;" : "=l"(v) : "l"(p), "l"(pol));
+  return v;
+}
 __device__ __forceinline__ uint64_t l2_policy_evict_last() {
   uint64_t pol;
   asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));

@@ -41,8 +41,17 @@ namespace wh {
 
 constexpr int kDxGroup = 256;                       // threads per group = rows per tile
 constexpr unsigned kDxFlag = 0x80000000u;           // code bit: a table key; the low bits hold its slot
-constexpr int kDxIlp = 4;                           // ids in flight per thread in P1
-constexpr int kDxGather = 8;                        // weight gathers in flight per thread in P2
+#ifndef WH_DX_ILP
+#define WH_DX_ILP 4
+#endif
+#ifndef WH_DX_GATHER
+#define WH_DX_GATHER 12
+#endif
+#ifndef WH_DX_MAXNREG
+#define WH_DX_MAXNREG 64      // one 1024-thread block per SM (shared memory decides that): 64 registers are free
+#endif
+constexpr int kDxIlp = WH_DX_ILP;                   // ids in flight per thread in P1
+constexpr int kDxGather = WH_DX_GATHER;             // weight gathers in flight per thread in P2
 
 __device__ __forceinline__ void group_bar(int g) {
   asm volatile("bar.sync %0, %1;" ::"r"(g + 1), "r"(kDxGroup) : "memory");
@@ -123,8 +132,9 @@ __device__ __forceinline__ void dx_stage(const DxArgs& a, const uint4* s_tags, u
   const unsigned mask = (unsigned)(a.xf.max_key - 1);
   const uint64_t* ids = a.index + base;
   uint64_t nxt[kDxIlp];
+  const uint64_t once = l2_policy_evict_first();      // (one createpolicy per call, not one per load)
 #pragma unroll
-  for (int u = 0; u < kDxIlp; ++u) { const unsigned e = tg + u * kDxGroup; nxt[u] = e < E ? ld_stream_evict_first_u64(ids + e) : 0; }
+  for (int u = 0; u < kDxIlp; ++u) { const unsigned e = tg + u * kDxGroup; nxt[u] = e < E ? ld_stream_evict_first_u64(ids + e, once) : 0; }
   for (unsigned e0 = tg; e0 < E; e0 += kDxGroup * kDxIlp) {
     uint64_t id[kDxIlp];
     float v[kDxIlp];
@@ -132,7 +142,7 @@ __device__ __forceinline__ void dx_stage(const DxArgs& a, const uint4* s_tags, u
     for (int u = 0; u < kDxIlp; ++u) {
       id[u] = nxt[u];
       const unsigned en = e0 + (kDxIlp + u) * kDxGroup;
-      nxt[u] = en < E ? ld_stream_evict_first_u64(ids + en) : 0;
+      nxt[u] = en < E ? ld_stream_evict_first_u64(ids + en, once) : 0;
       if (HAS_VAL) { const unsigned e = e0 + u * kDxGroup; v[u] = e < E ? __ldcs(a.value + base + e) : 0.f; }
     }
 #pragma unroll
@@ -235,7 +245,7 @@ __global__ void __launch_bounds__(kDxGroup) dx_stage_kernel(const DxArgs a, size
 }
 
 template <bool TRAIN, bool POW2, bool HAS_VAL, int NG>
-__global__ void __maxnreg__(48) fused_direct_kernel(const DxArgs a) {
+__global__ void __maxnreg__(WH_DX_MAXNREG) fused_direct_kernel(const DxArgs a) {
   extern __shared__ __align__(16) unsigned char smem[];
   // (with the codes staged ahead of time the table's tags and flags are not needed here, and their 20 KB are left
   //  to the next minibatch's dx_stage_kernel blocks, which run beside this kernel)
