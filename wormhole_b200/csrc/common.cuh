@@ -94,6 +94,7 @@ struct whContext {
   size_t l2_bytes = 0;
   cudaStream_t stream = nullptr;
   bool own_stream = true;
+  bool avoid_coop = false;   // this context's kernels run beside other cooperative launches (sharded jobs, several lanes)
   // scratch shared by the stateless entry points (grow-only)
   wh::DevBuf directory;      // direct-address localizer: {bits, prefix} per 32 keys
   size_t directory_words = 0;  // words currently known to be all-zero

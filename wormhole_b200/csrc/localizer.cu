@@ -475,8 +475,13 @@ __global__ void hot_rank_kernel(HotView hot, const uint2* __restrict__ dir) {
 //  its own in front of the look-back scan)
 static int dir_scan_hot(whContext* ctx, uint2* dir, uint64_t* d_uniq, size_t words, unsigned* d_nuniq, const HotView& hot,
                         const PullAtEmit* pull, bool* pulled) {
-  static int coop = -1;
-  if (coop < 0) { const char* e = getenv("WH_SCAN_COOP"); coop = e ? atoi(e) : 1; }
+  // One cooperative launch (scan + the table keys' ranks) or five plain ones. Alone on the GPU the cooperative scan is the
+  // shorter (20 against 23.5 us); in a sharded job with several minibatches in flight it has to become co-resident beside
+  // the cooperative apply and the forward/backward kernel of its neighbours, and the plain launches win: 0.139 against
+  // 0.146 ms per step on 2 GPUs. WH_SCAN_COOP=0|1 forces one.
+  static int forced = -2;
+  if (forced == -2) { const char* e = getenv("WH_SCAN_COOP"); forced = e ? atoi(e) : -1; }
+  const bool coop = forced >= 0 ? forced != 0 : !ctx->avoid_coop;
   *pulled = false;
   if (coop && scan_coop_fits(ctx, words)) {
     WH_TRY(ctx->scan_tmp.reserve(div_up(words, kScanThreads * kOnepassItems) * sizeof(unsigned) + 256));

@@ -420,6 +420,7 @@ int wh_worker_submit(whWorker* w, const whRowBlock* blk, int mem, size_t nnz, in
   // apply it; "every owner has served pull tk - depth + 1" says they are done with it
   if (served && w->depth > 1 && tk > (unsigned long long)w->depth)
     WH_CUDA(cudaStreamWaitEvent(cx->stream, w->ev_served[(tk - w->depth + 1) % ring], 0));
+  cx->avoid_coop = outboxed && w->depth > 1;
   // With the table of frequent keys the step's kernel leaves its fixed-point sums in the outbox itself and the owners
   // convert while they apply (one launch less between push and pull): zero the words of the lane's previous minibatch,
   // and tell the owners how to read this one's
