@@ -52,6 +52,38 @@ def test_criteo_shape_minibatches(gpu, checker, criteo, algo, loss):
     wk.close(); srv.close(); checker.linear_destroy(job)
 
 
+def test_criteo_shape_pass_of_50_minibatches(gpu, checker):
+    """One pass of 50 minibatches (5 M examples) in the benchmark's configuration -- FTRL L1+L2, logit, 2^24 keys, four
+    minibatches in flight -- beside the reference's own worker + server: the numbers the scheduler prints (learn/linear/
+    progress.h:21-23: logloss = sum objv / sum examples, accuracy and AUC = means of the per-minibatch values) agree
+    within the north star's 1e-4, the AUC of every 100 000-row minibatch within 1e-4, |w|_0 within a few keys on the
+    L1 threshold."""
+    max_key, N, depth = 2 ** 24, 50, 4
+    job = checker.linear_create(capi.ALGO_FTRL, capi.LOSS_LOGIT, 1.0, 0.1, 0.1, 1.0, max_key)
+    srv = capi.Server(gpu, capi.ALGO_FTRL, 1.0, 0.1, 0.1, 1.0, 0, max_key)
+    wk = capi.Worker(gpu, srv, capi.LOSS_LOGIT, max_key, depth=depth)
+    pg, pc, pending = [], [], []
+    for m in range(N):
+        blk = synth.criteo_minibatch(500 + m)
+        if len(pending) == depth:
+            pg.append(wk.wait(pending.pop(0)[0]))
+        pending.append((wk.submit(blk), blk))          # (the block stays alive until its ticket is collected)
+        pc.append(checker.linear_minibatch(job, blk))
+    pg += [wk.wait(t) for t, _ in pending]
+    pg, pc = np.array(pg), np.array(pc)
+    assert np.array_equal(pg[:, 3:5], pc[:, 3:5])                              # count, examples
+    assert np.all(np.abs(pg[1:, 2] - pc[1:, 2]) <= 1e-4)                       # AUC per minibatch (0: all scores tie)
+    assert np.all(np.abs(pg[:, 1] - pc[:, 1]) <= 1e-4)                         # accuracy per minibatch (a fraction of its rows)
+    logloss = lambda p: p[:, 0].sum() / p[:, 4].sum()
+    assert abs(logloss(pg) - logloss(pc)) <= 1e-4
+    assert abs(pg[1:, 2].mean() - pc[1:, 2].mean()) <= 1e-4
+    assert abs(pg[:, 1].mean() - pc[:, 1].mean()) <= 1e-4
+    nnz_ref = int((checker.linear_model(job)[1] != 0).sum())
+    assert abs(srv.nnz_w() - nnz_ref) <= max(5, 2e-4 * nnz_ref)
+    assert pg[-1, 2] > 0.6 and logloss(pg[-10:]) < logloss(pg[:10])            # it did learn something
+    wk.close(); srv.close(); checker.linear_destroy(job)
+
+
 def test_criteo_localize_properties(gpu, criteo):
     blk = criteo[0]
     a = gpu.localize(blk, 2 ** 24, method=capi.LOC_DIRECT)
