@@ -33,6 +33,25 @@ def test_linear_b200_compiles_and_links(tmp_path):
     assert os.path.exists(build_binary(tmp_path))
 
 
+def test_rank_hub_without_a_gpu(tmp_path):
+    """RunRanks / Peer::Allgather (the few host messages of `linear_b200 -gpus S`: IPC handles, step flags, progress sums):
+    every rank gets every rank's bytes in rank order; a rank that leaves early fails the job instead of hanging it."""
+    from wormhole_b200 import build
+    build.build()
+    exe = os.path.join(str(tmp_path), "hub_test")
+    cmd = ["/usr/bin/g++", "-std=c++14", "-O1", "-Wall", "-I" + os.path.join(ROOT, "include"),
+           "-I" + os.path.join(ROOT, "wormhole_b200", "host"), os.path.join(ROOT, "tests", "cpp", "hub_test.cc"),
+           "-o", exe, "-L" + os.path.join(ROOT, "wormhole_b200"), "-lwormhole_b200",
+           "-Wl,-rpath," + os.path.join(ROOT, "wormhole_b200"), "-L/usr/local/cuda/lib64", "-lcudart"]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    for ranks in ("2", "3", "8"):
+        r = subprocess.run([exe, ranks], capture_output=True, text=True, timeout=60)
+        assert r.returncode == 0 and "hub_test ok" in r.stdout, r.stdout + r.stderr
+    r = subprocess.run([exe, "3", "quit"], capture_output=True, text=True, timeout=60)
+    assert r.returncode != 0 and "hub_test failed" in r.stdout, r.stdout + r.stderr
+
+
 def strip_seconds(log):
     """progress rows start with the elapsed seconds: drop that column"""
     return [re.sub(r"^\s*\d+  ", "", l) if re.match(r"^\s*\d+  \s*[\d.e+]+", l) else l for l in log.splitlines()]

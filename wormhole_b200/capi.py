@@ -259,6 +259,10 @@ class Server:
     def load(self, path):
         _check(lib().wh_server_load(self.h, path.encode()))
 
+    def set_active_sources(self, mask):
+        """Bit r: rank r sends a push message in the next step (SGD's per-message t advances for those only)."""
+        _check(lib().wh_server_set_active_sources(self.h, C.c_uint64(mask)))
+
     def ipc_export(self):
         """The bytes other ranks need to map this shard (wh_server_ipc_export)."""
         buf = C.create_string_buffer(192)
@@ -422,6 +426,13 @@ class Worker:
         rb = _rowblock(blk)
         _check(lib().wh_worker_submit(self.h, C.byref(rb), C.c_int(mem), C.c_size_t(nnz), C.c_int(train), C.byref(t)))
         self._keep[t.value] = blk   # the arrays must outlive the call
+        return t.value
+
+    def submit_idle(self, train=True):
+        """A step of a sharded job in which this rank has no minibatch (ragged streams): joins the collective barriers,
+        serves the others' pulls, applies their pushes. Returns the ticket; its progress is all zero."""
+        t = C.c_uint64()
+        _check(lib().wh_worker_submit_idle(self.h, C.c_int(train), C.byref(t)))
         return t.value
 
     def predict(self, blk, prob_predict=True, mem=WH_HOST):
