@@ -729,7 +729,10 @@ def run_ours(args):
                          "kernel_algorithmic_bytes": top_bytes},
             "step_roofline": {"bytes_per_example": bytes_per_ex,
                               "frac_of_hbm_peak": value * bytes_per_ex / (world * pk["hbm_gbs"] * 1e9)},
-            "kernel_ms": {n: round(ms, 5) for n, ms in segs},
+            "kernel_ms": {n: round(ms, 5) for n, ms in segs if n != "auc_tail"},
+            # (not a kernel of the chain: how long the one-at-a-time pass idles at the join with the AUC side stream; with
+            #  several minibatches in flight the next minibatch runs in that time)
+            "side_stream_join_ms": {n: round(ms, 5) for n, ms in segs if n == "auc_tail"},
             "kernel_ms_note": "one minibatch at a time (depth 1), CUDA events on the launching stream" +
                               ("; at N > 1 these segments include the waits at the rank barriers" if world > 1 else ""),
             "hot": {"hit_rate": round(hit, 4), "keys_placed": int(len(table_keys)), "census_ms": round(census_ms, 3),
