@@ -645,8 +645,10 @@ int wh_difacto_process_minibatch(whDifacto* d, const whRowBlock* blk, int mem, i
   unsigned* d_nuniq = d->scal.as<unsigned>();
   // Localizer<FeaID>::Localize(mb, data, feaid, feacnt): async_sgd.h:368-371
   LocInput in{d_index, n, make_xform(d->c.max_key)};
-  if (direct_supported(d->c.max_key)) WH_TRY(localize_direct(ctx, in, d->uniq.as<uint64_t>(), d->cnt.as<uint32_t>(), d->index.as<uint32_t>(), d_nuniq));
-  else WH_TRY(localize_sort(ctx, in, d->uniq.as<uint64_t>(), d->cnt.as<uint32_t>(), d->index.as<uint32_t>(), d_nuniq));
+  // (the counts are only pushed in the first pass, async_sgd.h:374: every later minibatch saves one atomic per entry)
+  uint32_t* want_cnt = (train && data_pass == 0 && d->c.dim > 0) ? d->cnt.as<uint32_t>() : nullptr;
+  if (direct_supported(d->c.max_key)) WH_TRY(localize_direct(ctx, in, d->uniq.as<uint64_t>(), want_cnt, d->index.as<uint32_t>(), d_nuniq));
+  else WH_TRY(localize_sort(ctx, in, d->uniq.as<uint64_t>(), want_cnt, d->index.as<uint32_t>(), d_nuniq));
   // the per-key buffers of a factorization machine are dim times wider than the linear model's: size them
   // by the actual number of unique keys (one small read-back) rather than by its upper bound
   WH_CUDA(cudaMemcpyAsync(d->pinned.p, d_nuniq, sizeof(unsigned), cudaMemcpyDeviceToHost, ctx->stream));
